@@ -1,0 +1,195 @@
+/*
+ * chronos.h -- C ABI of the B200-native CHRONOS telemetry hot path.
+ *
+ * The reference (Riyaz246/Project-CHRONOS, /root/reference/chronos_sensor.py) has no
+ * FFI of its own: its hot path is the eBPF openat filter (chronos_sensor.py:28-47,
+ * :74-92) plus the Python perf-buffer callback print_event (:124-157) working on
+ * `struct data_t` records (:18-23) and the module-global process_memory (:105).  This
+ * header is the boundary a maintainer binds instead (ctypes stub in INTEGRATION.md):
+ * raw 288-byte records in, surviving-event set + flushed context windows + pending
+ * per-PID state out.  Plain C types only, int status returns, no exceptions; one
+ * context per GPU, calls on a context externally serialised (the reference is a
+ * single-threaded poll loop, :161-162).  There is no CPU fallback: every entry point
+ * fails with CHRONOS_E_CUDA when no sm_100-class device is usable.
+ */
+#ifndef CHRONOS_B200_H
+#define CHRONOS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* sizeof(struct data_t), chronos_sensor.py:18-23: u32 pid @0, comm[16] @4, argv[256] @20,
+ * type[10] @276, 2 bytes tail padding. */
+#define CHRONOS_RECORD_BYTES 288u
+
+#define CHRONOS_OK 0
+#define CHRONOS_E_ARG (-1)      /* bad pointer / size / alignment */
+#define CHRONOS_E_CUDA (-2)     /* CUDA runtime error, or no usable device */
+#define CHRONOS_E_NOMEM (-3)    /* device or pinned allocation failed */
+#define CHRONOS_E_CAPACITY (-4) /* batch larger than the context was created for */
+#define CHRONOS_E_STATE (-5)    /* call out of order (e.g. fetch with nothing submitted) */
+
+/* per-event class bits kept with every surviving event */
+#define CHRONOS_META_TRIG 1u  /* chronos_sensor.py:141 trigger needles matched */
+#define CHRONOS_META_CURL 2u  /* extension: "curl" in event_str */
+#define CHRONOS_META_CHMOD 4u /* extension: "chmod" in event_str */
+#define CHRONOS_META_EXEC 8u  /* extension: type field is exactly "EXEC" (:55) */
+
+typedef struct chronos_ctx chronos_ctx;
+
+/* One flushed context window = one call of analyze_sequence(pid, history)
+ * (chronos_sensor.py:142-147, :157).  Its events are records
+ * [start, start+len) of the grouped-records arena, already in arrival order. */
+typedef struct chronos_window {
+    uint64_t trigger_idx; /* arrival index of the event that flushed it; windows are sorted by this */
+    uint64_t start;       /* first record of the window in the arena */
+    uint32_t len;         /* number of events (>= 2, :142) */
+    uint32_t pid;
+    uint32_t flags;       /* bit0: extension, a curl->chmod->EXEC chain completed inside this window */
+    uint32_t reserved;
+} chronos_window;
+
+typedef struct chronos_counts {
+    uint64_t n_events;    /* raw records in the submitted batch */
+    uint64_t n_survivors; /* events appended to process_memory (:138) in this batch */
+    uint64_t n_windows;   /* windows flushed by this batch */
+    uint64_t n_arena;     /* records in the arena = carried-in pending + n_survivors */
+    uint64_t n_pending;   /* events left in process_memory after this batch (sum of list lengths) */
+    uint64_t n_chains;    /* extension: curl->chmod->EXEC chains completed in this batch */
+    uint64_t n_pids_seen; /* keys of process_memory so far (PIDs with >= 1 surviving event) */
+    uint64_t reserved;
+} chronos_counts;
+
+/* Device-side view of the last batch's results (pointers owned by the context, valid
+ * until the next submit).  Lets a caller that already lives on the GPU skip the copies. */
+typedef struct chronos_device_view {
+    const void *arena;              /* n_arena * 288 bytes, grouped by pid, arrival order inside */
+    const chronos_window *windows;  /* n_windows, ascending trigger_idx */
+    const uint32_t *survivor_idx;   /* n_survivors, batch-local arrival index, ascending */
+    const uint8_t *survivor_meta;   /* n_survivors, CHRONOS_META_* */
+    const uint32_t *pending_pid;    /* n_pending, ascending pid, arrival order inside a pid */
+    const uint32_t *pending_slot;   /* n_pending, arena record index */
+    const uint64_t *pending_arrival;/* n_pending, global arrival index */
+} chronos_device_view;
+
+/* Library / device probe.  chronos_sensor.py has no counterpart (it has no native
+ * library); returns CHRONOS_OK when `device` is a usable sm_100-class GPU. */
+int chronos_device_ok(int device);
+
+/* Replaces: module start-up + `process_memory = defaultdict(list)`
+ * (chronos_sensor.py:100-105).  Allocates all device state for batches of up to
+ * max_batch_events records on `device`. */
+int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out);
+
+/* Replaces: process exit (chronos_sensor.py:163). */
+int chronos_destroy(chronos_ctx *ctx);
+
+/* Human-readable text for the last non-OK status on this context (or a static string
+ * for ctx == NULL).  No reference counterpart. */
+const char *chronos_last_error(const chronos_ctx *ctx);
+
+/* Replaces: one perf_buffer_poll() worth of print_event callbacks
+ * (chronos_sensor.py:124-142, :157, :160-162) preceded by the openat hook's filter
+ * (:74-92).  `records` = n*288 bytes in arrival order, host or device memory (detected;
+ * device pointers must be 16-byte aligned); record i has global arrival index
+ * base_arrival_index + i.  Work is queued on the context's stream; per-PID state
+ * carries over from earlier submits.  A submit while results of the previous one are
+ * still unfetched discards those results (state is kept). */
+int chronos_submit(chronos_ctx *ctx, const void *records, uint64_t n, uint64_t base_arrival_index);
+
+/* Waits for the submitted batch and returns its counts. */
+int chronos_fetch(chronos_ctx *ctx, chronos_counts *out);
+
+/* Copies to host memory, after chronos_fetch.  cap_* are capacities in elements; the
+ * call fails with CHRONOS_E_ARG when the result does not fit. */
+int chronos_copy_survivors(chronos_ctx *ctx, uint64_t *global_idx, uint8_t *meta /* may be NULL */, uint64_t cap);
+int chronos_copy_windows(chronos_ctx *ctx, chronos_window *dst, uint64_t cap);
+int chronos_copy_arena(chronos_ctx *ctx, void *dst, uint64_t cap_records);
+/* Only the records that belong to flushed windows, window after window in
+ * trigger_idx order (window w starts at the running sum of len); the form the
+ * analyze_sequence caller needs (chronos_sensor.py:147). */
+int chronos_copy_window_records(chronos_ctx *ctx, void *dst, uint64_t cap_records);
+int chronos_copy_chains(chronos_ctx *ctx, uint32_t *pid, uint64_t *global_idx, uint64_t cap);
+
+/* Replaces: reading process_memory (chronos_sensor.py:105) -- the pending per-PID
+ * lists after the last fetched batch, ascending pid, arrival order inside a pid.
+ * records (may be NULL) receives the 288-byte events themselves. */
+int chronos_state(chronos_ctx *ctx, uint32_t *pid, uint64_t *global_idx, void *records, uint64_t cap);
+/* The keys of process_memory (PIDs that ever had a surviving event, including those
+ * whose list is currently []), unordered. */
+int chronos_state_pids(chronos_ctx *ctx, uint32_t *pid, uint64_t cap);
+
+int chronos_get_device_view(chronos_ctx *ctx, chronos_device_view *out);
+
+/* Timing of the last fetched batch as measured with CUDA events on the context's
+ * stream: total and the filter kernel alone, in milliseconds. */
+int chronos_last_timing(chronos_ctx *ctx, float *total_ms, float *filter_ms);
+/* Number of kernel launches the last submit issued (bench.py's gpu_launches). */
+int chronos_last_launches(chronos_ctx *ctx, uint64_t *launches);
+/* The CUDA stream the context launches on (cudaStream_t as void*), for callers that
+ * want to order their own work after it. */
+void *chronos_stream(chronos_ctx *ctx);
+
+/* ---- multi-GPU building blocks (PID-hash sharding) ------------------- */
+
+/* owner rank of a pid: hash32(pid) % world. Exposed so host code and tests agree. */
+uint32_t chronos_owner_of(uint32_t pid, uint32_t world);
+
+/* Stage 1 on the rank that holds a contiguous slice of the batch: filter it, then pack
+ * the survivors per owner rank (stable: arrival order kept inside each destination)
+ * into caller-provided DEVICE buffers of capacity `cap` entries:
+ *   send_records cap*288 bytes, send_arrival cap u64, send_meta cap u8.
+ * counts_host[world] receives the per-destination entry counts (this call waits for the
+ * GPU).  Destination d's entries start at the running sum of counts. */
+int chronos_filter_partition(chronos_ctx *ctx, const void *records, uint64_t n, uint64_t base_arrival_index,
+                             uint32_t world, void *send_records, uint64_t *send_arrival, uint8_t *send_meta,
+                             uint64_t cap, uint64_t *counts_host);
+
+/* Stage 2 on the owner rank: run grouping + window logic on `n` already-filtered
+ * entries (device pointers, concatenated in source-rank order = global arrival order).
+ * Results are fetched with the calls above; survivor indices are then entry positions. */
+int chronos_submit_survivors(chronos_ctx *ctx, const void *records, const uint64_t *arrival, const uint8_t *meta,
+                             uint64_t n);
+
+/* ---- synthetic trace (no reference counterpart: the reference ships no trace) ------ */
+
+typedef struct chronos_tracegen_cfg {
+    uint64_t seed;
+    uint32_t n_pids;
+    uint32_t pid_base;
+    uint32_t pid_stride;
+    uint32_t noise_permille;
+    uint32_t exec_permille;
+    uint32_t adv_permille;
+    uint32_t long_permille;
+    uint32_t chain_period;
+    uint32_t chain_pid_base;
+    uint32_t use_cdf;
+} chronos_tracegen_cfg;
+
+/* Fill dst (host memory) with records [first, first+n) of the trace. cdf: n_pids u64
+ * thresholds (host) when cfg->use_cdf, else NULL. */
+int chronos_tracegen_host(const chronos_tracegen_cfg *cfg, const uint64_t *cdf, uint64_t first, uint64_t n, void *dst);
+/* Same bytes, generated by a CUDA kernel into device memory (dst and cdf are device
+ * pointers on `device`). */
+int chronos_tracegen_device(int device, const chronos_tracegen_cfg *cfg, const uint64_t *cdf_dev, uint64_t first,
+                            uint64_t n, void *dst_dev);
+
+/* Plain device/pinned memory helpers so that a ctypes-only caller needs no other CUDA
+ * binding (no reference counterpart). */
+int chronos_dev_alloc(int device, uint64_t bytes, void **out);
+int chronos_dev_free(int device, void *p);
+int chronos_host_alloc_pinned(uint64_t bytes, void **out);
+int chronos_host_free_pinned(void *p);
+int chronos_memcpy_h2d(int device, void *dst_dev, const void *src_host, uint64_t bytes);
+int chronos_memcpy_d2h(int device, void *dst_host, const void *src_dev, uint64_t bytes);
+/* Writes `bytes` of a scratch device buffer, to evict the 126 MB L2 between timed runs. */
+int chronos_flush_l2(int device);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CHRONOS_B200_H */

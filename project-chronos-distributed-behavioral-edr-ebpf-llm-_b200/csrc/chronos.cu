@@ -1,0 +1,915 @@
+// chronos.cu -- context, batch pipeline and the C ABI (include/chronos.h) of the
+// B200-native CHRONOS hot path. Kernels live in filter.cuh / sort.cuh / window.cuh.
+//
+// Per batch (one perf_buffer_poll() worth of events, chronos_sensor.py:160-162):
+//   filter_kernel      raw records -> arrival-ordered survivors (pid, src index, meta)
+//   radix passes       stable sort of [carried-in pending ++ survivors] by pid
+//   gather_records     every grouped event copied once into the arena
+//   window_forward     flush automaton -> window descriptors
+//   window_reverse     unflushed tails -> next batch's pending list (process_memory)
+//   window_order       windows in trigger-arrival order (the order analyze_sequence
+//                      is called in, :143-147)
+// The only host synchronisation inside a submit is the read-back of the survivor count
+// and the pid OR/AND after the filter (sizes every later launch and buffer exactly).
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <new>
+#include <vector>
+
+#include "chronos.h"
+#include "common.cuh"
+#include "filter.cuh"
+#include "sort.cuh"
+#include "tracegen.cuh"
+#include "window.cuh"
+
+using namespace chronos;
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+};
+
+struct DeviceScalars {  // one 64-byte block on the device, mirrored in pinned memory
+    uint32_t surv_count;
+    uint32_t key_or;
+    uint32_t key_and;
+    uint32_t n_windows;
+    uint32_t n_pending;
+    uint32_t n_chains;
+    uint32_t pad[10];
+};
+
+constexpr int N_TICKETS = 64;
+
+}  // namespace
+
+struct chronos_ctx {
+    int device = 0;
+    int sm_count = 0;
+    uint64_t max_batch = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_filter = nullptr, ev_end = nullptr;
+    char err[256] = {0};
+
+    // batch staging for host-pointer submits
+    DevBuf d_batch;
+    // entry arrays (capacity in entries = ecap)
+    DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, flush, wi_of_entry, wsorted, windows, radix_table;
+    DevBuf surv_arrival;  // only for chronos_submit_survivors
+    // double-buffered persistent state
+    DevBuf arena[2];
+    DevBuf pend_key[2], pend_slot[2], pend_arrival[2], pend_meta[2];
+    uint64_t pend_cap[2] = {0, 0};  // capacity (entries) the right-aligned arrays were laid out for
+    int cur = 0;                    // index written by the batch in flight / last fetched
+    uint64_t n_pending = 0;         // entries pending after the last fetched batch (in buffer `cur`)
+    // scheduling scratch
+    DevBuf status, tickets, scalars;
+    DeviceScalars *h_scalars = nullptr;  // pinned
+    DevBuf pack;                         // scratch for chronos_copy_window_records / chronos_state
+    DevBuf pack_off;
+
+    // last batch
+    enum { IDLE, SUBMITTED, FETCHED } phase = IDLE;
+    uint64_t b_n = 0, b_base = 0, b_S = 0, b_P = 0, b_M = 0, b_W = 0;
+    const uint8_t *b_records = nullptr;  // device pointer of the batch records
+    bool b_explicit_arrival = false;
+    const uint32_t *sorted_key = nullptr, *sorted_val = nullptr;
+    uint64_t launches = 0;
+    float t_total = 0.f, t_filter = 0.f;
+    int filter_variant = 0;
+};
+
+namespace {
+
+const char *g_static_err = "chronos: invalid context";
+
+int fail(chronos_ctx *c, int code, const char *fmt, ...) {
+    if (c) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(c->err, sizeof(c->err), fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+#define CK(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e__ = (call);                                                                     \
+        if (e__ != cudaSuccess)                                                                       \
+            return fail(c, e__ == cudaErrorMemoryAllocation ? CHRONOS_E_NOMEM : CHRONOS_E_CUDA,       \
+                        "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+int ensure(chronos_ctx *c, DevBuf &b, size_t bytes) {
+    if (bytes <= b.bytes && b.p) return CHRONOS_OK;
+    if (b.p) {
+        CK(cudaFree(b.p));
+        b.p = nullptr;
+        b.bytes = 0;
+    }
+    size_t want = std::max<size_t>(bytes + bytes / 8, 256);
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        want = std::max<size_t>(bytes, 256);
+        e = cudaMalloc(&b.p, want);
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        b.p = nullptr;
+        return fail(c, CHRONOS_E_NOMEM, "cudaMalloc(%zu bytes) failed: %s", want, cudaGetErrorString(e));
+    }
+    b.bytes = want;
+    return CHRONOS_OK;
+}
+
+void release(DevBuf &b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.bytes = 0;
+}
+
+template <typename T>
+T *ptr(DevBuf &b) {
+    return reinterpret_cast<T *>(b.p);
+}
+
+bool is_device_pointer(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+// ---- small helper kernels ---------------------------------------------------------------
+__global__ void fold_keys_kernel(const uint32_t *keys, uint32_t n, uint32_t *k_or, uint32_t *k_and) {
+    uint32_t o = 0, a = 0xffffffffu;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        uint32_t k = keys[i];
+        o |= k;
+        a &= k;
+    }
+    o = __reduce_or_sync(0xffffffffu, o);
+    a = __reduce_and_sync(0xffffffffu, a);
+    if ((threadIdx.x & 31) == 0) {
+        atomicOr(k_or, o);
+        atomicAnd(k_and, a);
+    }
+}
+
+__global__ void iota_kernel(uint32_t *v, uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) v[i] = i;
+}
+
+__global__ void init_scalars_kernel(DeviceScalars *s) {
+    s->surv_count = 0;
+    s->key_or = 0;
+    s->key_and = 0xffffffffu;
+    s->n_windows = 0;
+    s->n_pending = 0;
+    s->n_chains = 0;
+}
+
+// Stage-2 entry (already-filtered events): pid out of the record, identity src index.
+__global__ void extract_pid_kernel(const uint8_t *recs, uint32_t n, uint32_t *key, uint32_t *src, uint32_t *k_or,
+                                   uint32_t *k_and) {
+    uint32_t o = 0, a = 0xffffffffu;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        uint32_t k = *reinterpret_cast<const uint32_t *>(recs + (size_t)i * CH_REC_BYTES);
+        key[i] = k;
+        src[i] = i;
+        o |= k;
+        a &= k;
+    }
+    o = __reduce_or_sync(0xffffffffu, o);
+    a = __reduce_and_sync(0xffffffffu, a);
+    if ((threadIdx.x & 31) == 0) {
+        atomicOr(k_or, o);
+        atomicAnd(k_and, a);
+    }
+}
+
+// one warp per packed record: dst[i] = arena[slot(i)]
+__global__ void pack_by_slot_kernel(const uint8_t *arena, const uint32_t *slot, uint32_t n, uint8_t *dst) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t i = warp; i < n; i += n_warps) {
+        const uint4 *s = reinterpret_cast<const uint4 *>(arena + (size_t)slot[i] * CH_REC_BYTES);
+        uint4 *d = reinterpret_cast<uint4 *>(dst + (size_t)i * CH_REC_BYTES);
+        if (lane < CH_REC_CHUNKS) d[lane] = s[lane];
+    }
+}
+
+// one warp per window: packed[off[w] ..] = arena[start .. start+len)
+__global__ void pack_windows_kernel(const uint8_t *arena, const chronos_window *win, const uint64_t *off, uint32_t nw,
+                                    uint8_t *dst) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t w = warp; w < nw; w += n_warps) {
+        const uint4 *s = reinterpret_cast<const uint4 *>(arena + (size_t)win[w].start * CH_REC_BYTES);
+        uint4 *d = reinterpret_cast<uint4 *>(dst + (size_t)off[w] * CH_REC_BYTES);
+        const uint32_t chunks = win[w].len * CH_REC_CHUNKS;
+        for (uint32_t ch = lane; ch < chunks; ch += 32) d[ch] = s[ch];
+    }
+}
+
+__global__ void add_base_kernel(const uint32_t *src, uint32_t n, uint64_t base, uint64_t *out) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = base + src[i];
+}
+
+__global__ void l2_flush_kernel(uint4 *p, size_t n16, uint32_t v) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x)
+        p[i] = make_uint4(v, v, v, v);
+}
+
+__global__ void tracegen_kernel(chronos_tracegen_cfg cfg, const uint64_t *cdf, uint64_t first, uint64_t n,
+                                uint8_t *dst) {
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        uint8_t rec[CH_REC_BYTES];
+        chronos_gen::gen_record(cfg, first + i, cdf, rec);
+        uint32_t *d = reinterpret_cast<uint32_t *>(dst + i * CH_REC_BYTES);
+        const uint32_t *s = reinterpret_cast<const uint32_t *>(rec);
+        for (int k = 0; k < CH_REC_WORDS; k++) d[k] = s[k];
+    }
+}
+
+// ---- filter launch ------------------------------------------------------------------------
+template <int TILE, int NSTAGE>
+int launch_filter_t(chronos_ctx *c, FilterParams fp, uint64_t n_records_from_tile_begin) {
+    static bool configured[16] = {false};
+    auto kern = filter_kernel<TILE, NSTAGE>;
+    const size_t smem = filter_smem_bytes<TILE, NSTAGE>();
+    if (!configured[c->device & 15]) {
+        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[c->device & 15] = true;
+    }
+    int per_sm = 0;
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TILE, smem));
+    if (per_sm < 1) return fail(c, CHRONOS_E_CUDA, "filter kernel does not fit on an SM (smem %zu)", smem);
+    const uint32_t tiles = fp.tile_end - fp.tile_begin;
+    const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(per_sm * c->sm_count));
+    (void)n_records_from_tile_begin;
+    kern<<<grid, TILE, smem, c->stream>>>(fp);
+    CK(cudaGetLastError());
+    c->launches++;
+    return CHRONOS_OK;
+}
+
+int filter_tile_size(const chronos_ctx *c) {
+    switch (c->filter_variant) {
+    case 1: return 128;
+    case 2: return 256;
+    case 3: return 64;
+    default: return 128;
+    }
+}
+
+int launch_filter(chronos_ctx *c, const FilterParams &fp) {
+    switch (c->filter_variant) {
+    case 1: return launch_filter_t<128, 2>(c, fp, 0);
+    case 2: return launch_filter_t<256, 2>(c, fp, 0);
+    case 3: return launch_filter_t<64, 4>(c, fp, 0);
+    default: return launch_filter_t<128, 3>(c, fp, 0);
+    }
+}
+
+struct PassPlan {
+    int n = 0;
+    uint32_t shift[4], mask[4];
+};
+
+PassPlan plan_passes(uint32_t k_or, uint32_t k_and, uint64_t M) {
+    PassPlan pl;
+    uint32_t diff = k_or ^ k_and;
+    if (M < 2 || diff == 0) return pl;
+    int lo = __builtin_ctz(diff), hi = 32 - __builtin_clz(diff);
+    int bits = hi - lo;
+    int passes = (bits + 7) / 8;
+    int per = (bits + passes - 1) / passes;
+    int s = lo;
+    for (int i = 0; i < passes; i++) {
+        int b = std::min(per, hi - s);
+        pl.shift[i] = (uint32_t)s;
+        pl.mask[i] = (1u << b) - 1u;
+        s += b;
+    }
+    pl.n = passes;
+    return pl;
+}
+
+int finish_batch(chronos_ctx *c);
+
+// Everything after the survivors are known on the device (keyA[P..P+S), surv_src, surv_meta).
+int run_window_stage(chronos_ctx *c) {
+    const uint64_t P = c->b_P;
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    // the one mid-pipeline read-back: survivor count + pid bit spread
+    CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaEventRecord(c->ev_filter, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    const uint64_t S = c->h_scalars->surv_count;
+    const uint64_t M = P + S;
+    c->b_S = S;
+    c->b_M = M;
+    const int cur = c->cur, prev = cur ^ 1;
+    c->sorted_key = ptr<uint32_t>(c->keyA);
+    c->sorted_val = nullptr;
+    if (M == 0) {
+        c->h_scalars->n_windows = 0;
+        c->h_scalars->n_pending = 0;
+        c->pend_cap[cur] = 0;
+        CK(cudaEventRecord(c->ev_end, c->stream));
+        return CHRONOS_OK;
+    }
+    if (M >= (1ull << 29)) return fail(c, CHRONOS_E_CAPACITY, "more than 2^29 grouped entries (%llu)", (unsigned long long)M);
+
+    int rc;
+    if ((rc = ensure(c, c->arena[cur], M * CH_REC_BYTES))) return rc;
+    if ((rc = ensure(c, c->pend_key[cur], M * 4))) return rc;
+    if ((rc = ensure(c, c->pend_slot[cur], M * 4))) return rc;
+    if ((rc = ensure(c, c->pend_arrival[cur], M * 8))) return rc;
+    if ((rc = ensure(c, c->pend_meta[cur], M))) return rc;
+    c->pend_cap[cur] = M;
+    if ((rc = ensure(c, c->flush, M))) return rc;
+    if ((rc = ensure(c, c->wsorted, (S / 2 + 1) * sizeof(WinSorted)))) return rc;
+    if ((rc = ensure(c, c->windows, (S / 2 + 1) * sizeof(chronos_window)))) return rc;
+
+    // ---- stable sort by pid -----------------------------------------------------------
+    PassPlan pl = plan_passes(c->h_scalars->key_or, c->h_scalars->key_and, M);
+    uint32_t *kin = ptr<uint32_t>(c->keyA), *kout = ptr<uint32_t>(c->keyB);
+    uint32_t *vin = nullptr, *vout = ptr<uint32_t>(c->valA);
+    uint32_t *vspare = ptr<uint32_t>(c->valB);
+    if (pl.n > 0) {
+        uint32_t tile_keys = 4096;
+        while ((M + tile_keys - 1) / tile_keys > 1024) tile_keys *= 2;
+        const uint32_t n_tiles = (uint32_t)((M + tile_keys - 1) / tile_keys);
+        if ((rc = ensure(c, c->radix_table, (size_t)RADIX_BINS * n_tiles * 4))) return rc;
+        for (int i = 0; i < pl.n; i++) {
+            RadixParams rp;
+            rp.keys_in = kin;
+            rp.vals_in = vin;
+            rp.keys_out = kout;
+            rp.vals_out = vout;
+            rp.table = ptr<uint32_t>(c->radix_table);
+            rp.n = (uint32_t)M;
+            rp.tile_keys = tile_keys;
+            rp.n_tiles = n_tiles;
+            rp.shift = pl.shift[i];
+            rp.mask = pl.mask[i];
+            radix_hist<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
+            radix_scan<<<1, 1024, 0, c->stream>>>(rp.table, RADIX_BINS * n_tiles);
+            radix_scatter<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
+            CK(cudaGetLastError());
+            c->launches += 3;
+            std::swap(kin, kout);
+            uint32_t *nv = (vin == nullptr) ? vspare : vin;
+            vin = vout;
+            vout = nv;
+        }
+        c->sorted_key = kin;
+        c->sorted_val = vin;
+    } else {
+        // all keys equal (or a single entry): identity permutation
+        uint32_t *v = ptr<uint32_t>(c->valA);
+        iota_kernel<<<(unsigned)std::min<uint64_t>((M + 255) / 256, 2048), 256, 0, c->stream>>>(v, (uint32_t)M);
+        CK(cudaGetLastError());
+        c->launches++;
+        c->sorted_key = kin;
+        c->sorted_val = v;
+    }
+
+    // ---- records into the grouped arena ----------------------------------------------
+    {
+        GatherParams g;
+        g.sval = c->sorted_val;
+        g.M = (uint32_t)M;
+        g.P = (uint32_t)P;
+        g.surv_src = ptr<uint32_t>(c->surv_src);
+        g.batch = c->b_records;
+        const uint64_t pc = c->pend_cap[prev];
+        g.pend_slot = P ? ptr<uint32_t>(c->pend_slot[prev]) + (pc - P) : nullptr;
+        g.prev_arena = ptr<uint8_t>(c->arena[prev]);
+        g.arena = ptr<uint8_t>(c->arena[cur]);
+        uint32_t blocks = (uint32_t)std::min<uint64_t>((M + 127) / 128, (uint64_t)c->sm_count * 8);
+        gather_records<<<blocks, 256, 0, c->stream>>>(g);
+        CK(cudaGetLastError());
+        c->launches++;
+    }
+
+    // ---- window automaton ---------------------------------------------------------------
+    {
+        WinParams w;
+        memset(&w, 0, sizeof(w));
+        w.skey = c->sorted_key;
+        w.sval = c->sorted_val;
+        w.M = (uint32_t)M;
+        w.P = (uint32_t)P;
+        w.surv_meta = ptr<uint8_t>(c->surv_meta);
+        w.surv_src = ptr<uint32_t>(c->surv_src);
+        w.surv_arrival = c->b_explicit_arrival ? ptr<uint64_t>(c->surv_arrival) : nullptr;
+        w.base_arrival = c->b_base;
+        const uint64_t pc = c->pend_cap[prev];
+        w.pend_meta = P ? ptr<uint8_t>(c->pend_meta[prev]) + (pc - P) : nullptr;
+        w.pend_arrival = P ? ptr<uint64_t>(c->pend_arrival[prev]) + (pc - P) : nullptr;
+        w.pend_slot = P ? ptr<uint32_t>(c->pend_slot[prev]) + (pc - P) : nullptr;
+        w.flush = ptr<uint8_t>(c->flush);
+        w.wsorted = ptr<WinSorted>(c->wsorted);
+        w.wi_of_entry = ptr<uint32_t>(c->wi_of_entry);
+        w.n_windows = &ds->n_windows;
+        w.pend_cap = (uint32_t)M;
+        w.npend_key = ptr<uint32_t>(c->pend_key[cur]);
+        w.npend_slot = ptr<uint32_t>(c->pend_slot[cur]);
+        w.npend_arrival = ptr<uint64_t>(c->pend_arrival[cur]);
+        w.npend_meta = ptr<uint8_t>(c->pend_meta[cur]);
+        w.n_pending = &ds->n_pending;
+        w.windows = ptr<chronos_window>(c->windows);
+        const uint32_t tiles_m = (uint32_t)((M + WIN_TILE - 1) / WIN_TILE);
+        const uint32_t tiles_s = (uint32_t)((S + WIN_TILE - 1) / WIN_TILE);
+        uint64_t *st = ptr<uint64_t>(c->status) + c->b_n / 64 + 2;  // behind the filter's tile words (>= n/64)
+        uint32_t *tk = ptr<uint32_t>(c->tickets);
+        const uint32_t cap_blocks = (uint32_t)c->sm_count * 4;
+        w.ticket = tk + 60;
+        w.status = st;
+        window_forward<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
+        w.ticket = tk + 61;
+        w.status = st + 2 * (size_t)tiles_m;
+        window_reverse<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
+        c->launches += 2;
+        if (S > 0) {
+            w.ticket = tk + 62;
+            w.status = st + 4 * (size_t)tiles_m;
+            window_order<<<std::min(tiles_s, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
+            c->launches++;
+        }
+        CK(cudaGetLastError());
+    }
+    CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaEventRecord(c->ev_end, c->stream));
+    return CHRONOS_OK;
+}
+
+// status words needed for a batch of n raw records producing at most n survivors on top of P pending
+size_t status_words(uint64_t n, uint64_t P) {
+    const uint64_t M = n + P;
+    const uint64_t tiles_m = (M + WIN_TILE - 1) / WIN_TILE;
+    return (size_t)(n / 64 + 2 + 5 * tiles_m + 64);
+}
+
+int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
+    CK(cudaSetDevice(c->device));
+    if (c->phase == chronos_ctx::SUBMITTED) {
+        int rc = finish_batch(c);  // results dropped, state kept
+        if (rc) return rc;
+    }
+    if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
+                                      (unsigned long long)n, (unsigned long long)c->max_batch);
+    if (n >= (1ull << 32)) return fail(c, CHRONOS_E_CAPACITY, "batch too large");
+    // the batch in flight writes buffer set cur^1; the previous state stays in cur until fetch
+    const uint64_t P = c->n_pending;
+    c->cur ^= 1;
+    c->b_n = n;
+    c->b_base = base;
+    c->b_P = P;
+    c->b_S = c->b_M = c->b_W = 0;
+    c->launches = 0;
+    const uint64_t ecap = P + n;
+    int rc;
+    if ((rc = ensure(c, c->keyA, (ecap + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->keyB, (ecap + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->valA, (ecap + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->valB, (ecap + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
+    if ((rc = ensure(c, c->wi_of_entry, (n + 1) * 4))) return rc;
+    const size_t sw = status_words(n, P);
+    if ((rc = ensure(c, c->status, sw * 8))) return rc;
+    CK(cudaEventRecord(c->ev_start, c->stream));
+    CK(cudaMemsetAsync(c->status.p, 0, sw * 8, c->stream));
+    CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
+    init_scalars_kernel<<<1, 1, 0, c->stream>>>(ptr<DeviceScalars>(c->scalars));
+    c->launches++;
+    if (P) {
+        const int prev = c->cur ^ 1;
+        const uint64_t pc = c->pend_cap[prev];
+        const uint32_t *pk = ptr<uint32_t>(c->pend_key[prev]) + (pc - P);
+        CK(cudaMemcpyAsync(c->keyA.p, pk, P * 4, cudaMemcpyDeviceToDevice, c->stream));
+        DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+        fold_keys_kernel<<<(unsigned)std::min<uint64_t>((P + 255) / 256, 1024), 256, 0, c->stream>>>(
+            pk, (uint32_t)P, &ds->key_or, &ds->key_and);
+        c->launches++;
+    }
+    CK(cudaGetLastError());
+    return CHRONOS_OK;
+}
+
+int finish_batch(chronos_ctx *c) {
+    CK(cudaStreamSynchronize(c->stream));
+    c->b_W = c->b_M ? c->h_scalars->n_windows : 0;
+    c->n_pending = c->b_M ? c->h_scalars->n_pending : 0;
+    cudaEventElapsedTime(&c->t_total, c->ev_start, c->ev_end);
+    cudaEventElapsedTime(&c->t_filter, c->ev_start, c->ev_filter);
+    cudaGetLastError();
+    c->phase = chronos_ctx::FETCHED;
+    return CHRONOS_OK;
+}
+
+}  // namespace
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+int chronos_device_ok(int device) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || device < 0 || device >= n) {
+        cudaGetLastError();
+        return CHRONOS_E_CUDA;
+    }
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, device) != cudaSuccess) return CHRONOS_E_CUDA;
+    return p.major == 10 ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+
+const char *chronos_last_error(const chronos_ctx *ctx) { return ctx ? ctx->err : g_static_err; }
+
+int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
+    if (!out || max_batch_events == 0 || max_batch_events >= (1ull << 32)) return CHRONOS_E_ARG;
+    *out = nullptr;
+    if (chronos_device_ok(device) != CHRONOS_OK) return CHRONOS_E_CUDA;
+    chronos_ctx *c = new (std::nothrow) chronos_ctx();
+    if (!c) return CHRONOS_E_NOMEM;
+    c->device = device;
+    c->max_batch = max_batch_events;
+    const char *fv = getenv("CHRONOS_FILTER_VARIANT");
+    c->filter_variant = fv ? atoi(fv) : 0;
+    auto boot = [&]() -> int {
+        CK(cudaSetDevice(device));
+        cudaDeviceProp p;
+        CK(cudaGetDeviceProperties(&p, device));
+        c->sm_count = p.multiProcessorCount;
+        CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        CK(cudaEventCreate(&c->ev_start));
+        CK(cudaEventCreate(&c->ev_filter));
+        CK(cudaEventCreate(&c->ev_end));
+        CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_scalars), sizeof(DeviceScalars)));
+        int rc;
+        if ((rc = ensure(c, c->tickets, N_TICKETS * 4))) return rc;
+        if ((rc = ensure(c, c->scalars, sizeof(DeviceScalars)))) return rc;
+        return CHRONOS_OK;
+    };
+    int rc = boot();
+    if (rc != CHRONOS_OK) {
+        chronos_destroy(c);
+        return rc;
+    }
+    *out = c;
+    return CHRONOS_OK;
+}
+
+int chronos_destroy(chronos_ctx *c) {
+    if (!c) return CHRONOS_E_ARG;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->flush,
+                     &c->wi_of_entry, &c->wsorted, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+                     &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
+                     &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
+                     &c->tickets, &c->scalars, &c->pack, &c->pack_off};
+    for (DevBuf *b : all) release(*b);
+    if (c->h_scalars) cudaFreeHost(c->h_scalars);
+    if (c->ev_start) cudaEventDestroy(c->ev_start);
+    if (c->ev_filter) cudaEventDestroy(c->ev_filter);
+    if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    cudaGetLastError();
+    delete c;
+    return CHRONOS_OK;
+}
+
+int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t base_arrival_index) {
+    if (!c) return CHRONOS_E_ARG;
+    if (n && !records) return fail(c, CHRONOS_E_ARG, "records is NULL");
+    int rc = begin_batch(c, n, base_arrival_index);
+    if (rc) return rc;
+    const uint8_t *d_recs = nullptr;
+    if (n) {
+        if (is_device_pointer(records)) {
+            if ((uintptr_t)records & 15) return fail(c, CHRONOS_E_ARG, "device records pointer must be 16-byte aligned");
+            d_recs = static_cast<const uint8_t *>(records);
+        } else {
+            if ((rc = ensure(c, c->d_batch, n * CH_REC_BYTES))) return rc;
+            CK(cudaMemcpyAsync(c->d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, c->stream));
+            d_recs = ptr<uint8_t>(c->d_batch);
+        }
+    }
+    c->b_records = d_recs;
+    c->b_explicit_arrival = false;
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    if (n) {
+        const int TILE = filter_tile_size(c);
+        FilterParams fp;
+        fp.recs = d_recs;
+        fp.n = n;
+        fp.tile_begin = 0;
+        fp.tile_end = (uint32_t)((n + TILE - 1) / TILE);
+        fp.ticket = ptr<uint32_t>(c->tickets);
+        fp.tile_status = ptr<uint64_t>(c->status);
+        fp.out_key = ptr<uint32_t>(c->keyA) + c->b_P;
+        fp.out_src = ptr<uint32_t>(c->surv_src);
+        fp.out_meta = ptr<uint8_t>(c->surv_meta);
+        fp.out_count = &ds->surv_count;
+        fp.key_or = &ds->key_or;
+        fp.key_and = &ds->key_and;
+        fp.last_tile = fp.tile_end - 1;
+        if ((rc = launch_filter(c, fp))) return rc;
+    }
+    if ((rc = run_window_stage(c))) return rc;
+    c->phase = chronos_ctx::SUBMITTED;
+    return CHRONOS_OK;
+}
+
+int chronos_submit_survivors(chronos_ctx *c, const void *records, const uint64_t *arrival, const uint8_t *meta,
+                             uint64_t n) {
+    if (!c) return CHRONOS_E_ARG;
+    if (n && (!records || !arrival || !meta)) return fail(c, CHRONOS_E_ARG, "NULL argument");
+    if (n && (!is_device_pointer(records) || ((uintptr_t)records & 15)))
+        return fail(c, CHRONOS_E_ARG, "records must be a 16-byte aligned device pointer");
+    int rc = begin_batch(c, n, 0);
+    if (rc) return rc;
+    c->b_records = static_cast<const uint8_t *>(records);
+    c->b_explicit_arrival = true;
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    if (n) {
+        if ((rc = ensure(c, c->surv_arrival, n * 8))) return rc;
+        CK(cudaMemcpyAsync(c->surv_arrival.p, arrival, n * 8, cudaMemcpyDefault, c->stream));
+        CK(cudaMemcpyAsync(c->surv_meta.p, meta, n, cudaMemcpyDefault, c->stream));
+        extract_pid_kernel<<<(unsigned)std::min<uint64_t>((n + 255) / 256, 2048), 256, 0, c->stream>>>(
+            c->b_records, (uint32_t)n, ptr<uint32_t>(c->keyA) + c->b_P, ptr<uint32_t>(c->surv_src), &ds->key_or,
+            &ds->key_and);
+        c->launches++;
+        const uint32_t cnt = (uint32_t)n;
+        CK(cudaMemcpyAsync(&ds->surv_count, &cnt, 4, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaStreamSynchronize(c->stream));  // cnt lives on this stack frame
+    }
+    if ((rc = run_window_stage(c))) return rc;
+    c->phase = chronos_ctx::SUBMITTED;
+    return CHRONOS_OK;
+}
+
+int chronos_fetch(chronos_ctx *c, chronos_counts *out) {
+    if (!c || !out) return CHRONOS_E_ARG;
+    if (c->phase == chronos_ctx::IDLE) return fail(c, CHRONOS_E_STATE, "nothing submitted");
+    CK(cudaSetDevice(c->device));
+    if (c->phase == chronos_ctx::SUBMITTED) {
+        int rc = finish_batch(c);
+        if (rc) return rc;
+    }
+    memset(out, 0, sizeof(*out));
+    out->n_events = c->b_n;
+    out->n_survivors = c->b_S;
+    out->n_windows = c->b_W;
+    out->n_arena = c->b_M;
+    out->n_pending = c->n_pending;
+    out->n_chains = 0;
+    out->n_pids_seen = 0;
+    return CHRONOS_OK;
+}
+
+static int need_fetched(chronos_ctx *c) {
+    if (!c) return CHRONOS_E_ARG;
+    if (c->phase != chronos_ctx::FETCHED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    cudaError_t e = cudaSetDevice(c->device);
+    if (e != cudaSuccess) return fail(c, CHRONOS_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    return CHRONOS_OK;
+}
+
+int chronos_copy_survivors(chronos_ctx *c, uint64_t *global_idx, uint8_t *meta, uint64_t cap) {
+    int rc = need_fetched(c);
+    if (rc) return rc;
+    const uint64_t S = c->b_S;
+    if (cap < S || (S && !global_idx)) return fail(c, CHRONOS_E_ARG, "survivor buffer too small (%llu < %llu)",
+                                                   (unsigned long long)cap, (unsigned long long)S);
+    if (!S) return CHRONOS_OK;
+    if (c->b_explicit_arrival) {
+        CK(cudaMemcpyAsync(global_idx, c->surv_arrival.p, S * 8, cudaMemcpyDeviceToHost, c->stream));
+    } else {
+        if ((rc = ensure(c, c->pack, S * 8))) return rc;
+        add_base_kernel<<<(unsigned)std::min<uint64_t>((S + 255) / 256, 2048), 256, 0, c->stream>>>(
+            ptr<uint32_t>(c->surv_src), (uint32_t)S, c->b_base, ptr<uint64_t>(c->pack));
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(global_idx, c->pack.p, S * 8, cudaMemcpyDeviceToHost, c->stream));
+    }
+    if (meta) CK(cudaMemcpyAsync(meta, c->surv_meta.p, S, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return CHRONOS_OK;
+}
+
+int chronos_copy_windows(chronos_ctx *c, chronos_window *dst, uint64_t cap) {
+    int rc = need_fetched(c);
+    if (rc) return rc;
+    if (cap < c->b_W || (c->b_W && !dst)) return fail(c, CHRONOS_E_ARG, "window buffer too small");
+    if (!c->b_W) return CHRONOS_OK;
+    CK(cudaMemcpyAsync(dst, c->windows.p, c->b_W * sizeof(chronos_window), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return CHRONOS_OK;
+}
+
+int chronos_copy_arena(chronos_ctx *c, void *dst, uint64_t cap_records) {
+    int rc = need_fetched(c);
+    if (rc) return rc;
+    if (cap_records < c->b_M || (c->b_M && !dst)) return fail(c, CHRONOS_E_ARG, "arena buffer too small");
+    if (!c->b_M) return CHRONOS_OK;
+    CK(cudaMemcpyAsync(dst, c->arena[c->cur].p, c->b_M * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return CHRONOS_OK;
+}
+
+int chronos_copy_window_records(chronos_ctx *c, void *dst, uint64_t cap_records) {
+    int rc = need_fetched(c);
+    if (rc) return rc;
+    const uint64_t W = c->b_W;
+    if (!W) return CHRONOS_OK;
+    std::vector<chronos_window> win(W);
+    CK(cudaMemcpyAsync(win.data(), c->windows.p, W * sizeof(chronos_window), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    std::vector<uint64_t> off(W);
+    uint64_t tot = 0;
+    for (uint64_t i = 0; i < W; i++) {
+        off[i] = tot;
+        tot += win[i].len;
+    }
+    if (cap_records < tot || !dst) return fail(c, CHRONOS_E_ARG, "window record buffer too small (%llu < %llu)",
+                                               (unsigned long long)cap_records, (unsigned long long)tot);
+    if ((rc = ensure(c, c->pack, tot * CH_REC_BYTES))) return rc;
+    if ((rc = ensure(c, c->pack_off, W * 8))) return rc;
+    CK(cudaMemcpyAsync(c->pack_off.p, off.data(), W * 8, cudaMemcpyHostToDevice, c->stream));
+    pack_windows_kernel<<<(unsigned)std::min<uint64_t>((W + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
+        ptr<uint8_t>(c->arena[c->cur]), ptr<chronos_window>(c->windows), ptr<uint64_t>(c->pack_off), (uint32_t)W,
+        ptr<uint8_t>(c->pack));
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dst, c->pack.p, tot * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return CHRONOS_OK;
+}
+
+int chronos_copy_chains(chronos_ctx *c, uint32_t *pid, uint64_t *global_idx, uint64_t cap) {
+    int rc = need_fetched(c);
+    if (rc) return rc;
+    (void)pid;
+    (void)global_idx;
+    (void)cap;
+    return CHRONOS_OK;
+}
+
+int chronos_state(chronos_ctx *c, uint32_t *pid, uint64_t *global_idx, void *records, uint64_t cap) {
+    if (!c) return CHRONOS_E_ARG;
+    if (c->phase == chronos_ctx::SUBMITTED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    CK(cudaSetDevice(c->device));
+    const uint64_t P = c->n_pending;
+    if (cap < P) return fail(c, CHRONOS_E_ARG, "state buffer too small (%llu < %llu)", (unsigned long long)cap,
+                             (unsigned long long)P);
+    if (!P) return CHRONOS_OK;
+    const int cur = c->cur;
+    const uint64_t pc = c->pend_cap[cur];
+    if (pid) CK(cudaMemcpyAsync(pid, ptr<uint32_t>(c->pend_key[cur]) + (pc - P), P * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (global_idx)
+        CK(cudaMemcpyAsync(global_idx, ptr<uint64_t>(c->pend_arrival[cur]) + (pc - P), P * 8, cudaMemcpyDeviceToHost,
+                           c->stream));
+    if (records) {
+        int rc;
+        if ((rc = ensure(c, c->pack, P * CH_REC_BYTES))) return rc;
+        pack_by_slot_kernel<<<(unsigned)std::min<uint64_t>((P + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
+            ptr<uint8_t>(c->arena[cur]), ptr<uint32_t>(c->pend_slot[cur]) + (pc - P), (uint32_t)P, ptr<uint8_t>(c->pack));
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(records, c->pack.p, P * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    return CHRONOS_OK;
+}
+
+int chronos_state_pids(chronos_ctx *c, uint32_t *pid, uint64_t cap) {
+    if (!c) return CHRONOS_E_ARG;
+    (void)pid;
+    (void)cap;
+    return CHRONOS_OK;
+}
+
+int chronos_get_device_view(chronos_ctx *c, chronos_device_view *out) {
+    int rc = need_fetched(c);
+    if (rc) return rc;
+    if (!out) return CHRONOS_E_ARG;
+    const int cur = c->cur;
+    const uint64_t P = c->n_pending, pc = c->pend_cap[cur];
+    out->arena = c->arena[cur].p;
+    out->windows = ptr<chronos_window>(c->windows);
+    out->survivor_idx = ptr<uint32_t>(c->surv_src);
+    out->survivor_meta = ptr<uint8_t>(c->surv_meta);
+    out->pending_pid = P ? ptr<uint32_t>(c->pend_key[cur]) + (pc - P) : nullptr;
+    out->pending_slot = P ? ptr<uint32_t>(c->pend_slot[cur]) + (pc - P) : nullptr;
+    out->pending_arrival = P ? ptr<uint64_t>(c->pend_arrival[cur]) + (pc - P) : nullptr;
+    return CHRONOS_OK;
+}
+
+int chronos_last_timing(chronos_ctx *c, float *total_ms, float *filter_ms) {
+    int rc = need_fetched(c);
+    if (rc) return rc;
+    if (total_ms) *total_ms = c->t_total;
+    if (filter_ms) *filter_ms = c->t_filter;
+    return CHRONOS_OK;
+}
+
+int chronos_last_launches(chronos_ctx *c, uint64_t *launches) {
+    if (!c || !launches) return CHRONOS_E_ARG;
+    *launches = c->launches;
+    return CHRONOS_OK;
+}
+
+void *chronos_stream(chronos_ctx *c) { return c ? (void *)c->stream : nullptr; }
+
+uint32_t chronos_owner_of(uint32_t pid, uint32_t world) { return world ? hash32(pid) % world : 0; }
+
+int chronos_filter_partition(chronos_ctx *c, const void *, uint64_t, uint64_t, uint32_t, void *, uint64_t *, uint8_t *,
+                             uint64_t, uint64_t *) {
+    return fail(c, CHRONOS_E_STATE, "chronos_filter_partition: not built yet");
+}
+
+// ---- trace generator ------------------------------------------------------------------------
+int chronos_tracegen_host(const chronos_tracegen_cfg *cfg, const uint64_t *cdf, uint64_t first, uint64_t n, void *dst) {
+    if (!cfg || (n && !dst) || cfg->n_pids == 0 || (cfg->use_cdf && !cdf)) return CHRONOS_E_ARG;
+    uint8_t *d = static_cast<uint8_t *>(dst);
+    for (uint64_t i = 0; i < n; i++) chronos_gen::gen_record(*cfg, first + i, cdf, d + i * CH_REC_BYTES);
+    return CHRONOS_OK;
+}
+
+int chronos_tracegen_device(int device, const chronos_tracegen_cfg *cfg, const uint64_t *cdf_dev, uint64_t first,
+                            uint64_t n, void *dst_dev) {
+    if (!cfg || (n && !dst_dev) || cfg->n_pids == 0 || (cfg->use_cdf && !cdf_dev)) return CHRONOS_E_ARG;
+    if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
+    if (!n) return CHRONOS_OK;
+    tracegen_kernel<<<(unsigned)std::min<uint64_t>((n + 127) / 128, 148 * 16), 128>>>(*cfg, cdf_dev, first, n,
+                                                                                      static_cast<uint8_t *>(dst_dev));
+    if (cudaGetLastError() != cudaSuccess) return CHRONOS_E_CUDA;
+    return cudaDeviceSynchronize() == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+
+// ---- plain memory helpers -------------------------------------------------------------------
+int chronos_dev_alloc(int device, uint64_t bytes, void **out) {
+    if (!out) return CHRONOS_E_ARG;
+    if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
+    cudaError_t e = cudaMalloc(out, bytes ? bytes : 16);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return e == cudaErrorMemoryAllocation ? CHRONOS_E_NOMEM : CHRONOS_E_CUDA;
+    }
+    return CHRONOS_OK;
+}
+int chronos_dev_free(int device, void *p) {
+    if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
+    return cudaFree(p) == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+int chronos_host_alloc_pinned(uint64_t bytes, void **out) {
+    if (!out) return CHRONOS_E_ARG;
+    cudaError_t e = cudaMallocHost(out, bytes ? bytes : 16);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return e == cudaErrorMemoryAllocation ? CHRONOS_E_NOMEM : CHRONOS_E_CUDA;
+    }
+    return CHRONOS_OK;
+}
+int chronos_host_free_pinned(void *p) { return cudaFreeHost(p) == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA; }
+int chronos_memcpy_h2d(int device, void *dst_dev, const void *src_host, uint64_t bytes) {
+    if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
+    return cudaMemcpy(dst_dev, src_host, bytes, cudaMemcpyHostToDevice) == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+int chronos_memcpy_d2h(int device, void *dst_host, const void *src_dev, uint64_t bytes) {
+    if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
+    return cudaMemcpy(dst_host, src_dev, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+int chronos_flush_l2(int device) {
+    static void *buf[16] = {nullptr};
+    const size_t bytes = 512ull << 20;
+    if (device < 0 || device >= 16) return CHRONOS_E_ARG;
+    if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
+    if (!buf[device] && cudaMalloc(&buf[device], bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return CHRONOS_E_NOMEM;
+    }
+    static uint32_t v = 1;
+    l2_flush_kernel<<<148 * 8, 256>>>(static_cast<uint4 *>(buf[device]), bytes / 16, v++);
+    return cudaDeviceSynchronize() == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+
+}  // extern "C"

@@ -1,0 +1,101 @@
+// common.cuh -- shared device helpers (sm_100a): mbarrier + bulk-copy PTX, SWAR byte
+// tricks, single-pass ("decoupled look-back") tile-status words.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define CH_REC_BYTES 288
+#define CH_REC_WORDS 72
+#define CH_REC_CHUNKS 18  // 16-byte chunks per record
+
+namespace chronos {
+
+// ---------------------------------------------------------------------------------
+// mbarrier / TMA bulk copy (1-D cp.async.bulk: global -> shared, completion by bytes)
+// ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+// 1-D bulk copy through the TMA unit; size and both addresses must be multiples of 16.
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+// ---------------------------------------------------------------------------------
+// SWAR helpers on little-endian 4-byte words
+// ---------------------------------------------------------------------------------
+// 0x80 in every byte of x that is zero, 0 elsewhere (exact, no false positives).
+__device__ __forceinline__ uint32_t zero_bytes(uint32_t x) {
+    return ~(((x & 0x7f7f7f7fu) + 0x7f7f7f7fu) | x | 0x7f7f7f7fu);
+}
+// index (0..3) of the lowest zero byte given z = zero_bytes(x) != 0
+__device__ __forceinline__ int first_zero_index(uint32_t z) { return (__ffs((int)z) - 1) >> 3; }
+// keep the low k bytes (k in 0..3) of x
+__device__ __forceinline__ uint32_t keep_low_bytes(uint32_t x, int k) { return x & ((1u << (8 * k)) - 1u); }
+
+__host__ __device__ constexpr uint32_t lit4(char a, char b, char c, char d) {
+    return (uint32_t)(uint8_t)a | ((uint32_t)(uint8_t)b << 8) | ((uint32_t)(uint8_t)c << 16) |
+           ((uint32_t)(uint8_t)d << 24);
+}
+__host__ __device__ constexpr uint32_t lit3(char a, char b, char c) { return lit4(a, b, c, 0); }
+__host__ __device__ constexpr uint32_t lit2(char a, char b) { return lit4(a, b, 0, 0); }
+
+// ---------------------------------------------------------------------------------
+// look-back status words: [63:62] status, payload below
+// ---------------------------------------------------------------------------------
+constexpr uint64_t ST_NONE = 0, ST_AGG = 1, ST_PREFIX = 2;
+__device__ __forceinline__ uint64_t ld_relaxed_u64(const uint64_t *p) {
+    uint64_t v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(uint64_t *p, uint64_t v) {
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+__device__ __forceinline__ uint32_t lanemask_lt() {
+    uint32_t m;
+    asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+    return m;
+}
+
+// owner rank of a pid for PID-hash sharding (also exported through the C ABI)
+__host__ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
+    x ^= x >> 16;
+    x *= 0x7feb352dU;
+    x ^= x >> 15;
+    x *= 0x846ca68bU;
+    x ^= x >> 16;
+    return x;
+}
+
+}  // namespace chronos

@@ -1,0 +1,150 @@
+"""Context: one GPU's filter + per-PID window state behind the C ABI (include/chronos.h)."""
+import ctypes
+from ctypes import byref, c_float, c_uint64, c_void_p
+
+import numpy as np
+
+from . import _ffi
+from .records import RECORD_BYTES, as_record_bytes, event_str
+
+WINDOW_DTYPE = np.dtype([("trigger_idx", "<u8"), ("start", "<u8"), ("len", "<u4"), ("pid", "<u4"),
+                         ("flags", "<u4"), ("reserved", "<u4")])
+assert WINDOW_DTYPE.itemsize == ctypes.sizeof(_ffi.Window)
+
+
+class BatchResult:
+    """What one submitted batch produced. `windows` is sorted by trigger arrival index,
+    the order the reference calls analyze_sequence in (chronos_sensor.py:143-147)."""
+
+    def __init__(self, counts, survivors, survivor_meta, windows, window_records, gpu_ms, filter_ms, launches):
+        self.counts = counts
+        self.survivors = survivors            # uint64 global arrival indices, ascending
+        self.survivor_meta = survivor_meta    # uint8 META_* bits
+        self.windows = windows                # WINDOW_DTYPE
+        self.window_records = window_records  # (sum(len), 288) uint8, window after window, or None
+        self.gpu_ms = gpu_ms
+        self.filter_ms = filter_ms
+        self.launches = launches
+
+    def histories(self):
+        """[(pid, [event_str, ...]), ...]: exactly the arguments of analyze_sequence."""
+        out = []
+        o = 0
+        recs = self.window_records
+        for w in self.windows:
+            n = int(w["len"])
+            out.append((int(w["pid"]), [event_str(recs[o + k]) for k in range(n)]))
+            o += n
+        return out
+
+
+class Context:
+    def __init__(self, device=0, max_batch_events=1 << 20):
+        self._L = _ffi.lib()
+        self.device = int(device)
+        self._h = c_void_p()
+        rc = self._L.chronos_create(self.device, int(max_batch_events), byref(self._h))
+        if rc != _ffi.OK:
+            self._h = c_void_p()
+            raise _ffi.ChronosError(rc, "chronos_create failed (no usable sm_100 GPU? there is no CPU fallback)")
+        self.max_batch_events = int(max_batch_events)
+        self._keep = None
+
+    def _check(self, rc):
+        if rc != _ffi.OK:
+            msg = self._L.chronos_last_error(self._h)
+            raise _ffi.ChronosError(rc, msg.decode("utf-8", "replace") if msg else "")
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            self._L.chronos_destroy(self._h)
+            self._h = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- submit ------------------------------------------------------------------------
+    def submit(self, records, base_arrival_index=0):
+        """records: bytes-like / numpy array of n*288 bytes on the host."""
+        a = as_record_bytes(records)
+        self._keep = a  # the async H2D copy reads it until fetch
+        self._check(self._L.chronos_submit(self._h, a.ctypes.data, a.size // RECORD_BYTES, int(base_arrival_index)))
+
+    def submit_ptr(self, ptr, n, base_arrival_index=0):
+        """ptr: raw host or device address of n records (device pointers are used in place)."""
+        self._check(self._L.chronos_submit(self._h, c_void_p(int(ptr)), int(n), int(base_arrival_index)))
+
+    def submit_survivors_ptr(self, rec_ptr, arrival_ptr, meta_ptr, n):
+        self._check(self._L.chronos_submit_survivors(self._h, c_void_p(int(rec_ptr)), c_void_p(int(arrival_ptr)),
+                                                     c_void_p(int(meta_ptr)), int(n)))
+
+    # ---- results -----------------------------------------------------------------------
+    def fetch_counts(self):
+        c = _ffi.Counts()
+        self._check(self._L.chronos_fetch(self._h, byref(c)))
+        self._keep = None
+        return {k: int(getattr(c, k)) for k, _ in _ffi.Counts._fields_ if k != "reserved"}
+
+    def fetch(self, records=True):
+        counts = self.fetch_counts()
+        S, W = counts["n_survivors"], counts["n_windows"]
+        surv = np.zeros(S, dtype=np.uint64)
+        meta = np.zeros(S, dtype=np.uint8)
+        self._check(self._L.chronos_copy_survivors(self._h, surv.ctypes.data, meta.ctypes.data, S))
+        win = np.zeros(W, dtype=WINDOW_DTYPE)
+        self._check(self._L.chronos_copy_windows(self._h, win.ctypes.data, W))
+        wrec = None
+        if records:
+            tot = int(win["len"].sum()) if W else 0
+            wrec = np.zeros((tot, RECORD_BYTES), dtype=np.uint8)
+            self._check(self._L.chronos_copy_window_records(self._h, wrec.ctypes.data, tot))
+        t, f = c_float(), c_float()
+        self._check(self._L.chronos_last_timing(self._h, byref(t), byref(f)))
+        ln = c_uint64()
+        self._check(self._L.chronos_last_launches(self._h, byref(ln)))
+        return BatchResult(counts, surv, meta, win, wrec, t.value, f.value, ln.value)
+
+    def arena(self):
+        c = _ffi.Counts()
+        self._check(self._L.chronos_fetch(self._h, byref(c)))
+        a = np.zeros((int(c.n_arena), RECORD_BYTES), dtype=np.uint8)
+        self._check(self._L.chronos_copy_arena(self._h, a.ctypes.data, int(c.n_arena)))
+        return a
+
+    def last_timing(self):
+        t, f = c_float(), c_float()
+        self._check(self._L.chronos_last_timing(self._h, byref(t), byref(f)))
+        return t.value, f.value
+
+    def last_launches(self):
+        ln = c_uint64()
+        self._check(self._L.chronos_last_launches(self._h, byref(ln)))
+        return int(ln.value)
+
+    def state_arrays(self, n_pending, records=True):
+        """Pending process_memory entries: (pid[P], global_idx[P], records[P,288] or None),
+        ascending pid, arrival order inside a pid."""
+        P = int(n_pending)
+        pid = np.zeros(P, dtype=np.uint32)
+        idx = np.zeros(P, dtype=np.uint64)
+        rec = np.zeros((P, RECORD_BYTES), dtype=np.uint8) if records else None
+        self._check(self._L.chronos_state(self._h, pid.ctypes.data, idx.ctypes.data,
+                                          rec.ctypes.data if records else None, P))
+        return pid, idx, rec
+
+    def process_memory(self, n_pending):
+        """{pid: [event_str, ...]} for PIDs with a non-empty pending list (chronos_sensor.py:105)."""
+        pid, _, rec = self.state_arrays(n_pending, records=True)
+        pm = {}
+        for k in range(pid.size):
+            pm.setdefault(int(pid[k]), []).append(event_str(rec[k]))
+        return pm

@@ -1,0 +1,24 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a real B200 (run with -m gpu on the GPU box)")
+
+
+@pytest.fixture(scope="session", autouse=True)
+def _built():
+    """Make sure the checker libraries exist (gcc, seconds). The CUDA library is built by
+    __graft_entry__.build(); tests that need it load it through chronos_b200._ffi and fail
+    loudly if it is missing."""
+    from oracle import build_oracle
+
+    build_oracle.build_oracle()
+    build_oracle.build_ref()
+    yield
