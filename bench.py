@@ -1,0 +1,429 @@
+#!/usr/bin/env python
+"""bench.py -- events/sec through the CHRONOS hot path (filter + per-PID grouping +
+window/flush logic + compaction) on N B200s, with the roofline of the dominant kernel
+and the reference-style CPU path timed beside it.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one pass of the whole hot path over one batch of synthetic records:
+  N=1  : BASELINE.json configs[1]  -- 10M events, 4K PIDs, 256-byte path fields
+  N>1  : BASELINE.json configs[2]  -- 12.5M events per GPU (100M at N=8), 1M PIDs,
+         contiguous slice per rank, survivors repartitioned by PID hash (one all-to-all)
+`value` is measured with the batch already resident in HBM; `e2e` goes through the
+public host API with pinned HOST buffers (H2D of the batch and D2H of the results inside
+the timed region). The input (2.88 GB per step) is far larger than the 126 MB L2, so no
+explicit L2 flush is needed between steps (stated in config.l2).
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+REC = 288
+METRIC = "events/sec filtered+chain-matched"
+UNIT = "events/s"
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(p) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------------------
+# clocks sampling during the timed region
+# ------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self._stop = threading.Event()
+        self._t = None
+        self._proc = None
+
+    def start(self):
+        try:
+            self._proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self._proc = None
+            return
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+
+    def _run(self):
+        for line in self._proc.stdout:
+            if self._stop.is_set():
+                break
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        self._stop.set()
+        if self._proc is not None:
+            self._proc.terminate()
+            try:
+                self._proc.wait(timeout=2)
+            except Exception:
+                self._proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+                for k, nm in enumerate(names):
+                    if r[2 + k].lower().startswith("active"):
+                        reasons.add(nm)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the reference's own path on the host cores (oracle/_ref C filter + Python port
+# of print_event, one worker per core, records partitioned by pid -- exact, PIDs are
+# independent: chronos_sensor.py:105,138,142,157)
+# ------------------------------------------------------------------------------------------
+_CPU_PARTS = None
+
+
+def _cpu_worker(k):
+    from oracle import pyoracle
+
+    part, drop = _CPU_PARTS[k]
+    t0 = time.perf_counter()
+    s = pyoracle.PySensor()
+    s.feed(part, 0, drop=drop)
+    return time.perf_counter() - t0, len(s.survivors), len(s.windows)
+
+
+def cpu_reference_rate(rows, cores, repeats=1):
+    """Returns (events/s, seconds, kind). rows: (n, 288) uint8 sample."""
+    global _CPU_PARTS
+    import multiprocessing as mp
+
+    from oracle import build_oracle
+
+    n = len(rows)
+    ref_so = build_oracle.build_ref()
+    pid = rows[:, :4].copy().view("<u4").reshape(-1)
+    parts = []
+    t_filter = 0.0
+    for k in range(cores):
+        sel = rows[(pid % cores) == k]
+        buf = sel.tobytes()
+        drop = None
+        if ref_so is not None:  # stage A: the reference's own C helpers (chronos_sensor.py:28-47)
+            lib = ctypes.CDLL(ref_so)
+            lib.chronos_ref_filter_batch.argtypes = [ctypes.c_char_p, ctypes.c_uint64, ctypes.c_char_p]
+            out = ctypes.create_string_buffer(max(len(sel), 1))
+            t0 = time.perf_counter()
+            lib.chronos_ref_filter_batch(buf, len(sel), out)
+            t_filter = max(t_filter, time.perf_counter() - t0)
+            drop = out.raw[:len(sel)]
+        parts.append((buf, drop))
+    _CPU_PARTS = parts
+    best = None
+    ctx = mp.get_context("fork")
+    for _ in range(repeats):
+        with ctx.Pool(cores) as pool:
+            res = pool.map(_cpu_worker, range(cores))
+        t = max(r[0] for r in res) + t_filter
+        best = t if best is None else min(best, t)
+    kind = "port"
+    return n / best, best, kind, ("oracle/_ref C filter + " if ref_so else "") + "oracle.pyoracle.PySensor"
+
+
+def cpu_sample_rows(spec, n):
+    from chronos_b200 import tracegen
+
+    return tracegen.generate_host(spec, first=0, n=n)
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    from chronos_b200 import tracegen
+
+    spec = tracegen.WORKLOADS["uniform_10m_4k" if world == 1 else "sharded_100m_1m"]
+    cores = os.cpu_count() or 1
+    # bounded sample: ~0.5M raw events/s/core for this path -> about 3 s of work per step
+    n_sample = int(min(spec["n"], 1_000_000 * cores))
+    rows = cpu_sample_rows(spec, n_sample)
+    times = []
+    for i in range(args.warmup + args.steps):
+        rate, secs, kind, what = cpu_reference_rate(rows, cores)
+        if i >= args.warmup:
+            times.append(secs)
+    ms = 1e3 * float(np.mean(times))
+    value = n_sample / (ms / 1e3)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8", "data": "synthetic",
+        "config": {"workload": workload_name(world), "sample_events_per_step": n_sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"first {n_sample} events of the workload, partitioned by pid over {cores} processes; {what}"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(world):
+    if world == 1:
+        return "configs[1]: 10M synthetic events, 4K PIDs, 256-byte path fields, 1xB200 (uniform_10m_4k)"
+    return (f"configs[2]: {12.5 * world:g}M events ({'100M' if world == 8 else 'scaled'}), 1M PIDs, PID-hash sharded "
+            f"across {world}xB200 with all-to-all (sharded_100m_1m)")
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+class Pinned:
+    def __init__(self, nbytes):
+        from chronos_b200 import _ffi
+
+        self.nbytes = int(nbytes)
+        p = ctypes.c_void_p()
+        rc = _ffi.lib().chronos_host_alloc_pinned(max(self.nbytes, 16), ctypes.byref(p))
+        if rc != 0:
+            raise RuntimeError(f"pinned allocation of {nbytes} bytes failed ({rc})")
+        self.ptr = p.value
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * max(self.nbytes, 16)).from_address(self.ptr))
+
+    def free(self):
+        from chronos_b200 import _ffi
+
+        if self.ptr:
+            self.array = None
+            _ffi.lib().chronos_host_free_pinned(ctypes.c_void_p(self.ptr))
+            self.ptr = None
+
+
+def run_gpu_arm(args, rank, world, local_rank):
+    import torch
+
+    import chronos_b200
+    from chronos_b200 import _ffi, tracegen
+
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+
+        dist = dist_mod
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    device = local_rank
+    torch.cuda.set_device(device)
+    L = _ffi.lib()
+    if L.chronos_device_ok(device) != 0:
+        raise SystemExit("chronos_b200 needs a B200 (sm_100); there is no CPU fallback")
+
+    if world == 1:
+        spec = tracegen.WORKLOADS["uniform_10m_4k"]
+        n = int(args.events or spec["n"])
+        first = 0
+    else:
+        spec = tracegen.WORKLOADS["sharded_100m_1m"]
+        n = int(args.events or 12_500_000)
+        first = rank * n
+    dev = tracegen.generate_device(spec, device=device, first=first, n=n)
+    peak, peak_src = measured_peak_gbs()
+
+    if world == 1:
+        runner = SingleGpuRunner(chronos_b200, dev, n, device)
+    else:
+        from chronos_b200.sharded import ShardedRunner
+
+        runner = ShardedRunner(dev.ptr, n, first, device, rank, world)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        runner.step()
+    barrier()
+    sampler = ClockSampler(device)
+    if rank == 0:
+        sampler.start()
+    ext = torch.cuda.ExternalStream(runner.stream_ptr(), device=torch.device("cuda", device))
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    filt_ms, step_ms, launches, last = [], [], 0, None
+    e0.record(ext)
+    t_wall0 = time.perf_counter()
+    for _ in range(args.steps):
+        last = runner.step()
+        filt_ms.append(last["filter_ms"])
+        step_ms.append(last["gpu_ms"])
+        launches += last["launches"]
+    e1.record(ext)
+    e1.synchronize()
+    barrier()
+    t_wall = time.perf_counter() - t_wall0
+    dev_ms = e0.elapsed_time(e1)
+    clocks = sampler.stop() if rank == 0 else None
+    if dist is not None:
+        t = torch.tensor([dev_ms], device=f"cuda:{device}", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms = float(t.item())
+        lt = torch.tensor([launches], device=f"cuda:{device}", dtype=torch.int64)
+        dist.all_reduce(lt)
+        launches = int(lt.item())
+    ms_per_step = dev_ms / args.steps
+    total_events = n * world
+    value = total_events / (ms_per_step / 1e3)
+
+    # ---- end-to-end through the public host API with pinned host buffers -------------------
+    e2e = runner.e2e(max(1, min(args.steps, 5)), barrier, dist)
+
+    # ---- CPU baseline on a bounded sample (rank 0, N=1 only) -------------------------------
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        n_sample = int(min(n, 1_000_000 * cores))
+        rows = dev.download(n_sample * REC).reshape(-1, REC)
+        rate, secs, kind, what = cpu_reference_rate(rows, cores)
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": f"first {n_sample} events of the workload in {secs:.2f}s, partitioned by pid over {cores} processes; {what}"}
+
+    if rank == 0:
+        f_ms = float(np.mean(filt_ms))
+        alg_bytes = REC * n  # the filter reads every raw record once (288 B per event)
+        achieved = alg_bytes / (f_ms / 1e3) / 1e9
+        S, W = last["n_survivors"], last["n_windows"]
+        pipe_bytes = REC * n + REC * S + 16 * W
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u8", "data": "synthetic",
+            "config": {"workload": workload_name(world), "events_per_gpu": n, "record_bytes": REC,
+                       "survivors_rank0": S, "windows_rank0": W, "pending_rank0": last["n_pending"],
+                       "l2": "input per step (2.88 GB+) exceeds the 126 MB L2; no flush needed",
+                       "timing": "torch CUDA events on the library stream around all K steps, max over ranks"},
+            "roofline": {"bound": "hbm", "kernel": "filter_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": TRAFFIC_NCU, "peak_source": peak_src,
+                         "kernel_ms": f_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                         "pipeline": {"algorithmic_bytes": pipe_bytes, "gpu_ms": float(np.mean(step_ms)),
+                                      "achieved": pipe_bytes / (float(np.mean(step_ms)) / 1e3) / 1e9,
+                                      "frac": pipe_bytes / (float(np.mean(step_ms)) / 1e3) / 1e9 / peak,
+                                      "frac_of_8TBs_nominal": pipe_bytes / (float(np.mean(step_ms)) / 1e3) / 1e9 / 8000.0}},
+            "cpu_baseline": cpu,
+            "e2e": e2e,
+            "gpu_launches": launches,
+            "clocks": clocks,
+            "wall_ms_per_step": 1e3 * t_wall / args.steps,
+        }
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum of filter_kernel for one launch of the N=1
+# workload, from the committed `ncu --set full` capture (profiles/); None until captured.
+TRAFFIC_NCU = None
+
+
+class SingleGpuRunner:
+    def __init__(self, chronos_b200, dev, n, device):
+        self.ctx = chronos_b200.Context(device=device, max_batch_events=n)
+        self.dev, self.n, self.device = dev, n, device
+        self.mod = chronos_b200
+
+    def stream_ptr(self):
+        from chronos_b200 import _ffi
+
+        return int(_ffi.lib().chronos_stream(self.ctx._h))
+
+    def step(self):
+        self.ctx.reset()  # every step is the same one-shot batch on a fresh process_memory
+        self.ctx.submit_ptr(self.dev.ptr, self.n, 0)
+        c = self.ctx.fetch_counts()
+        t, f = self.ctx.last_timing()
+        c.update(gpu_ms=t, filter_ms=f, launches=self.ctx.last_launches())
+        return c
+
+    def e2e(self, steps, barrier, dist):
+        from chronos_b200 import _ffi
+
+        L = _ffi.lib()
+        n = self.n
+        host = Pinned(n * REC)
+        rc = L.chronos_memcpy_d2h(self.device, ctypes.c_void_p(host.ptr), ctypes.c_void_p(self.dev.ptr), n * REC)
+        assert rc == 0
+        # result buffers sized from a dry run
+        self.ctx.reset()
+        self.ctx.submit_ptr(host.ptr, n, 0)
+        c = self.ctx.fetch_counts()
+        S, W = c["n_survivors"], c["n_windows"]
+        r_idx, r_meta, r_win = Pinned(S * 8), Pinned(S), Pinned(W * 32)
+        r_rec = Pinned(S * REC)
+        h = self.ctx._h
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            self.ctx.reset()
+            self.ctx.submit_ptr(host.ptr, n, 0)          # H2D of the whole batch inside
+            c = self.ctx.fetch_counts()
+            assert L.chronos_copy_survivors(h, ctypes.c_void_p(r_idx.ptr), ctypes.c_void_p(r_meta.ptr), S) == 0
+            assert L.chronos_copy_windows(h, ctypes.c_void_p(r_win.ptr), W) == 0
+            assert L.chronos_copy_window_records(h, ctypes.c_void_p(r_rec.ptr), S) == 0
+        barrier()
+        dt = (time.perf_counter() - t0) / steps
+        win = np.frombuffer(r_win.array[:W * 32], dtype=self.mod.WINDOW_DTYPE)
+        d2h = S * 9 + W * 32 + int(win["len"].sum()) * REC + 64
+        for p in (host, r_idx, r_meta, r_win, r_rec):
+            p.free()
+        return {"value": n / dt, "unit": UNIT, "h2d_bytes_per_step": n * REC, "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": 1e3 * dt, "steps": steps,
+                "path": "Context.submit(pinned host records) -> fetch -> copy_survivors/windows/window_records"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--events", type=int, default=0, help="override events per GPU (testing only)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        # launched without torchrun: re-exec under it so that one rank drives each GPU
+        port = 29500 + (os.getpid() % 2000)
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={args.gpus}",
+               "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+        raise SystemExit(subprocess.call(cmd))
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+    else:
+        run_gpu_arm(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -87,6 +87,10 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out);
 /* Replaces: process exit (chronos_sensor.py:163). */
 int chronos_destroy(chronos_ctx *ctx);
 
+/* Replaces: restarting the sensor, i.e. a fresh `process_memory` (chronos_sensor.py:105).
+ * Drops all per-PID state and any unfetched results; buffers stay allocated. */
+int chronos_reset(chronos_ctx *ctx);
+
 /* Human-readable text for the last non-OK status on this context (or a static string
  * for ctx == NULL).  No reference counterpart. */
 const char *chronos_last_error(const chronos_ctx *ctx);
@@ -125,7 +129,8 @@ int chronos_state_pids(chronos_ctx *ctx, uint32_t *pid, uint64_t cap);
 int chronos_get_device_view(chronos_ctx *ctx, chronos_device_view *out);
 
 /* Timing of the last fetched batch as measured with CUDA events on the context's
- * stream: total and the filter kernel alone, in milliseconds. */
+ * stream: the whole submit and the filter kernel alone (events right around its
+ * launch), in milliseconds. */
 int chronos_last_timing(chronos_ctx *ctx, float *total_ms, float *filter_ms);
 /* Number of kernel launches the last submit issued (bench.py's gpu_launches). */
 int chronos_last_launches(chronos_ctx *ctx, uint64_t *launches);

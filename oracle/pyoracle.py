@@ -69,13 +69,18 @@ class PySensor:
         self.survivors = []   # arrival indices appended to process_memory
         self.trigger_idx = []
 
-    def feed(self, records, base=0):
+    def feed(self, records, base=0, drop=None):
+        """drop: optional per-record 0/1 decisions of stage A already taken by the
+        reference's own C helpers (oracle/_ref); without it the filter is restated here."""
         n = len(records) // REC_BYTES
         pm = self.process_memory
         for i in range(n):
             rec = records[i * REC_BYTES:(i + 1) * REC_BYTES]
             etype_b = c_char_field(rec, OFF_TYPE, 10)
-            if etype_b == b"OPEN" and openat_noise(rec[OFF_ARGV:OFF_ARGV + 256]):
+            if drop is not None:
+                if drop[i]:
+                    continue
+            elif etype_b == b"OPEN" and openat_noise(rec[OFF_ARGV:OFF_ARGV + 256]):
                 continue  # never submitted by the kernel hook (:79, :86, :91)
             pid = int.from_bytes(rec[0:4], "little")
             try:  # :127-131

@@ -57,13 +57,14 @@ struct chronos_ctx {
     int sm_count = 0;
     uint64_t max_batch = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev_start = nullptr, ev_filter = nullptr, ev_end = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_filter = nullptr, ev_end = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
     char err[256] = {0};
 
     // batch staging for host-pointer submits
     DevBuf d_batch;
     // entry arrays (capacity in entries = ecap)
     DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, flush, wi_of_entry, wsorted, windows, radix_table;
+    DevBuf sp_key, sp_src, sp_meta, tile_count;  // filter's tile-local compaction
     DevBuf surv_arrival;  // only for chronos_submit_survivors
     // double-buffered persistent state
     DevBuf arena[2];
@@ -84,7 +85,8 @@ struct chronos_ctx {
     bool b_explicit_arrival = false;
     const uint32_t *sorted_key = nullptr, *sorted_val = nullptr;
     uint64_t launches = 0;
-    float t_total = 0.f, t_filter = 0.f;
+    float t_total = 0.f, t_filter = 0.f, t_filter_kernel = 0.f;
+    bool filter_timed = false;
     int filter_variant = 0;
 };
 
@@ -484,6 +486,7 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
     c->b_P = P;
     c->b_S = c->b_M = c->b_W = 0;
     c->launches = 0;
+    c->filter_timed = false;
     const uint64_t ecap = P + n;
     int rc;
     if ((rc = ensure(c, c->keyA, (ecap + 1) * 4))) return rc;
@@ -520,6 +523,8 @@ int finish_batch(chronos_ctx *c) {
     c->n_pending = c->b_M ? c->h_scalars->n_pending : 0;
     cudaEventElapsedTime(&c->t_total, c->ev_start, c->ev_end);
     cudaEventElapsedTime(&c->t_filter, c->ev_start, c->ev_filter);
+    c->t_filter_kernel = 0.f;
+    if (c->filter_timed) cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
     cudaGetLastError();
     c->phase = chronos_ctx::FETCHED;
     return CHRONOS_OK;
@@ -564,6 +569,8 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
         CK(cudaEventCreate(&c->ev_start));
         CK(cudaEventCreate(&c->ev_filter));
         CK(cudaEventCreate(&c->ev_end));
+        CK(cudaEventCreate(&c->ev_f0));
+        CK(cudaEventCreate(&c->ev_f1));
         CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_scalars), sizeof(DeviceScalars)));
         int rc;
         if ((rc = ensure(c, c->tickets, N_TICKETS * 4))) return rc;
@@ -584,7 +591,7 @@ int chronos_destroy(chronos_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->flush,
-                     &c->wi_of_entry, &c->wsorted, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+                     &c->wi_of_entry, &c->wsorted, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
                      &c->tickets, &c->scalars, &c->pack, &c->pack_off};
@@ -593,6 +600,8 @@ int chronos_destroy(chronos_ctx *c) {
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_filter) cudaEventDestroy(c->ev_filter);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
+    if (c->ev_f0) cudaEventDestroy(c->ev_f0);
+    if (c->ev_f1) cudaEventDestroy(c->ev_f1);
     if (c->stream) cudaStreamDestroy(c->stream);
     cudaGetLastError();
     delete c;
@@ -626,15 +635,39 @@ int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t bas
         fp.tile_begin = 0;
         fp.tile_end = (uint32_t)((n + TILE - 1) / TILE);
         fp.ticket = ptr<uint32_t>(c->tickets);
-        fp.tile_status = ptr<uint64_t>(c->status);
-        fp.out_key = ptr<uint32_t>(c->keyA) + c->b_P;
-        fp.out_src = ptr<uint32_t>(c->surv_src);
-        fp.out_meta = ptr<uint8_t>(c->surv_meta);
+        const uint64_t slots = (uint64_t)fp.tile_end * TILE;
+        if ((rc = ensure(c, c->sp_key, slots * 4))) return rc;
+        if ((rc = ensure(c, c->sp_src, slots * 4))) return rc;
+        if ((rc = ensure(c, c->sp_meta, slots))) return rc;
+        if ((rc = ensure(c, c->tile_count, ((uint64_t)fp.tile_end + 1) * 4))) return rc;
+        fp.tile_count = ptr<uint32_t>(c->tile_count);
+        fp.sp_key = ptr<uint32_t>(c->sp_key);
+        fp.sp_src = ptr<uint32_t>(c->sp_src);
+        fp.sp_meta = ptr<uint8_t>(c->sp_meta);
         fp.out_count = &ds->surv_count;
         fp.key_or = &ds->key_or;
         fp.key_and = &ds->key_and;
-        fp.last_tile = fp.tile_end - 1;
+        CK(cudaEventRecord(c->ev_f0, c->stream));
         if ((rc = launch_filter(c, fp))) return rc;
+        CK(cudaEventRecord(c->ev_f1, c->stream));
+        c->filter_timed = true;
+        // cross-tile prefix + dense, arrival-ordered survivor arrays
+        radix_scan<<<1, 1024, 0, c->stream>>>(ptr<uint32_t>(c->tile_count), fp.tile_end);
+        CompactParams cp;
+        cp.tile_off = ptr<uint32_t>(c->tile_count);
+        cp.sp_key = fp.sp_key;
+        cp.sp_src = fp.sp_src;
+        cp.sp_meta = fp.sp_meta;
+        cp.out_key = ptr<uint32_t>(c->keyA) + c->b_P;
+        cp.out_src = ptr<uint32_t>(c->surv_src);
+        cp.out_meta = ptr<uint8_t>(c->surv_meta);
+        cp.n_tiles = fp.tile_end;
+        cp.tile = (uint32_t)TILE;
+        cp.total = &ds->surv_count;
+        compact_survivors<<<(unsigned)std::min<uint32_t>((fp.tile_end + 7) / 8, (uint32_t)c->sm_count * 8), 256, 0,
+                            c->stream>>>(cp);
+        CK(cudaGetLastError());
+        c->launches += 2;
     }
     if ((rc = run_window_stage(c))) return rc;
     c->phase = chronos_ctx::SUBMITTED;
@@ -827,7 +860,16 @@ int chronos_last_timing(chronos_ctx *c, float *total_ms, float *filter_ms) {
     int rc = need_fetched(c);
     if (rc) return rc;
     if (total_ms) *total_ms = c->t_total;
-    if (filter_ms) *filter_ms = c->t_filter;
+    if (filter_ms) *filter_ms = c->t_filter_kernel;
+    return CHRONOS_OK;
+}
+
+int chronos_reset(chronos_ctx *c) {
+    if (!c) return CHRONOS_E_ARG;
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    c->n_pending = 0;
+    c->phase = chronos_ctx::IDLE;
     return CHRONOS_OK;
 }
 

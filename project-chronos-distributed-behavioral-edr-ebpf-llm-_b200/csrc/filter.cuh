@@ -18,8 +18,8 @@
 //      the still-alive records are compacted into a work list,
 //   B  thread-per-alive-record: NUL scan (16-byte LDS), suffix table, SWAR needle
 //      search, slow-path UTF-8 DFA only when a high bit was seen,
-//   C  ordered compaction: ballot ranks + single-pass decoupled look-back over tile
-//      status words gives every survivor its arrival-ordered output slot.
+//   C  ordered compaction inside the tile (ballot ranks); compact_survivors then applies
+//      the exclusive scan of the per-tile counts, so CTAs never wait on each other.
 #pragma once
 #include "common.cuh"
 
@@ -33,14 +33,13 @@ struct FilterParams {
     uint32_t tile_begin;     // this launch covers tiles [tile_begin, tile_end)
     uint32_t tile_end;
     uint32_t *ticket;        // per-launch tile ticket counter (zeroed)
-    uint64_t *tile_status;   // look-back words, one per tile of the batch (zeroed per batch)
-    uint32_t *out_key;       // survivor pid       (arrival order)
-    uint32_t *out_src;       // survivor batch-local record index
-    uint8_t *out_meta;       // survivor META_* bits
-    uint32_t *out_count;     // total survivors, written by the batch's last tile
+    uint32_t *tile_count;    // survivors per tile (one word per tile of the batch)
+    uint32_t *sp_key;        // tile-local compaction: slot tile*TILE + rank holds the pid,
+    uint32_t *sp_src;        //   the batch-local record index
+    uint8_t *sp_meta;        //   and the META_* bits of the tile's rank-th survivor
+    uint32_t *out_count;     // total survivors (atomicAdd, one per CTA)
     uint32_t *key_or;        // OR / AND over survivor pids (radix pass planning)
     uint32_t *key_and;
-    uint32_t last_tile;      // index of the batch's last tile
 };
 
 // ---- needle tests on one 4-byte window `t` (bytes k..k+3) and the byte after it ------
@@ -306,6 +305,7 @@ __global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; s++) mbar_init(&S.bar[s], 1);
         S.n_alive = 0;
+        S.base = 0;
         S.k_or = 0;
         S.k_and = 0xffffffffu;
         fence_mbar_init();
@@ -360,7 +360,9 @@ __global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
             claim_and_issue(s);
         }
 
-        // ---- phase C: arrival-ordered compaction ---------------------------------------
+        // ---- phase C: tile-local, arrival-ordered compaction -----------------------------
+        // (the cross-tile prefix is taken by compact_survivors afterwards: a blocking
+        //  look-back here would chain every CTA's stage ring to its neighbour's)
         const uint32_t code = S.res[tid];
         const bool keep = (code & 0x80u) != 0;
         const uint32_t kb = __ballot_sync(0xffffffffu, keep);
@@ -377,30 +379,62 @@ __global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
             }
         }
         __syncthreads();
-        if (warp == 0) {
-            uint32_t tot = 0;
+        {
+            uint32_t before = rank, tot = 0;
 #pragma unroll
-            for (int k = 0; k < NW; k++) tot += S.wcnt[k];
-            uint32_t excl = lookback_count(p.tile_status, tile, tot, lane);
-            if (lane == 0) {
-                S.base = excl;
-                if (tile == p.last_tile) *p.out_count = excl + tot;
+            for (int k = 0; k < NW; k++) {
+                const uint32_t c = S.wcnt[k];
+                before += (k < warp) ? c : 0u;
+                tot += c;
             }
-        }
-        __syncthreads();
-        if (keep) {
-            uint32_t dst = S.base + rank;
-#pragma unroll
-            for (int k = 0; k < NW; k++) dst += (k < warp) ? S.wcnt[k] : 0u;
-            p.out_key[dst] = pid;
-            p.out_src[dst] = (uint32_t)first + tid;
-            p.out_meta[dst] = (uint8_t)(code & 0x7Fu);
+            if (keep) {
+                const size_t slot = (size_t)tile * TILE + before;
+                p.sp_key[slot] = pid;
+                p.sp_src[slot] = (uint32_t)first + tid;
+                p.sp_meta[slot] = (uint8_t)(code & 0x7Fu);
+            }
+            if (tid == 0) {
+                p.tile_count[tile] = tot;
+                S.base += tot;
+            }
         }
     }
     if (tid == 0) {
+        if (S.base) atomicAdd(p.out_count, S.base);
         if (S.k_or != 0 || S.k_and != 0xffffffffu) {
             atomicOr(p.key_or, S.k_or);
             atomicAnd(p.key_and, S.k_and);
+        }
+    }
+}
+
+// Cross-tile step of the ordered compaction: tile_off[] = exclusive scan of tile_count[]
+// (radix_scan); one warp per filter tile moves its run to the dense arrays.
+struct CompactParams {
+    const uint32_t *tile_off;
+    const uint32_t *sp_key;
+    const uint32_t *sp_src;
+    const uint8_t *sp_meta;
+    uint32_t *out_key;
+    uint32_t *out_src;
+    uint8_t *out_meta;
+    uint32_t n_tiles;
+    uint32_t tile;       // records per filter tile
+    const uint32_t *total;  // device scalar: survivor count == tile_off[n_tiles]
+};
+
+__global__ void __launch_bounds__(256) compact_survivors(const CompactParams c) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t t = warp; t < c.n_tiles; t += n_warps) {
+        const uint32_t lo = c.tile_off[t];
+        const uint32_t hi = (t + 1 < c.n_tiles) ? c.tile_off[t + 1] : *c.total;
+        const size_t base = (size_t)t * c.tile;
+        for (uint32_t j = lane; j < hi - lo; j += 32) {
+            c.out_key[lo + j] = c.sp_key[base + j];
+            c.out_src[lo + j] = c.sp_src[base + j];
+            c.out_meta[lo + j] = c.sp_meta[base + j];
         }
     }
 }

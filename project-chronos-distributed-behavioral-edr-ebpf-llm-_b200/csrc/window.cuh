@@ -114,12 +114,12 @@ __device__ __forceinline__ St2 fn_lookback(uint64_t *status, uint32_t tile, cons
             int64_t idx = look - lane;
             uint64_t w0 = fn_pack(ST_PREFIX, init.s, init.a, init.b), w1 = w0;  // virtual tiles below 0
             if (idx >= 0) {
+                // the owner rewrites both words when it upgrades AGG -> PREFIX: only accept a
+                // pair whose status fields agree (a torn pair mixes two encodings)
                 do {
                     w0 = ld_relaxed_u64(status + 2 * (size_t)idx);
-                } while ((w0 >> 62) == ST_NONE);
-                do {
                     w1 = ld_relaxed_u64(status + 2 * (size_t)idx + 1);
-                } while ((w1 >> 62) == ST_NONE);
+                } while ((w0 >> 62) == ST_NONE || (w0 >> 62) != (w1 >> 62));
             }
             Fn2 mine;
             mine.out = (uint32_t)((w0 >> 61) & 1u) | ((uint32_t)((w1 >> 61) & 1u) << 1);

@@ -72,6 +72,10 @@ class Context:
     def __exit__(self, *a):
         self.close()
 
+    def reset(self):
+        """Forget all per-PID state (a fresh process_memory, chronos_sensor.py:105)."""
+        self._check(self._L.chronos_reset(self._h))
+
     # ---- submit ------------------------------------------------------------------------
     def submit(self, records, base_arrival_index=0):
         """records: bytes-like / numpy array of n*288 bytes on the host."""

@@ -96,7 +96,8 @@ def test_random_pids_and_single_pid(ctx):
         recs.append(R(pid, comms[rng.integers(len(comms))], paths[rng.integers(len(paths))],
                       b"EXEC" if rng.integers(8) == 0 else b"OPEN"))
     compare_batch(ctx, coracle.COracle(), Trace(), b"".join(recs))
-    one = b"".join(R(4242, comms[i % 5], paths[(i * 7) % 7], b"OPEN") for i in range(5000))
+    one = b"".join(R(4242, comms[i % 5], paths[(i * 3) % 7], b"OPEN") for i in range(5000))
+    ctx.reset()  # fresh process_memory, like the fresh oracle below
     compare_batch(ctx, coracle.COracle(), Trace(), one)
 
 
