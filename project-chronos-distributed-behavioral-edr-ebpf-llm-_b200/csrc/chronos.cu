@@ -73,7 +73,9 @@ struct chronos_ctx {
     int cur = 0;                    // index written by the batch in flight / last fetched
     uint64_t n_pending = 0;         // entries pending after the last fetched batch (in buffer `cur`)
     // scheduling scratch
-    DevBuf status, tickets, scalars;
+    DevBuf status, tickets, scalars, scan_status;
+    uint32_t scan_epoch = 0;
+    int scan_slot = 0;  // next free ticket counter for scans in this batch
     DeviceScalars *h_scalars = nullptr;  // pinned
     DevBuf pack;                         // scratch for chronos_copy_window_records / chronos_state
     DevBuf pack_off;
@@ -269,22 +271,50 @@ int launch_filter_t(chronos_ctx *c, FilterParams fp, uint64_t n_records_from_til
     return CHRONOS_OK;
 }
 
+// (TILE, NSTAGE) variants of the filter kernel; CHRONOS_FILTER_VARIANT picks one (tuning knob).
+#define CHRONOS_FILTER_VARIANTS(X) X(0, 64, 2) X(1, 128, 2) X(2, 128, 3) X(3, 64, 3) X(4, 32, 2) X(5, 32, 3) X(6, 256, 2) X(7, 32, 1) X(8, 64, 1)
+
 int filter_tile_size(const chronos_ctx *c) {
     switch (c->filter_variant) {
-    case 1: return 128;
-    case 2: return 256;
-    case 3: return 64;
-    default: return 128;
+#define X(id, tile, nstage) \
+    case id: return tile;
+        CHRONOS_FILTER_VARIANTS(X)
+#undef X
+    default: return 32;
     }
 }
 
 int launch_filter(chronos_ctx *c, const FilterParams &fp) {
     switch (c->filter_variant) {
-    case 1: return launch_filter_t<128, 2>(c, fp, 0);
-    case 2: return launch_filter_t<256, 2>(c, fp, 0);
-    case 3: return launch_filter_t<64, 4>(c, fp, 0);
-    default: return launch_filter_t<128, 3>(c, fp, 0);
+#define X(id, tile, nstage) \
+    case id: return launch_filter_t<tile, nstage>(c, fp, 0);
+        CHRONOS_FILTER_VARIANTS(X)
+#undef X
+    default: return launch_filter_t<32, 1>(c, fp, 0);
     }
+}
+
+// exclusive scan in place (device array of n u32) on the context's stream
+int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n) {
+    if (n == 0) return CHRONOS_OK;
+    const uint32_t n_tiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
+    int rc;
+    const void *before = c->scan_status.p;
+    if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_tiles * 8, 4096)))) return rc;
+    if (c->scan_status.p != before || c->scan_epoch == 0)  // fresh memory or wrapped epoch: tag 0 = "never"
+        CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, c->stream));
+    if (c->scan_slot >= 48) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
+    ScanParams sp;
+    sp.data = data;
+    sp.n = (uint32_t)n;
+    sp.ticket = ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
+    sp.status = ptr<uint64_t>(c->scan_status);
+    sp.epoch = ++c->scan_epoch;
+    if (c->scan_epoch >= (1u << 29)) c->scan_epoch = 0;  // re-zero on the next call
+    scan_exclusive_u32<<<std::min<uint32_t>(n_tiles, (uint32_t)c->sm_count * 2), SCAN_THREADS, 0, c->stream>>>(sp);
+    CK(cudaGetLastError());
+    c->launches++;
+    return CHRONOS_OK;
 }
 
 struct PassPlan {
@@ -371,10 +401,10 @@ int run_window_stage(chronos_ctx *c) {
             rp.shift = pl.shift[i];
             rp.mask = pl.mask[i];
             radix_hist<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
-            radix_scan<<<1, 1024, 0, c->stream>>>(rp.table, RADIX_BINS * n_tiles);
+            if ((rc = launch_scan(c, rp.table, (uint64_t)RADIX_BINS * n_tiles))) return rc;
             radix_scatter<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
             CK(cudaGetLastError());
-            c->launches += 3;
+            c->launches += 2;
             std::swap(kin, kout);
             uint32_t *nv = (vin == nullptr) ? vspare : vin;
             vin = vout;
@@ -486,6 +516,7 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
     c->b_P = P;
     c->b_S = c->b_M = c->b_W = 0;
     c->launches = 0;
+    c->scan_slot = 0;
     c->filter_timed = false;
     const uint64_t ecap = P + n;
     int rc;
@@ -559,7 +590,7 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
     c->device = device;
     c->max_batch = max_batch_events;
     const char *fv = getenv("CHRONOS_FILTER_VARIANT");
-    c->filter_variant = fv ? atoi(fv) : 0;
+    c->filter_variant = fv ? atoi(fv) : -1;  // -1: the tuned default (TILE 32, 1 stage)
     auto boot = [&]() -> int {
         CK(cudaSetDevice(device));
         cudaDeviceProp p;
@@ -594,7 +625,7 @@ int chronos_destroy(chronos_ctx *c) {
                      &c->wi_of_entry, &c->wsorted, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
-                     &c->tickets, &c->scalars, &c->pack, &c->pack_off};
+                     &c->tickets, &c->scalars, &c->scan_status, &c->pack, &c->pack_off};
     for (DevBuf *b : all) release(*b);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->ev_start) cudaEventDestroy(c->ev_start);
@@ -652,7 +683,7 @@ int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t bas
         CK(cudaEventRecord(c->ev_f1, c->stream));
         c->filter_timed = true;
         // cross-tile prefix + dense, arrival-ordered survivor arrays
-        radix_scan<<<1, 1024, 0, c->stream>>>(ptr<uint32_t>(c->tile_count), fp.tile_end);
+        if ((rc = launch_scan(c, ptr<uint32_t>(c->tile_count), fp.tile_end))) return rc;
         CompactParams cp;
         cp.tile_off = ptr<uint32_t>(c->tile_count);
         cp.sp_key = fp.sp_key;
@@ -667,7 +698,7 @@ int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t bas
         compact_survivors<<<(unsigned)std::min<uint32_t>((fp.tile_end + 7) / 8, (uint32_t)c->sm_count * 8), 256, 0,
                             c->stream>>>(cp);
         CK(cudaGetLastError());
-        c->launches += 2;
+        c->launches += 1;
     }
     if ((rc = run_window_stage(c))) return rc;
     c->phase = chronos_ctx::SUBMITTED;

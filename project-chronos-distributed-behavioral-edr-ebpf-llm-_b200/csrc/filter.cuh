@@ -16,8 +16,13 @@
 //   A  thread-per-record: pid, "type is OPEN", the 8 anchored prefixes (first 12 argv
 //      bytes) -> most noise dies here touching 3 of the 18 16-byte chunks in smem;
 //      the still-alive records are compacted into a work list,
-//   B  thread-per-alive-record: NUL scan (16-byte LDS), suffix table, SWAR needle
-//      search, slow-path UTF-8 DFA only when a high bit was seen,
+//   B1 thread-per-alive-record (lanes packed): comm through a per-warp memo table
+//      (ignore-list, trigger bits, UTF-8 of the 16 comm bytes are a pure function of
+//      them and process names repeat), type, argv NUL search over the first 60 bytes,
+//      suffix table, UTF-8 DFA only when a high bit was seen,
+//   B1b argv longer than 60 bytes: 16 lanes per record, one 16-byte chunk per lane,
+//   B2 survivors only: SWAR trigger-needle search as (record, 16-byte chunk) work items
+//      spread over all threads, so long paths do not serialise a warp,
 //   C  ordered compaction inside the tile (ballot ranks); compact_survivors then applies
 //      the exclusive scan of the per-tile counts, so CTAs never wait on each other.
 #pragma once
@@ -135,102 +140,99 @@ __device__ __forceinline__ bool prefix_noise(uint32_t a0, uint32_t a1, uint32_t 
     return d;
 }
 
-// Full analysis of one record that passed the prefix test. `w` = 72 words in shared
-// memory (16-byte aligned). Returns 0 when the event is dropped, else 0x80 | META bits.
-__device__ __forceinline__ uint32_t analyze_record(const uint32_t *w) {
-    uint32_t meta = 0;
-    // ---- comm: words 1..4 -----------------------------------------------------------
+// ---- per-field classifiers --------------------------------------------------------------
+constexpr uint32_t CR_IGN = 1u << 8, CR_INVALID = 1u << 9, CR_VALID = 1u << 31;
+constexpr uint32_t RW_KEEP = 0x80u, RW_OPEN = 1u << 16, RW_HI = 1u << 17;
+
+// comm (16 raw bytes at record words 1..4): trigger bits | CR_IGN | CR_INVALID.
+// A pure function of the 16 bytes, which is what makes the per-warp memo table exact.
+__device__ __noinline__ uint32_t comm_classify(const uint32_t *w) {
     uint32_t c0 = w[1], c1 = w[2], c2 = w[3], c3 = w[4];
     int clen = truncate_field(c0, c1, c2, c3, 16);
+    uint32_t meta = 0;
     bool ign = false;
     scan_small_field(c0, c1, c2, c3, clen, true, ign, meta);
-    if (ign) return 0;  // :134-135
-    bool hi_comm = ((c0 | c1 | c2 | c3) & 0x80808080u) != 0;
+    uint32_t r = meta | (ign ? CR_IGN : 0u);  // :134-135
+    if (((c0 | c1 | c2 | c3) & 0x80808080u) != 0 &&
+        !utf8_valid_smem(reinterpret_cast<const uint8_t *>(w) + 4, clen))
+        r |= CR_INVALID;  // :128, :131
+    return r;
+}
 
-    // ---- type: words 69, 70 and half of 71 ------------------------------------------
+// type field that is neither "OPEN" nor "EXEC" (replays only): trigger bits | CR_INVALID
+__device__ __noinline__ uint32_t type_classify(const uint32_t *w) {
     uint32_t t0 = w[69], t1 = w[70], t2 = w[71] & 0xFFFFu, t3 = 0;
-    bool nul4 = (t1 & 0xFFu) == 0;
-    bool is_open = (t0 == lit4('O', 'P', 'E', 'N')) & nul4;
-    bool is_exec = (t0 == lit4('E', 'X', 'E', 'C')) & nul4;
-    bool hi_type = false;
-    int tlen = 4;
-    if (!(is_open | is_exec)) {  // replayed records may carry any <=10 bytes here
-        tlen = truncate_field(t0, t1, t2, t3, 10);
-        bool dummy = false;
-        scan_small_field(t0, t1, t2, t3, tlen, false, dummy, meta);
-        hi_type = ((t0 | t1 | t2) & 0x80808080u) != 0;
-    }
-    if (is_exec) meta |= META_EXEC;
+    int tlen = truncate_field(t0, t1, t2, t3, 10);
+    uint32_t meta = 0;
+    bool dummy = false;
+    scan_small_field(t0, t1, t2, t3, tlen, false, dummy, meta);
+    if (((t0 | t1 | t2) & 0x80808080u) != 0 &&
+        !utf8_valid_smem(reinterpret_cast<const uint8_t *>(w) + 276, tlen))
+        meta |= CR_INVALID;  // :130-131
+    return meta;
+}
 
-    // ---- argv pass 1: length (first NUL, cap 256) + "any byte >= 0x80 before it" -----
-    const uint4 *v4 = reinterpret_cast<const uint4 *>(w);
-    int alen = 256;
-    uint32_t hi = 0;
-#pragma unroll 1
-    for (int q = 1; q <= 17; q++) {
-        uint4 v = v4[q];
-        if (q == 1) v.x = 0x01010101u;               // word 4 is comm's tail, not argv
-        if (q == 17) { v.y = 0; v.z = 0; v.w = 0; }  // words 69.. are `type`: act as the cap
-        uint32_t zx = zero_bytes(v.x), zy = zero_bytes(v.y), zz = zero_bytes(v.z), zw = zero_bytes(v.w);
-        if ((zx | zy | zz | zw) != 0) {
-            int base = (4 * q - 5) * 4;  // argv byte position of v.x
-            if (zx) { int k = first_zero_index(zx); alen = base + k; hi |= keep_low_bytes(v.x, k); }
-            else if (zy) { int k = first_zero_index(zy); alen = base + 4 + k; hi |= v.x | keep_low_bytes(v.y, k); }
-            else if (zz) { int k = first_zero_index(zz); alen = base + 8 + k; hi |= v.x | v.y | keep_low_bytes(v.z, k); }
-            else { int k = first_zero_index(zw); alen = base + 12 + k; hi |= v.x | v.y | v.z | keep_low_bytes(v.w, k); }
-            break;
-        }
+// NUL search in one 16-byte chunk q (1..17) of the record, argv-relative.
+// Returns true when the chunk holds argv's end; pos = argv length, hi = OR of the bytes
+// before the end (only bit 7 of each byte matters to the caller).
+__device__ __forceinline__ bool argv_chunk_end(const uint4 *v4, int q, int &pos, uint32_t &hi) {
+    uint4 v = v4[q];
+    if (q == 1) v.x = 0x01010101u;               // word 4 is comm's tail, not argv
+    if (q == 17) { v.y = 0; v.z = 0; v.w = 0; }  // words 69.. are `type`: they act as the 256 cap
+    const uint32_t zx = zero_bytes(v.x), zy = zero_bytes(v.y), zz = zero_bytes(v.z), zw = zero_bytes(v.w);
+    if ((zx | zy | zz | zw) == 0) {
         hi |= v.x | v.y | v.z | v.w;
+        return false;
     }
-    bool hi_argv = (hi & 0x80808080u) != 0;
+    const int base = (4 * q - 5) * 4;  // argv byte position of v.x
+    if (zx) { int k = first_zero_index(zx); pos = base + k; hi |= keep_low_bytes(v.x, k); }
+    else if (zy) { int k = first_zero_index(zy); pos = base + 4 + k; hi |= v.x | keep_low_bytes(v.y, k); }
+    else if (zz) { int k = first_zero_index(zz); pos = base + 8 + k; hi |= v.x | v.y | keep_low_bytes(v.z, k); }
+    else { int k = first_zero_index(zw); pos = base + 12 + k; hi |= v.x | v.y | v.z | keep_low_bytes(v.w, k); }
+    return true;
+}
 
-    // ---- suffix table of the openat hook (:83-85) on the last <=8 bytes --------------
-    if (is_open) {
-        uint64_t T = 0;
-        if (alen > 0) {
-            int o = 12 + alen;  // record byte offset of argv[alen-8]
-            int i = o >> 2, s = (o & 3) * 8;
-            uint32_t W0 = w[i], W1 = w[i + 1], W2 = w[i + 2];
-            uint32_t lo = __funnelshift_r(W0, W1, s), hi32 = __funnelshift_r(W1, W2, s);
-            T = ((uint64_t)hi32 << 32) | lo;
-            if (alen < 8) T &= ~0ULL << (8 * (8 - alen));
-        }
-        bool d = (T >> 40) == lit64(".so", 3);
-        d |= (T >> 16) == lit64(".cache", 6);
-        d |= (T >> 40) == lit64(".mo", 3);
-        d |= (T >> 24) == lit64(".conf", 5);
-        d |= (T >> 32) == lit64(".crt", 4);
-        d |= (T >> 8) == lit64(".curlrc", 7);
-        if (d) return 0;
+// Suffix table of the openat hook (:83-85) on the last <= 8 bytes of argv.
+__device__ __forceinline__ bool suffix_noise(const uint32_t *w, int alen) {
+    uint64_t T = 0;
+    if (alen > 0) {
+        int o = 12 + alen;  // record byte offset of argv[alen-8]
+        int i = o >> 2, s = (o & 3) * 8;
+        uint32_t W0 = w[i], W1 = w[i + 1], W2 = w[i + 2];
+        uint32_t lo = __funnelshift_r(W0, W1, s), hi32 = __funnelshift_r(W1, W2, s);
+        T = ((uint64_t)hi32 << 32) | lo;
+        if (alen < 8) T &= ~0ULL << (8 * (8 - alen));
     }
+    bool d = (T >> 40) == lit64(".so", 3);
+    d |= (T >> 16) == lit64(".cache", 6);
+    d |= (T >> 40) == lit64(".mo", 3);
+    d |= (T >> 24) == lit64(".conf", 5);
+    d |= (T >> 32) == lit64(".crt", 4);
+    d |= (T >> 8) == lit64(".curlrc", 7);
+    return d;
+}
 
-    // ---- strict UTF-8 gate (:128-131); ASCII-only fields are valid by construction ----
-    const uint8_t *b = reinterpret_cast<const uint8_t *>(w);
-    if (hi_comm && !utf8_valid_smem(b + 4, clen)) return 0;
-    if (hi_type && !utf8_valid_smem(b + 276, tlen)) return 0;
-    if (hi_argv && !utf8_valid_smem(b + 20, alen)) return 0;
-
-    // ---- argv pass 2 (survivors only): trigger needles (:141) ------------------------
-    {
-        const uint32_t *a = w + 5;
-        auto ldm = [&](int j) -> uint32_t {
-            int rem = alen - 4 * j;
-            if (rem <= 0) return 0u;
-            uint32_t x = a[j];
-            return rem >= 4 ? x : keep_low_bytes(x, rem);
-        };
-        uint32_t cur = ldm(0);
-#pragma unroll 1
-        for (int j = 0; 4 * j < alen; j++) {
-            uint32_t nxt = ldm(j + 1);
-            meta |= trigger_bits(cur, nxt);
-            meta |= trigger_bits(__funnelshift_r(cur, nxt, 8), nxt >> 8);
-            meta |= trigger_bits(__funnelshift_r(cur, nxt, 16), nxt >> 16);
-            meta |= trigger_bits(__funnelshift_r(cur, nxt, 24), nxt >> 24);
-            cur = nxt;
-        }
+// Trigger needles (:141) starting in argv bytes [16j, 16j+16) of a survivor.
+__device__ __forceinline__ uint32_t argv_trigger_chunk(const uint32_t *w, int alen, int j) {
+    const uint32_t *a = w + 5;
+    auto ldm = [&](int k) -> uint32_t {
+        int rem = alen - 4 * k;
+        if (rem <= 0) return 0u;
+        uint32_t x = a[k];
+        return rem >= 4 ? x : keep_low_bytes(x, rem);
+    };
+    uint32_t meta = 0;
+    uint32_t cur = ldm(4 * j);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+        uint32_t nxt = ldm(4 * j + k + 1);
+        meta |= trigger_bits(cur, nxt);
+        meta |= trigger_bits(__funnelshift_r(cur, nxt, 8), nxt >> 8);
+        meta |= trigger_bits(__funnelshift_r(cur, nxt, 16), nxt >> 16);
+        meta |= trigger_bits(__funnelshift_r(cur, nxt, 24), nxt >> 24);
+        cur = nxt;
     }
-    return 0x80u | meta;
+    return meta;
 }
 
 // Single-pass exclusive prefix over per-tile counts (decoupled look-back). Called by one
@@ -264,21 +266,45 @@ __device__ __forceinline__ uint32_t lookback_count(uint64_t *status, uint32_t ti
     return excl;
 }
 
+constexpr int MEMO_SLOTS = 64;   // per-warp comm memo entries
+constexpr int SHORT_CHUNKS = 4;  // argv NUL search done thread-per-record over chunks 1..4 (60 bytes)
+
 template <int TILE, int NSTAGE>
 struct FilterSmemTail {
+    uint4 memo_key[TILE / 32][MEMO_SLOTS];   // raw 16 comm bytes
+    uint32_t memo_val[TILE / 32][MEMO_SLOTS];
     uint64_t bar[NSTAGE];
     uint32_t tile[NSTAGE];
-    uint32_t n_alive;
+    uint32_t n_alive, n_long, n_items;
     uint32_t base;
     uint32_t k_or, k_and;
     uint32_t wcnt[TILE / 32];
-    uint16_t alive[TILE];
-    uint8_t res[TILE];
+    uint32_t resw[TILE];         // per record: RW_KEEP | META bits (+ RW_OPEN/RW_HI while pending)
+    uint16_t alive[TILE];        // records that passed the prefix test
+    uint16_t longl[TILE];        // alive records whose argv has no NUL in its first 60 bytes
+    uint16_t alen[TILE];         // argv length of survivors
+    uint16_t items[TILE * 16];   // (record << 4 | 16-byte argv chunk) trigger-scan work items
 };
 
 template <int TILE, int NSTAGE>
 constexpr size_t filter_smem_bytes() {
     return (size_t)NSTAGE * TILE * CH_REC_BYTES + sizeof(FilterSmemTail<TILE, NSTAGE>) + 128;
+}
+
+// Last stage of the per-record decision once argv's length is known: suffix drop,
+// argv UTF-8 gate, then the survivor's trigger-scan work items.
+template <int TILE, int NSTAGE>
+__device__ __forceinline__ void finalize_record(FilterSmemTail<TILE, NSTAGE> &S, const uint32_t *w, uint32_t r,
+                                                int alen, bool hi_argv, uint32_t meta, bool is_open) {
+    if (is_open && suffix_noise(w, alen)) { S.resw[r] = 0; return; }
+    if (hi_argv && !utf8_valid_smem(reinterpret_cast<const uint8_t *>(w) + 20, alen)) { S.resw[r] = 0; return; }
+    S.resw[r] = RW_KEEP | (meta & 0x7Fu);
+    S.alen[r] = (uint16_t)alen;
+    const uint32_t nch = (uint32_t)(alen + 15) >> 4;
+    if (nch) {
+        uint32_t at = atomicAdd(&S.n_items, nch);
+        for (uint32_t j = 0; j < nch; j++) S.items[at + j] = (uint16_t)((r << 4) | j);
+    }
 }
 
 template <int TILE, int NSTAGE>
@@ -305,11 +331,14 @@ __global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
     if (tid == 0) {
         for (int s = 0; s < NSTAGE; s++) mbar_init(&S.bar[s], 1);
         S.n_alive = 0;
+        S.n_long = 0;
+        S.n_items = 0;
         S.base = 0;
         S.k_or = 0;
         S.k_and = 0xffffffffu;
         fence_mbar_init();
     }
+    for (int i = lane; i < MEMO_SLOTS; i += 32) S.memo_val[warp][i] = 0;
     __syncthreads();
     if (tid == 0)
         for (int s = 0; s < NSTAGE; s++) claim_and_issue(s);
@@ -324,19 +353,18 @@ __global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
         mbar_wait(&S.bar[s], (it / NSTAGE) & 1);
         const uint8_t *tile_base = stages + (size_t)s * TILE * CH_REC_BYTES;
 
-        // ---- phase A: one record per thread ------------------------------------------
+        // ---- phase A: one record per thread: pid + "OPEN with a noise prefix" -----------
         uint32_t pid = 0;
         bool alive = false;
         if (tid < n_in) {
             const uint4 *r4 = reinterpret_cast<const uint4 *>(tile_base + (size_t)tid * CH_REC_BYTES);
-            uint4 q0 = r4[0];    // pid, comm[0:12]
             uint4 q1 = r4[1];    // comm[12:16], argv[0:12]
             uint4 q17 = r4[17];  // argv[252:256], type[0:10], pad
-            pid = q0.x;
+            pid = reinterpret_cast<const uint32_t *>(r4)[0];
             bool is_open = (q17.y == lit4('O', 'P', 'E', 'N')) & ((q17.z & 0xFFu) == 0);
             alive = !(is_open && prefix_noise(q1.y, q1.z, q1.w));
         }
-        S.res[tid] = 0;
+        S.resw[tid] = 0;
         {
             uint32_t bal = __ballot_sync(0xffffffffu, alive);
             uint32_t pos = 0;
@@ -346,24 +374,116 @@ __global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
         }
         __syncthreads();
 
-        // ---- phase B: one alive record per thread, lanes packed ------------------------
+        // ---- phase B1: one alive record per thread, lanes packed --------------------------
         const uint32_t n_alive = S.n_alive;
-        if ((uint32_t)tid < n_alive) {
-            uint32_t r = S.alive[tid];
+        if ((uint32_t)(warp * 32) < n_alive) {  // warp-uniform
+            const bool act = (uint32_t)tid < n_alive;
+            const uint32_t r = act ? S.alive[tid] : 0u;
             const uint32_t *w = reinterpret_cast<const uint32_t *>(tile_base + (size_t)r * CH_REC_BYTES);
-            S.res[r] = (uint8_t)analyze_record(w);
+            // comm through the per-warp memo table (process names repeat massively)
+            const uint32_t c0 = w[1], c1 = w[2], c2 = w[3], c3 = w[4];
+            const uint32_t h =
+                ((c0 * 0x9E3779B1u) ^ (c1 * 0x85EBCA77u) ^ (c2 * 0xC2B2AE3Du) ^ (c3 * 0x27D4EB2Fu)) >> 26;
+            const uint4 mk = S.memo_key[warp][h];
+            uint32_t cres = S.memo_val[warp][h];
+            const bool hit = (cres & CR_VALID) && mk.x == c0 && mk.y == c1 && mk.z == c2 && mk.w == c3;
+            const bool miss = act && !hit;
+            if (miss) cres = comm_classify(w) | CR_VALID;
+            {
+                const uint32_t peers = __match_any_sync(0xffffffffu, miss ? h : 0x100u + lane);
+                if (miss && (peers & lanemask_lt()) == 0) {
+                    S.memo_key[warp][h] = make_uint4(c0, c1, c2, c3);
+                    S.memo_val[warp][h] = cres;
+                }
+                __syncwarp();
+            }
+            bool live = act && (cres & (CR_IGN | CR_INVALID)) == 0;
+            uint32_t meta = cres & 7u;
+            bool is_open = false;
+            if (live) {
+                const uint32_t t0 = w[69], t1 = w[70];
+                const bool nul4 = (t1 & 0xFFu) == 0;
+                is_open = (t0 == lit4('O', 'P', 'E', 'N')) & nul4;
+                const bool is_exec = (t0 == lit4('E', 'X', 'E', 'C')) & nul4;
+                if (is_exec) meta |= META_EXEC;
+                if (!(is_open | is_exec)) {
+                    const uint32_t tr = type_classify(w);
+                    if (tr & CR_INVALID) live = false;
+                    meta |= tr & 7u;
+                }
+            }
+            if (live) {
+                const uint4 *v4 = reinterpret_cast<const uint4 *>(w);
+                int alen = -1;
+                uint32_t hi = 0;
+#pragma unroll
+                for (int q = 1; q <= SHORT_CHUNKS; q++) {
+                    if (alen < 0) {
+                        int pos = 0;
+                        if (argv_chunk_end(v4, q, pos, hi)) alen = pos;
+                    }
+                }
+                const bool hi_argv = (hi & 0x80808080u) != 0;
+                if (alen >= 0) {
+                    finalize_record<TILE, NSTAGE>(S, w, r, alen, hi_argv, meta, is_open);
+                } else {  // long path: finish cooperatively in phase B1b
+                    S.resw[r] = meta | (is_open ? RW_OPEN : 0u) | (hi_argv ? RW_HI : 0u);
+                    S.longl[atomicAdd(&S.n_long, 1u)] = (uint16_t)r;
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- phase B1b: long argv, 16 lanes per record, one 16-byte chunk per lane -------
+        const uint32_t n_long = S.n_long;
+        if (n_long) {
+            for (uint32_t l0 = (uint32_t)warp * 2; l0 < n_long; l0 += NW * 2) {
+                const uint32_t li = l0 + (lane >> 4);
+                const bool valid = li < n_long;
+                const uint32_t r = valid ? S.longl[li] : 0u;
+                const uint32_t *w = reinterpret_cast<const uint32_t *>(tile_base + (size_t)r * CH_REC_BYTES);
+                const int sub = lane & 15, q = SHORT_CHUNKS + 1 + sub;
+                bool has = false;
+                int pos = 0;
+                uint32_t hi = 0;
+                if (valid && q <= 17) has = argv_chunk_end(reinterpret_cast<const uint4 *>(w), q, pos, hi);
+                const uint32_t hb = (__ballot_sync(0xffffffffu, has) >> (lane & 16)) & 0xFFFFu;
+                const int fz = hb ? __ffs((int)hb) - 1 : 0;  // chunk 17 always ends argv, so hb != 0 when valid
+                const int alen = __shfl_sync(0xffffffffu, pos, (lane & 16) + fz);
+                const uint32_t contrib = (valid && sub <= fz) ? hi : 0u;
+                const uint32_t o_lo = __reduce_or_sync(0xffffffffu, lane < 16 ? contrib : 0u);
+                const uint32_t o_hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? contrib : 0u);
+                if (valid && sub == 0) {
+                    const uint32_t st = S.resw[r];
+                    const bool hi_argv = (((lane < 16 ? o_lo : o_hi) & 0x80808080u) != 0) || (st & RW_HI);
+                    finalize_record<TILE, NSTAGE>(S, w, r, alen, hi_argv, st & 0x7Fu, (st & RW_OPEN) != 0);
+                }
+            }
+            __syncthreads();
+        }
+
+        // ---- phase B2: trigger needles over survivors' argv, one 16-byte chunk per thread --
+        const uint32_t n_items = S.n_items;
+        for (uint32_t k = tid; k < n_items; k += TILE) {
+            const uint32_t itv = S.items[k];
+            const uint32_t r = itv >> 4;
+            const uint32_t *w = reinterpret_cast<const uint32_t *>(tile_base + (size_t)r * CH_REC_BYTES);
+            const uint32_t m = argv_trigger_chunk(w, (int)S.alen[r], (int)(itv & 15u));
+            if (m) atomicOr(&S.resw[r], m);
         }
         __syncthreads();
         // the stage is dead now: refill it while we compact
         if (tid == 0) {
             S.n_alive = 0;
+            S.n_long = 0;
+            S.n_items = 0;
             claim_and_issue(s);
         }
 
         // ---- phase C: tile-local, arrival-ordered compaction -----------------------------
         // (the cross-tile prefix is taken by compact_survivors afterwards: a blocking
         //  look-back here would chain every CTA's stage ring to its neighbour's)
-        const uint32_t code = S.res[tid];
+        const uint32_t code = S.resw[tid];
         const bool keep = (code & 0x80u) != 0;
         const uint32_t kb = __ballot_sync(0xffffffffu, keep);
         const uint32_t rank = __popc(kb & lanemask_lt());

@@ -7,7 +7,7 @@
 // LSD radix sort, <=8-bit digits, only over the bit range in which the keys actually
 // differ (planned on the host from the OR/AND the filter kernel folded). One pass =
 //   radix_hist    per-tile digit histograms            (digit-major table)
-//   radix_scan    exclusive scan of the table          (single CTA)
+//   scan_exclusive_u32  exclusive scan of the table     (look-back, multi-CTA)
 //   radix_scatter stable scatter: per-warp sub-ranges, __match_any_sync ranking
 // Values are entry ids; pass 0 synthesises them (iota) instead of reading them.
 #pragma once
@@ -45,37 +45,112 @@ __global__ void __launch_bounds__(RADIX_THREADS) radix_hist(const RadixParams p)
     p.table[(size_t)threadIdx.x * p.n_tiles + tile] = h[threadIdx.x];
 }
 
-// Exclusive scan of `len` counters in place, one CTA of 1024 threads.
-__global__ void __launch_bounds__(1024) radix_scan(uint32_t *table, uint32_t len) {
-    __shared__ uint32_t warp_sums[32];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t per = (len + 1023u) / 1024u;
-    const uint32_t lo = min(len, (uint32_t)tid * per), hi = min(len, lo + per);
-    uint32_t sum = 0;
-    for (uint32_t i = lo; i < hi; i++) sum += table[i];
-    uint32_t inc = sum;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
-        if (lane >= d) inc += t;
+// Exclusive scan of n counters in place: persistent CTAs, 4096 counters per tile, chained
+// with decoupled look-back. Status words carry an epoch tag ([63:34] epoch, [33:32] state,
+// [31:0] value) so the same status buffer serves every scan without being cleared.
+constexpr int SCAN_THREADS = 512;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+struct ScanParams {
+    uint32_t *data;
+    uint32_t n;
+    uint32_t *ticket;   // zeroed counter
+    uint64_t *status;   // ceil(n / SCAN_TILE) words, any content from older epochs
+    uint32_t epoch;     // > 0, unique per launch sharing `status`
+};
+
+__device__ __forceinline__ uint32_t lookback_count_epoch(uint64_t *status, uint32_t tile, uint32_t agg, int lane,
+                                                         uint32_t epoch) {
+    const uint64_t tag = (uint64_t)epoch << 34;
+    if (tile == 0) {
+        if (lane == 0) st_relaxed_u64(status, tag | (ST_PREFIX << 32) | agg);
+        return 0;
     }
-    if (lane == 31) warp_sums[warp] = inc;
-    __syncthreads();
-    if (warp == 0) {
-        uint32_t w = warp_sums[lane], winc = w;
+    if (lane == 0) st_relaxed_u64(status + tile, tag | (ST_AGG << 32) | agg);
+    uint32_t excl = 0;
+    int64_t look = (int64_t)tile - 1;
+    while (true) {
+        int64_t idx = look - lane;
+        uint64_t v = tag | (ST_PREFIX << 32);  // virtual tiles below 0: prefix 0
+        if (idx >= 0) {
+            do {
+                v = ld_relaxed_u64(status + idx);
+            } while ((v >> 34) != epoch || ((v >> 32) & 3u) == ST_NONE);
+        }
+        const uint32_t is_p = __ballot_sync(0xffffffffu, ((v >> 32) & 3u) == ST_PREFIX);
+        if (is_p) {
+            const int first = __ffs((int)is_p) - 1;
+            excl += __reduce_add_sync(0xffffffffu, lane <= first ? (uint32_t)v : 0u);
+            break;
+        }
+        excl += __reduce_add_sync(0xffffffffu, (uint32_t)v);
+        look -= 32;
+    }
+    if (lane == 0) st_relaxed_u64(status + tile, tag | (ST_PREFIX << 32) | (uint64_t)(excl + agg));
+    return excl;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_exclusive_u32(const ScanParams p) {
+    __shared__ uint32_t warp_sums[SCAN_THREADS / 32];
+    __shared__ uint32_t s_tile, s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n_tiles = (p.n + SCAN_TILE - 1) / SCAN_TILE;
+    while (true) {
+        __syncthreads();
+        if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= n_tiles) break;
+        const uint32_t i0 = tile * SCAN_TILE + tid * SCAN_ITEMS;
+        uint32_t v[SCAN_ITEMS];
+        if (i0 + SCAN_ITEMS <= p.n) {
+            const uint4 a = *reinterpret_cast<const uint4 *>(p.data + i0);
+            const uint4 b = *reinterpret_cast<const uint4 *>(p.data + i0 + 4);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        } else {
+#pragma unroll
+            for (int k = 0; k < SCAN_ITEMS; k++) v[k] = (i0 + k < p.n) ? p.data[i0 + k] : 0u;
+        }
+        uint32_t sum = 0;
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; k++) sum += v[k];
+        uint32_t inc = sum;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, winc, d);
-            if (lane >= d) winc += t;
+            uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
         }
-        warp_sums[lane] = winc - w;
-    }
-    __syncthreads();
-    uint32_t run = warp_sums[warp] + inc - sum;
-    for (uint32_t i = lo; i < hi; i++) {
-        uint32_t v = table[i];
-        table[i] = run;
-        run += v;
+        if (lane == 31) warp_sums[warp] = inc;
+        __syncthreads();
+        if (warp == 0) {
+            uint32_t w = lane < SCAN_THREADS / 32 ? warp_sums[lane] : 0u, winc = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                uint32_t t = __shfl_up_sync(0xffffffffu, winc, d);
+                if (lane >= d) winc += t;
+            }
+            if (lane < SCAN_THREADS / 32) warp_sums[lane] = winc - w;
+            const uint32_t tot = __shfl_sync(0xffffffffu, winc, 31);
+            const uint32_t excl = lookback_count_epoch(p.status, tile, tot, lane, p.epoch);
+            if (lane == 0) s_base = excl;
+        }
+        __syncthreads();
+        uint32_t run = s_base + warp_sums[warp] + inc - sum;
+        uint32_t o[SCAN_ITEMS];
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; k++) {
+            o[k] = run;
+            run += v[k];
+        }
+        if (i0 + SCAN_ITEMS <= p.n) {
+            *reinterpret_cast<uint4 *>(p.data + i0) = make_uint4(o[0], o[1], o[2], o[3]);
+            *reinterpret_cast<uint4 *>(p.data + i0 + 4) = make_uint4(o[4], o[5], o[6], o[7]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < SCAN_ITEMS; k++)
+                if (i0 + k < p.n) p.data[i0 + k] = o[k];
+        }
     }
 }
 
