@@ -250,48 +250,32 @@ __global__ void tracegen_kernel(chronos_tracegen_cfg cfg, const uint64_t *cdf, u
 }
 
 // ---- filter launch ------------------------------------------------------------------------
-template <int TILE, int NSTAGE>
-int launch_filter_t(chronos_ctx *c, FilterParams fp, uint64_t n_records_from_tile_begin) {
+template <int NSTAGE>
+int launch_filter_t(chronos_ctx *c, FilterParams fp) {
     static bool configured[16] = {false};
-    auto kern = filter_kernel<TILE, NSTAGE>;
-    const size_t smem = filter_smem_bytes<TILE, NSTAGE>();
+    auto kern = filter_kernel<NSTAGE>;
+    const size_t smem = filter_smem_bytes<NSTAGE>();
     if (!configured[c->device & 15]) {
         CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured[c->device & 15] = true;
     }
     int per_sm = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, TILE, smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FILTER_TILE, smem));
     if (per_sm < 1) return fail(c, CHRONOS_E_CUDA, "filter kernel does not fit on an SM (smem %zu)", smem);
     const uint32_t tiles = fp.tile_end - fp.tile_begin;
     const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(per_sm * c->sm_count));
-    (void)n_records_from_tile_begin;
-    kern<<<grid, TILE, smem, c->stream>>>(fp);
+    kern<<<grid, FILTER_TILE, smem, c->stream>>>(fp);
     CK(cudaGetLastError());
     c->launches++;
     return CHRONOS_OK;
 }
 
-// (TILE, NSTAGE) variants of the filter kernel; CHRONOS_FILTER_VARIANT picks one (tuning knob).
-#define CHRONOS_FILTER_VARIANTS(X) X(0, 64, 2) X(1, 128, 2) X(2, 128, 3) X(3, 64, 3) X(4, 32, 2) X(5, 32, 3) X(6, 256, 2) X(7, 32, 1) X(8, 64, 1)
+int filter_tile_size(const chronos_ctx *) { return FILTER_TILE; }
 
-int filter_tile_size(const chronos_ctx *c) {
-    switch (c->filter_variant) {
-#define X(id, tile, nstage) \
-    case id: return tile;
-        CHRONOS_FILTER_VARIANTS(X)
-#undef X
-    default: return 32;
-    }
-}
-
+// CHRONOS_FILTER_VARIANT=2 selects the double-buffered build of the filter (tuning knob)
 int launch_filter(chronos_ctx *c, const FilterParams &fp) {
-    switch (c->filter_variant) {
-#define X(id, tile, nstage) \
-    case id: return launch_filter_t<tile, nstage>(c, fp, 0);
-        CHRONOS_FILTER_VARIANTS(X)
-#undef X
-    default: return launch_filter_t<32, 1>(c, fp, 0);
-    }
+    if (c->filter_variant == 2) return launch_filter_t<2>(c, fp);
+    return launch_filter_t<1>(c, fp);
 }
 
 // exclusive scan in place (device array of n u32) on the context's stream

@@ -9,22 +9,23 @@
 //   comm ignore-list    :134-135
 //   trigger needles     :137, :141 (a match always lies inside one field)
 //
-// Execution model: persistent CTAs pull tiles of TILE records from an atomic ticket
+// Execution model: persistent single-warp CTAs pull 32-record tiles from an atomic ticket
 // counter; each tile is fetched with ONE 1-D TMA bulk copy (cp.async.bulk, UBLKCP) into
-// a ring of NSTAGE shared-memory stages, completion tracked by mbarrier transaction
-// bytes, so the HBM stream is fully coalesced and asynchronous.  Per tile:
-//   A  thread-per-record: pid, "type is OPEN", the 8 anchored prefixes (first 12 argv
-//      bytes) -> most noise dies here touching 3 of the 18 16-byte chunks in smem;
-//      the still-alive records are compacted into a work list,
-//   B1 thread-per-alive-record (lanes packed): comm through a per-warp memo table
-//      (ignore-list, trigger bits, UTF-8 of the 16 comm bytes are a pure function of
-//      them and process names repeat), type, argv NUL search over the first 60 bytes,
-//      suffix table, UTF-8 DFA only when a high bit was seen,
-//   B1b argv longer than 60 bytes: 16 lanes per record, one 16-byte chunk per lane,
-//   B2 survivors only: SWAR trigger-needle search as (record, 16-byte chunk) work items
-//      spread over all threads, so long paths do not serialise a warp,
-//   C  ordered compaction inside the tile (ballot ranks); compact_survivors then applies
-//      the exclusive scan of the per-tile counts, so CTAs never wait on each other.
+// shared memory, completion tracked by mbarrier transaction bytes, so the HBM stream is
+// fully coalesced and asynchronous. ~19 such CTAs are resident per SM; their independent
+// progress is what overlaps copy latency with the byte work. Per tile, lane i <-> record i:
+//   A   pid, "type is OPEN", the 8 anchored prefixes (first 12 argv bytes): most noise
+//       dies here after touching 3 of the record's 18 16-byte chunks,
+//   B1  comm through a per-CTA memo table (ignore-list, trigger bits and UTF-8 validity are
+//       a pure function of the 16 comm bytes, and process names repeat), type, argv NUL
+//       search over the first 60 bytes,
+//   B1b argv longer than that: 16 lanes per record, one 16-byte chunk per lane,
+//       then suffix table and (only when a byte >= 0x80 was seen) the UTF-8 DFA,
+//   B2  survivors only: SWAR trigger-needle search as (record, 8-byte chunk) work items
+//       spread over all 32 lanes with a shuffle binary search, so long paths do not
+//       serialise the warp,
+//   C   ballot-ranked, arrival-ordered compaction inside the tile; compact_survivors then
+//       applies the exclusive scan of the per-tile counts, so CTAs never wait on each other.
 #pragma once
 #include "common.cuh"
 
@@ -266,145 +267,130 @@ __device__ __forceinline__ uint32_t lookback_count(uint64_t *status, uint32_t ti
     return excl;
 }
 
-constexpr int MEMO_SLOTS = 64;   // per-warp comm memo entries
-constexpr int SHORT_CHUNKS = 4;  // argv NUL search done thread-per-record over chunks 1..4 (60 bytes)
+constexpr int FILTER_TILE = 32;  // records per tile: one per lane of the (single) warp of a CTA
+constexpr int MEMO_SLOTS = 64;   // comm memo entries per CTA
+constexpr int SHORT_CHUNKS = 4;  // argv NUL search done lane-per-record over chunks 1..4 (60 bytes)
 
-template <int TILE, int NSTAGE>
+template <int NSTAGE>
 struct FilterSmemTail {
-    uint4 memo_key[TILE / 32][MEMO_SLOTS];   // raw 16 comm bytes
-    uint32_t memo_val[TILE / 32][MEMO_SLOTS];
+    uint4 memo_key[MEMO_SLOTS];  // raw 16 comm bytes
+    uint32_t memo_val[MEMO_SLOTS];
     uint64_t bar[NSTAGE];
     uint32_t tile[NSTAGE];
-    uint32_t n_alive, n_long, n_items;
-    uint32_t base;
-    uint32_t k_or, k_and;
-    uint32_t wcnt[TILE / 32];
-    uint32_t resw[TILE];         // per record: RW_KEEP | META bits (+ RW_OPEN/RW_HI while pending)
-    uint16_t alive[TILE];        // records that passed the prefix test
-    uint16_t longl[TILE];        // alive records whose argv has no NUL in its first 60 bytes
-    uint16_t alen[TILE];         // argv length of survivors
-    uint16_t items[TILE * 16];   // (record << 4 | 16-byte argv chunk) trigger-scan work items
+    uint32_t resw[FILTER_TILE];  // trigger bits found by other lanes for lane i's record
 };
 
-template <int TILE, int NSTAGE>
+template <int NSTAGE>
 constexpr size_t filter_smem_bytes() {
-    return (size_t)NSTAGE * TILE * CH_REC_BYTES + sizeof(FilterSmemTail<TILE, NSTAGE>) + 128;
+    return (size_t)NSTAGE * FILTER_TILE * CH_REC_BYTES + sizeof(FilterSmemTail<NSTAGE>) + 128;
 }
 
-// Last stage of the per-record decision once argv's length is known: suffix drop,
-// argv UTF-8 gate, then the survivor's trigger-scan work items.
-template <int TILE, int NSTAGE>
-__device__ __forceinline__ void finalize_record(FilterSmemTail<TILE, NSTAGE> &S, const uint32_t *w, uint32_t r,
-                                                int alen, bool hi_argv, uint32_t meta, bool is_open) {
-    if (is_open && suffix_noise(w, alen)) { S.resw[r] = 0; return; }
-    if (hi_argv && !utf8_valid_smem(reinterpret_cast<const uint8_t *>(w) + 20, alen)) { S.resw[r] = 0; return; }
-    S.resw[r] = RW_KEEP | (meta & 0x7Fu);
-    S.alen[r] = (uint16_t)alen;
-    const uint32_t nch = (uint32_t)(alen + 15) >> 4;
-    if (nch) {
-        uint32_t at = atomicAdd(&S.n_items, nch);
-        for (uint32_t j = 0; j < nch; j++) S.items[at + j] = (uint16_t)((r << 4) | j);
-    }
+// Trigger needles (:141) starting in argv bytes [8j, 8j+8) of a survivor.
+__device__ __forceinline__ uint32_t argv_trigger_item(const uint32_t *w, int alen, int j) {
+    const uint32_t *a = w + 5;
+    auto ldm = [&](int k) -> uint32_t {
+        int rem = alen - 4 * k;
+        if (rem <= 0) return 0u;
+        uint32_t x = a[k];
+        return rem >= 4 ? x : keep_low_bytes(x, rem);
+    };
+    const uint32_t x0 = ldm(2 * j), x1 = ldm(2 * j + 1), x2 = ldm(2 * j + 2);
+    uint32_t meta = trigger_bits(x0, x1);
+    meta |= trigger_bits(__funnelshift_r(x0, x1, 8), x1 >> 8);
+    meta |= trigger_bits(__funnelshift_r(x0, x1, 16), x1 >> 16);
+    meta |= trigger_bits(__funnelshift_r(x0, x1, 24), x1 >> 24);
+    meta |= trigger_bits(x1, x2);
+    meta |= trigger_bits(__funnelshift_r(x1, x2, 8), x2 >> 8);
+    meta |= trigger_bits(__funnelshift_r(x1, x2, 16), x2 >> 16);
+    meta |= trigger_bits(__funnelshift_r(x1, x2, 24), x2 >> 24);
+    return meta;
 }
 
-template <int TILE, int NSTAGE>
-__global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
+// One warp per CTA, one 32-record tile per step, everything warp-synchronous: no block
+// barriers, no shared work lists. Many such CTAs are resident per SM (about 9 KB of
+// staged records + a small tail each), which is what hides the TMA and LDS latencies.
+template <int NSTAGE>
+__global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~(uintptr_t)127);
     uint8_t *stages = smem;
-    auto &S = *reinterpret_cast<FilterSmemTail<TILE, NSTAGE> *>(smem + (size_t)NSTAGE * TILE * CH_REC_BYTES);
-    constexpr int NW = TILE / 32;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    auto &S = *reinterpret_cast<FilterSmemTail<NSTAGE> *>(smem + (size_t)NSTAGE * FILTER_TILE * CH_REC_BYTES);
+    constexpr uint32_t FULL = 0xffffffffu;
+    constexpr uint32_t STAGE_BYTES = FILTER_TILE * CH_REC_BYTES;
+    const int lane = threadIdx.x;
 
-    auto claim_and_issue = [&](int s) {  // thread 0 only
-        uint32_t t = p.tile_begin + atomicAdd(p.ticket, 1u);
+    auto issue = [&](int s, uint32_t t) {  // lane 0 only
         S.tile[s] = t;
         if (t < p.tile_end) {
-            uint64_t first = (uint64_t)t * TILE;
-            uint32_t cnt = (uint32_t)min((uint64_t)TILE, p.n - first);
-            uint32_t bytes = cnt * CH_REC_BYTES;
+            const uint64_t first = (uint64_t)t * FILTER_TILE;
+            const uint32_t bytes = (uint32_t)min((uint64_t)FILTER_TILE, p.n - first) * CH_REC_BYTES;
             mbar_arrive_expect_tx(&S.bar[s], bytes);
-            bulk_g2s(stages + (size_t)s * TILE * CH_REC_BYTES, p.recs + first * CH_REC_BYTES, bytes, &S.bar[s]);
+            bulk_g2s(stages + (size_t)s * STAGE_BYTES, p.recs + first * CH_REC_BYTES, bytes, &S.bar[s]);
         }
     };
 
-    if (tid == 0) {
+    for (int i = lane; i < MEMO_SLOTS; i += 32) S.memo_val[i] = 0;
+    if (lane == 0) {
         for (int s = 0; s < NSTAGE; s++) mbar_init(&S.bar[s], 1);
-        S.n_alive = 0;
-        S.n_long = 0;
-        S.n_items = 0;
-        S.base = 0;
-        S.k_or = 0;
-        S.k_and = 0xffffffffu;
         fence_mbar_init();
+        for (int s = 0; s < NSTAGE; s++) issue(s, p.tile_begin + atomicAdd(p.ticket, 1u));
     }
-    for (int i = lane; i < MEMO_SLOTS; i += 32) S.memo_val[warp][i] = 0;
-    __syncthreads();
-    if (tid == 0)
-        for (int s = 0; s < NSTAGE; s++) claim_and_issue(s);
-    __syncthreads();
+    __syncwarp();
 
+    uint32_t cta_total = 0, k_or = 0, k_and = 0xffffffffu;
     for (uint32_t it = 0;; it++) {
-        const int s = it % NSTAGE;
+        const int s = (NSTAGE == 1) ? 0 : (int)(it % NSTAGE);
         const uint32_t tile = S.tile[s];
         if (tile >= p.tile_end) break;
-        const uint64_t first = (uint64_t)tile * TILE;
-        const uint32_t n_in = (uint32_t)min((uint64_t)TILE, p.n - first);
+        // ticket for this stage's NEXT tile: claimed now, needed only after phase B2
+        uint32_t next_ticket = 0;
+        if (lane == 0) next_ticket = atomicAdd(p.ticket, 1u);
+        const uint64_t first = (uint64_t)tile * FILTER_TILE;
+        const uint32_t n_in = (uint32_t)min((uint64_t)FILTER_TILE, p.n - first);
         mbar_wait(&S.bar[s], (it / NSTAGE) & 1);
-        const uint8_t *tile_base = stages + (size_t)s * TILE * CH_REC_BYTES;
+        const uint8_t *tile_base = stages + (size_t)s * STAGE_BYTES;
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(tile_base + (size_t)lane * CH_REC_BYTES);
+        const uint4 *v4 = reinterpret_cast<const uint4 *>(w);
 
-        // ---- phase A: one record per thread: pid + "OPEN with a noise prefix" -----------
+        // ---- phase A: lane i <-> record i: pid + "OPEN with a noise prefix" ----------------
         uint32_t pid = 0;
-        bool alive = false;
-        if (tid < n_in) {
-            const uint4 *r4 = reinterpret_cast<const uint4 *>(tile_base + (size_t)tid * CH_REC_BYTES);
-            uint4 q1 = r4[1];    // comm[12:16], argv[0:12]
-            uint4 q17 = r4[17];  // argv[252:256], type[0:10], pad
-            pid = reinterpret_cast<const uint32_t *>(r4)[0];
-            bool is_open = (q17.y == lit4('O', 'P', 'E', 'N')) & ((q17.z & 0xFFu) == 0);
+        bool alive = false, is_open = false, is_exec = false;
+        if ((uint32_t)lane < n_in) {
+            const uint4 q1 = v4[1];    // comm[12:16], argv[0:12]
+            const uint4 q17 = v4[17];  // argv[252:256], type[0:10], pad
+            pid = w[0];
+            const bool nul4 = (q17.z & 0xFFu) == 0;
+            is_open = (q17.y == lit4('O', 'P', 'E', 'N')) & nul4;
+            is_exec = (q17.y == lit4('E', 'X', 'E', 'C')) & nul4;
             alive = !(is_open && prefix_noise(q1.y, q1.z, q1.w));
         }
-        S.resw[tid] = 0;
-        {
-            uint32_t bal = __ballot_sync(0xffffffffu, alive);
-            uint32_t pos = 0;
-            if (lane == 0 && bal) pos = atomicAdd(&S.n_alive, (uint32_t)__popc(bal));
-            pos = __shfl_sync(0xffffffffu, pos, 0);
-            if (alive) S.alive[pos + __popc(bal & lanemask_lt())] = (uint16_t)tid;
-        }
-        __syncthreads();
+        S.resw[lane] = 0;
+        __syncwarp();
 
-        // ---- phase B1: one alive record per thread, lanes packed --------------------------
-        const uint32_t n_alive = S.n_alive;
-        if ((uint32_t)(warp * 32) < n_alive) {  // warp-uniform
-            const bool act = (uint32_t)tid < n_alive;
-            const uint32_t r = act ? S.alive[tid] : 0u;
-            const uint32_t *w = reinterpret_cast<const uint32_t *>(tile_base + (size_t)r * CH_REC_BYTES);
-            // comm through the per-warp memo table (process names repeat massively)
+        // ---- phase B1 (in place): comm memo, type, argv NUL search in the first 60 bytes ----
+        bool live = false;
+        int alen = -1;
+        uint32_t meta = 0, hi = 0;
+        if (__any_sync(FULL, alive)) {
             const uint32_t c0 = w[1], c1 = w[2], c2 = w[3], c3 = w[4];
             const uint32_t h =
                 ((c0 * 0x9E3779B1u) ^ (c1 * 0x85EBCA77u) ^ (c2 * 0xC2B2AE3Du) ^ (c3 * 0x27D4EB2Fu)) >> 26;
-            const uint4 mk = S.memo_key[warp][h];
-            uint32_t cres = S.memo_val[warp][h];
+            const uint4 mk = S.memo_key[h];
+            uint32_t cres = S.memo_val[h];
             const bool hit = (cres & CR_VALID) && mk.x == c0 && mk.y == c1 && mk.z == c2 && mk.w == c3;
-            const bool miss = act && !hit;
+            const bool miss = alive && !hit;
             if (miss) cres = comm_classify(w) | CR_VALID;
             {
-                const uint32_t peers = __match_any_sync(0xffffffffu, miss ? h : 0x100u + lane);
+                const uint32_t peers = __match_any_sync(FULL, miss ? h : 0x100u + lane);
                 if (miss && (peers & lanemask_lt()) == 0) {
-                    S.memo_key[warp][h] = make_uint4(c0, c1, c2, c3);
-                    S.memo_val[warp][h] = cres;
+                    S.memo_key[h] = make_uint4(c0, c1, c2, c3);
+                    S.memo_val[h] = cres;
                 }
                 __syncwarp();
             }
-            bool live = act && (cres & (CR_IGN | CR_INVALID)) == 0;
-            uint32_t meta = cres & 7u;
-            bool is_open = false;
+            live = alive && (cres & (CR_IGN | CR_INVALID)) == 0;
+            meta = cres & 7u;
             if (live) {
-                const uint32_t t0 = w[69], t1 = w[70];
-                const bool nul4 = (t1 & 0xFFu) == 0;
-                is_open = (t0 == lit4('O', 'P', 'E', 'N')) & nul4;
-                const bool is_exec = (t0 == lit4('E', 'X', 'E', 'C')) & nul4;
                 if (is_exec) meta |= META_EXEC;
                 if (!(is_open | is_exec)) {
                     const uint32_t tr = type_classify(w);
@@ -413,9 +399,6 @@ __global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
                 }
             }
             if (live) {
-                const uint4 *v4 = reinterpret_cast<const uint4 *>(w);
-                int alen = -1;
-                uint32_t hi = 0;
 #pragma unroll
                 for (int q = 1; q <= SHORT_CHUNKS; q++) {
                     if (alen < 0) {
@@ -423,108 +406,105 @@ __global__ void __launch_bounds__(TILE) filter_kernel(const FilterParams p) {
                         if (argv_chunk_end(v4, q, pos, hi)) alen = pos;
                     }
                 }
-                const bool hi_argv = (hi & 0x80808080u) != 0;
-                if (alen >= 0) {
-                    finalize_record<TILE, NSTAGE>(S, w, r, alen, hi_argv, meta, is_open);
-                } else {  // long path: finish cooperatively in phase B1b
-                    S.resw[r] = meta | (is_open ? RW_OPEN : 0u) | (hi_argv ? RW_HI : 0u);
-                    S.longl[atomicAdd(&S.n_long, 1u)] = (uint16_t)r;
-                }
             }
         }
-        __syncthreads();
 
-        // ---- phase B1b: long argv, 16 lanes per record, one 16-byte chunk per lane -------
-        const uint32_t n_long = S.n_long;
-        if (n_long) {
-            for (uint32_t l0 = (uint32_t)warp * 2; l0 < n_long; l0 += NW * 2) {
-                const uint32_t li = l0 + (lane >> 4);
-                const bool valid = li < n_long;
-                const uint32_t r = valid ? S.longl[li] : 0u;
-                const uint32_t *w = reinterpret_cast<const uint32_t *>(tile_base + (size_t)r * CH_REC_BYTES);
-                const int sub = lane & 15, q = SHORT_CHUNKS + 1 + sub;
-                bool has = false;
-                int pos = 0;
-                uint32_t hi = 0;
-                if (valid && q <= 17) has = argv_chunk_end(reinterpret_cast<const uint4 *>(w), q, pos, hi);
-                const uint32_t hb = (__ballot_sync(0xffffffffu, has) >> (lane & 16)) & 0xFFFFu;
-                const int fz = hb ? __ffs((int)hb) - 1 : 0;  // chunk 17 always ends argv, so hb != 0 when valid
-                const int alen = __shfl_sync(0xffffffffu, pos, (lane & 16) + fz);
-                const uint32_t contrib = (valid && sub <= fz) ? hi : 0u;
-                const uint32_t o_lo = __reduce_or_sync(0xffffffffu, lane < 16 ? contrib : 0u);
-                const uint32_t o_hi = __reduce_or_sync(0xffffffffu, lane >= 16 ? contrib : 0u);
-                if (valid && sub == 0) {
-                    const uint32_t st = S.resw[r];
-                    const bool hi_argv = (((lane < 16 ? o_lo : o_hi) & 0x80808080u) != 0) || (st & RW_HI);
-                    finalize_record<TILE, NSTAGE>(S, w, r, alen, hi_argv, st & 0x7Fu, (st & RW_OPEN) != 0);
-                }
+        // ---- phase B1b: argv longer than 60 bytes: 16 lanes per record, a chunk per lane ----
+        uint32_t lm = __ballot_sync(FULL, live && alen < 0);
+        while (lm) {
+            const int ra = __ffs((int)lm) - 1;
+            lm &= lm - 1;
+            int rb = -1;
+            if (lm) {
+                rb = __ffs((int)lm) - 1;
+                lm &= lm - 1;
             }
-            __syncthreads();
+            const int r = (lane < 16) ? ra : rb;
+            const bool valid = r >= 0;
+            const uint4 *rv4 = reinterpret_cast<const uint4 *>(tile_base + (size_t)(valid ? r : 0) * CH_REC_BYTES);
+            const int sub = lane & 15, q = SHORT_CHUNKS + 1 + sub;
+            bool has = false;
+            int pos = 0;
+            uint32_t h2 = 0;
+            if (valid && q <= 17) has = argv_chunk_end(rv4, q, pos, h2);
+            const uint32_t bal = __ballot_sync(FULL, has);
+            const uint32_t hbA = bal & 0xFFFFu, hbB = bal >> 16;
+            const int fzA = hbA ? __ffs((int)hbA) - 1 : 0;  // chunk 17 always ends argv: hb != 0 when valid
+            const int fzB = hbB ? __ffs((int)hbB) - 1 : 0;
+            const int alenA = __shfl_sync(FULL, pos, fzA), alenB = __shfl_sync(FULL, pos, 16 + fzB);
+            const uint32_t oA = __reduce_or_sync(FULL, (lane < 16 && sub <= fzA) ? h2 : 0u);
+            const uint32_t oB = __reduce_or_sync(FULL, (lane >= 16 && valid && sub <= fzB) ? h2 : 0u);
+            if (lane == ra) { alen = alenA; hi |= oA; }
+            if (lane == rb) { alen = alenB; hi |= oB; }
         }
 
-        // ---- phase B2: trigger needles over survivors' argv, one 16-byte chunk per thread --
-        const uint32_t n_items = S.n_items;
-        for (uint32_t k = tid; k < n_items; k += TILE) {
-            const uint32_t itv = S.items[k];
-            const uint32_t r = itv >> 4;
-            const uint32_t *w = reinterpret_cast<const uint32_t *>(tile_base + (size_t)r * CH_REC_BYTES);
-            const uint32_t m = argv_trigger_chunk(w, (int)S.alen[r], (int)(itv & 15u));
-            if (m) atomicOr(&S.resw[r], m);
-        }
-        __syncthreads();
-        // the stage is dead now: refill it while we compact
-        if (tid == 0) {
-            S.n_alive = 0;
-            S.n_long = 0;
-            S.n_items = 0;
-            claim_and_issue(s);
+        // ---- finalize (in place): suffix table, argv UTF-8 gate ----------------------------
+        bool keep = false;
+        if (live) {
+            const bool hi_argv = (hi & 0x80808080u) != 0;
+            if (is_open && suffix_noise(w, alen)) keep = false;
+            else if (hi_argv && !utf8_valid_smem(reinterpret_cast<const uint8_t *>(w) + 20, alen)) keep = false;
+            else keep = true;
         }
 
-        // ---- phase C: tile-local, arrival-ordered compaction -----------------------------
-        // (the cross-tile prefix is taken by compact_survivors afterwards: a blocking
-        //  look-back here would chain every CTA's stage ring to its neighbour's)
-        const uint32_t code = S.resw[tid];
-        const bool keep = (code & 0x80u) != 0;
-        const uint32_t kb = __ballot_sync(0xffffffffu, keep);
-        const uint32_t rank = __popc(kb & lanemask_lt());
+        // ---- phase B2: trigger needles over survivors' argv as 8-byte work items ------------
         {
-            uint32_t o = __reduce_or_sync(0xffffffffu, keep ? pid : 0u);
-            uint32_t a = __reduce_and_sync(0xffffffffu, keep ? pid : 0xffffffffu);
-            if (lane == 0) {
-                S.wcnt[warp] = __popc(kb);
-                if (kb) {
-                    atomicOr(&S.k_or, o);
-                    atomicAnd(&S.k_and, a);
-                }
-            }
-        }
-        __syncthreads();
-        {
-            uint32_t before = rank, tot = 0;
+            const uint32_t nitems = keep ? (uint32_t)(alen + 7) >> 3 : 0u;
+            uint32_t incl = nitems;
 #pragma unroll
-            for (int k = 0; k < NW; k++) {
-                const uint32_t c = S.wcnt[k];
-                before += (k < warp) ? c : 0u;
-                tot += c;
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(FULL, incl, d);
+                if (lane >= d) incl += t;
             }
+            const uint32_t excl = incl - nitems;
+            const uint32_t total = __shfl_sync(FULL, incl, 31);
+            for (uint32_t b0 = 0; b0 < total; b0 += 32) {
+                const uint32_t k = b0 + lane;
+                int sidx = 0;  // owner of item k = number of lanes whose inclusive count is <= k
+#pragma unroll
+                for (int step = 16; step >= 1; step >>= 1) {
+                    const uint32_t vv = __shfl_sync(FULL, incl, sidx + step - 1);
+                    if (vv <= k) sidx += step;
+                }
+                const uint32_t ex = __shfl_sync(FULL, excl, sidx);
+                const int al = __shfl_sync(FULL, alen, sidx);
+                if (k < total) {
+                    const uint32_t *rw = reinterpret_cast<const uint32_t *>(tile_base + (size_t)sidx * CH_REC_BYTES);
+                    const uint32_t m = argv_trigger_item(rw, al, (int)(k - ex));
+                    if (m) atomicOr(&S.resw[sidx], m);
+                }
+            }
+        }
+        __syncwarp();
+        const uint32_t found = S.resw[lane];
+
+        // ---- the stage is dead: refill it, then compact while the copy is in flight -------
+        next_ticket = __shfl_sync(FULL, next_ticket, 0);
+        if (lane == 0) issue(s, p.tile_begin + next_ticket);
+        __syncwarp();
+
+        // ---- phase C: tile-local, arrival-ordered compaction ---------------------------------
+        // (compact_survivors applies the cross-tile prefix afterwards, so CTAs never wait
+        //  on each other)
+        const uint32_t kb = __ballot_sync(FULL, keep);
+        if (kb) {
+            const uint32_t rank = __popc(kb & lanemask_lt());
             if (keep) {
-                const size_t slot = (size_t)tile * TILE + before;
+                const size_t slot = (size_t)tile * FILTER_TILE + rank;
                 p.sp_key[slot] = pid;
-                p.sp_src[slot] = (uint32_t)first + tid;
-                p.sp_meta[slot] = (uint8_t)(code & 0x7Fu);
+                p.sp_src[slot] = (uint32_t)first + lane;
+                p.sp_meta[slot] = (uint8_t)((meta | found) & 0x7Fu);
             }
-            if (tid == 0) {
-                p.tile_count[tile] = tot;
-                S.base += tot;
-            }
+            k_or |= __reduce_or_sync(FULL, keep ? pid : 0u);
+            k_and &= __reduce_and_sync(FULL, keep ? pid : 0xffffffffu);
         }
+        if (lane == 0) p.tile_count[tile] = __popc(kb);
+        cta_total += __popc(kb);
     }
-    if (tid == 0) {
-        if (S.base) atomicAdd(p.out_count, S.base);
-        if (S.k_or != 0 || S.k_and != 0xffffffffu) {
-            atomicOr(p.key_or, S.k_or);
-            atomicAnd(p.key_and, S.k_and);
-        }
+    if (lane == 0 && cta_total) {
+        atomicAdd(p.out_count, cta_total);
+        atomicOr(p.key_or, k_or);
+        atomicAnd(p.key_and, k_and);
     }
 }
 
