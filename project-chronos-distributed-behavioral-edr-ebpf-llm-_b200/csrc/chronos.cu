@@ -56,7 +56,8 @@ struct chronos_ctx {
     int device = 0;
     int sm_count = 0;
     uint64_t max_batch = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr, stream2 = nullptr;  // stream2: record gather, overlapped with the window scans
+    cudaEvent_t ev_sorted = nullptr, ev_gathered = nullptr;
     cudaEvent_t ev_start = nullptr, ev_filter = nullptr, ev_end = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
     char err[256] = {0};
 
@@ -419,8 +420,12 @@ int run_window_stage(chronos_ctx *c) {
         g.prev_arena = ptr<uint8_t>(c->arena[prev]);
         g.arena = ptr<uint8_t>(c->arena[cur]);
         uint32_t blocks = (uint32_t)std::min<uint64_t>((M + 127) / 128, (uint64_t)c->sm_count * 8);
-        gather_records<<<blocks, 256, 0, c->stream>>>(g);
+        // bandwidth-bound copy on a second stream, next to the latency-bound window scans
+        CK(cudaEventRecord(c->ev_sorted, c->stream));
+        CK(cudaStreamWaitEvent(c->stream2, c->ev_sorted, 0));
+        gather_records<<<blocks, 256, 0, c->stream2>>>(g);
         CK(cudaGetLastError());
+        CK(cudaEventRecord(c->ev_gathered, c->stream2));
         c->launches++;
     }
 
@@ -471,6 +476,7 @@ int run_window_stage(chronos_ctx *c) {
         }
         CK(cudaGetLastError());
     }
+    CK(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
     CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaEventRecord(c->ev_end, c->stream));
     return CHRONOS_OK;
@@ -581,6 +587,9 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
         CK(cudaGetDeviceProperties(&p, device));
         c->sm_count = p.multiProcessorCount;
         CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&c->ev_sorted, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
         CK(cudaEventCreate(&c->ev_start));
         CK(cudaEventCreate(&c->ev_filter));
         CK(cudaEventCreate(&c->ev_end));
@@ -617,6 +626,9 @@ int chronos_destroy(chronos_ctx *c) {
     if (c->ev_end) cudaEventDestroy(c->ev_end);
     if (c->ev_f0) cudaEventDestroy(c->ev_f0);
     if (c->ev_f1) cudaEventDestroy(c->ev_f1);
+    if (c->ev_sorted) cudaEventDestroy(c->ev_sorted);
+    if (c->ev_gathered) cudaEventDestroy(c->ev_gathered);
+    if (c->stream2) cudaStreamDestroy(c->stream2);
     if (c->stream) cudaStreamDestroy(c->stream);
     cudaGetLastError();
     delete c;
@@ -679,7 +691,7 @@ int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t bas
         cp.n_tiles = fp.tile_end;
         cp.tile = (uint32_t)TILE;
         cp.total = &ds->surv_count;
-        compact_survivors<<<(unsigned)std::min<uint32_t>((fp.tile_end + 7) / 8, (uint32_t)c->sm_count * 8), 256, 0,
+        compact_survivors<<<(unsigned)std::min<uint32_t>((fp.tile_end + 255) / 256, (uint32_t)c->sm_count * 8), 256, 0,
                             c->stream>>>(cp);
         CK(cudaGetLastError());
         c->launches += 1;

@@ -509,7 +509,7 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
 }
 
 // Cross-tile step of the ordered compaction: tile_off[] = exclusive scan of tile_count[]
-// (radix_scan); one warp per filter tile moves its run to the dense arrays.
+// (scan_exclusive_u32); one thread per filter tile moves its short run to the dense arrays.
 struct CompactParams {
     const uint32_t *tile_off;
     const uint32_t *sp_key;
@@ -524,14 +524,12 @@ struct CompactParams {
 };
 
 __global__ void __launch_bounds__(256) compact_survivors(const CompactParams c) {
-    const uint32_t lane = threadIdx.x & 31;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t t = warp; t < c.n_tiles; t += n_warps) {
+    // a tile holds 32 records and on average only a few survivors: one thread per tile
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < c.n_tiles; t += gridDim.x * blockDim.x) {
         const uint32_t lo = c.tile_off[t];
         const uint32_t hi = (t + 1 < c.n_tiles) ? c.tile_off[t + 1] : *c.total;
         const size_t base = (size_t)t * c.tile;
-        for (uint32_t j = lane; j < hi - lo; j += 32) {
+        for (uint32_t j = 0; j < hi - lo; j++) {
             c.out_key[lo + j] = c.sp_key[base + j];
             c.out_src[lo + j] = c.sp_src[base + j];
             c.out_meta[lo + j] = c.sp_meta[base + j];

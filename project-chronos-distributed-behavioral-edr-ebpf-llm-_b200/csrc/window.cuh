@@ -25,7 +25,7 @@ namespace chronos {
 
 constexpr uint32_t NONE32 = 0xffffffffu;
 constexpr int WIN_THREADS = 256;
-constexpr int WIN_ITEMS = 8;
+constexpr int WIN_ITEMS = 16;
 constexpr int WIN_TILE = WIN_THREADS * WIN_ITEMS;
 
 // What a run of elements does to the automaton, for either entry state s in {0,1}:
@@ -129,8 +129,15 @@ __device__ __forceinline__ St2 fn_lookback(uint64_t *status, uint32_t tile, cons
             mine.b[1] = (uint32_t)w1;
             const uint32_t is_p = __ballot_sync(0xffffffffu, (w0 >> 62) == ST_PREFIX);
             const int first = is_p ? __ffs((int)is_p) - 1 : 32;
-            Fn2 G = fn_identity();  // tiles (look-first, look] in ascending tile order
-            for (int l = first - 1; l >= 0; l--) G = fn_compose(G, fn_shfl(mine, l));
+            // G = tiles (look-first, look] composed in ascending tile order (= descending
+            // lane order): ordered tree reduction over the lanes below `first`
+            Fn2 G = (lane < first) ? mine : fn_identity();
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const Fn2 older = fn_shfl(G, (lane + d) & 31);
+                if (lane + d < 32) G = fn_compose(older, G);
+            }
+            G = fn_shfl(G, 0);
             H = fn_compose(G, H);
             if (is_p) {
                 Fn2 pf = fn_shfl(mine, first);
