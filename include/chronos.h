@@ -159,6 +159,38 @@ int chronos_filter_partition(chronos_ctx *ctx, const void *records, uint64_t n, 
 int chronos_submit_survivors(chronos_ctx *ctx, const void *records, const uint64_t *arrival, const uint8_t *meta,
                              uint64_t n);
 
+/* ---- allocation-free filtering ------------------------------------------------------------ */
+
+/* Largest batch chronos_filter_noalloc accepts. Its scratch is a fixed array inside the
+ * library image (about 2.3 MiB of device memory held by every GPU that loads the library,
+ * until the process exits), sized for this many events: four 64K-event micro-batches. */
+#define CHRONOS_NOALLOC_MAX_EVENTS 262144u
+
+/* No counterpart in the reference. The filter stage alone (openat noise filter, UTF-8
+ * gate, comm ignore-list, trigger bits: the same decisions chronos_submit takes), for
+ * callers that must not allocate GPU memory when they call us: a sensor thread on a
+ * fixed latency budget (cudaMalloc and cudaFree take a device-wide lock and may wait for
+ * running work), a process whose GPU memory is wholly owned by another framework's pool,
+ * or a plug-in host that forbids allocation after start-up. The call makes no cudaMalloc,
+ * cudaFree or other allocating call; the caller passes every input and output:
+ *   records        n*288 bytes, DEVICE memory, 16-byte aligned, arrival order
+ *   survivor_idx   DEVICE, room for n u32: batch-local index of each surviving event, ascending
+ *   survivor_pid   DEVICE, room for n u32: its pid
+ *   survivor_meta  DEVICE, room for n u8 : its CHRONOS_META_* bits
+ *   count          DEVICE, one u32       : number of survivors
+ * Work is queued on `stream` (a cudaStream_t, NULL for the default stream) and not waited
+ * for. n above CHRONOS_NOALLOC_MAX_EVENTS is refused with CHRONOS_E_CAPACITY; errbuf
+ * (may be NULL) receives a readable message for any failure.
+ * Every call on a GPU shares the one scratch array, which still holds the previous
+ * call's data; the parts that must start at zero are cleared at the head of each call.
+ * Two calls whose GPU work overlaps in time (different streams, no ordering between
+ * them) therefore race: keep the calls of one GPU on one stream or order them with events.
+ * The first call on each device also looks up the scratch array's device address and the
+ * launch geometry; make that first call before starting any stream capture. */
+int chronos_filter_noalloc(int device, void *stream, const void *records, uint64_t n, uint32_t *survivor_idx,
+                           uint32_t *survivor_pid, uint8_t *survivor_meta, uint32_t *count, char *errbuf,
+                           uint64_t errbuf_len);
+
 /* ---- synthetic trace (no reference counterpart: the reference ships no trace) ------ */
 
 typedef struct chronos_tracegen_cfg {

@@ -10,6 +10,7 @@ RECORD_BYTES = 288
 
 OK, E_ARG, E_CUDA, E_NOMEM, E_CAPACITY, E_STATE = 0, -1, -2, -3, -4, -5
 META_TRIG, META_CURL, META_CHMOD, META_EXEC = 1, 2, 4, 8
+NOALLOC_MAX_EVENTS = 262144
 
 
 class ChronosError(RuntimeError):
@@ -64,6 +65,8 @@ SIGNATURES = {
     "chronos_filter_partition": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64, c_uint32, c_void_p, c_void_p,
                                          c_void_p, c_uint64, c_void_p]),
     "chronos_submit_survivors": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_uint64]),
+    "chronos_filter_noalloc": (c_int, [c_int, c_void_p, c_void_p, c_uint64, c_void_p, c_void_p, c_void_p, c_void_p,
+                                       c_char_p, c_uint64]),
     "chronos_tracegen_host": (c_int, [POINTER(TracegenCfg), c_void_p, c_uint64, c_uint64, c_void_p]),
     "chronos_tracegen_device": (c_int, [c_int, POINTER(TracegenCfg), c_void_p, c_uint64, c_uint64, c_void_p]),
     "chronos_dev_alloc": (c_int, [c_int, c_uint64, POINTER(c_void_p)]),

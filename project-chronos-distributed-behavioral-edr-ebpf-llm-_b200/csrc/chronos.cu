@@ -19,6 +19,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <mutex>
 #include <new>
 #include <vector>
 
@@ -553,6 +554,29 @@ int finish_batch(chronos_ctx *c) {
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------
+// Fixed scratch for chronos_filter_noalloc (the one entry point that never allocates).
+// It lives in the library image: every GPU that loads the library holds these ~2.3 MiB
+// until the process exits. In HOST code the symbol below is only a stand-in, not a device
+// address; the real address is fetched once per device with cudaGetSymbolAddress.
+// ---------------------------------------------------------------------------------------------
+namespace noalloc {
+constexpr uint64_t MAX_EVENTS = CHRONOS_NOALLOC_MAX_EVENTS;
+constexpr uint64_t MAX_TILES = MAX_EVENTS / FILTER_TILE;
+constexpr size_t OFF_HEADER = 0;        // u32[64]: [0] filter ticket [1] scan ticket [2] survivors [3] pid OR [4] pid AND
+constexpr size_t OFF_STATUS = 256;      // look-back words of the tile-count scan
+constexpr size_t STATUS_BYTES = ((MAX_TILES + SCAN_TILE - 1) / SCAN_TILE * 8 + 255) / 256 * 256;
+constexpr size_t OFF_TILE_COUNT = OFF_STATUS + STATUS_BYTES;
+constexpr size_t TILE_COUNT_BYTES = ((MAX_TILES + 1) * 4 + 255) / 256 * 256;
+constexpr size_t OFF_SP_KEY = OFF_TILE_COUNT + TILE_COUNT_BYTES;
+constexpr size_t OFF_SP_SRC = OFF_SP_KEY + MAX_EVENTS * 4;
+constexpr size_t OFF_SP_META = OFF_SP_SRC + MAX_EVENTS * 4;
+constexpr size_t TOTAL_BYTES = OFF_SP_META + MAX_EVENTS;
+constexpr size_t CLEAR_BYTES = OFF_TILE_COUNT;  // tickets, counters and scan status must start at zero
+}  // namespace noalloc
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[noalloc::TOTAL_BYTES];
+
 // =============================================================================================
 // C ABI
 // =============================================================================================
@@ -979,6 +1003,108 @@ int chronos_flush_l2(int device) {
     static uint32_t v = 1;
     l2_flush_kernel<<<148 * 8, 256>>>(static_cast<uint4 *>(buf[device]), bytes / 16, v++);
     return cudaDeviceSynchronize() == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+
+// ---- the allocation-free entry point ------------------------------------------------------------
+int chronos_filter_noalloc(int device, void *stream, const void *records, uint64_t n, uint32_t *survivor_idx,
+                           uint32_t *survivor_pid, uint8_t *survivor_meta, uint32_t *count, char *errbuf,
+                           uint64_t errbuf_len) {
+    auto say = [&](int code, const char *fmt, ...) -> int {
+        if (errbuf && errbuf_len) {
+            va_list ap;
+            va_start(ap, fmt);
+            vsnprintf(errbuf, (size_t)errbuf_len, fmt, ap);
+            va_end(ap);
+        }
+        return code;
+    };
+    if (n > noalloc::MAX_EVENTS)
+        return say(CHRONOS_E_CAPACITY,
+                   "chronos_filter_noalloc: %llu events exceed the fixed scratch, which is sized for at most %llu "
+                   "(CHRONOS_NOALLOC_MAX_EVENTS); split the batch or use chronos_submit",
+                   (unsigned long long)n, (unsigned long long)noalloc::MAX_EVENTS);
+    if (!count || (n && (!records || !survivor_idx || !survivor_pid || !survivor_meta)))
+        return say(CHRONOS_E_ARG, "chronos_filter_noalloc: NULL argument");
+    if ((uintptr_t)records & 15) return say(CHRONOS_E_ARG, "chronos_filter_noalloc: records must be 16-byte aligned");
+    if (device < 0 || device >= 16) return say(CHRONOS_E_ARG, "chronos_filter_noalloc: device index out of range");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return say(CHRONOS_E_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+
+    // one-time set-up per device, with that device current: turn the host-side stand-in
+    // symbol into the array's real device address, and learn the launch geometry
+    static unsigned char *scratch_of[16] = {nullptr};
+    static int grid_of[16] = {0};
+    static std::mutex setup_lock;
+    unsigned char *base;
+    int grid_cap;
+    {
+        std::lock_guard<std::mutex> g(setup_lock);
+        if (!scratch_of[device]) {
+            void *p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p)
+                return say(CHRONOS_E_CUDA, "cudaGetSymbolAddress(scratch) on device %d: %s", device,
+                           cudaGetErrorString(e));
+            int sms = 0, per_sm = 0;
+            const size_t smem = filter_smem_bytes<1>();
+            if ((e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess ||
+                (e = cudaFuncSetAttribute(filter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)) !=
+                    cudaSuccess ||
+                (e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, filter_kernel<1>, FILTER_TILE, smem)) !=
+                    cudaSuccess ||
+                per_sm < 1)
+                return say(CHRONOS_E_CUDA, "filter kernel set-up on device %d: %s", device, cudaGetErrorString(e));
+            grid_of[device] = sms * per_sm;
+            scratch_of[device] = static_cast<unsigned char *>(p);
+        }
+        base = scratch_of[device];
+        grid_cap = grid_of[device];
+    }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    uint32_t *hdr = reinterpret_cast<uint32_t *>(base + noalloc::OFF_HEADER);
+    // the array keeps whatever the previous call left: tickets, counters, scan status start at zero
+    if ((e = cudaMemsetAsync(base, 0, noalloc::CLEAR_BYTES, st)) != cudaSuccess)
+        return say(CHRONOS_E_CUDA, "cudaMemsetAsync(scratch): %s", cudaGetErrorString(e));
+    if (n) {
+        FilterParams fp;
+        fp.recs = static_cast<const uint8_t *>(records);
+        fp.n = n;
+        fp.tile_begin = 0;
+        fp.tile_end = (uint32_t)((n + FILTER_TILE - 1) / FILTER_TILE);
+        fp.ticket = hdr + 0;
+        fp.tile_count = reinterpret_cast<uint32_t *>(base + noalloc::OFF_TILE_COUNT);
+        fp.sp_key = reinterpret_cast<uint32_t *>(base + noalloc::OFF_SP_KEY);
+        fp.sp_src = reinterpret_cast<uint32_t *>(base + noalloc::OFF_SP_SRC);
+        fp.sp_meta = base + noalloc::OFF_SP_META;
+        fp.out_count = hdr + 2;
+        fp.key_or = hdr + 3;
+        fp.key_and = hdr + 4;
+        filter_kernel<1><<<std::min<uint32_t>(fp.tile_end, (uint32_t)grid_cap), FILTER_TILE, filter_smem_bytes<1>(), st>>>(fp);
+        ScanParams sp;
+        sp.data = fp.tile_count;
+        sp.n = fp.tile_end;
+        sp.ticket = hdr + 1;
+        sp.status = reinterpret_cast<uint64_t *>(base + noalloc::OFF_STATUS);
+        sp.epoch = 1;  // the status words were just zeroed, tag 0 means "not written yet"
+        scan_exclusive_u32<<<std::min<uint32_t>((fp.tile_end + SCAN_TILE - 1) / SCAN_TILE, 64u), SCAN_THREADS, 0, st>>>(sp);
+        CompactParams cp;
+        cp.tile_off = fp.tile_count;
+        cp.sp_key = fp.sp_key;
+        cp.sp_src = fp.sp_src;
+        cp.sp_meta = fp.sp_meta;
+        cp.out_key = survivor_pid;
+        cp.out_src = survivor_idx;
+        cp.out_meta = survivor_meta;
+        cp.n_tiles = fp.tile_end;
+        cp.tile = FILTER_TILE;
+        cp.total = hdr + 2;
+        compact_survivors<<<std::min<uint32_t>((fp.tile_end + 255) / 256, 1024u), 256, 0, st>>>(cp);
+        if ((e = cudaGetLastError()) != cudaSuccess)
+            return say(CHRONOS_E_CUDA, "kernel launch: %s", cudaGetErrorString(e));
+    }
+    if ((e = cudaMemcpyAsync(count, hdr + 2, 4, cudaMemcpyDeviceToDevice, st)) != cudaSuccess)
+        return say(CHRONOS_E_CUDA, "cudaMemcpyAsync(count): %s", cudaGetErrorString(e));
+    return CHRONOS_OK;
 }
 
 }  // extern "C"
