@@ -1,0 +1,90 @@
+"""CPU: the C-ABI library loads without a GPU and exports exactly what include/chronos.h
+declares; host-side helpers that need no device."""
+import ctypes
+import os
+import re
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def header_functions():
+    src = open(os.path.join(ROOT, "include", "chronos.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(chronos_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    from chronos_b200 import _ffi
+
+    L = _ffi.lib()
+    names = header_functions()
+    assert len(names) >= 25
+    for n in names:
+        assert hasattr(L, n), f"{n} declared in chronos.h but not exported"
+        assert n in _ffi.SIGNATURES, f"{n} has no ctypes signature"
+    assert sorted(_ffi.SIGNATURES) == names
+
+
+def test_struct_sizes_match_the_header():
+    from chronos_b200 import _ffi, engine
+
+    assert ctypes.sizeof(_ffi.Window) == 32 == engine.WINDOW_DTYPE.itemsize
+    assert ctypes.sizeof(_ffi.Counts) == 64
+    assert ctypes.sizeof(_ffi.TracegenCfg) == 48
+    assert ctypes.sizeof(_ffi.DeviceView) == 7 * ctypes.sizeof(ctypes.c_void_p)
+
+
+def test_no_gpu_means_a_loud_failure_not_a_fallback():
+    import chronos_b200
+    from chronos_b200 import _ffi
+
+    if _ffi.lib().chronos_device_ok(0) == 0:
+        return  # running on a GPU box: nothing to check here
+    try:
+        chronos_b200.Context(device=0, max_batch_events=16)
+    except chronos_b200.ChronosError as e:
+        assert e.code == _ffi.E_CUDA
+    else:
+        raise AssertionError("Context() must fail without a B200")
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "project-chronos-distributed-behavioral-edr-ebpf-llm-_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle\b", text, flags=re.M), f
+                assert "oracle/" not in text or f.endswith(".md"), f
+
+
+def test_owner_of_is_stable_and_in_range():
+    import chronos_b200
+
+    for world in (1, 2, 4, 8):
+        owners = [chronos_b200.owner_of(p, world) for p in (0, 1, 2, 4096, 0xFFFFFFFF, 2769, 2779, 2780)]
+        assert all(0 <= o < world for o in owners)
+        assert owners == [chronos_b200.owner_of(p, world) for p in (0, 1, 2, 4096, 0xFFFFFFFF, 2769, 2779, 2780)]
+
+
+def test_tracegen_host_is_deterministic_and_sliceable():
+    from chronos_b200 import tracegen
+
+    spec = tracegen.WORKLOADS["skewed_zipf_chains"]
+    a = tracegen.generate_host(spec, first=0, n=3000)
+    b = tracegen.generate_host(spec, first=1000, n=500)
+    assert np.array_equal(a[1000:1500], b)
+    assert np.array_equal(a, tracegen.generate_host(spec, first=0, n=3000))
+    # records look like struct data_t: type field is OPEN/EXEC for almost all of them
+    types = [bytes(r[276:280]) for r in a]
+    assert sum(t in (b"OPEN", b"EXEC") for t in types) > 2900
+
+
+def test_event_str_formatter_matches_reference_format():
+    from chronos_b200.records import event_str, pack_record
+
+    assert event_str(pack_record(1, b"chmod", b"", b"OPEN")) == "[OPEN] chmod -> "
+    assert event_str(pack_record(1, b"attack_chain.sh", b"curl", b"EXEC")) == "[EXEC] attack_chain.sh -> curl"
+    assert event_str(pack_record(1, b"caf\xc3\xa9", b"/tmp/\xe2\x82\xac", b"OPEN")) == "[OPEN] café -> /tmp/€"

@@ -19,26 +19,9 @@ def ctx():
 
 
 def screenshot_trace():
-    return b"".join([
-        R(2769, b"attack_chain.sh", b"/tmp/malware.bin", b"OPEN"),
-        R(2769, b"attack_chain.sh", b"curl", b"EXEC"),
-        R(2769, b"curl", b"/etc/ld.so.cache", b"OPEN"),
-        R(2769, b"curl", b"/lib/x86_64-linux-gnu/libcurl.so.4", b"OPEN"),
-        R(2780, b"attack_chain.sh", b"/dev/null", b"OPEN"),
-        R(2780, b"attack_chain.sh", b"cat", b"EXEC"),
-        R(2780, b"cat", b"/etc/ld.so.cache", b"OPEN"),
-        R(2780, b"cat", b"/usr/lib/locale/locale-archive", b"OPEN"),
-        R(2780, b"cat", b"/tmp/malware.bin", b"OPEN"),
-        R(2779, b"attack_chain.sh", b"chmod", b"EXEC"),
-        R(2779, b"chmod", b"/lib/x86_64-linux-gnu/libc.so.6", b"OPEN"),
-        R(2779, b"chmod", b"", b"OPEN"),
-        R(2769, b"curl", b"/etc/ssl/openssl.cnf", b"OPEN"),
-        R(2769, b"curl", b"/etc/localtime", b"OPEN"),
-        R(2769, b"curl", b"/usr/share/locale/en/LC_MESSAGES/curl.mo", b"OPEN"),
-        R(2769, b"curl", b"/home/kali/.config/curlrc", b"OPEN"),
-        R(2769, b"curl", b"/home/kali/.curlrc", b"OPEN"),
-        R(2769, b"curl", b"/etc/hosts", b"OPEN"),
-    ])
+    import cases
+
+    return b"".join(cases.screenshot_trace())
 
 
 def test_screenshot_kat(ctx):
@@ -111,3 +94,35 @@ def test_tracegen_device_twin_matches_host():
         got = dev.download().reshape(-1, 288)
         dev.free()
         np.testing.assert_array_equal(got, host)
+
+
+@pytest.mark.parametrize("name", ["screenshot_kat.json", "adversarial.json", "config1_trace.json"])
+def test_golden_vectors_from_the_unmodified_reference(ctx, name):
+    """CUDA path vs what chronos_sensor.py itself produced (tests/golden, made in the build
+    container by running the unmodified script)."""
+    from test_oracle_golden import fixture_records
+
+    data, ref = fixture_records(name)
+    ctx.submit(np.frombuffer(data, dtype=np.uint8), 0)
+    res = ctx.fetch(records=True)
+    assert res.survivors.tolist() == ref["survivors"]
+    assert [[p, h] for p, h in res.histories()] == ref["windows"]
+    pm = ctx.process_memory(res.counts["n_pending"])
+    expect = {int(k): v for k, v in ref["process_memory"].items() if v}
+    assert pm == expect
+
+
+def test_random_adversarial_records(ctx):
+    """Needle fragments, separators, multi-byte and broken UTF-8, 15/16/255/256-byte fields,
+    junk after the NUL, odd type fields: differential against the oracle."""
+    import random
+
+    from test_oracle_pinning import rand_record
+
+    rng = random.Random(77)
+    eng, tr = coracle.COracle(), Trace()
+    base = 0
+    for n in (1, 33, 4000, 20_000):
+        data = b"".join(rand_record(rng) for _ in range(n))
+        compare_batch(ctx, eng, tr, data, base)
+        base += n
