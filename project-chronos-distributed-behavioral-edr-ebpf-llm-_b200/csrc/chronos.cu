@@ -231,6 +231,30 @@ __global__ void pack_windows_kernel(const uint8_t *arena, const chronos_window *
     }
 }
 
+// owner rank of every survivor + per-owner counts (shared-memory histogram per block)
+__global__ void owner_keys_kernel(const uint32_t *pid, uint32_t n, uint32_t world, uint32_t *owner, uint32_t *counts) {
+    __shared__ uint32_t h[64];
+    if (threadIdx.x < 64) h[threadIdx.x] = 0;
+    __syncthreads();
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t o = hash32(pid[i]) % world;
+        owner[i] = o;
+        atomicAdd(&h[o], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < world && h[threadIdx.x]) atomicAdd(&counts[threadIdx.x], h[threadIdx.x]);
+}
+
+// send-side metadata in destination order: arrival index and meta of survivor perm[i]
+__global__ void pack_meta_kernel(const uint32_t *perm, const uint32_t *src, const uint8_t *meta, uint32_t n,
+                                 uint64_t base, uint64_t *out_arrival, uint8_t *out_meta) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t j = perm[i];
+        out_arrival[i] = base + src[j];
+        out_meta[i] = meta[j];
+    }
+}
+
 __global__ void add_base_kernel(const uint32_t *src, uint32_t n, uint64_t base, uint64_t *out) {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = base + src[i];
 }
@@ -325,6 +349,54 @@ PassPlan plan_passes(uint32_t k_or, uint32_t k_and, uint64_t M) {
     }
     pl.n = passes;
     return pl;
+}
+
+// filter + cross-tile compaction: dense, arrival-ordered survivors (pid -> out_key,
+// batch-local index -> surv_src, META bits -> surv_meta, count -> scalars.surv_count)
+int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t *out_key) {
+    int rc;
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    const int TILE = filter_tile_size(c);
+    FilterParams fp;
+    fp.recs = d_recs;
+    fp.n = n;
+    fp.tile_begin = 0;
+    fp.tile_end = (uint32_t)((n + TILE - 1) / TILE);
+    fp.ticket = ptr<uint32_t>(c->tickets);
+    const uint64_t slots = (uint64_t)fp.tile_end * TILE;
+    if ((rc = ensure(c, c->sp_key, slots * 4))) return rc;
+    if ((rc = ensure(c, c->sp_src, slots * 4))) return rc;
+    if ((rc = ensure(c, c->sp_meta, slots))) return rc;
+    if ((rc = ensure(c, c->tile_count, ((uint64_t)fp.tile_end + 1) * 4))) return rc;
+    fp.tile_count = ptr<uint32_t>(c->tile_count);
+    fp.sp_key = ptr<uint32_t>(c->sp_key);
+    fp.sp_src = ptr<uint32_t>(c->sp_src);
+    fp.sp_meta = ptr<uint8_t>(c->sp_meta);
+    fp.out_count = &ds->surv_count;
+    fp.key_or = &ds->key_or;
+    fp.key_and = &ds->key_and;
+    CK(cudaEventRecord(c->ev_f0, c->stream));
+    if ((rc = launch_filter(c, fp))) return rc;
+    CK(cudaEventRecord(c->ev_f1, c->stream));
+    c->filter_timed = true;
+    // cross-tile prefix + dense, arrival-ordered survivor arrays
+    if ((rc = launch_scan(c, ptr<uint32_t>(c->tile_count), fp.tile_end))) return rc;
+    CompactParams cp;
+    cp.tile_off = ptr<uint32_t>(c->tile_count);
+    cp.sp_key = fp.sp_key;
+    cp.sp_src = fp.sp_src;
+    cp.sp_meta = fp.sp_meta;
+    cp.out_key = out_key;
+    cp.out_src = ptr<uint32_t>(c->surv_src);
+    cp.out_meta = ptr<uint8_t>(c->surv_meta);
+    cp.n_tiles = fp.tile_end;
+    cp.tile = (uint32_t)TILE;
+    cp.total = &ds->surv_count;
+    compact_survivors<<<(unsigned)std::min<uint32_t>((fp.tile_end + 255) / 256, (uint32_t)c->sm_count * 8), 256, 0,
+                        c->stream>>>(cp);
+    CK(cudaGetLastError());
+    c->launches += 1;
+    return CHRONOS_OK;
 }
 
 int finish_batch(chronos_ctx *c);
@@ -677,49 +749,7 @@ int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t bas
     }
     c->b_records = d_recs;
     c->b_explicit_arrival = false;
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    if (n) {
-        const int TILE = filter_tile_size(c);
-        FilterParams fp;
-        fp.recs = d_recs;
-        fp.n = n;
-        fp.tile_begin = 0;
-        fp.tile_end = (uint32_t)((n + TILE - 1) / TILE);
-        fp.ticket = ptr<uint32_t>(c->tickets);
-        const uint64_t slots = (uint64_t)fp.tile_end * TILE;
-        if ((rc = ensure(c, c->sp_key, slots * 4))) return rc;
-        if ((rc = ensure(c, c->sp_src, slots * 4))) return rc;
-        if ((rc = ensure(c, c->sp_meta, slots))) return rc;
-        if ((rc = ensure(c, c->tile_count, ((uint64_t)fp.tile_end + 1) * 4))) return rc;
-        fp.tile_count = ptr<uint32_t>(c->tile_count);
-        fp.sp_key = ptr<uint32_t>(c->sp_key);
-        fp.sp_src = ptr<uint32_t>(c->sp_src);
-        fp.sp_meta = ptr<uint8_t>(c->sp_meta);
-        fp.out_count = &ds->surv_count;
-        fp.key_or = &ds->key_or;
-        fp.key_and = &ds->key_and;
-        CK(cudaEventRecord(c->ev_f0, c->stream));
-        if ((rc = launch_filter(c, fp))) return rc;
-        CK(cudaEventRecord(c->ev_f1, c->stream));
-        c->filter_timed = true;
-        // cross-tile prefix + dense, arrival-ordered survivor arrays
-        if ((rc = launch_scan(c, ptr<uint32_t>(c->tile_count), fp.tile_end))) return rc;
-        CompactParams cp;
-        cp.tile_off = ptr<uint32_t>(c->tile_count);
-        cp.sp_key = fp.sp_key;
-        cp.sp_src = fp.sp_src;
-        cp.sp_meta = fp.sp_meta;
-        cp.out_key = ptr<uint32_t>(c->keyA) + c->b_P;
-        cp.out_src = ptr<uint32_t>(c->surv_src);
-        cp.out_meta = ptr<uint8_t>(c->surv_meta);
-        cp.n_tiles = fp.tile_end;
-        cp.tile = (uint32_t)TILE;
-        cp.total = &ds->surv_count;
-        compact_survivors<<<(unsigned)std::min<uint32_t>((fp.tile_end + 255) / 256, (uint32_t)c->sm_count * 8), 256, 0,
-                            c->stream>>>(cp);
-        CK(cudaGetLastError());
-        c->launches += 1;
-    }
+    if (n && (rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA) + c->b_P))) return rc;
     if ((rc = run_window_stage(c))) return rc;
     c->phase = chronos_ctx::SUBMITTED;
     return CHRONOS_OK;
@@ -934,9 +964,101 @@ void *chronos_stream(chronos_ctx *c) { return c ? (void *)c->stream : nullptr; }
 
 uint32_t chronos_owner_of(uint32_t pid, uint32_t world) { return world ? hash32(pid) % world : 0; }
 
-int chronos_filter_partition(chronos_ctx *c, const void *, uint64_t, uint64_t, uint32_t, void *, uint64_t *, uint8_t *,
-                             uint64_t, uint64_t *) {
-    return fail(c, CHRONOS_E_STATE, "chronos_filter_partition: not built yet");
+int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, uint64_t base_arrival_index,
+                             uint32_t world, void *send_records, uint64_t *send_arrival, uint8_t *send_meta,
+                             uint64_t cap, uint64_t *counts_host) {
+    if (!c || !counts_host || world == 0 || world > 64) return c ? fail(c, CHRONOS_E_ARG, "bad argument") : CHRONOS_E_ARG;
+    if (n && (!records || !send_records || !send_arrival || !send_meta)) return fail(c, CHRONOS_E_ARG, "NULL argument");
+    CK(cudaSetDevice(c->device));
+    if (c->phase == chronos_ctx::SUBMITTED) {
+        int rc0 = finish_batch(c);
+        if (rc0) return rc0;
+    }
+    if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
+                                      (unsigned long long)n, (unsigned long long)c->max_batch);
+    for (uint32_t d = 0; d < world; d++) counts_host[d] = 0;
+    if (!n) return CHRONOS_OK;
+    int rc;
+    const uint8_t *d_recs;
+    if (is_device_pointer(records)) {
+        if ((uintptr_t)records & 15) return fail(c, CHRONOS_E_ARG, "device records pointer must be 16-byte aligned");
+        d_recs = static_cast<const uint8_t *>(records);
+    } else {
+        if ((rc = ensure(c, c->d_batch, n * CH_REC_BYTES))) return rc;
+        CK(cudaMemcpyAsync(c->d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, c->stream));
+        d_recs = ptr<uint8_t>(c->d_batch);
+    }
+    // scratch only: the per-PID state of this context is not touched by stage 1
+    c->launches = 0;
+    c->scan_slot = 0;
+    if ((rc = ensure(c, c->keyA, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->keyB, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->valA, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->valB, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    CK(cudaEventRecord(c->ev_start, c->stream));
+    CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
+    init_scalars_kernel<<<1, 1, 0, c->stream>>>(ds);
+    c->launches++;
+    if ((rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA)))) return rc;
+    CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    const uint64_t S = c->h_scalars->surv_count;
+    if (S > cap) return fail(c, CHRONOS_E_CAPACITY, "%llu survivors do not fit the send buffers (%llu)",
+                             (unsigned long long)S, (unsigned long long)cap);
+    if (S) {
+        // stable counting sort by owner rank = one radix pass over the owner keys
+        uint32_t *owner = ptr<uint32_t>(c->valB);
+        uint32_t *ocount = &ds->pad[0];  // world <= 10 words live here; larger worlds use the tickets tail
+        if (world > 10) ocount = ptr<uint32_t>(c->tickets);
+        CK(cudaMemsetAsync(ocount, 0, world * 4, c->stream));
+        const unsigned blocks = (unsigned)std::min<uint64_t>((S + 255) / 256, 2048);
+        owner_keys_kernel<<<blocks, 256, 0, c->stream>>>(ptr<uint32_t>(c->keyA), (uint32_t)S, world, owner, ocount);
+        uint32_t tile_keys = 4096;
+        while ((S + tile_keys - 1) / tile_keys > 1024) tile_keys *= 2;
+        const uint32_t n_tiles = (uint32_t)((S + tile_keys - 1) / tile_keys);
+        if ((rc = ensure(c, c->radix_table, (size_t)RADIX_BINS * n_tiles * 4))) return rc;
+        RadixParams rp;
+        rp.keys_in = owner;
+        rp.vals_in = nullptr;
+        rp.keys_out = ptr<uint32_t>(c->keyB);
+        rp.vals_out = ptr<uint32_t>(c->valA);  // permutation: survivors in (owner, arrival) order
+        rp.table = ptr<uint32_t>(c->radix_table);
+        rp.n = (uint32_t)S;
+        rp.tile_keys = tile_keys;
+        rp.n_tiles = n_tiles;
+        rp.shift = 0;
+        rp.mask = 0xFFu;
+        radix_hist<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
+        if ((rc = launch_scan(c, rp.table, (uint64_t)RADIX_BINS * n_tiles))) return rc;
+        radix_scatter<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
+        GatherParams g;
+        g.sval = rp.vals_out;
+        g.M = (uint32_t)S;
+        g.P = 0;
+        g.surv_src = ptr<uint32_t>(c->surv_src);
+        g.batch = d_recs;
+        g.pend_slot = nullptr;
+        g.prev_arena = nullptr;
+        g.arena = static_cast<uint8_t *>(send_records);
+        gather_records<<<(unsigned)std::min<uint64_t>((S + 127) / 128, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(g);
+        pack_meta_kernel<<<blocks, 256, 0, c->stream>>>(rp.vals_out, ptr<uint32_t>(c->surv_src),
+                                                        ptr<uint8_t>(c->surv_meta), (uint32_t)S, base_arrival_index,
+                                                        send_arrival, send_meta);
+        CK(cudaGetLastError());
+        c->launches += 5;
+        uint32_t hc[64];
+        CK(cudaMemcpyAsync(hc, ocount, world * 4, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaEventRecord(c->ev_end, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        for (uint32_t d = 0; d < world; d++) counts_host[d] = hc[d];
+        if (world > 10) CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
+    }
+    cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
+    cudaGetLastError();
+    return CHRONOS_OK;
 }
 
 // ---- trace generator ------------------------------------------------------------------------

@@ -1,0 +1,143 @@
+"""PID-hash sharding of the hot path over the GPUs of one box.
+
+Each rank filters a contiguous slice of the arrival-ordered batch, survivors are
+repartitioned with ONE all-to-all so that every PID's events meet on
+`owner = hash32(pid) % world`, and the window logic runs there against that rank's
+resident per-PID state (process_memory is independent per PID: chronos_sensor.py:105,
+:138, :142, :157). Receivers concatenate what they get in source-rank order; since the
+slices are contiguous and ordered, that is global arrival order, which is all the
+reference's semantics need (there is no timestamp in struct data_t, :18-23).
+
+`exchange()` is plain torch.distributed host logic and works on any backend/device (the
+CPU tests run it over gloo); `ShardedRunner` binds it to the CUDA stages of the C ABI.
+"""
+import ctypes
+from ctypes import c_void_p
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _ffi
+from .engine import Context
+from .records import RECORD_BYTES
+
+
+def hash32_np(x):
+    """Vectorised twin of chronos_owner_of's hash (csrc/common.cuh hash32)."""
+    x = np.asarray(x, dtype=np.uint64) & np.uint64(0xFFFFFFFF)
+    m = np.uint64(0xFFFFFFFF)
+    x ^= x >> np.uint64(16)
+    x = (x * np.uint64(0x7FEB352D)) & m
+    x ^= x >> np.uint64(15)
+    x = (x * np.uint64(0x846CA68B)) & m
+    x ^= x >> np.uint64(16)
+    return x.astype(np.uint32)
+
+
+def owner_of_np(pids, world):
+    return (hash32_np(pids) % np.uint32(world)).astype(np.int64)
+
+
+def exchange(send_records, send_arrival, send_meta, send_counts, recv_records, recv_arrival, recv_meta, group=None):
+    """One all-to-all-v of packed survivors.
+
+    send_*: tensors holding, destination after destination, `send_counts[d]` entries for
+    rank d (records as uint8 rows of 288 bytes). recv_* are filled in source-rank order.
+    Returns (n_received, recv_counts). Counts travel first, then the three payloads."""
+    world = dist.get_world_size(group)
+    dev = send_records.device
+    sc = torch.as_tensor(np.asarray(send_counts, dtype=np.int64), device=dev)
+    rc = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(rc, sc, group=group)
+    recv_counts = rc.cpu().numpy().astype(np.int64)
+    send_counts = np.asarray(send_counts, dtype=np.int64)
+    n_send, n_recv = int(send_counts.sum()), int(recv_counts.sum())
+    if n_recv > recv_arrival.numel():
+        raise _ffi.ChronosError(_ffi.E_CAPACITY, f"{n_recv} received survivors exceed the receive buffers")
+    ss, rs = send_counts.tolist(), recv_counts.tolist()
+    dist.all_to_all_single(recv_records.view(-1)[: n_recv * RECORD_BYTES], send_records.view(-1)[: n_send * RECORD_BYTES],
+                           [x * RECORD_BYTES for x in rs], [x * RECORD_BYTES for x in ss], group=group)
+    dist.all_to_all_single(recv_arrival[:n_recv], send_arrival[:n_send], rs, ss, group=group)
+    dist.all_to_all_single(recv_meta[:n_recv], send_meta[:n_send], rs, ss, group=group)
+    return n_recv, recv_counts
+
+
+class ShardedRunner:
+    """One rank of the sharded pipeline: CUDA stage 1 -> all-to-all (NCCL) -> CUDA stage 2."""
+
+    def __init__(self, rec_ptr, n, first, device, rank, world, cap=None):
+        self.rec_ptr, self.n, self.first = int(rec_ptr), int(n), int(first)
+        self.device, self.rank, self.world = int(device), int(rank), int(world)
+        self.cap = int(cap or max(n // 2, 1024))  # survivors per rank, sent or received
+        self.ctx = Context(device=self.device, max_batch_events=max(self.n, self.cap))
+        dev = torch.device("cuda", self.device)
+        self.send_records = torch.empty(self.cap * RECORD_BYTES, dtype=torch.uint8, device=dev)
+        self.send_arrival = torch.empty(self.cap, dtype=torch.int64, device=dev)
+        self.send_meta = torch.empty(self.cap, dtype=torch.uint8, device=dev)
+        self.recv_records = torch.empty(self.cap * RECORD_BYTES, dtype=torch.uint8, device=dev)
+        self.recv_arrival = torch.empty(self.cap, dtype=torch.int64, device=dev)
+        self.recv_meta = torch.empty(self.cap, dtype=torch.uint8, device=dev)
+        self._counts = (ctypes.c_uint64 * self.world)()
+        self._L = _ffi.lib()
+
+    def stream_ptr(self):
+        return int(self._L.chronos_stream(self.ctx._h))
+
+    def filter_partition(self, rec_ptr, n, base):
+        rc = self._L.chronos_filter_partition(self.ctx._h, c_void_p(int(rec_ptr)), int(n), int(base), self.world,
+                                              c_void_p(self.send_records.data_ptr()),
+                                              c_void_p(self.send_arrival.data_ptr()),
+                                              c_void_p(self.send_meta.data_ptr()), self.cap, self._counts)
+        self.ctx._check(rc)
+        return np.array(list(self._counts), dtype=np.int64)
+
+    def step(self, reset=True):
+        if reset:
+            self.ctx.reset()  # benchmark steps repeat the same batch on a fresh process_memory
+        send_counts = self.filter_partition(self.rec_ptr, self.n, self.first)  # waits for stage 1
+        launches = self.ctx.last_launches()
+        n_recv, _ = exchange(self.send_records, self.send_arrival, self.send_meta, send_counts, self.recv_records,
+                             self.recv_arrival, self.recv_meta)
+        torch.cuda.current_stream().synchronize()  # NCCL ran on torch's stream; stage 2 runs on the library's
+        self.ctx.submit_survivors_ptr(self.recv_records.data_ptr(), self.recv_arrival.data_ptr(),
+                                      self.recv_meta.data_ptr(), n_recv)
+        c = self.ctx.fetch_counts()
+        t, f = self.ctx.last_timing()
+        c.update(gpu_ms=t, filter_ms=f, launches=launches + self.ctx.last_launches(), n_sent=int(send_counts.sum()),
+                 n_received=n_recv)
+        return c
+
+    def e2e(self, steps, barrier, dist_mod):
+        """Same step, but the slice starts in pinned HOST memory (H2D inside the timed region)
+        and the windows + their records are read back to the host."""
+        import time
+
+        L = self._L
+        n = self.n
+        p = c_void_p()
+        assert L.chronos_host_alloc_pinned(n * RECORD_BYTES, ctypes.byref(p)) == 0
+        assert L.chronos_memcpy_d2h(self.device, p, c_void_p(self.rec_ptr), n * RECORD_BYTES) == 0
+        dev_ptr, self.rec_ptr = self.rec_ptr, p.value
+        c = self.step()
+        W, S = c["n_windows"], c["n_survivors"]
+        win = np.zeros(max(W, 1) * 32, dtype=np.uint8)
+        rec = np.zeros((max(S, 1), RECORD_BYTES), dtype=np.uint8)
+        barrier()
+        t0 = time.perf_counter()
+        d2h = 0
+        for _ in range(steps):
+            c = self.step()
+            W = c["n_windows"]
+            self.ctx._check(L.chronos_copy_windows(self.ctx._h, win.ctypes.data, max(W, 1)))
+            self.ctx._check(L.chronos_copy_window_records(self.ctx._h, rec.ctypes.data, max(S, 1)))
+            d2h = W * 32 + int(np.frombuffer(win[:W * 32], dtype="<u4").reshape(-1, 8)[:, 4].sum()) * RECORD_BYTES
+        barrier()
+        dt = (time.perf_counter() - t0) / steps
+        self.rec_ptr = dev_ptr
+        L.chronos_host_free_pinned(p)
+        total = n * self.world
+        return {"value": total / dt, "unit": "events/s", "h2d_bytes_per_step": n * RECORD_BYTES * self.world,
+                "d2h_bytes_per_step": int(d2h) * self.world, "ms_per_step": 1e3 * dt, "steps": steps,
+                "path": "per rank: chronos_filter_partition(pinned host slice) -> all_to_all -> "
+                        "chronos_submit_survivors -> copy_windows/window_records"}
