@@ -47,54 +47,61 @@ def measured_peak_gbs():
 # clocks sampling during the timed region
 # ------------------------------------------------------------------------------------------
 class ClockSampler:
-    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
-         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    """SM clock + throttle reasons sampled every few ms DURING the timed region (NVML in a
+    thread; the timed region of a default run is only tens of milliseconds long, far too
+    short for an `nvidia-smi -lms` loop to land a sample in it)."""
 
-    def __init__(self, index):
-        self.index = index
-        self.rows = []
+    def __init__(self, index, period_s=0.002):
+        self.index, self.period = index, period_s
+        self.sm, self.reasons = [], set()
+        self.sm_max = None
         self._stop = threading.Event()
         self._t = None
-        self._proc = None
+        self._h = None
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = float(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self._h = None
+
+    def _sample(self):
+        nv = self._nv
+        try:
+            self.sm.append(float(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+            get = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+            r = get(self._h)
+            for bit, name in ((nv.nvmlClocksEventReasonHwSlowdown, "hw_slowdown"),
+                              (nv.nvmlClocksEventReasonHwThermalSlowdown, "hw_thermal_slowdown"),
+                              (nv.nvmlClocksEventReasonSwThermalSlowdown, "sw_thermal_slowdown"),
+                              (nv.nvmlClocksEventReasonSwPowerCap, "sw_power_cap")):
+                if r & bit:
+                    self.reasons.add(name)
+        except Exception:
+            pass
+
+    def _run(self):
+        while not self._stop.is_set():
+            self._sample()
+            time.sleep(self.period)
 
     def start(self):
-        try:
-            self._proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
-                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except Exception:
-            self._proc = None
+        if self._h is None:
             return
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
 
-    def _run(self):
-        for line in self._proc.stdout:
-            if self._stop.is_set():
-                break
-            self.rows.append([x.strip() for x in line.split(",")])
-
     def stop(self):
         self._stop.set()
-        if self._proc is not None:
-            self._proc.terminate()
-            try:
-                self._proc.wait(timeout=2)
-            except Exception:
-                self._proc.kill()
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
-            try:
-                sm.append(float(r[0]))
-                mx.append(float(r[1]))
-                for k, nm in enumerate(names):
-                    if r[2 + k].lower().startswith("active"):
-                        reasons.add(nm)
-            except Exception:
-                pass
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self._t is not None:
+            self._t.join(timeout=1)
+        if self._h is not None and not self.sm:
+            self._sample()
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(self.sm), "source": "nvml, sampled inside the timed region"}
 
 
 # ------------------------------------------------------------------------------------------
@@ -324,10 +331,11 @@ def run_gpu_arm(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "kernel": "filter_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": TRAFFIC_NCU, "peak_source": peak_src,
                          "kernel_ms": f_ms, "algorithmic_bytes_per_launch": alg_bytes,
-                         "pipeline": {"algorithmic_bytes": pipe_bytes, "gpu_ms": float(np.mean(step_ms)),
-                                      "achieved": pipe_bytes / (float(np.mean(step_ms)) / 1e3) / 1e9,
-                                      "frac": pipe_bytes / (float(np.mean(step_ms)) / 1e3) / 1e9 / peak,
-                                      "frac_of_8TBs_nominal": pipe_bytes / (float(np.mean(step_ms)) / 1e3) / 1e9 / 8000.0}},
+                         "pipeline": {"algorithmic_bytes_per_gpu": pipe_bytes, "ms_per_step": ms_per_step,
+                                      "achieved": pipe_bytes / (ms_per_step / 1e3) / 1e9,
+                                      "frac": pipe_bytes / (ms_per_step / 1e3) / 1e9 / peak,
+                                      "frac_of_8TBs_nominal": pipe_bytes / (ms_per_step / 1e3) / 1e9 / 8000.0,
+                                      "library_event_ms": float(np.mean(step_ms))}},
             "cpu_baseline": cpu,
             "e2e": e2e,
             "gpu_launches": launches,

@@ -617,7 +617,7 @@ int finish_batch(chronos_ctx *c) {
     c->n_pending = c->b_M ? c->h_scalars->n_pending : 0;
     cudaEventElapsedTime(&c->t_total, c->ev_start, c->ev_end);
     cudaEventElapsedTime(&c->t_filter, c->ev_start, c->ev_filter);
-    c->t_filter_kernel = 0.f;
+    // (a stage-2-only batch keeps the filter time measured by chronos_filter_partition)
     if (c->filter_timed) cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
     cudaGetLastError();
     c->phase = chronos_ctx::FETCHED;

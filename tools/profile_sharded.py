@@ -1,0 +1,35 @@
+#!/usr/bin/env python
+"""Phase timing of one rank of the sharded step (run under torchrun, 2+ GPUs)."""
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+
+import chronos_b200  # noqa
+from chronos_b200 import sharded, tracegen
+
+rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(lr)
+dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 12_500_000
+dev = tracegen.generate_device(tracegen.WORKLOADS["sharded_100m_1m"], device=lr, first=rank * n, n=n)
+r = sharded.ShardedRunner(dev.ptr, n, rank * n, lr, rank, world)
+for it in range(6):
+    dist.barrier(); torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    r.ctx.reset()
+    sc = r.filter_partition(r.rec_ptr, r.n, r.first)
+    t1 = time.perf_counter()
+    n_recv, _ = sharded.exchange(r.send_records, r.send_arrival, r.send_meta, sc, r.recv_records, r.recv_arrival, r.recv_meta)
+    torch.cuda.current_stream().synchronize()
+    t2 = time.perf_counter()
+    r.ctx.submit_survivors_ptr(r.recv_records.data_ptr(), r.recv_arrival.data_ptr(), r.recv_meta.data_ptr(), n_recv)
+    c = r.ctx.fetch_counts()
+    t3 = time.perf_counter()
+    if rank == 0:
+        print(f"it{it}: stage1 {1e3*(t1-t0):.3f} ms  exchange {1e3*(t2-t1):.3f} ms  stage2 {1e3*(t3-t2):.3f} ms  sent {int(sc.sum())} recv {n_recv} filter_ms {r.ctx.last_timing()[1]:.3f}", flush=True)
+dist.destroy_process_group()
