@@ -391,12 +391,15 @@ class SingleGpuRunner:
         barrier()
         t0 = time.perf_counter()
         for _ in range(steps):
+            ts = time.perf_counter()
             self.ctx.reset()
             self.ctx.submit_ptr(host.ptr, n, 0)          # H2D of the whole batch inside
             c = self.ctx.fetch_counts()
             assert L.chronos_copy_survivors(h, ctypes.c_void_p(r_idx.ptr), ctypes.c_void_p(r_meta.ptr), S) == 0
             assert L.chronos_copy_windows(h, ctypes.c_void_p(r_win.ptr), W) == 0
             assert L.chronos_copy_window_records(h, ctypes.c_void_p(r_rec.ptr), S) == 0
+            if os.environ.get("CHRONOS_BENCH_DEBUG"):
+                print(f"e2e step {1e3 * (time.perf_counter() - ts):.2f} ms", file=sys.stderr, flush=True)
         barrier()
         dt = (time.perf_counter() - t0) / steps
         win = np.frombuffer(r_win.array[:W * 32], dtype=self.mod.WINDOW_DTYPE)

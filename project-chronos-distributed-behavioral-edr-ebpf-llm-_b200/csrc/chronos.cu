@@ -29,6 +29,7 @@
 #include "sort.cuh"
 #include "tracegen.cuh"
 #include "window.cuh"
+#include "chain.cuh"
 
 using namespace chronos;
 
@@ -67,6 +68,11 @@ struct chronos_ctx {
     // entry arrays (capacity in entries = ecap)
     DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, flush, wi_of_entry, wsorted, windows, radix_table;
     DevBuf sp_key, sp_src, sp_meta, tile_count;  // filter's tile-local compaction
+    // kill-chain labeller + persistent per-PID table (chain.cuh)
+    DevBuf pid_tab, pt_count, match, mcnt, match_entry, chain_pid, chain_idx;
+    uint32_t pt_cap = 0;
+    uint32_t *h_pt_count = nullptr;  // pinned
+    uint64_t n_pids_seen = 0, b_chains = 0;
     DevBuf surv_arrival;  // only for chronos_submit_survivors
     // double-buffered persistent state
     DevBuf arena[2];
@@ -401,6 +407,31 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
 
 int finish_batch(chronos_ctx *c);
 
+// The per-PID table must stay at most half full: room for every PID seen so far plus one new
+// PID per grouped entry of this batch.
+int ensure_pid_table(chronos_ctx *c, uint64_t M) {
+    const uint64_t need = 2 * (c->n_pids_seen + M) + 64;
+    if (c->pt_cap >= need) return CHRONOS_OK;
+    uint64_t cap = 1024;
+    while (cap < need) cap <<= 1;
+    if (cap > (1ull << 31)) return fail(c, CHRONOS_E_CAPACITY, "per-PID table would need %llu slots", (unsigned long long)cap);
+    DevBuf fresh;
+    int rc;
+    if ((rc = ensure(c, fresh, cap * 8))) return rc;
+    CK(cudaMemsetAsync(fresh.p, 0, cap * 8, c->stream));
+    if (c->pt_cap && c->n_pids_seen) {
+        pt_rehash_kernel<<<(unsigned)std::min<uint64_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
+            ptr<uint64_t>(c->pid_tab), c->pt_cap, static_cast<uint64_t *>(fresh.p), (uint32_t)cap - 1);
+        CK(cudaGetLastError());
+        c->launches++;
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    release(c->pid_tab);
+    c->pid_tab = fresh;
+    c->pt_cap = (uint32_t)cap;
+    return CHRONOS_OK;
+}
+
 // Everything after the survivors are known on the device (keyA[P..P+S), surv_src, surv_meta).
 int run_window_stage(chronos_ctx *c) {
     const uint64_t P = c->b_P;
@@ -419,6 +450,7 @@ int run_window_stage(chronos_ctx *c) {
     if (M == 0) {
         c->h_scalars->n_windows = 0;
         c->h_scalars->n_pending = 0;
+        c->h_scalars->n_chains = 0;
         c->pend_cap[cur] = 0;
         CK(cudaEventRecord(c->ev_end, c->stream));
         return CHRONOS_OK;
@@ -435,6 +467,12 @@ int run_window_stage(chronos_ctx *c) {
     if ((rc = ensure(c, c->flush, M))) return rc;
     if ((rc = ensure(c, c->wsorted, (S / 2 + 1) * sizeof(WinSorted)))) return rc;
     if ((rc = ensure(c, c->windows, (S / 2 + 1) * sizeof(chronos_window)))) return rc;
+    if ((rc = ensure(c, c->match, M))) return rc;
+    if ((rc = ensure(c, c->mcnt, M * 4))) return rc;
+    if ((rc = ensure(c, c->match_entry, S + 1))) return rc;
+    if ((rc = ensure(c, c->chain_pid, (S + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->chain_idx, (S + 1) * 8))) return rc;
+    if ((rc = ensure_pid_table(c, M))) return rc;
 
     // ---- stable sort by pid -----------------------------------------------------------
     PassPlan pl = plan_passes(c->h_scalars->key_or, c->h_scalars->key_and, M);
@@ -529,6 +567,8 @@ int run_window_stage(chronos_ctx *c) {
         w.npend_meta = ptr<uint8_t>(c->pend_meta[cur]);
         w.n_pending = &ds->n_pending;
         w.windows = ptr<chronos_window>(c->windows);
+        w.match = ptr<uint8_t>(c->match);
+        w.mcnt = ptr<uint32_t>(c->mcnt);
         const uint32_t tiles_m = (uint32_t)((M + WIN_TILE - 1) / WIN_TILE);
         const uint32_t tiles_s = (uint32_t)((S + WIN_TILE - 1) / WIN_TILE);
         uint64_t *st = ptr<uint64_t>(c->status) + c->b_n / 64 + 2;  // behind the filter's tile words (>= n/64)
@@ -537,20 +577,52 @@ int run_window_stage(chronos_ctx *c) {
         w.ticket = tk + 60;
         w.status = st;
         window_forward<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
+        {
+            ChainParams cp;
+            cp.skey = w.skey;
+            cp.sval = w.sval;
+            cp.M = w.M;
+            cp.P = w.P;
+            cp.surv_meta = w.surv_meta;
+            cp.pend_meta = w.pend_meta;
+            cp.pid_tab = ptr<uint64_t>(c->pid_tab);
+            cp.pid_mask = c->pt_cap - 1;
+            cp.pid_count = ptr<uint32_t>(c->pt_count);
+            cp.match = ptr<uint8_t>(c->match);
+            cp.match_entry = ptr<uint8_t>(c->match_entry);
+            cp.mcnt = ptr<uint32_t>(c->mcnt);
+            cp.ticket = tk + 58;
+            cp.status = st + 5 * (size_t)tiles_m;
+            chain_scan<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(cp);
+        }
         w.ticket = tk + 61;
         w.status = st + 2 * (size_t)tiles_m;
         window_reverse<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
-        c->launches += 2;
+        c->launches += 3;
         if (S > 0) {
             w.ticket = tk + 62;
             w.status = st + 4 * (size_t)tiles_m;
             window_order<<<std::min(tiles_s, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
-            c->launches++;
+            ChainOrderParams co;
+            co.match_entry = ptr<uint8_t>(c->match_entry);
+            co.batch = c->b_records;
+            co.surv_src = w.surv_src;
+            co.surv_arrival = w.surv_arrival;
+            co.base_arrival = w.base_arrival;
+            co.S = (uint32_t)S;
+            co.chain_pid = ptr<uint32_t>(c->chain_pid);
+            co.chain_idx = ptr<uint64_t>(c->chain_idx);
+            co.n_chains = &ds->n_chains;
+            co.ticket = tk + 57;
+            co.status = st + 8 * (size_t)tiles_m;
+            chain_order<<<std::min(tiles_s, cap_blocks), WIN_THREADS, 0, c->stream>>>(co);
+            c->launches += 2;
         }
         CK(cudaGetLastError());
     }
     CK(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
     CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(c->h_pt_count, c->pt_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaEventRecord(c->ev_end, c->stream));
     return CHRONOS_OK;
 }
@@ -559,7 +631,7 @@ int run_window_stage(chronos_ctx *c) {
 size_t status_words(uint64_t n, uint64_t P) {
     const uint64_t M = n + P;
     const uint64_t tiles_m = (M + WIN_TILE - 1) / WIN_TILE;
-    return (size_t)(n / 64 + 2 + 5 * tiles_m + 64);
+    return (size_t)(n / 64 + 2 + 9 * tiles_m + 64);
 }
 
 int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
@@ -615,6 +687,8 @@ int finish_batch(chronos_ctx *c) {
     CK(cudaStreamSynchronize(c->stream));
     c->b_W = c->b_M ? c->h_scalars->n_windows : 0;
     c->n_pending = c->b_M ? c->h_scalars->n_pending : 0;
+    c->b_chains = c->b_M ? c->h_scalars->n_chains : 0;
+    c->n_pids_seen = *c->h_pt_count;
     cudaEventElapsedTime(&c->t_total, c->ev_start, c->ev_end);
     cudaEventElapsedTime(&c->t_filter, c->ev_start, c->ev_filter);
     // (a stage-2-only batch keeps the filter time measured by chronos_filter_partition)
@@ -692,9 +766,13 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
         CK(cudaEventCreate(&c->ev_f0));
         CK(cudaEventCreate(&c->ev_f1));
         CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_scalars), sizeof(DeviceScalars)));
+        CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_pt_count), 64));
+        *c->h_pt_count = 0;
         int rc;
         if ((rc = ensure(c, c->tickets, N_TICKETS * 4))) return rc;
         if ((rc = ensure(c, c->scalars, sizeof(DeviceScalars)))) return rc;
+        if ((rc = ensure(c, c->pt_count, 256))) return rc;
+        CK(cudaMemsetAsync(c->pt_count.p, 0, 256, c->stream));
         return CHRONOS_OK;
     };
     int rc = boot();
@@ -711,12 +789,13 @@ int chronos_destroy(chronos_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->flush,
-                     &c->wi_of_entry, &c->wsorted, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+                     &c->wi_of_entry, &c->wsorted, &c->pid_tab, &c->pt_count, &c->match, &c->mcnt, &c->match_entry, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
                      &c->tickets, &c->scalars, &c->scan_status, &c->pack, &c->pack_off};
     for (DevBuf *b : all) release(*b);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
+    if (c->h_pt_count) cudaFreeHost(c->h_pt_count);
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_filter) cudaEventDestroy(c->ev_filter);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -797,8 +876,8 @@ int chronos_fetch(chronos_ctx *c, chronos_counts *out) {
     out->n_windows = c->b_W;
     out->n_arena = c->b_M;
     out->n_pending = c->n_pending;
-    out->n_chains = 0;
-    out->n_pids_seen = 0;
+    out->n_chains = c->b_chains;
+    out->n_pids_seen = c->n_pids_seen;
     return CHRONOS_OK;
 }
 
@@ -882,9 +961,13 @@ int chronos_copy_window_records(chronos_ctx *c, void *dst, uint64_t cap_records)
 int chronos_copy_chains(chronos_ctx *c, uint32_t *pid, uint64_t *global_idx, uint64_t cap) {
     int rc = need_fetched(c);
     if (rc) return rc;
-    (void)pid;
-    (void)global_idx;
-    (void)cap;
+    const uint64_t K = c->b_chains;
+    if (cap < K) return fail(c, CHRONOS_E_ARG, "chain buffer too small (%llu < %llu)", (unsigned long long)cap,
+                             (unsigned long long)K);
+    if (!K) return CHRONOS_OK;
+    if (pid) CK(cudaMemcpyAsync(pid, c->chain_pid.p, K * 4, cudaMemcpyDeviceToHost, c->stream));
+    if (global_idx) CK(cudaMemcpyAsync(global_idx, c->chain_idx.p, K * 8, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
     return CHRONOS_OK;
 }
 
@@ -916,8 +999,22 @@ int chronos_state(chronos_ctx *c, uint32_t *pid, uint64_t *global_idx, void *rec
 
 int chronos_state_pids(chronos_ctx *c, uint32_t *pid, uint64_t cap) {
     if (!c) return CHRONOS_E_ARG;
-    (void)pid;
-    (void)cap;
+    if (c->phase == chronos_ctx::SUBMITTED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    CK(cudaSetDevice(c->device));
+    const uint64_t K = c->n_pids_seen;
+    if (cap < K || (K && !pid)) return fail(c, CHRONOS_E_ARG, "pid buffer too small (%llu < %llu)",
+                                            (unsigned long long)cap, (unsigned long long)K);
+    if (!K) return CHRONOS_OK;
+    int rc;
+    if ((rc = ensure(c, c->pack, K * 4 + 256))) return rc;
+    if ((rc = ensure(c, c->pack_off, 256))) return rc;
+    uint32_t *cnt = ptr<uint32_t>(c->pack_off);
+    CK(cudaMemsetAsync(cnt, 0, 4, c->stream));
+    pt_dump_kernel<<<(unsigned)std::min<uint32_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
+        ptr<uint64_t>(c->pid_tab), c->pt_cap, ptr<uint32_t>(c->pack), cnt);
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(pid, c->pack.p, K * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
     return CHRONOS_OK;
 }
 
@@ -950,6 +1047,10 @@ int chronos_reset(chronos_ctx *c) {
     CK(cudaSetDevice(c->device));
     CK(cudaStreamSynchronize(c->stream));
     c->n_pending = 0;
+    c->n_pids_seen = 0;
+    *c->h_pt_count = 0;
+    if (c->pt_cap) CK(cudaMemsetAsync(c->pid_tab.p, 0, (size_t)c->pt_cap * 8, c->stream));
+    CK(cudaMemsetAsync(c->pt_count.p, 0, 256, c->stream));
     c->phase = chronos_ctx::IDLE;
     return CHRONOS_OK;
 }

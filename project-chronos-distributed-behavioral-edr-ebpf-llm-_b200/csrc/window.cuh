@@ -184,6 +184,9 @@ struct WinParams {
     uint64_t *npend_arrival;
     uint8_t *npend_meta;
     uint32_t *n_pending;
+    // chain labeller outputs consumed here (chain.cuh); nullptr when not run
+    const uint8_t *match;           // M: this batch's event at pos completed a curl->chmod->EXEC chain
+    const uint32_t *mcnt;           // M: inclusive count of chain-complete events up to pos
     // ordering outputs
     chronos_window *windows;        // n_windows, ascending trigger arrival
     // scheduling
@@ -336,7 +339,9 @@ __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p)
                 p.npend_key[slot] = key[k];
                 p.npend_slot[slot] = pos;
                 p.npend_arrival[slot] = win_arrival_of(p, e);
-                p.npend_meta[slot] = (uint8_t)(win_meta_of(p, e) & ~META_TRIG);
+                uint8_t pm = (uint8_t)(win_meta_of(p, e) & ~META_TRIG);
+                if (p.match && p.match[pos]) pm |= (uint8_t)META_CHAIN;
+                p.npend_meta[slot] = pm;
             }
         }
     }
@@ -395,6 +400,10 @@ __global__ void __launch_bounds__(WIN_THREADS) window_order(const WinParams p) {
             o.len = d.len;
             o.pid = d.pid;
             o.flags = 0;
+            if (p.mcnt) {
+                const uint32_t hi = p.mcnt[d.start + d.len - 1], lo = d.start ? p.mcnt[d.start - 1] : 0u;
+                o.flags = hi != lo ? 1u : 0u;
+            }
             o.reserved = 0;
             p.windows[r++] = o;
         }

@@ -16,7 +16,8 @@ class BatchResult:
     """What one submitted batch produced. `windows` is sorted by trigger arrival index,
     the order the reference calls analyze_sequence in (chronos_sensor.py:143-147)."""
 
-    def __init__(self, counts, survivors, survivor_meta, windows, window_records, gpu_ms, filter_ms, launches):
+    def __init__(self, counts, survivors, survivor_meta, windows, window_records, gpu_ms, filter_ms, launches,
+                 chain_pid=None, chain_idx=None):
         self.counts = counts
         self.survivors = survivors            # uint64 global arrival indices, ascending
         self.survivor_meta = survivor_meta    # uint8 META_* bits
@@ -25,6 +26,9 @@ class BatchResult:
         self.gpu_ms = gpu_ms
         self.filter_ms = filter_ms
         self.launches = launches
+        # extension: completed curl -> chmod -> EXEC chains of this batch, in arrival order
+        self.chain_pid = chain_pid
+        self.chain_idx = chain_idx
 
     def histories(self):
         """[(pid, [event_str, ...]), ...]: exactly the arguments of analyze_sequence."""
@@ -111,11 +115,15 @@ class Context:
             tot = int(win["len"].sum()) if W else 0
             wrec = np.zeros((tot, RECORD_BYTES), dtype=np.uint8)
             self._check(self._L.chronos_copy_window_records(self._h, wrec.ctypes.data, tot))
+        K = counts["n_chains"]
+        cpid = np.zeros(K, dtype=np.uint32)
+        cidx = np.zeros(K, dtype=np.uint64)
+        self._check(self._L.chronos_copy_chains(self._h, cpid.ctypes.data, cidx.ctypes.data, K))
         t, f = c_float(), c_float()
         self._check(self._L.chronos_last_timing(self._h, byref(t), byref(f)))
         ln = c_uint64()
         self._check(self._L.chronos_last_launches(self._h, byref(ln)))
-        return BatchResult(counts, surv, meta, win, wrec, t.value, f.value, ln.value)
+        return BatchResult(counts, surv, meta, win, wrec, t.value, f.value, ln.value, cpid, cidx)
 
     def arena(self):
         c = _ffi.Counts()
@@ -145,10 +153,20 @@ class Context:
                                           rec.ctypes.data if records else None, P))
         return pid, idx, rec
 
-    def process_memory(self, n_pending):
-        """{pid: [event_str, ...]} for PIDs with a non-empty pending list (chronos_sensor.py:105)."""
+    def state_pids(self, n_pids_seen):
+        """Keys of process_memory: every PID that ever had a surviving event (unordered)."""
+        K = int(n_pids_seen)
+        out = np.zeros(K, dtype=np.uint32)
+        self._check(self._L.chronos_state_pids(self._h, out.ctypes.data, K))
+        return out
+
+    def process_memory(self, n_pending, n_pids_seen=None):
+        """{pid: [event_str, ...]} as the reference's process_memory (chronos_sensor.py:105).
+        With n_pids_seen the PIDs whose list is currently [] (:157) are included too."""
         pid, _, rec = self.state_arrays(n_pending, records=True)
         pm = {}
+        if n_pids_seen is not None:
+            pm = {int(p): [] for p in self.state_pids(n_pids_seen)}
         for k in range(pid.size):
             pm.setdefault(int(pid[k]), []).append(event_str(rec[k]))
         return pm

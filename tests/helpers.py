@@ -48,6 +48,10 @@ def compare_batch(ctx, engine, trace, records, base=0, check_state=True):
     np.testing.assert_array_equal(res.windows["trigger_idx"], ref["win_trigger"])
     ref_len = np.diff(ref["win_off"]).astype(np.uint32)
     np.testing.assert_array_equal(res.windows["len"], ref_len)
+    # extension outputs (semantics defined by the oracle, "parity unpinned" vs the reference)
+    np.testing.assert_array_equal(res.windows["flags"] & 1, ref["win_flags"] & 1, err_msg="t1105 window label")
+    np.testing.assert_array_equal(res.chain_pid, ref["chain_pid"], err_msg="chain pids")
+    np.testing.assert_array_equal(res.chain_idx, ref["chain_idx"], err_msg="chain arrival indices")
     # window contents, byte for byte, in window order
     if len(ref["members"]):
         exp = np.stack([trace.record(int(i)) for i in ref["members"]])
@@ -59,6 +63,8 @@ def compare_batch(ctx, engine, trace, records, base=0, check_state=True):
         pids, offs, mem = engine.state()
         exp_pid = np.repeat(pids, np.diff(offs).astype(np.int64))
         assert res.counts["n_pending"] == len(mem)
+        assert res.counts["n_pids_seen"] == len(pids)  # keys of process_memory, incl. PIDs whose list is []
+        np.testing.assert_array_equal(np.sort(ctx.state_pids(len(pids))), pids)
         gp, gi, grec = ctx.state_arrays(res.counts["n_pending"], records=True)
         np.testing.assert_array_equal(gp, exp_pid, err_msg="pending pids differ")
         np.testing.assert_array_equal(gi, mem, err_msg="pending arrival indices differ")

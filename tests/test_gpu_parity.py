@@ -107,8 +107,8 @@ def test_golden_vectors_from_the_unmodified_reference(ctx, name):
     res = ctx.fetch(records=True)
     assert res.survivors.tolist() == ref["survivors"]
     assert [[p, h] for p, h in res.histories()] == ref["windows"]
-    pm = ctx.process_memory(res.counts["n_pending"])
-    expect = {int(k): v for k, v in ref["process_memory"].items() if v}
+    pm = ctx.process_memory(res.counts["n_pending"], res.counts["n_pids_seen"])
+    expect = {int(k): v for k, v in ref["process_memory"].items()}  # including the [] of flushed PIDs (:157)
     assert pm == expect
 
 
