@@ -28,8 +28,9 @@
 #include "filter.cuh"
 #include "sort.cuh"
 #include "tracegen.cuh"
-#include "window.cuh"
 #include "chain.cuh"
+#include "fnscan.cuh"
+#include "window.cuh"
 
 using namespace chronos;
 
@@ -54,6 +55,10 @@ constexpr int N_TICKETS = 64;
 
 }  // namespace
 
+struct chronos_ctx;
+namespace {
+void mark(chronos_ctx *c, const char *name);
+}
 struct chronos_ctx {
     int device = 0;
     int sm_count = 0;
@@ -66,10 +71,10 @@ struct chronos_ctx {
     // batch staging for host-pointer submits
     DevBuf d_batch;
     // entry arrays (capacity in entries = ecap)
-    DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, flush, wi_of_entry, wsorted, windows, radix_table;
+    DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, pflag, entry_out, wsorted, windows, radix_table;
     DevBuf sp_key, sp_src, sp_meta, tile_count;  // filter's tile-local compaction
     // kill-chain labeller + persistent per-PID table (chain.cuh)
-    DevBuf pid_tab, pt_count, match, mcnt, match_entry, chain_pid, chain_idx;
+    DevBuf pid_tab, pt_count, chain_pid, chain_idx;
     uint32_t pt_cap = 0;
     uint32_t *h_pt_count = nullptr;  // pinned
     uint64_t n_pids_seen = 0, b_chains = 0;
@@ -98,11 +103,23 @@ struct chronos_ctx {
     float t_total = 0.f, t_filter = 0.f, t_filter_kernel = 0.f;
     bool filter_timed = false;
     int filter_variant = 0;
+    // CHRONOS_TRACE=1: CUDA events between the stages of a submit, printed at fetch
+    bool trace = false;
+    cudaEvent_t tev[12] = {nullptr};
+    const char *tname[12] = {nullptr};
+    int n_tev = 0;
 };
 
 namespace {
 
 const char *g_static_err = "chronos: invalid context";
+
+void mark(chronos_ctx *c, const char *name) {
+    if (!c->trace || c->n_tev >= 12) return;
+    if (!c->tev[c->n_tev]) cudaEventCreate(&c->tev[c->n_tev]);
+    cudaEventRecord(c->tev[c->n_tev], c->stream);
+    c->tname[c->n_tev++] = name;
+}
 
 int fail(chronos_ctx *c, int code, const char *fmt, ...) {
     if (c) {
@@ -179,10 +196,6 @@ __global__ void fold_keys_kernel(const uint32_t *keys, uint32_t n, uint32_t *k_o
         atomicOr(k_or, o);
         atomicAnd(k_and, a);
     }
-}
-
-__global__ void iota_kernel(uint32_t *v, uint32_t n) {
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) v[i] = i;
 }
 
 __global__ void init_scalars_kernel(DeviceScalars *s) {
@@ -437,6 +450,7 @@ int run_window_stage(chronos_ctx *c) {
     const uint64_t P = c->b_P;
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     // the one mid-pipeline read-back: survivor count + pid bit spread
+    mark(c, "filter+compact done");
     CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaEventRecord(c->ev_filter, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -455,7 +469,7 @@ int run_window_stage(chronos_ctx *c) {
         CK(cudaEventRecord(c->ev_end, c->stream));
         return CHRONOS_OK;
     }
-    if (M >= (1ull << 29)) return fail(c, CHRONOS_E_CAPACITY, "more than 2^29 grouped entries (%llu)", (unsigned long long)M);
+    if (M >= (1ull << VAL_ID_BITS)) return fail(c, CHRONOS_E_CAPACITY, "more than 2^27 grouped entries (%llu)", (unsigned long long)M);
 
     int rc;
     if ((rc = ensure(c, c->arena[cur], M * CH_REC_BYTES))) return rc;
@@ -464,16 +478,15 @@ int run_window_stage(chronos_ctx *c) {
     if ((rc = ensure(c, c->pend_arrival[cur], M * 8))) return rc;
     if ((rc = ensure(c, c->pend_meta[cur], M))) return rc;
     c->pend_cap[cur] = M;
-    if ((rc = ensure(c, c->flush, M))) return rc;
+    if ((rc = ensure(c, c->pflag, (M + 4) * 4))) return rc;
+    if ((rc = ensure(c, c->entry_out, (S + 4) * 4))) return rc;
     if ((rc = ensure(c, c->wsorted, (S / 2 + 1) * sizeof(WinSorted)))) return rc;
     if ((rc = ensure(c, c->windows, (S / 2 + 1) * sizeof(chronos_window)))) return rc;
-    if ((rc = ensure(c, c->match, M))) return rc;
-    if ((rc = ensure(c, c->mcnt, M * 4))) return rc;
-    if ((rc = ensure(c, c->match_entry, S + 1))) return rc;
     if ((rc = ensure(c, c->chain_pid, (S + 1) * 4))) return rc;
     if ((rc = ensure(c, c->chain_idx, (S + 1) * 8))) return rc;
     if ((rc = ensure_pid_table(c, M))) return rc;
 
+    mark(c, "host sync + sizing done");
     // ---- stable sort by pid -----------------------------------------------------------
     PassPlan pl = plan_passes(c->h_scalars->key_or, c->h_scalars->key_and, M);
     uint32_t *kin = ptr<uint32_t>(c->keyA), *kout = ptr<uint32_t>(c->keyB);
@@ -488,6 +501,9 @@ int run_window_stage(chronos_ctx *c) {
             RadixParams rp;
             rp.keys_in = kin;
             rp.vals_in = vin;
+            rp.meta_lo = P ? ptr<uint8_t>(c->pend_meta[prev]) + (c->pend_cap[prev] - P) : nullptr;
+            rp.meta_hi = ptr<uint8_t>(c->surv_meta);
+            rp.split = (uint32_t)P;
             rp.keys_out = kout;
             rp.vals_out = vout;
             rp.table = ptr<uint32_t>(c->radix_table);
@@ -511,13 +527,16 @@ int run_window_stage(chronos_ctx *c) {
     } else {
         // all keys equal (or a single entry): identity permutation
         uint32_t *v = ptr<uint32_t>(c->valA);
-        iota_kernel<<<(unsigned)std::min<uint64_t>((M + 255) / 256, 2048), 256, 0, c->stream>>>(v, (uint32_t)M);
+        synth_values_kernel<<<(unsigned)std::min<uint64_t>((M + 255) / 256, 2048), 256, 0, c->stream>>>(
+            v, (uint32_t)M, P ? ptr<uint8_t>(c->pend_meta[prev]) + (c->pend_cap[prev] - P) : nullptr,
+            ptr<uint8_t>(c->surv_meta), (uint32_t)P);
         CK(cudaGetLastError());
         c->launches++;
         c->sorted_key = kin;
         c->sorted_val = v;
     }
 
+    mark(c, "sort done");
     // ---- records into the grouped arena ----------------------------------------------
     {
         GatherParams g;
@@ -530,8 +549,9 @@ int run_window_stage(chronos_ctx *c) {
         g.pend_slot = P ? ptr<uint32_t>(c->pend_slot[prev]) + (pc - P) : nullptr;
         g.prev_arena = ptr<uint8_t>(c->arena[prev]);
         g.arena = ptr<uint8_t>(c->arena[cur]);
+        // bandwidth-bound copy on a second stream; it runs while the host enqueues the window
+        // scans and shares the GPU with them as far as registers allow
         uint32_t blocks = (uint32_t)std::min<uint64_t>((M + 127) / 128, (uint64_t)c->sm_count * 8);
-        // bandwidth-bound copy on a second stream, next to the latency-bound window scans
         CK(cudaEventRecord(c->ev_sorted, c->stream));
         CK(cudaStreamWaitEvent(c->stream2, c->ev_sorted, 0));
         gather_records<<<blocks, 256, 0, c->stream2>>>(g);
@@ -540,7 +560,7 @@ int run_window_stage(chronos_ctx *c) {
         c->launches++;
     }
 
-    // ---- window automaton ---------------------------------------------------------------
+    // ---- window automaton + chain labeller -------------------------------------------------
     {
         WinParams w;
         memset(&w, 0, sizeof(w));
@@ -548,17 +568,18 @@ int run_window_stage(chronos_ctx *c) {
         w.sval = c->sorted_val;
         w.M = (uint32_t)M;
         w.P = (uint32_t)P;
-        w.surv_meta = ptr<uint8_t>(c->surv_meta);
         w.surv_src = ptr<uint32_t>(c->surv_src);
         w.surv_arrival = c->b_explicit_arrival ? ptr<uint64_t>(c->surv_arrival) : nullptr;
         w.base_arrival = c->b_base;
         const uint64_t pc = c->pend_cap[prev];
-        w.pend_meta = P ? ptr<uint8_t>(c->pend_meta[prev]) + (pc - P) : nullptr;
         w.pend_arrival = P ? ptr<uint64_t>(c->pend_arrival[prev]) + (pc - P) : nullptr;
-        w.pend_slot = P ? ptr<uint32_t>(c->pend_slot[prev]) + (pc - P) : nullptr;
-        w.flush = ptr<uint8_t>(c->flush);
+        w.batch = c->b_records;
+        w.pid_tab = ptr<uint64_t>(c->pid_tab);
+        w.pid_mask = c->pt_cap - 1;
+        w.pid_count = ptr<uint32_t>(c->pt_count);
+        w.pflag = ptr<uint32_t>(c->pflag);
+        w.entry_out = ptr<uint32_t>(c->entry_out);
         w.wsorted = ptr<WinSorted>(c->wsorted);
-        w.wi_of_entry = ptr<uint32_t>(c->wi_of_entry);
         w.n_windows = &ds->n_windows;
         w.pend_cap = (uint32_t)M;
         w.npend_key = ptr<uint32_t>(c->pend_key[cur]);
@@ -567,60 +588,32 @@ int run_window_stage(chronos_ctx *c) {
         w.npend_meta = ptr<uint8_t>(c->pend_meta[cur]);
         w.n_pending = &ds->n_pending;
         w.windows = ptr<chronos_window>(c->windows);
-        w.match = ptr<uint8_t>(c->match);
-        w.mcnt = ptr<uint32_t>(c->mcnt);
+        w.chain_pid = ptr<uint32_t>(c->chain_pid);
+        w.chain_idx = ptr<uint64_t>(c->chain_idx);
+        w.n_chains = &ds->n_chains;
         const uint32_t tiles_m = (uint32_t)((M + WIN_TILE - 1) / WIN_TILE);
         const uint32_t tiles_s = (uint32_t)((S + WIN_TILE - 1) / WIN_TILE);
-        uint64_t *st = ptr<uint64_t>(c->status) + c->b_n / 64 + 2;  // behind the filter's tile words (>= n/64)
+        uint64_t *st = ptr<uint64_t>(c->status);
         uint32_t *tk = ptr<uint32_t>(c->tickets);
         const uint32_t cap_blocks = (uint32_t)c->sm_count * 4;
         w.ticket = tk + 60;
-        w.status = st;
-        window_forward<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
-        {
-            ChainParams cp;
-            cp.skey = w.skey;
-            cp.sval = w.sval;
-            cp.M = w.M;
-            cp.P = w.P;
-            cp.surv_meta = w.surv_meta;
-            cp.pend_meta = w.pend_meta;
-            cp.pid_tab = ptr<uint64_t>(c->pid_tab);
-            cp.pid_mask = c->pt_cap - 1;
-            cp.pid_count = ptr<uint32_t>(c->pt_count);
-            cp.match = ptr<uint8_t>(c->match);
-            cp.match_entry = ptr<uint8_t>(c->match_entry);
-            cp.mcnt = ptr<uint32_t>(c->mcnt);
-            cp.ticket = tk + 58;
-            cp.status = st + 5 * (size_t)tiles_m;
-            chain_scan<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(cp);
-        }
+        w.status = st;                              // 5 words per tile
+        group_forward<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
         w.ticket = tk + 61;
-        w.status = st + 2 * (size_t)tiles_m;
+        w.status = st + 5 * (size_t)tiles_m;        // 2 words per tile
         window_reverse<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
-        c->launches += 3;
+        c->launches += 2;
         if (S > 0) {
             w.ticket = tk + 62;
-            w.status = st + 4 * (size_t)tiles_m;
-            window_order<<<std::min(tiles_s, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
-            ChainOrderParams co;
-            co.match_entry = ptr<uint8_t>(c->match_entry);
-            co.batch = c->b_records;
-            co.surv_src = w.surv_src;
-            co.surv_arrival = w.surv_arrival;
-            co.base_arrival = w.base_arrival;
-            co.S = (uint32_t)S;
-            co.chain_pid = ptr<uint32_t>(c->chain_pid);
-            co.chain_idx = ptr<uint64_t>(c->chain_idx);
-            co.n_chains = &ds->n_chains;
-            co.ticket = tk + 57;
-            co.status = st + 8 * (size_t)tiles_m;
-            chain_order<<<std::min(tiles_s, cap_blocks), WIN_THREADS, 0, c->stream>>>(co);
-            c->launches += 2;
+            w.status = st + 7 * (size_t)tiles_m;    // 1 word per tile
+            emit_ordered<<<std::min(tiles_s, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
+            c->launches++;
         }
         CK(cudaGetLastError());
     }
+    mark(c, "window kernels done");
     CK(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
+    mark(c, "gather joined");
     CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(c->h_pt_count, c->pt_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaEventRecord(c->ev_end, c->stream));
@@ -631,7 +624,7 @@ int run_window_stage(chronos_ctx *c) {
 size_t status_words(uint64_t n, uint64_t P) {
     const uint64_t M = n + P;
     const uint64_t tiles_m = (M + WIN_TILE - 1) / WIN_TILE;
-    return (size_t)(n / 64 + 2 + 9 * tiles_m + 64);
+    return (size_t)(8 * tiles_m + 64);
 }
 
 int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
@@ -661,10 +654,11 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
     if ((rc = ensure(c, c->valB, (ecap + 1) * 4))) return rc;
     if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
-    if ((rc = ensure(c, c->wi_of_entry, (n + 1) * 4))) return rc;
     const size_t sw = status_words(n, P);
     if ((rc = ensure(c, c->status, sw * 8))) return rc;
     CK(cudaEventRecord(c->ev_start, c->stream));
+    c->n_tev = 0;
+    mark(c, "start");
     CK(cudaMemsetAsync(c->status.p, 0, sw * 8, c->stream));
     CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
     init_scalars_kernel<<<1, 1, 0, c->stream>>>(ptr<DeviceScalars>(c->scalars));
@@ -690,6 +684,13 @@ int finish_batch(chronos_ctx *c) {
     c->b_chains = c->b_M ? c->h_scalars->n_chains : 0;
     c->n_pids_seen = *c->h_pt_count;
     cudaEventElapsedTime(&c->t_total, c->ev_start, c->ev_end);
+    if (c->trace) {
+        for (int i = 1; i < c->n_tev; i++) {
+            float ms = 0;
+            cudaEventElapsedTime(&ms, c->tev[i - 1], c->tev[i]);
+            fprintf(stderr, "[chronos trace] %-28s %8.3f ms\n", c->tname[i], ms);
+        }
+    }
     cudaEventElapsedTime(&c->t_filter, c->ev_start, c->ev_filter);
     // (a stage-2-only batch keeps the filter time measured by chronos_filter_partition)
     if (c->filter_timed) cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
@@ -751,13 +752,17 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
     c->max_batch = max_batch_events;
     const char *fv = getenv("CHRONOS_FILTER_VARIANT");
     c->filter_variant = fv ? atoi(fv) : -1;  // -1: the tuned default (TILE 32, 1 stage)
+    c->trace = getenv("CHRONOS_TRACE") != nullptr;
     auto boot = [&]() -> int {
         CK(cudaSetDevice(device));
         cudaDeviceProp p;
         CK(cudaGetDeviceProperties(&p, device));
         c->sm_count = p.multiProcessorCount;
-        CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&c->stream2, cudaStreamNonBlocking));
+        int prio_lo = 0, prio_hi = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        // the latency-bound scans get priority over the bandwidth-bound record gather
+        CK(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi));
+        CK(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prio_lo));
         CK(cudaEventCreateWithFlags(&c->ev_sorted, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
         CK(cudaEventCreate(&c->ev_start));
@@ -788,8 +793,8 @@ int chronos_destroy(chronos_ctx *c) {
     if (!c) return CHRONOS_E_ARG;
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
-    DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->flush,
-                     &c->wi_of_entry, &c->wsorted, &c->pid_tab, &c->pt_count, &c->match, &c->mcnt, &c->match_entry, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+    DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->pflag,
+                     &c->entry_out, &c->wsorted, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
                      &c->tickets, &c->scalars, &c->scan_status, &c->pack, &c->pack_off};
@@ -1124,6 +1129,9 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
         RadixParams rp;
         rp.keys_in = owner;
         rp.vals_in = nullptr;
+        rp.meta_lo = nullptr;
+        rp.meta_hi = nullptr;
+        rp.split = 0;
         rp.keys_out = ptr<uint32_t>(c->keyB);
         rp.vals_out = ptr<uint32_t>(c->valA);  // permutation: survivors in (owner, arrival) order
         rp.table = ptr<uint32_t>(c->radix_table);

@@ -236,37 +236,6 @@ __device__ __forceinline__ uint32_t argv_trigger_chunk(const uint32_t *w, int al
     return meta;
 }
 
-// Single-pass exclusive prefix over per-tile counts (decoupled look-back). Called by one
-// full warp; tile 0 of the batch seeds the chain. Returns the exclusive prefix.
-__device__ __forceinline__ uint32_t lookback_count(uint64_t *status, uint32_t tile, uint32_t agg, int lane) {
-    if (tile == 0) {
-        if (lane == 0) st_relaxed_u64(status, (ST_PREFIX << 62) | agg);
-        return 0;
-    }
-    if (lane == 0) st_relaxed_u64(status + tile, (ST_AGG << 62) | agg);
-    uint32_t excl = 0;
-    int64_t look = (int64_t)tile - 1;
-    while (true) {
-        int64_t idx = look - lane;
-        uint64_t v = ST_PREFIX << 62;  // virtual tiles below 0: prefix 0
-        if (idx >= 0) {
-            do {
-                v = ld_relaxed_u64(status + idx);
-            } while ((v >> 62) == ST_NONE);
-        }
-        uint32_t is_p = __ballot_sync(0xffffffffu, (v >> 62) == ST_PREFIX);
-        if (is_p) {
-            int first = __ffs((int)is_p) - 1;
-            excl += __reduce_add_sync(0xffffffffu, lane <= first ? (uint32_t)v : 0u);
-            break;
-        }
-        excl += __reduce_add_sync(0xffffffffu, (uint32_t)v);
-        look -= 32;
-    }
-    if (lane == 0) st_relaxed_u64(status + tile, (ST_PREFIX << 62) | (uint64_t)(excl + agg));
-    return excl;
-}
-
 constexpr int FILTER_TILE = 32;  // records per tile: one per lane of the (single) warp of a CTA
 constexpr int MEMO_SLOTS = 64;   // comm memo entries per CTA
 constexpr int SHORT_CHUNKS = 4;  // argv NUL search done lane-per-record over chunks 1..4 (60 bytes)

@@ -21,7 +21,10 @@ constexpr int RADIX_WARPS = RADIX_THREADS / 32;
 
 struct RadixParams {
     const uint32_t *keys_in;
-    const uint32_t *vals_in;  // nullptr => value = index
+    const uint32_t *vals_in;  // nullptr => value = index | class bits << 27 (see synth_value)
+    const uint8_t *meta_lo;   // class bits of entries [0, split) (carried-in pending), may be nullptr
+    const uint8_t *meta_hi;   // class bits of entries [split, n) (this batch's survivors), may be nullptr
+    uint32_t split;
     uint32_t *keys_out;
     uint32_t *vals_out;
     uint32_t *table;          // RADIX_BINS * n_tiles counters, digit-major
@@ -31,6 +34,22 @@ struct RadixParams {
     uint32_t shift;
     uint32_t mask;            // (1<<bits)-1
 };
+
+// Pass 0 synthesises the sort values instead of reading them: the entry id in the low 27
+// bits and the event's class bits (CHRONOS_META_*) above, so that the kernels after the
+// sort never gather them again. Carried-in entries lose the trigger bit (a pending event
+// cannot trigger again, chronos_sensor.py:141 looks at the current event only).
+__device__ __forceinline__ uint32_t synth_value(const uint8_t *meta_lo, const uint8_t *meta_hi, uint32_t split, uint32_t i) {
+    uint32_t m = 0;
+    if (i < split) m = meta_lo ? (uint32_t)(meta_lo[i] & 0x1Eu) : 0u;
+    else m = meta_hi ? (uint32_t)(meta_hi[i - split] & 0x1Fu) : 0u;
+    return i | (m << 27);
+}
+
+__global__ void synth_values_kernel(uint32_t *v, uint32_t n, const uint8_t *meta_lo, const uint8_t *meta_hi, uint32_t split) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+        v[i] = synth_value(meta_lo, meta_hi, split, i);
+}
 
 __global__ void __launch_bounds__(RADIX_THREADS) radix_hist(const RadixParams p) {
     __shared__ uint32_t h[RADIX_BINS];
@@ -198,7 +217,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) radix_scatter(const RadixParams
         if (valid) {
             const uint32_t dst = base + before;
             p.keys_out[dst] = key;
-            p.vals_out[dst] = p.vals_in ? p.vals_in[i] : i;
+            p.vals_out[dst] = p.vals_in ? p.vals_in[i] : synth_value(p.meta_lo, p.meta_hi, p.split, i);
         }
     }
 }

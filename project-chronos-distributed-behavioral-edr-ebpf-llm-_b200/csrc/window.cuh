@@ -1,4 +1,5 @@
-// window.cuh -- kernels 3/4: per-PID context windows over the pid-grouped entries.
+// window.cuh -- kernels 3/4: per-PID context windows (and the kill-chain labeller) over the
+// pid-grouped entries.
 //
 // Reference semantics (chronos_sensor.py): append to process_memory[pid] (:138); if the
 // event string holds a trigger needle (:141) and the list now has >= 2 entries (:142)
@@ -8,154 +9,44 @@
 //     trigger in E: -> N (no flush)           trigger in N: FLUSH, -> E
 // The first event of a PID always ends in N. Events still pending from earlier batches
 // re-enter the grouped array as non-trigger entries ahead of the batch's survivors, so
-// no separate per-PID state lookup is needed for the window logic.
+// the window logic needs no per-PID state lookup.
 //
-// Both directions are single-pass scans with decoupled look-back whose carried value is
-// a FUNCTION over the 2-state automaton (what the tile does for either entry state),
-// which makes the composition associative:
-//   window_forward  : flush bits, window ordinals, group starts -> window descriptors
-//   window_reverse  : "is my group ever closed?" -> pending-list compaction
-//   window_order    : windows re-ordered by arrival index of their trigger event (:143-147)
+// EXTENSION (no reference semantics, SURVEY 8a "parity unpinned"; defined by
+// oracle/chronos_oracle.c::co_feed): chronos_sensor.py only *describes* the dropper
+// pattern to the LLM ("'curl' -> 'chmod' -> 'exec' is a Dropper", :112). Here it is a
+// per-PID DFA over the surviving events in arrival order,
+//     d=0 --"curl" in event_str--> 1 --"chmod"--> 2 --type is EXEC--> match, back to 0,
+// one step per event, state kept per PID across flushes and batches (pid table, chain.cuh).
+// It never changes which events survive or which windows are emitted.
+//
+//   group_forward   : both automata in ONE single-pass function scan (fnscan.cuh):
+//                     flush bits, window descriptors, chain matches, per-PID table update
+//   window_reverse  : "is my group ever closed?" -> pending-list compaction (process_memory)
+//   emit_ordered    : windows and chain matches in arrival order of their trigger event
+//                     (:143-147): two compactions over the batch's entries in one pass
 //   gather_records  : 288-byte records copied once into the pid-grouped arena
+//
+// Sorted values carry the event's class bits so that no kernel after the sort has to
+// gather them again: value = entry id (27 bits) | META bits << 27.
 #pragma once
+#include "chain.cuh"
 #include "common.cuh"
 #include "filter.cuh"
+#include "fnscan.cuh"
 
 namespace chronos {
 
-constexpr uint32_t NONE32 = 0xffffffffu;
+constexpr int VAL_ID_BITS = 27;
+constexpr uint32_t VAL_ID_MASK = (1u << VAL_ID_BITS) - 1u;
 constexpr int WIN_THREADS = 256;
 constexpr int WIN_ITEMS = 16;
 constexpr int WIN_TILE = WIN_THREADS * WIN_ITEMS;
-
-// What a run of elements does to the automaton, for either entry state s in {0,1}:
-//   out bit s  : exit state
-//   a[s]       : counter increment (flushes / open elements)
-//   b[s]       : last "marker" position set inside the run, NONE32 if it inherits
-struct Fn2 {
-    uint32_t out;
-    uint32_t a[2];
-    uint32_t b[2];
-};
-__device__ __forceinline__ Fn2 fn_identity() { return Fn2{0x2u, {0u, 0u}, {NONE32, NONE32}}; }
-// first x, then y
-__device__ __forceinline__ Fn2 fn_compose(const Fn2 &x, const Fn2 &y) {
-    Fn2 r;
-    uint32_t m0 = x.out & 1u, m1 = (x.out >> 1) & 1u;
-    r.out = ((y.out >> m0) & 1u) | (((y.out >> m1) & 1u) << 1);
-    r.a[0] = x.a[0] + y.a[m0];
-    r.a[1] = x.a[1] + y.a[m1];
-    r.b[0] = y.b[m0] != NONE32 ? y.b[m0] : x.b[0];
-    r.b[1] = y.b[m1] != NONE32 ? y.b[m1] : x.b[1];
-    return r;
-}
-struct St2 {  // concrete automaton state + carried counter + carried marker
-    uint32_t s, a, b;
-};
-__device__ __forceinline__ St2 fn_apply(const Fn2 &f, const St2 &c) {
-    St2 r;
-    r.s = (f.out >> c.s) & 1u;
-    r.a = c.a + f.a[c.s];
-    r.b = f.b[c.s] != NONE32 ? f.b[c.s] : c.b;
-    return r;
-}
-// status word for entry state s: [63:62] status [61] out_s [60:32] a_s (29 bits) [31:0] b_s
-__device__ __forceinline__ uint64_t fn_pack(uint64_t status, uint32_t out_s, uint32_t a_s, uint32_t b_s) {
-    return (status << 62) | ((uint64_t)(out_s & 1u) << 61) | ((uint64_t)(a_s & 0x1fffffffu) << 32) | b_s;
-}
-__device__ __forceinline__ Fn2 fn_shfl(const Fn2 &f, int src) {
-    Fn2 r;
-    r.out = __shfl_sync(0xffffffffu, f.out, src);
-    r.a[0] = __shfl_sync(0xffffffffu, f.a[0], src);
-    r.a[1] = __shfl_sync(0xffffffffu, f.a[1], src);
-    r.b[0] = __shfl_sync(0xffffffffu, f.b[0], src);
-    r.b[1] = __shfl_sync(0xffffffffu, f.b[1], src);
-    return r;
-}
-
-// Block-wide exclusive scan of per-thread Fn2 (WIN_THREADS threads). Returns the
-// exclusive prefix of the calling thread; *total (valid in every thread) is the tile's Fn2.
-__device__ __forceinline__ Fn2 fn_block_exclusive(const Fn2 &mine, Fn2 *warp_tot /*[8] smem*/, Fn2 *total) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    Fn2 inc = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        Fn2 o = fn_shfl(inc, lane >= d ? lane - d : lane);
-        if (lane >= d) inc = fn_compose(o, inc);
-    }
-    if (lane == 31) warp_tot[warp] = inc;
-    __syncthreads();
-    Fn2 prev = fn_shfl(inc, lane > 0 ? lane - 1 : 0);
-    Fn2 excl = lane > 0 ? prev : fn_identity();
-    Fn2 run = fn_identity();
-    Fn2 wpre = fn_identity();
-#pragma unroll
-    for (int w = 0; w < WIN_THREADS / 32; w++) {
-        if (w == warp) wpre = run;
-        run = fn_compose(run, warp_tot[w]);
-    }
-    *total = run;
-    return fn_compose(wpre, excl);
-}
-
-// Decoupled look-back over Fn2 tile summaries; one full warp. status has 2 words per
-// tile. Publishes this tile's summary / inclusive state; returns the concrete state in
-// front of the tile. `init` is the state in front of tile 0.
-__device__ __forceinline__ St2 fn_lookback(uint64_t *status, uint32_t tile, const Fn2 &agg, St2 init, int lane) {
-    St2 in = init;
-    if (tile != 0) {
-        if (lane == 0) {
-            st_relaxed_u64(status + 2 * (size_t)tile, fn_pack(ST_AGG, agg.out, agg.a[0], agg.b[0]));
-            st_relaxed_u64(status + 2 * (size_t)tile + 1, fn_pack(ST_AGG, agg.out >> 1, agg.a[1], agg.b[1]));
-        }
-        Fn2 H = fn_identity();  // everything between the tiles inspected so far and us
-        int64_t look = (int64_t)tile - 1;
-        while (true) {
-            int64_t idx = look - lane;
-            uint64_t w0 = fn_pack(ST_PREFIX, init.s, init.a, init.b), w1 = w0;  // virtual tiles below 0
-            if (idx >= 0) {
-                // the owner rewrites both words when it upgrades AGG -> PREFIX: only accept a
-                // pair whose status fields agree (a torn pair mixes two encodings)
-                do {
-                    w0 = ld_relaxed_u64(status + 2 * (size_t)idx);
-                    w1 = ld_relaxed_u64(status + 2 * (size_t)idx + 1);
-                } while ((w0 >> 62) == ST_NONE || (w0 >> 62) != (w1 >> 62));
-            }
-            Fn2 mine;
-            mine.out = (uint32_t)((w0 >> 61) & 1u) | ((uint32_t)((w1 >> 61) & 1u) << 1);
-            mine.a[0] = (uint32_t)(w0 >> 32) & 0x1fffffffu;
-            mine.a[1] = (uint32_t)(w1 >> 32) & 0x1fffffffu;
-            mine.b[0] = (uint32_t)w0;
-            mine.b[1] = (uint32_t)w1;
-            const uint32_t is_p = __ballot_sync(0xffffffffu, (w0 >> 62) == ST_PREFIX);
-            const int first = is_p ? __ffs((int)is_p) - 1 : 32;
-            // G = tiles (look-first, look] composed in ascending tile order (= descending
-            // lane order): ordered tree reduction over the lanes below `first`
-            Fn2 G = (lane < first) ? mine : fn_identity();
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const Fn2 older = fn_shfl(G, (lane + d) & 31);
-                if (lane + d < 32) G = fn_compose(older, G);
-            }
-            G = fn_shfl(G, 0);
-            H = fn_compose(G, H);
-            if (is_p) {
-                Fn2 pf = fn_shfl(mine, first);
-                St2 c{pf.out & 1u, pf.a[0], pf.b[0]};
-                in = fn_apply(H, c);
-                break;
-            }
-            look -= 32;
-        }
-    }
-    St2 outc = fn_apply(agg, in);
-    if (lane == 0) {
-        uint64_t w = fn_pack(ST_PREFIX, outc.s, outc.a, outc.b);
-        st_relaxed_u64(status + 2 * (size_t)tile, w);
-        st_relaxed_u64(status + 2 * (size_t)tile + 1, w);
-    }
-    return in;
-}
+// per-position flags written by group_forward: bit0 flush, bit1 chain match, bits 31:2 =
+// inclusive count of chain-complete events up to this position
+constexpr uint32_t PF_FLUSH = 1u, PF_MATCH = 2u;
+// per-entry result: bit 31 = this event completed a chain, low 31 bits = ordinal of the
+// window it flushed (EO_NONE if it flushed nothing)
+constexpr uint32_t EO_NONE = 0x7fffffffu, EO_MATCH = 0x80000000u;
 
 struct WinSorted {  // window descriptor in pid-grouped order
     uint32_t pid, trig_entry, start, len;
@@ -163,19 +54,21 @@ struct WinSorted {  // window descriptor in pid-grouped order
 
 struct WinParams {
     const uint32_t *skey;   // M sorted pids
-    const uint32_t *sval;   // M entry ids: [0,P) carried-in pending, [P,M) this batch's survivors
+    const uint32_t *sval;   // M values: entry id | meta << 27; ids [0,P) carried-in pending, [P,M) survivors
     uint32_t M, P;
-    const uint8_t *surv_meta;       // S
     const uint32_t *surv_src;       // S batch-local record index
     const uint64_t *surv_arrival;   // S explicit arrival indices, or nullptr => base_arrival + surv_src
     uint64_t base_arrival;
-    const uint8_t *pend_meta;       // P (previous batch)
-    const uint64_t *pend_arrival;   // P
-    const uint32_t *pend_slot;      // P record index in the previous arena
+    const uint64_t *pend_arrival;   // P (previous batch)
+    const uint8_t *batch;           // this batch's records (pid of a chain match is read back from there)
+    // per-PID table (chain.cuh)
+    uint64_t *pid_tab;
+    uint32_t pid_mask;
+    uint32_t *pid_count;
     // forward outputs
-    uint8_t *flush;                 // M
-    WinSorted *wsorted;             // <= S/1 descriptors in grouped order
-    uint32_t *wi_of_entry;          // S: window ordinal flushed by survivor j, or NONE32
+    uint32_t *pflag;                // M
+    uint32_t *entry_out;            // S
+    WinSorted *wsorted;             // window descriptors in grouped order
     uint32_t *n_windows;
     // reverse outputs (right-aligned in arrays of capacity pend_cap)
     uint32_t pend_cap;
@@ -184,32 +77,43 @@ struct WinParams {
     uint64_t *npend_arrival;
     uint8_t *npend_meta;
     uint32_t *n_pending;
-    // chain labeller outputs consumed here (chain.cuh); nullptr when not run
-    const uint8_t *match;           // M: this batch's event at pos completed a curl->chmod->EXEC chain
-    const uint32_t *mcnt;           // M: inclusive count of chain-complete events up to pos
-    // ordering outputs
+    // ordered outputs
     chronos_window *windows;        // n_windows, ascending trigger arrival
+    uint32_t *chain_pid;            // n_chains, ascending arrival
+    uint64_t *chain_idx;
+    uint32_t *n_chains;
     // scheduling
     uint32_t *ticket;               // one counter per kernel
     uint64_t *status;               // look-back words for this kernel
 };
 
-__device__ __forceinline__ uint8_t win_meta_of(const WinParams &p, uint32_t e) {
-    return e < p.P ? (uint8_t)(p.pend_meta[e] & ~META_TRIG) : p.surv_meta[e - p.P];
-}
 __device__ __forceinline__ uint64_t win_arrival_of(const WinParams &p, uint32_t e) {
     if (e < p.P) return p.pend_arrival[e];
-    uint32_t j = e - p.P;
+    const uint32_t j = e - p.P;
     return p.surv_arrival ? p.surv_arrival[j] : p.base_arrival + p.surv_src[j];
 }
 
+// what one surviving event does to the chain DFA
+__device__ __forceinline__ Fn3 chain_event(uint32_t meta) {
+    Fn3 e;
+    const uint32_t o0 = (meta & META_CURL) ? 1u : 0u;
+    const uint32_t o1 = (meta & META_CHMOD) ? 2u : 1u;
+    const uint32_t o2 = (meta & META_EXEC) ? 0u : 2u;
+    e.out = o0 | (o1 << 2) | (o2 << 4);
+    e.a[0] = 0;
+    e.a[1] = 0;
+    e.a[2] = (meta & META_EXEC) ? 1u : 0u;
+    return e;
+}
+
 // ---------------------------------------------------------------------------------------
-// forward: automaton state E=0 / N=1. Marker b = start position of the current group.
+// forward. Flush automaton: E=0 / N=1, marker b = start position of the current group,
+// counter a = windows flushed so far. Chain DFA: counter a = chain-complete events so far.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(WIN_THREADS) window_forward(const WinParams p) {
-    __shared__ Fn2 warp_tot[WIN_THREADS / 32];
+__global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) {
+    __shared__ FnG warp_tot[WIN_THREADS / 32];
     __shared__ uint32_t s_tile;
-    __shared__ St2 s_in;
+    __shared__ StG s_in;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t n_tiles = (p.M + WIN_TILE - 1) / WIN_TILE;
     while (true) {
@@ -219,56 +123,98 @@ __global__ void __launch_bounds__(WIN_THREADS) window_forward(const WinParams p)
         const uint32_t tile = s_tile;
         if (tile >= n_tiles) break;
         const uint32_t p0 = tile * WIN_TILE + tid * WIN_ITEMS;
-        uint32_t key[WIN_ITEMS], ent[WIN_ITEMS];
-        bool head[WIN_ITEMS], trig[WIN_ITEMS];
+        uint32_t key[WIN_ITEMS], val[WIN_ITEMS];
+        uint8_t kind[WIN_ITEMS];  // bit0 head, bits 2:1 the PID's stored DFA state at a head
         uint32_t prevk = (p0 > 0 && p0 - 1 < p.M) ? p.skey[p0 - 1] : 0;
-        Fn2 f = fn_identity();
+        FnG f = FnG::identity();
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t pos = p0 + k;
+            key[k] = 0; val[k] = 0; kind[k] = 0;
             if (pos < p.M) {
                 key[k] = p.skey[pos];
-                ent[k] = p.sval[pos];
-                head[k] = (pos == 0) || key[k] != prevk;
-                trig[k] = (win_meta_of(p, ent[k]) & META_TRIG) != 0;
+                val[k] = p.sval[pos];
+                const uint32_t meta = val[k] >> VAL_ID_BITS;
+                const bool carried = (val[k] & VAL_ID_MASK) < p.P;
+                const bool head = (pos == 0) || key[k] != prevk;
+                const bool trig = (meta & META_TRIG) != 0;  // carried entries were stored without it
                 prevk = key[k];
-                Fn2 e;
-                if (head[k]) e = Fn2{0x3u, {0u, 0u}, {pos, pos}};
-                else if (!trig[k]) e = Fn2{0x3u, {0u, 0u}, {pos, NONE32}};
-                else e = Fn2{0x1u, {0u, 1u}, {pos, NONE32}};
-                f = fn_compose(f, e);
-            } else {
-                key[k] = 0; ent[k] = 0; head[k] = false; trig[k] = false;
+                FnG e;
+                if (head) e.w = Fn2{0x3u, {0u, 0u}, {pos, pos}};
+                else if (!trig) e.w = Fn2{0x3u, {0u, 0u}, {pos, NONE32}};
+                else e.w = Fn2{0x1u, {0u, 1u}, {pos, NONE32}};
+                // a carried-in entry was stepped through the DFA when it arrived; it only brings
+                // its "completed a chain" mark along for the window label
+                const uint32_t cm = (meta & META_CHAIN) ? 1u : 0u;
+                e.c = carried ? Fn3{0x24u, {cm, cm, cm}} : chain_event(meta);
+                uint32_t kd = head ? 1u : 0u;
+                if (head) {  // the PID's stored DFA state replaces whatever is carried over
+                    const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, key[k], p.pid_count);
+                    const uint32_t d0 = (uint32_t)(ld_relaxed_u64(p.pid_tab + slot) >> 32) & 3u;
+                    kd |= d0 << 1;
+                    e.c = Fn3::constant(Fn3::o(e.c, d0), Fn3::av(e.c, d0));
+                }
+                kind[k] = (uint8_t)kd;
+                f = FnG::compose(f, e);
             }
         }
-        Fn2 total;
-        Fn2 excl = fn_block_exclusive(f, warp_tot, &total);
+        FnG total;
+        FnG excl = fn_block_exclusive<FnG, WIN_THREADS>(f, warp_tot, &total);
         if (warp == 0) {
-            St2 in = fn_lookback(p.status, tile, total, St2{0u, 0u, NONE32}, lane);
+            StG in = fn_lookback<FnG>(p.status, tile, total, StG{St2{0u, 0u, NONE32}, St3{0u, 0u}}, lane);
             if (lane == 0) {
                 s_in = in;
-                if (tile == n_tiles - 1) *p.n_windows = fn_apply(total, in).a;
+                if (tile == n_tiles - 1) *p.n_windows = FnG::apply(total, in).w.a;
             }
         }
         __syncthreads();
-        St2 st = fn_apply(excl, s_in);
+        StG st = FnG::apply(excl, s_in);
+        uint32_t pf[WIN_ITEMS];
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t pos = p0 + k;
-            if (pos >= p.M) break;
+            pf[k] = 0;
+            if (pos >= p.M) continue;
+            const uint32_t meta = val[k] >> VAL_ID_BITS, e = val[k] & VAL_ID_MASK;
+            const bool carried = e < p.P, head = kind[k] & 1u, trig = (meta & META_TRIG) != 0;
+            // ---- flush automaton
             bool fl = false;
-            uint32_t wi = NONE32;
-            if (head[k]) { st.b = pos; st.s = 1; }
-            else if (!trig[k]) { if (st.s == 0) st.b = pos; st.s = 1; }
-            else if (st.s == 0) { st.b = pos; st.s = 1; }
+            uint32_t wi = EO_NONE;
+            if (head) { st.w.b = pos; st.w.s = 1; }
+            else if (!trig) { if (st.w.s == 0) st.w.b = pos; st.w.s = 1; }
+            else if (st.w.s == 0) { st.w.b = pos; st.w.s = 1; }
             else {
                 fl = true;
-                wi = st.a++;
-                st.s = 0;
-                p.wsorted[wi] = WinSorted{key[k], ent[k], st.b, pos - st.b + 1};
+                wi = st.w.a++;
+                st.w.s = 0;
+                p.wsorted[wi] = WinSorted{key[k], e, st.w.b, pos - st.w.b + 1};
             }
-            p.flush[pos] = fl ? 1 : 0;
-            if (ent[k] >= p.P) p.wi_of_entry[ent[k] - p.P] = wi;
+            // ---- chain DFA
+            if (head) st.c.s = (kind[k] >> 1) & 3u;
+            bool m = false;
+            if (carried) {
+                st.c.a += (meta & META_CHAIN) ? 1u : 0u;
+            } else {
+                if (st.c.s == 2u) { if (meta & META_EXEC) { m = true; st.c.s = 0; st.c.a++; } }
+                else if (st.c.s == 1u) { if (meta & META_CHMOD) st.c.s = 2; }
+                else if (meta & META_CURL) st.c.s = 1;
+                p.entry_out[e - p.P] = wi | (m ? EO_MATCH : 0u);
+            }
+            pf[k] = (fl ? PF_FLUSH : 0u) | (m ? PF_MATCH : 0u) | (st.c.a << 2);
+            const bool tail = (pos + 1 == p.M) || p.skey[pos + 1] != key[k];
+            if (tail) {  // the PID's DFA state after this batch
+                const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, key[k], p.pid_count);
+                st_relaxed_u64(p.pid_tab + slot, PT_VALID | ((uint64_t)st.c.s << 32) | key[k]);
+            }
+        }
+        if (p0 + WIN_ITEMS <= p.M) {
+            uint4 *dst = reinterpret_cast<uint4 *>(p.pflag + p0);
+#pragma unroll
+            for (int k = 0; k < WIN_ITEMS; k += 4) dst[k / 4] = make_uint4(pf[k], pf[k + 1], pf[k + 2], pf[k + 3]);
+        } else {
+#pragma unroll
+            for (int k = 0; k < WIN_ITEMS; k++)
+                if (p0 + k < p.M) p.pflag[p0 + k] = pf[k];
         }
     }
 }
@@ -291,69 +237,70 @@ __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p)
         if (tile >= n_tiles) break;
         const uint32_t q0 = tile * WIN_TILE + tid * WIN_ITEMS;  // reversed index q = M-1-pos
         uint32_t key[WIN_ITEMS];
-        bool setter[WIN_ITEMS], fl[WIN_ITEMS];
-        uint32_t nextk = 0;  // key at pos+1
+        uint8_t kd[WIN_ITEMS];  // bit0 setter, bit1 flush, bit2 chain match
+        uint32_t nextk = 0;     // key at pos+1
         bool have_next = false;
         if (q0 > 0 && q0 <= p.M) { nextk = p.skey[p.M - q0]; have_next = true; }
-        Fn2 f = fn_identity();
+        Fn2 f = Fn2::identity();
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t q = q0 + k;
+            key[k] = 0; kd[k] = 0;
             if (q < p.M) {
                 const uint32_t pos = p.M - 1 - q;
                 key[k] = p.skey[pos];
-                fl[k] = p.flush[pos] != 0;
+                const uint32_t pfl = p.pflag[pos];
+                const bool fl = (pfl & PF_FLUSH) != 0;
                 const bool tail = !have_next || key[k] != nextk;
-                setter[k] = tail || fl[k];
+                const bool setter = tail || fl;
                 nextk = key[k];
                 have_next = true;
+                kd[k] = (uint8_t)((setter ? 1u : 0u) | (fl ? 2u : 0u) | ((pfl & PF_MATCH) ? 4u : 0u));
                 Fn2 e;
-                if (setter[k]) e = fl[k] ? Fn2{0x0u, {0u, 0u}, {NONE32, NONE32}} : Fn2{0x3u, {1u, 1u}, {NONE32, NONE32}};
+                if (setter) e = fl ? Fn2{0x0u, {0u, 0u}, {NONE32, NONE32}} : Fn2{0x3u, {1u, 1u}, {NONE32, NONE32}};
                 else e = Fn2{0x2u, {0u, 1u}, {NONE32, NONE32}};
-                f = fn_compose(f, e);
-            } else {
-                key[k] = 0; setter[k] = false; fl[k] = false;
+                f = Fn2::compose(f, e);
             }
         }
         Fn2 total;
-        Fn2 excl = fn_block_exclusive(f, warp_tot, &total);
+        Fn2 excl = fn_block_exclusive<Fn2, WIN_THREADS>(f, warp_tot, &total);
         if (warp == 0) {
-            St2 in = fn_lookback(p.status, tile, total, St2{0u, 0u, NONE32}, lane);
+            St2 in = fn_lookback<Fn2>(p.status, tile, total, St2{0u, 0u, NONE32}, lane);
             if (lane == 0) {
                 s_in = in;
-                if (tile == n_tiles - 1) *p.n_pending = fn_apply(total, in).a;
+                if (tile == n_tiles - 1) *p.n_pending = Fn2::apply(total, in).a;
             }
         }
         __syncthreads();
-        St2 st = fn_apply(excl, s_in);
+        St2 st = Fn2::apply(excl, s_in);
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t q = q0 + k;
             if (q >= p.M) break;
             const uint32_t pos = p.M - 1 - q;
-            if (setter[k]) st.s = fl[k] ? 0u : 1u;
+            if (kd[k] & 1u) st.s = (kd[k] & 2u) ? 0u : 1u;
             if (st.s == 1u) {
                 const uint32_t slot = p.pend_cap - 1u - st.a;
                 st.a++;
-                const uint32_t e = p.sval[pos];
+                const uint32_t v = p.sval[pos];
                 p.npend_key[slot] = key[k];
                 p.npend_slot[slot] = pos;
-                p.npend_arrival[slot] = win_arrival_of(p, e);
-                uint8_t pm = (uint8_t)(win_meta_of(p, e) & ~META_TRIG);
-                if (p.match && p.match[pos]) pm |= (uint8_t)META_CHAIN;
-                p.npend_meta[slot] = pm;
+                p.npend_arrival[slot] = win_arrival_of(p, v & VAL_ID_MASK);
+                // stored without the trigger bit (a pending event never triggers again), with
+                // the chain mark if it completed a chain, for the label of its future window
+                p.npend_meta[slot] = (uint8_t)(((v >> VAL_ID_BITS) & ~META_TRIG) | ((kd[k] & 4u) ? META_CHAIN : 0u));
             }
         }
     }
 }
 
 // ---------------------------------------------------------------------------------------
-// order: windows sorted by the arrival index of their trigger event = compaction of
-// wi_of_entry in entry order (entry order of this batch's survivors IS arrival order).
+// ordered emission: compaction of entry_out over this batch's survivors, whose entry order
+// IS arrival order: windows by trigger arrival (:143-147) and chain matches by arrival.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(WIN_THREADS) window_order(const WinParams p) {
-    __shared__ uint32_t warp_sum[WIN_THREADS / 32];
-    __shared__ uint32_t s_tile, s_base;
+__global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) {
+    __shared__ uint32_t warp_w[WIN_THREADS / 32], warp_c[WIN_THREADS / 32];
+    __shared__ uint32_t s_tile, s_base_w, s_base_c;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t S = p.M - p.P;
     const uint32_t n_tiles = (S + WIN_TILE - 1) / WIN_TILE;
@@ -364,48 +311,71 @@ __global__ void __launch_bounds__(WIN_THREADS) window_order(const WinParams p) {
         const uint32_t tile = s_tile;
         if (tile >= n_tiles) break;
         const uint32_t j0 = tile * WIN_TILE + tid * WIN_ITEMS;
-        uint32_t wi[WIN_ITEMS];
-        uint32_t cnt = 0;
+        uint32_t eo[WIN_ITEMS];
+        uint32_t cw = 0, cc = 0;
+        if (j0 + WIN_ITEMS <= S) {
+            const uint4 *src = reinterpret_cast<const uint4 *>(p.entry_out + j0);
+#pragma unroll
+            for (int k = 0; k < WIN_ITEMS; k += 4) {
+                const uint4 v = src[k / 4];
+                eo[k] = v.x; eo[k + 1] = v.y; eo[k + 2] = v.z; eo[k + 3] = v.w;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < WIN_ITEMS; k++) eo[k] = (j0 + k < S) ? p.entry_out[j0 + k] : EO_NONE;
+        }
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
-            wi[k] = (j0 + k < S) ? p.wi_of_entry[j0 + k] : NONE32;
-            cnt += wi[k] != NONE32;
+            cw += (eo[k] & EO_NONE) != EO_NONE;
+            cc += (eo[k] & EO_MATCH) != 0;
         }
-        uint32_t inc = cnt;
+        uint32_t iw = cw, ic = cc;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
-            if (lane >= d) inc += t;
+            const uint32_t tw = __shfl_up_sync(0xffffffffu, iw, d), tc = __shfl_up_sync(0xffffffffu, ic, d);
+            if (lane >= d) { iw += tw; ic += tc; }
         }
-        if (lane == 31) warp_sum[warp] = inc;
+        if (lane == 31) { warp_w[warp] = iw; warp_c[warp] = ic; }
         __syncthreads();
         if (warp == 0) {
-            uint32_t tot = 0;
+            uint32_t tw = 0, tc = 0;
 #pragma unroll
-            for (int w = 0; w < WIN_THREADS / 32; w++) tot += warp_sum[w];
-            uint32_t excl = lookback_count(p.status, tile, tot, lane);
-            if (lane == 0) s_base = excl;
+            for (int w = 0; w < WIN_THREADS / 32; w++) { tw += warp_w[w]; tc += warp_c[w]; }
+            const uint2 ex = lookback_count2(p.status, tile, tw, tc, lane);
+            if (lane == 0) {
+                s_base_w = ex.x;
+                s_base_c = ex.y;
+                if (tile == n_tiles - 1) *p.n_chains = ex.y + tc;
+            }
         }
         __syncthreads();
-        uint32_t r = s_base + inc - cnt;
+        uint32_t rw = s_base_w + iw - cw, rc = s_base_c + ic - cc;
 #pragma unroll
-        for (int w = 0; w < WIN_THREADS / 32; w++) r += (w < warp) ? warp_sum[w] : 0u;
+        for (int w = 0; w < WIN_THREADS / 32; w++) {
+            rw += (w < warp) ? warp_w[w] : 0u;
+            rc += (w < warp) ? warp_c[w] : 0u;
+        }
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
-            if (wi[k] == NONE32) continue;
-            const WinSorted d = p.wsorted[wi[k]];
-            chronos_window o;
-            o.trigger_idx = win_arrival_of(p, d.trig_entry);
-            o.start = d.start;
-            o.len = d.len;
-            o.pid = d.pid;
-            o.flags = 0;
-            if (p.mcnt) {
-                const uint32_t hi = p.mcnt[d.start + d.len - 1], lo = d.start ? p.mcnt[d.start - 1] : 0u;
-                o.flags = hi != lo ? 1u : 0u;
+            const uint32_t wi = eo[k] & EO_NONE;
+            if (wi != EO_NONE) {
+                const WinSorted d = p.wsorted[wi];
+                chronos_window o;
+                o.trigger_idx = win_arrival_of(p, d.trig_entry);
+                o.start = d.start;
+                o.len = d.len;
+                o.pid = d.pid;
+                const uint32_t hi = p.pflag[d.start + d.len - 1] >> 2, lo = d.start ? (p.pflag[d.start - 1] >> 2) : 0u;
+                o.flags = hi != lo ? 1u : 0u;  // a chain-complete event lies inside the window
+                o.reserved = 0;
+                p.windows[rw++] = o;
             }
-            o.reserved = 0;
-            p.windows[r++] = o;
+            if (eo[k] & EO_MATCH) {
+                const uint32_t j = j0 + k;
+                p.chain_pid[rc] = *reinterpret_cast<const uint32_t *>(p.batch + (size_t)p.surv_src[j] * CH_REC_BYTES);
+                p.chain_idx[rc] = p.surv_arrival ? p.surv_arrival[j] : p.base_arrival + p.surv_src[j];
+                rc++;
+            }
         }
     }
 }
@@ -415,7 +385,7 @@ __global__ void __launch_bounds__(WIN_THREADS) window_order(const WinParams p) {
 // exactly once (the 288*S term of the algorithmic bytes).
 // ---------------------------------------------------------------------------------------
 struct GatherParams {
-    const uint32_t *sval;
+    const uint32_t *sval;        // sorted values (entry id in the low 27 bits)
     uint32_t M, P;
     const uint32_t *surv_src;
     const uint8_t *batch;        // this batch's records (device)
@@ -434,7 +404,7 @@ __global__ void __launch_bounds__(256) gather_records(const GatherParams g) {
         // lane r (< cnt) resolves the source of record base+r
         const uint8_t *src = nullptr;
         if ((uint32_t)lane < cnt) {
-            uint32_t e = g.sval[base + lane];
+            uint32_t e = g.sval[base + lane] & VAL_ID_MASK;
             src = e < g.P ? g.prev_arena + (size_t)g.pend_slot[e] * CH_REC_BYTES
                           : g.batch + (size_t)g.surv_src[e - g.P] * CH_REC_BYTES;
         }
