@@ -143,21 +143,27 @@ void *chronos_stream(chronos_ctx *ctx);
 /* owner rank of a pid: hash32(pid) % world. Exposed so host code and tests agree. */
 uint32_t chronos_owner_of(uint32_t pid, uint32_t world);
 
-/* Stage 1 on the rank that holds a contiguous slice of the batch: filter it, then pack
- * the survivors per owner rank (stable: arrival order kept inside each destination)
- * into caller-provided DEVICE buffers of capacity `cap` entries:
- *   send_records cap*288 bytes, send_arrival cap u64, send_meta cap u8.
- * counts_host[world] receives the per-destination entry counts (this call waits for the
- * GPU).  Destination d's entries start at the running sum of counts. */
+/* Stage 1 on the rank that holds a contiguous slice of the batch: filter it, then pack the
+ * survivors per owner rank (stable: arrival order kept inside each destination) into
+ * caller-provided DEVICE buffers in TRANSPORT FORM:
+ *   send_hdr   one u64 per surviving event: arrival index (48 bits) | META bits << 48 |
+ *              slot count << 56
+ *   send_slots the event's record as 3..18 slots of 16 bytes: chunk 0 (pid, comm[0:12]),
+ *              chunk 1 (comm[12:16], argv[0:12]), chunk 17 (argv[252:256], type) and then as
+ *              many of the chunks 2..16 as argv reaches into. Bytes behind a field's NUL
+ *              are not transported (a live sensor zero-fills them, chronos_sensor.py:52/:69;
+ *              the receiver restores zeros), which cuts the NVLink volume about 3.5x.
+ * entry_counts_host[world] / slot_counts_host[world] receive the per-destination counts
+ * (this call waits for the GPU). Destination d's data starts at the running sums. */
 int chronos_filter_partition(chronos_ctx *ctx, const void *records, uint64_t n, uint64_t base_arrival_index,
-                             uint32_t world, void *send_records, uint64_t *send_arrival, uint8_t *send_meta,
-                             uint64_t cap, uint64_t *counts_host);
+                             uint32_t world, void *send_slots, uint64_t cap_slots, uint64_t *send_hdr,
+                             uint64_t cap_entries, uint64_t *entry_counts_host, uint64_t *slot_counts_host);
 
-/* Stage 2 on the owner rank: run grouping + window logic on `n` already-filtered
- * entries (device pointers, concatenated in source-rank order = global arrival order).
- * Results are fetched with the calls above; survivor indices are then entry positions. */
-int chronos_submit_survivors(chronos_ctx *ctx, const void *records, const uint64_t *arrival, const uint8_t *meta,
-                             uint64_t n);
+/* Stage 2 on the owner rank: run grouping + window logic on `n_entries` already-filtered
+ * events in transport form (device pointers, concatenated in source-rank order = global
+ * arrival order). Results are fetched with the calls above. */
+int chronos_submit_survivors(chronos_ctx *ctx, const void *slots, const uint64_t *hdr, uint64_t n_entries,
+                             uint64_t n_slots);
 
 /* ---- allocation-free filtering ------------------------------------------------------------ */
 

@@ -62,9 +62,9 @@ SIGNATURES = {
     "chronos_last_launches": (c_int, [c_void_p, POINTER(c_uint64)]),
     "chronos_stream": (c_void_p, [c_void_p]),
     "chronos_owner_of": (c_uint32, [c_uint32, c_uint32]),
-    "chronos_filter_partition": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64, c_uint32, c_void_p, c_void_p,
-                                         c_void_p, c_uint64, c_void_p]),
-    "chronos_submit_survivors": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_uint64]),
+    "chronos_filter_partition": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64, c_uint32, c_void_p, c_uint64,
+                                         c_void_p, c_uint64, c_void_p, c_void_p]),
+    "chronos_submit_survivors": (c_int, [c_void_p, c_void_p, c_void_p, c_uint64, c_uint64]),
     "chronos_filter_noalloc": (c_int, [c_int, c_void_p, c_void_p, c_uint64, c_void_p, c_void_p, c_void_p, c_void_p,
                                        c_char_p, c_uint64]),
     "chronos_tracegen_host": (c_int, [POINTER(TracegenCfg), c_void_p, c_uint64, c_uint64, c_void_p]),

@@ -72,7 +72,9 @@ struct chronos_ctx {
     DevBuf d_batch;
     // entry arrays (capacity in entries = ecap)
     DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, pflag, entry_out, wsorted, windows, radix_table;
-    DevBuf sp_key, sp_src, sp_meta, tile_count;  // filter's tile-local compaction
+    DevBuf sp_key, sp_src, sp_meta, sp_ns, tile_count;  // filter's tile-local compaction
+    DevBuf surv_pid, surv_ns, ns32, slot_off;            // arrival-ordered pid copy; transport-form bookkeeping
+    const uint4 *b_slots = nullptr;                      // transport-form batch (chronos_submit_survivors)
     // kill-chain labeller + persistent per-PID table (chain.cuh)
     DevBuf pid_tab, pt_count, chain_pid, chain_idx;
     uint32_t pt_cap = 0;
@@ -207,13 +209,28 @@ __global__ void init_scalars_kernel(DeviceScalars *s) {
     s->n_chains = 0;
 }
 
-// Stage-2 entry (already-filtered events): pid out of the record, identity src index.
-__global__ void extract_pid_kernel(const uint8_t *recs, uint32_t n, uint32_t *key, uint32_t *src, uint32_t *k_or,
-                                   uint32_t *k_and) {
+// Stage 2 of the sharded path, step 1: split the header words of the received entries
+// (arrival 48 bits | meta << 48 | slots << 56)
+__global__ void unpack_hdr_kernel(const uint64_t *hdr, uint32_t n, uint64_t *arrival, uint8_t *meta, uint8_t *ns,
+                                  uint32_t *ns32) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint64_t h = hdr[i];
+        arrival[i] = h & 0xFFFFFFFFFFFFull;
+        meta[i] = (uint8_t)(h >> 48);
+        const uint32_t k = (uint32_t)(h >> 56);
+        ns[i] = (uint8_t)k;
+        ns32[i] = k;
+    }
+}
+
+// step 2 (after the scan of the slot counts): the pid is the first word of an entry's slot 0
+__global__ void extract_pid_kernel(const uint4 *slots, const uint32_t *slot_off, uint32_t n, uint32_t *key,
+                                   uint32_t *pid_copy, uint32_t *src, uint32_t *k_or, uint32_t *k_and) {
     uint32_t o = 0, a = 0xffffffffu;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        uint32_t k = *reinterpret_cast<const uint32_t *>(recs + (size_t)i * CH_REC_BYTES);
+        const uint32_t k = reinterpret_cast<const uint32_t *>(slots + slot_off[i])[0];
         key[i] = k;
+        pid_copy[i] = k;
         src[i] = i;
         o |= k;
         a &= k;
@@ -250,28 +267,28 @@ __global__ void pack_windows_kernel(const uint8_t *arena, const chronos_window *
     }
 }
 
-// owner rank of every survivor + per-owner counts (shared-memory histogram per block)
-__global__ void owner_keys_kernel(const uint32_t *pid, uint32_t n, uint32_t world, uint32_t *owner, uint32_t *counts) {
-    __shared__ uint32_t h[64];
-    if (threadIdx.x < 64) h[threadIdx.x] = 0;
+// owner rank of every survivor + per-owner entry and slot counts (shared-memory histograms)
+__global__ void owner_keys_kernel(const uint32_t *pid, const uint8_t *ns, uint32_t n, uint32_t world, uint32_t *owner,
+                                  uint32_t *entry_counts, uint32_t *slot_counts) {
+    __shared__ uint32_t h[64], hs[64];
+    if (threadIdx.x < 64) { h[threadIdx.x] = 0; hs[threadIdx.x] = 0; }
     __syncthreads();
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t o = hash32(pid[i]) % world;
         owner[i] = o;
         atomicAdd(&h[o], 1u);
+        atomicAdd(&hs[o], (uint32_t)ns[i]);
     }
     __syncthreads();
-    if (threadIdx.x < world && h[threadIdx.x]) atomicAdd(&counts[threadIdx.x], h[threadIdx.x]);
+    if (threadIdx.x < world && h[threadIdx.x]) {
+        atomicAdd(&entry_counts[threadIdx.x], h[threadIdx.x]);
+        atomicAdd(&slot_counts[threadIdx.x], hs[threadIdx.x]);
+    }
 }
 
-// send-side metadata in destination order: arrival index and meta of survivor perm[i]
-__global__ void pack_meta_kernel(const uint32_t *perm, const uint32_t *src, const uint8_t *meta, uint32_t n,
-                                 uint64_t base, uint64_t *out_arrival, uint8_t *out_meta) {
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t j = perm[i];
-        out_arrival[i] = base + src[j];
-        out_meta[i] = meta[j];
-    }
+// slot counts in stream order: ns32[i] = ns[perm[i]]
+__global__ void permute_ns_kernel(const uint32_t *perm, const uint8_t *ns, uint32_t n, uint32_t *ns32) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) ns32[i] = ns[perm[i]];
 }
 
 __global__ void add_base_kernel(const uint32_t *src, uint32_t n, uint64_t base, uint64_t *out) {
@@ -386,11 +403,15 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
     if ((rc = ensure(c, c->sp_key, slots * 4))) return rc;
     if ((rc = ensure(c, c->sp_src, slots * 4))) return rc;
     if ((rc = ensure(c, c->sp_meta, slots))) return rc;
+    if ((rc = ensure(c, c->sp_ns, slots))) return rc;
+    if ((rc = ensure(c, c->surv_pid, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_ns, n + 1))) return rc;
     if ((rc = ensure(c, c->tile_count, ((uint64_t)fp.tile_end + 1) * 4))) return rc;
     fp.tile_count = ptr<uint32_t>(c->tile_count);
     fp.sp_key = ptr<uint32_t>(c->sp_key);
     fp.sp_src = ptr<uint32_t>(c->sp_src);
     fp.sp_meta = ptr<uint8_t>(c->sp_meta);
+    fp.sp_ns = ptr<uint8_t>(c->sp_ns);
     fp.out_count = &ds->surv_count;
     fp.key_or = &ds->key_or;
     fp.key_and = &ds->key_and;
@@ -405,9 +426,12 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
     cp.sp_key = fp.sp_key;
     cp.sp_src = fp.sp_src;
     cp.sp_meta = fp.sp_meta;
+    cp.sp_ns = fp.sp_ns;
     cp.out_key = out_key;
     cp.out_src = ptr<uint32_t>(c->surv_src);
     cp.out_meta = ptr<uint8_t>(c->surv_meta);
+    cp.out_ns = ptr<uint8_t>(c->surv_ns);
+    cp.out_pid = ptr<uint32_t>(c->surv_pid);
     cp.n_tiles = fp.tile_end;
     cp.tile = (uint32_t)TILE;
     cp.total = &ds->surv_count;
@@ -549,6 +573,9 @@ int run_window_stage(chronos_ctx *c) {
         g.pend_slot = P ? ptr<uint32_t>(c->pend_slot[prev]) + (pc - P) : nullptr;
         g.prev_arena = ptr<uint8_t>(c->arena[prev]);
         g.arena = ptr<uint8_t>(c->arena[cur]);
+        g.slots = c->b_slots;
+        g.slot_off = c->b_slots ? ptr<uint32_t>(c->slot_off) : nullptr;
+        g.slot_ns = c->b_slots ? ptr<uint8_t>(c->surv_ns) : nullptr;
         // bandwidth-bound copy on a second stream; it runs while the host enqueues the window
         // scans and shares the GPU with them as far as registers allow
         uint32_t blocks = (uint32_t)std::min<uint64_t>((M + 127) / 128, (uint64_t)c->sm_count * 8);
@@ -573,7 +600,7 @@ int run_window_stage(chronos_ctx *c) {
         w.base_arrival = c->b_base;
         const uint64_t pc = c->pend_cap[prev];
         w.pend_arrival = P ? ptr<uint64_t>(c->pend_arrival[prev]) + (pc - P) : nullptr;
-        w.batch = c->b_records;
+        w.surv_pid = ptr<uint32_t>(c->surv_pid);
         w.pid_tab = ptr<uint64_t>(c->pid_tab);
         w.pid_mask = c->pt_cap - 1;
         w.pid_count = ptr<uint32_t>(c->pt_count);
@@ -794,7 +821,7 @@ int chronos_destroy(chronos_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->pflag,
-                     &c->entry_out, &c->wsorted, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+                     &c->entry_out, &c->wsorted, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->ns32, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
                      &c->tickets, &c->scalars, &c->scan_status, &c->pack, &c->pack_off};
@@ -832,6 +859,7 @@ int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t bas
         }
     }
     c->b_records = d_recs;
+    c->b_slots = nullptr;
     c->b_explicit_arrival = false;
     if (n && (rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA) + c->b_P))) return rc;
     if ((rc = run_window_stage(c))) return rc;
@@ -839,28 +867,36 @@ int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t bas
     return CHRONOS_OK;
 }
 
-int chronos_submit_survivors(chronos_ctx *c, const void *records, const uint64_t *arrival, const uint8_t *meta,
-                             uint64_t n) {
+int chronos_submit_survivors(chronos_ctx *c, const void *slots, const uint64_t *hdr, uint64_t n, uint64_t n_slots) {
     if (!c) return CHRONOS_E_ARG;
-    if (n && (!records || !arrival || !meta)) return fail(c, CHRONOS_E_ARG, "NULL argument");
-    if (n && (!is_device_pointer(records) || ((uintptr_t)records & 15)))
-        return fail(c, CHRONOS_E_ARG, "records must be a 16-byte aligned device pointer");
+    if (n && (!slots || !hdr)) return fail(c, CHRONOS_E_ARG, "NULL argument");
+    if (n && (!is_device_pointer(slots) || ((uintptr_t)slots & 15) || !is_device_pointer(hdr)))
+        return fail(c, CHRONOS_E_ARG, "slots and hdr must be device pointers (slots 16-byte aligned)");
+    if (n_slots < 3 * n || n_slots > 18 * n) return fail(c, CHRONOS_E_ARG, "slot count inconsistent with entry count");
     int rc = begin_batch(c, n, 0);
     if (rc) return rc;
-    c->b_records = static_cast<const uint8_t *>(records);
+    c->b_records = nullptr;
+    c->b_slots = static_cast<const uint4 *>(slots);
     c->b_explicit_arrival = true;
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     if (n) {
         if ((rc = ensure(c, c->surv_arrival, n * 8))) return rc;
-        CK(cudaMemcpyAsync(c->surv_arrival.p, arrival, n * 8, cudaMemcpyDefault, c->stream));
-        CK(cudaMemcpyAsync(c->surv_meta.p, meta, n, cudaMemcpyDefault, c->stream));
-        extract_pid_kernel<<<(unsigned)std::min<uint64_t>((n + 255) / 256, 2048), 256, 0, c->stream>>>(
-            c->b_records, (uint32_t)n, ptr<uint32_t>(c->keyA) + c->b_P, ptr<uint32_t>(c->surv_src), &ds->key_or,
-            &ds->key_and);
-        c->launches++;
-        const uint32_t cnt = (uint32_t)n;
-        CK(cudaMemcpyAsync(&ds->surv_count, &cnt, 4, cudaMemcpyHostToDevice, c->stream));
-        CK(cudaStreamSynchronize(c->stream));  // cnt lives on this stack frame
+        if ((rc = ensure(c, c->surv_pid, (n + 1) * 4))) return rc;
+        if ((rc = ensure(c, c->surv_ns, n + 1))) return rc;
+        if ((rc = ensure(c, c->slot_off, (n + 8) * 4))) return rc;
+        const unsigned blocks = (unsigned)std::min<uint64_t>((n + 255) / 256, 2048);
+        unpack_hdr_kernel<<<blocks, 256, 0, c->stream>>>(hdr, (uint32_t)n, ptr<uint64_t>(c->surv_arrival),
+                                                         ptr<uint8_t>(c->surv_meta), ptr<uint8_t>(c->surv_ns),
+                                                         ptr<uint32_t>(c->slot_off));
+        if ((rc = launch_scan(c, ptr<uint32_t>(c->slot_off), n))) return rc;
+        extract_pid_kernel<<<blocks, 256, 0, c->stream>>>(c->b_slots, ptr<uint32_t>(c->slot_off), (uint32_t)n,
+                                                          ptr<uint32_t>(c->keyA) + c->b_P, ptr<uint32_t>(c->surv_pid),
+                                                          ptr<uint32_t>(c->surv_src), &ds->key_or, &ds->key_and);
+        CK(cudaGetLastError());
+        c->launches += 2;
+        c->h_scalars->pad[0] = (uint32_t)n;  // pinned: stays valid until the copy has run
+        CK(cudaMemcpyAsync(&ds->surv_count, &c->h_scalars->pad[0], 4, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
     }
     if ((rc = run_window_stage(c))) return rc;
     c->phase = chronos_ctx::SUBMITTED;
@@ -1071,10 +1107,11 @@ void *chronos_stream(chronos_ctx *c) { return c ? (void *)c->stream : nullptr; }
 uint32_t chronos_owner_of(uint32_t pid, uint32_t world) { return world ? hash32(pid) % world : 0; }
 
 int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, uint64_t base_arrival_index,
-                             uint32_t world, void *send_records, uint64_t *send_arrival, uint8_t *send_meta,
-                             uint64_t cap, uint64_t *counts_host) {
-    if (!c || !counts_host || world == 0 || world > 64) return c ? fail(c, CHRONOS_E_ARG, "bad argument") : CHRONOS_E_ARG;
-    if (n && (!records || !send_records || !send_arrival || !send_meta)) return fail(c, CHRONOS_E_ARG, "NULL argument");
+                             uint32_t world, void *send_slots, uint64_t cap_slots, uint64_t *send_hdr,
+                             uint64_t cap_entries, uint64_t *entry_counts_host, uint64_t *slot_counts_host) {
+    if (!c || !entry_counts_host || !slot_counts_host || world == 0 || world > 64)
+        return c ? fail(c, CHRONOS_E_ARG, "bad argument") : CHRONOS_E_ARG;
+    if (n && (!records || !send_slots || !send_hdr)) return fail(c, CHRONOS_E_ARG, "NULL argument");
     CK(cudaSetDevice(c->device));
     if (c->phase == chronos_ctx::SUBMITTED) {
         int rc0 = finish_batch(c);
@@ -1082,7 +1119,7 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
     }
     if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
                                       (unsigned long long)n, (unsigned long long)c->max_batch);
-    for (uint32_t d = 0; d < world; d++) counts_host[d] = 0;
+    for (uint32_t d = 0; d < world; d++) entry_counts_host[d] = slot_counts_host[d] = 0;
     if (!n) return CHRONOS_OK;
     int rc;
     const uint8_t *d_recs;
@@ -1097,12 +1134,14 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
     // scratch only: the per-PID state of this context is not touched by stage 1
     c->launches = 0;
     c->scan_slot = 0;
+    c->n_tev = 0;
     if ((rc = ensure(c, c->keyA, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->keyB, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->valA, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->valB, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
+    if ((rc = ensure(c, c->ns32, (n + 8) * 4))) return rc;
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     CK(cudaEventRecord(c->ev_start, c->stream));
     CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
@@ -1112,16 +1151,17 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
     CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     const uint64_t S = c->h_scalars->surv_count;
-    if (S > cap) return fail(c, CHRONOS_E_CAPACITY, "%llu survivors do not fit the send buffers (%llu)",
-                             (unsigned long long)S, (unsigned long long)cap);
+    if (S > cap_entries) return fail(c, CHRONOS_E_CAPACITY, "%llu survivors do not fit the header buffer (%llu)",
+                                     (unsigned long long)S, (unsigned long long)cap_entries);
     if (S) {
         // stable counting sort by owner rank = one radix pass over the owner keys
         uint32_t *owner = ptr<uint32_t>(c->valB);
-        uint32_t *ocount = &ds->pad[0];  // world <= 10 words live here; larger worlds use the tickets tail
-        if (world > 10) ocount = ptr<uint32_t>(c->tickets);
-        CK(cudaMemsetAsync(ocount, 0, world * 4, c->stream));
+        if ((rc = ensure(c, c->pack_off, 1024))) return rc;
+        uint32_t *ocount = ptr<uint32_t>(c->pack_off);  // [0,64) entries per owner, [64,128) slots per owner
+        CK(cudaMemsetAsync(ocount, 0, 512, c->stream));
         const unsigned blocks = (unsigned)std::min<uint64_t>((S + 255) / 256, 2048);
-        owner_keys_kernel<<<blocks, 256, 0, c->stream>>>(ptr<uint32_t>(c->keyA), (uint32_t)S, world, owner, ocount);
+        owner_keys_kernel<<<blocks, 256, 0, c->stream>>>(ptr<uint32_t>(c->keyA), ptr<uint8_t>(c->surv_ns), (uint32_t)S,
+                                                         world, owner, ocount, ocount + 64);
         uint32_t tile_keys = 4096;
         while ((S + tile_keys - 1) / tile_keys > 1024) tile_keys *= 2;
         const uint32_t n_tiles = (uint32_t)((S + tile_keys - 1) / tile_keys);
@@ -1143,27 +1183,37 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
         radix_hist<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
         if ((rc = launch_scan(c, rp.table, (uint64_t)RADIX_BINS * n_tiles))) return rc;
         radix_scatter<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
-        GatherParams g;
-        g.sval = rp.vals_out;
-        g.M = (uint32_t)S;
-        g.P = 0;
-        g.surv_src = ptr<uint32_t>(c->surv_src);
-        g.batch = d_recs;
-        g.pend_slot = nullptr;
-        g.prev_arena = nullptr;
-        g.arena = static_cast<uint8_t *>(send_records);
-        gather_records<<<(unsigned)std::min<uint64_t>((S + 127) / 128, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(g);
-        pack_meta_kernel<<<blocks, 256, 0, c->stream>>>(rp.vals_out, ptr<uint32_t>(c->surv_src),
-                                                        ptr<uint8_t>(c->surv_meta), (uint32_t)S, base_arrival_index,
-                                                        send_arrival, send_meta);
+        // slot offsets of the transport stream, then the pack itself
+        permute_ns_kernel<<<blocks, 256, 0, c->stream>>>(rp.vals_out, ptr<uint8_t>(c->surv_ns), (uint32_t)S,
+                                                         ptr<uint32_t>(c->ns32));
+        if ((rc = launch_scan(c, ptr<uint32_t>(c->ns32), S))) return rc;
+        uint32_t hc[128];
+        CK(cudaMemcpyAsync(hc, ocount, 512, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        uint64_t tot_slots = 0;
+        for (uint32_t d = 0; d < world; d++) {
+            entry_counts_host[d] = hc[d];
+            slot_counts_host[d] = hc[64 + d];
+            tot_slots += hc[64 + d];
+        }
+        if (tot_slots > cap_slots) return fail(c, CHRONOS_E_CAPACITY, "%llu transport slots do not fit the send buffer (%llu)",
+                                               (unsigned long long)tot_slots, (unsigned long long)cap_slots);
+        PackParams pk;
+        pk.perm = rp.vals_out;
+        pk.surv_src = ptr<uint32_t>(c->surv_src);
+        pk.surv_meta = ptr<uint8_t>(c->surv_meta);
+        pk.surv_ns = ptr<uint8_t>(c->surv_ns);
+        pk.off = ptr<uint32_t>(c->ns32);
+        pk.batch = d_recs;
+        pk.base_arrival = base_arrival_index;
+        pk.S = (uint32_t)S;
+        pk.slots = static_cast<uint4 *>(send_slots);
+        pk.hdr = send_hdr;
+        pack_transport<<<(unsigned)std::min<uint64_t>((S + 255) / 256, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(pk);
         CK(cudaGetLastError());
         c->launches += 5;
-        uint32_t hc[64];
-        CK(cudaMemcpyAsync(hc, ocount, world * 4, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaEventRecord(c->ev_end, c->stream));
         CK(cudaStreamSynchronize(c->stream));
-        for (uint32_t d = 0; d < world; d++) counts_host[d] = hc[d];
-        if (world > 10) CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
     }
     cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
     cudaGetLastError();
@@ -1307,6 +1357,7 @@ int chronos_filter_noalloc(int device, void *stream, const void *records, uint64
         fp.sp_key = reinterpret_cast<uint32_t *>(base + noalloc::OFF_SP_KEY);
         fp.sp_src = reinterpret_cast<uint32_t *>(base + noalloc::OFF_SP_SRC);
         fp.sp_meta = base + noalloc::OFF_SP_META;
+        fp.sp_ns = nullptr;
         fp.out_count = hdr + 2;
         fp.key_or = hdr + 3;
         fp.key_and = hdr + 4;
@@ -1323,9 +1374,12 @@ int chronos_filter_noalloc(int device, void *stream, const void *records, uint64
         cp.sp_key = fp.sp_key;
         cp.sp_src = fp.sp_src;
         cp.sp_meta = fp.sp_meta;
+        cp.sp_ns = nullptr;
         cp.out_key = survivor_pid;
         cp.out_src = survivor_idx;
         cp.out_meta = survivor_meta;
+        cp.out_ns = nullptr;
+        cp.out_pid = nullptr;
         cp.n_tiles = fp.tile_end;
         cp.tile = FILTER_TILE;
         cp.total = hdr + 2;

@@ -42,7 +42,8 @@ struct FilterParams {
     uint32_t *tile_count;    // survivors per tile (one word per tile of the batch)
     uint32_t *sp_key;        // tile-local compaction: slot tile*TILE + rank holds the pid,
     uint32_t *sp_src;        //   the batch-local record index
-    uint8_t *sp_meta;        //   and the META_* bits of the tile's rank-th survivor
+    uint8_t *sp_meta;        //   the META_* bits of the tile's rank-th survivor
+    uint8_t *sp_ns;          //   and (optional, may be nullptr) its size in 16-byte transport slots
     uint32_t *out_count;     // total survivors (atomicAdd, one per CTA)
     uint32_t *key_or;        // OR / AND over survivor pids (radix pass planning)
     uint32_t *key_and;
@@ -234,6 +235,15 @@ __device__ __forceinline__ uint32_t argv_trigger_chunk(const uint32_t *w, int al
         cur = nxt;
     }
     return meta;
+}
+
+// Transport form of a surviving record (multi-GPU exchange, chronos_filter_partition): the
+// 16-byte chunks that can hold anything before argv's NUL -- chunk 0 (pid, comm[0:12]),
+// chunk 1 (comm[12:16], argv[0:12]), chunk 17 (argv[252:256], type) and as many of the
+// chunks 2..16 as argv reaches into. Bytes after the NUL are not transported.
+__host__ __device__ __forceinline__ uint32_t transport_slots(int alen) {
+    const int extra = alen <= 12 ? 0 : (alen - 12 + 15) >> 4;
+    return 3u + (uint32_t)(extra > 15 ? 15 : extra);
 }
 
 constexpr int FILTER_TILE = 32;  // records per tile: one per lane of the (single) warp of a CTA
@@ -463,6 +473,7 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
                 p.sp_key[slot] = pid;
                 p.sp_src[slot] = (uint32_t)first + lane;
                 p.sp_meta[slot] = (uint8_t)((meta | found) & 0x7Fu);
+                if (p.sp_ns) p.sp_ns[slot] = (uint8_t)transport_slots(alen);
             }
             k_or |= __reduce_or_sync(FULL, keep ? pid : 0u);
             k_and &= __reduce_and_sync(FULL, keep ? pid : 0xffffffffu);
@@ -484,9 +495,12 @@ struct CompactParams {
     const uint32_t *sp_key;
     const uint32_t *sp_src;
     const uint8_t *sp_meta;
+    const uint8_t *sp_ns;    // optional
     uint32_t *out_key;
     uint32_t *out_src;
     uint8_t *out_meta;
+    uint8_t *out_ns;         // optional
+    uint32_t *out_pid;       // optional second copy of the pids (the sort consumes out_key)
     uint32_t n_tiles;
     uint32_t tile;       // records per filter tile
     const uint32_t *total;  // device scalar: survivor count == tile_off[n_tiles]
@@ -502,6 +516,8 @@ __global__ void __launch_bounds__(256) compact_survivors(const CompactParams c) 
             c.out_key[lo + j] = c.sp_key[base + j];
             c.out_src[lo + j] = c.sp_src[base + j];
             c.out_meta[lo + j] = c.sp_meta[base + j];
+            if (c.out_ns) c.out_ns[lo + j] = c.sp_ns[base + j];
+            if (c.out_pid) c.out_pid[lo + j] = c.sp_key[base + j];
         }
     }
 }

@@ -60,7 +60,7 @@ struct WinParams {
     const uint64_t *surv_arrival;   // S explicit arrival indices, or nullptr => base_arrival + surv_src
     uint64_t base_arrival;
     const uint64_t *pend_arrival;   // P (previous batch)
-    const uint8_t *batch;           // this batch's records (pid of a chain match is read back from there)
+    const uint32_t *surv_pid;       // S pids in arrival order (the sort consumed the key array)
     // per-PID table (chain.cuh)
     uint64_t *pid_tab;
     uint32_t pid_mask;
@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) {
             }
             if (eo[k] & EO_MATCH) {
                 const uint32_t j = j0 + k;
-                p.chain_pid[rc] = *reinterpret_cast<const uint32_t *>(p.batch + (size_t)p.surv_src[j] * CH_REC_BYTES);
+                p.chain_pid[rc] = p.surv_pid[j];
                 p.chain_idx[rc] = p.surv_arrival ? p.surv_arrival[j] : p.base_arrival + p.surv_src[j];
                 rc++;
             }
@@ -392,6 +392,11 @@ struct GatherParams {
     const uint32_t *pend_slot;   // P
     const uint8_t *prev_arena;
     uint8_t *arena;
+    // transport form (chronos_submit_survivors): entry j's record is slot_ns[j] 16-byte slots
+    // starting at slot_off[j] of `slots`; nullptr => `batch` holds plain 288-byte records
+    const uint4 *slots;
+    const uint32_t *slot_off;
+    const uint8_t *slot_ns;
 };
 
 __global__ void __launch_bounds__(256) gather_records(const GatherParams g) {
@@ -403,10 +408,14 @@ __global__ void __launch_bounds__(256) gather_records(const GatherParams g) {
         const uint32_t cnt = min(GROUP, g.M - base);
         // lane r (< cnt) resolves the source of record base+r
         const uint8_t *src = nullptr;
+        uint32_t ns = 0;  // 0: plain 288-byte record at src; else transport form of ns slots
         if ((uint32_t)lane < cnt) {
-            uint32_t e = g.sval[base + lane] & VAL_ID_MASK;
-            src = e < g.P ? g.prev_arena + (size_t)g.pend_slot[e] * CH_REC_BYTES
-                          : g.batch + (size_t)g.surv_src[e - g.P] * CH_REC_BYTES;
+            const uint32_t e = g.sval[base + lane] & VAL_ID_MASK;
+            if (e < g.P) src = g.prev_arena + (size_t)g.pend_slot[e] * CH_REC_BYTES;
+            else if (g.slots) {
+                src = reinterpret_cast<const uint8_t *>(g.slots + g.slot_off[e - g.P]);
+                ns = g.slot_ns[e - g.P];
+            } else src = g.batch + (size_t)g.surv_src[e - g.P] * CH_REC_BYTES;
         }
         uint4 *dst = reinterpret_cast<uint4 *>(g.arena + (size_t)base * CH_REC_BYTES);
 #pragma unroll
@@ -416,7 +425,77 @@ __global__ void __launch_bounds__(256) gather_records(const GatherParams g) {
             const uint32_t ch = c - r * CH_REC_CHUNKS;
             const unsigned long long sp =
                 __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, (int)(r & 31u));
-            if (r < cnt) dst[c] = reinterpret_cast<const uint4 *>((uintptr_t)sp)[ch];
+            const uint32_t rns = __shfl_sync(0xffffffffu, ns, (int)(r & 31u));
+            if (r < cnt) {
+                const uint4 *s4 = reinterpret_cast<const uint4 *>((uintptr_t)sp);
+                uint4 v = make_uint4(0u, 0u, 0u, 0u);
+                if (rns == 0) v = s4[ch];
+                else {  // slot 0,1 = chunks 0,1; slot 2 = chunk 17; slots 3.. = chunks 2..
+                    const uint32_t sl = ch < 2 ? ch : (ch == 17 ? 2u : ch + 1u);
+                    if (sl < rns) v = s4[sl];
+                }
+                dst[c] = v;
+            }
+        }
+    }
+}
+
+// Sender side of the transport form: entry i of the (owner, arrival)-ordered stream is
+// survivor perm[i]; its needed chunks go to slots [off[i], off[i]+ns) and its header word
+// (arrival 48 bits | meta << 48 | ns << 56) to hdr[i]. One lane per entry resolves the
+// source, then the warp copies the 16-byte slots of its 32 entries cooperatively.
+struct PackParams {
+    const uint32_t *perm;      // S
+    const uint32_t *surv_src;  // S
+    const uint8_t *surv_meta;  // S
+    const uint8_t *surv_ns;    // S
+    const uint32_t *off;       // S: exclusive scan of ns in stream order
+    const uint8_t *batch;
+    uint64_t base_arrival;
+    uint32_t S;
+    uint4 *slots;
+    uint64_t *hdr;
+};
+
+__global__ void __launch_bounds__(256) pack_transport(const PackParams g) {
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t base = warp_global * 32; base < g.S; base += n_warps * 32) {
+        const uint32_t i = base + lane;
+        const uint4 *src = nullptr;
+        uint32_t ns = 0, off = 0;
+        if (i < g.S) {
+            const uint32_t j = g.perm[i];
+            const uint32_t rec = g.surv_src[j];
+            src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
+            ns = g.surv_ns[j];
+            off = g.off[i];
+            g.hdr[i] = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)g.surv_meta[j] << 48) | ((uint64_t)ns << 56);
+        }
+        uint32_t incl = ns;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        const uint32_t excl = incl - ns, total = __shfl_sync(0xffffffffu, incl, 31);
+        const uint32_t first_off = __shfl_sync(0xffffffffu, off, 0);
+        for (uint32_t b0 = 0; b0 < total; b0 += 32) {
+            const uint32_t k = b0 + lane;
+            int sidx = 0;  // owner lane of slot k (see filter.cuh phase B2)
+#pragma unroll
+            for (int step = 16; step >= 1; step >>= 1) {
+                const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
+                if (vv <= k) sidx += step;
+            }
+            const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
+            const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
+            if (k < total) {
+                const uint32_t sl = k - ex;  // slot within the entry
+                const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
+                g.slots[first_off + k] = reinterpret_cast<const uint4 *>((uintptr_t)sp)[ch];
+            }
         }
     }
 }

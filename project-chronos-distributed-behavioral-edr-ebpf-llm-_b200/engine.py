@@ -91,9 +91,10 @@ class Context:
         """ptr: raw host or device address of n records (device pointers are used in place)."""
         self._check(self._L.chronos_submit(self._h, c_void_p(int(ptr)), int(n), int(base_arrival_index)))
 
-    def submit_survivors_ptr(self, rec_ptr, arrival_ptr, meta_ptr, n):
-        self._check(self._L.chronos_submit_survivors(self._h, c_void_p(int(rec_ptr)), c_void_p(int(arrival_ptr)),
-                                                     c_void_p(int(meta_ptr)), int(n)))
+    def submit_survivors_ptr(self, slots_ptr, hdr_ptr, n_entries, n_slots):
+        """Stage 2 of the sharded path: already-filtered events in transport form (device pointers)."""
+        self._check(self._L.chronos_submit_survivors(self._h, c_void_p(int(slots_ptr)), c_void_p(int(hdr_ptr)),
+                                                     int(n_entries), int(n_slots)))
 
     # ---- results -----------------------------------------------------------------------
     def fetch_counts(self):

@@ -39,28 +39,44 @@ def owner_of_np(pids, world):
     return (hash32_np(pids) % np.uint32(world)).astype(np.int64)
 
 
-def exchange(send_records, send_arrival, send_meta, send_counts, recv_records, recv_arrival, recv_meta, group=None):
+SLOT_BYTES = 16
+HDR_ARRIVAL_MASK = (1 << 48) - 1
+
+
+def pack_hdr(arrival, meta, nslots):
+    """Header word of the transport form: arrival (48 bits) | META bits << 48 | slot count << 56."""
+    return (np.asarray(arrival, dtype=np.uint64) & np.uint64(HDR_ARRIVAL_MASK)) | \
+        (np.asarray(meta, dtype=np.uint64) << np.uint64(48)) | (np.asarray(nslots, dtype=np.uint64) << np.uint64(56))
+
+
+def exchange(send_payload, send_hdr, entry_counts, unit_counts, unit_bytes, recv_payload, recv_hdr, group=None):
     """One all-to-all-v of packed survivors.
 
-    send_*: tensors holding, destination after destination, `send_counts[d]` entries for
-    rank d (records as uint8 rows of 288 bytes). recv_* are filled in source-rank order.
-    Returns (n_received, recv_counts). Counts travel first, then the three payloads."""
+    send_payload: uint8 tensor holding, destination after destination, `unit_counts[d]`
+    units of `unit_bytes` bytes for rank d (16-byte transport slots on the GPU path);
+    send_hdr: int64 tensor with `entry_counts[d]` header words for rank d. The recv_*
+    tensors are filled in source-rank order, which -- the slices being contiguous and
+    ordered -- is global arrival order. Counts travel first, then the two payloads.
+    Returns (n_entries_received, n_units_received)."""
     world = dist.get_world_size(group)
-    dev = send_records.device
-    sc = torch.as_tensor(np.asarray(send_counts, dtype=np.int64), device=dev)
-    rc = torch.empty(world, dtype=torch.int64, device=dev)
-    dist.all_to_all_single(rc, sc, group=group)
-    recv_counts = rc.cpu().numpy().astype(np.int64)
-    send_counts = np.asarray(send_counts, dtype=np.int64)
-    n_send, n_recv = int(send_counts.sum()), int(recv_counts.sum())
-    if n_recv > recv_arrival.numel():
-        raise _ffi.ChronosError(_ffi.E_CAPACITY, f"{n_recv} received survivors exceed the receive buffers")
-    ss, rs = send_counts.tolist(), recv_counts.tolist()
-    dist.all_to_all_single(recv_records.view(-1)[: n_recv * RECORD_BYTES], send_records.view(-1)[: n_send * RECORD_BYTES],
-                           [x * RECORD_BYTES for x in rs], [x * RECORD_BYTES for x in ss], group=group)
-    dist.all_to_all_single(recv_arrival[:n_recv], send_arrival[:n_send], rs, ss, group=group)
-    dist.all_to_all_single(recv_meta[:n_recv], send_meta[:n_send], rs, ss, group=group)
-    return n_recv, recv_counts
+    dev = send_hdr.device
+    sc = torch.as_tensor(np.concatenate([np.asarray(entry_counts, dtype=np.int64), np.asarray(unit_counts, dtype=np.int64)]),
+                         device=dev)
+    rc = torch.empty(2 * world, dtype=torch.int64, device=dev)
+    # counts of (entries, units) for every peer in one small all-to-all: layout [e_0..e_{w-1}, u_0..u_{w-1}]
+    # is regrouped so that rank d receives (e_d, u_d) from everybody
+    sc2 = torch.stack([sc[:world], sc[world:]], dim=1).contiguous().view(-1)
+    dist.all_to_all_single(rc, sc2, group=group)
+    rcn = rc.cpu().numpy().astype(np.int64).reshape(world, 2)
+    re_, ru = rcn[:, 0], rcn[:, 1]
+    se, su = np.asarray(entry_counts, dtype=np.int64), np.asarray(unit_counts, dtype=np.int64)
+    n_re, n_ru, n_se, n_su = int(re_.sum()), int(ru.sum()), int(se.sum()), int(su.sum())
+    if n_re > recv_hdr.numel() or n_ru * unit_bytes > recv_payload.numel():
+        raise _ffi.ChronosError(_ffi.E_CAPACITY, f"{n_re} entries / {n_ru} units received exceed the receive buffers")
+    dist.all_to_all_single(recv_payload.view(-1)[: n_ru * unit_bytes], send_payload.view(-1)[: n_su * unit_bytes],
+                           [int(x) * unit_bytes for x in ru], [int(x) * unit_bytes for x in su], group=group)
+    dist.all_to_all_single(recv_hdr[:n_re], send_hdr[:n_se], re_.tolist(), se.tolist(), group=group)
+    return n_re, n_ru
 
 
 class ShardedRunner:
@@ -69,16 +85,16 @@ class ShardedRunner:
     def __init__(self, rec_ptr, n, first, device, rank, world, cap=None):
         self.rec_ptr, self.n, self.first = int(rec_ptr), int(n), int(first)
         self.device, self.rank, self.world = int(device), int(rank), int(world)
-        self.cap = int(cap or max(n // 2, 1024))  # survivors per rank, sent or received
+        self.cap = int(cap or max(n // 2, 1024))   # survivors per rank, sent or received
+        self.cap_slots = self.cap * 8              # 16-byte transport slots (3..18 per survivor)
         self.ctx = Context(device=self.device, max_batch_events=max(self.n, self.cap))
         dev = torch.device("cuda", self.device)
-        self.send_records = torch.empty(self.cap * RECORD_BYTES, dtype=torch.uint8, device=dev)
-        self.send_arrival = torch.empty(self.cap, dtype=torch.int64, device=dev)
-        self.send_meta = torch.empty(self.cap, dtype=torch.uint8, device=dev)
-        self.recv_records = torch.empty(self.cap * RECORD_BYTES, dtype=torch.uint8, device=dev)
-        self.recv_arrival = torch.empty(self.cap, dtype=torch.int64, device=dev)
-        self.recv_meta = torch.empty(self.cap, dtype=torch.uint8, device=dev)
-        self._counts = (ctypes.c_uint64 * self.world)()
+        self.send_slots = torch.empty(self.cap_slots * SLOT_BYTES, dtype=torch.uint8, device=dev)
+        self.send_hdr = torch.empty(self.cap, dtype=torch.int64, device=dev)
+        self.recv_slots = torch.empty(self.cap_slots * SLOT_BYTES, dtype=torch.uint8, device=dev)
+        self.recv_hdr = torch.empty(self.cap, dtype=torch.int64, device=dev)
+        self._ec = (ctypes.c_uint64 * self.world)()
+        self._sc = (ctypes.c_uint64 * self.world)()
         self._L = _ffi.lib()
 
     def stream_ptr(self):
@@ -86,26 +102,23 @@ class ShardedRunner:
 
     def filter_partition(self, rec_ptr, n, base):
         rc = self._L.chronos_filter_partition(self.ctx._h, c_void_p(int(rec_ptr)), int(n), int(base), self.world,
-                                              c_void_p(self.send_records.data_ptr()),
-                                              c_void_p(self.send_arrival.data_ptr()),
-                                              c_void_p(self.send_meta.data_ptr()), self.cap, self._counts)
+                                              c_void_p(self.send_slots.data_ptr()), self.cap_slots,
+                                              c_void_p(self.send_hdr.data_ptr()), self.cap, self._ec, self._sc)
         self.ctx._check(rc)
-        return np.array(list(self._counts), dtype=np.int64)
+        return np.array(list(self._ec), dtype=np.int64), np.array(list(self._sc), dtype=np.int64)
 
     def step(self, reset=True):
         if reset:
             self.ctx.reset()  # benchmark steps repeat the same batch on a fresh process_memory
-        send_counts = self.filter_partition(self.rec_ptr, self.n, self.first)  # waits for stage 1
+        ec, sc = self.filter_partition(self.rec_ptr, self.n, self.first)  # waits for stage 1
         launches = self.ctx.last_launches()
-        n_recv, _ = exchange(self.send_records, self.send_arrival, self.send_meta, send_counts, self.recv_records,
-                             self.recv_arrival, self.recv_meta)
+        n_recv, n_slots = exchange(self.send_slots, self.send_hdr, ec, sc, SLOT_BYTES, self.recv_slots, self.recv_hdr)
         torch.cuda.current_stream().synchronize()  # NCCL ran on torch's stream; stage 2 runs on the library's
-        self.ctx.submit_survivors_ptr(self.recv_records.data_ptr(), self.recv_arrival.data_ptr(),
-                                      self.recv_meta.data_ptr(), n_recv)
+        self.ctx.submit_survivors_ptr(self.recv_slots.data_ptr(), self.recv_hdr.data_ptr(), n_recv, n_slots)
         c = self.ctx.fetch_counts()
         t, f = self.ctx.last_timing()
-        c.update(gpu_ms=t, filter_ms=f, launches=launches + self.ctx.last_launches(), n_sent=int(send_counts.sum()),
-                 n_received=n_recv)
+        c.update(gpu_ms=t, filter_ms=f, launches=launches + self.ctx.last_launches(), n_sent=int(ec.sum()),
+                 n_received=n_recv, slots_sent=int(sc.sum()))
         return c
 
     def e2e(self, steps, barrier, dist_mod):

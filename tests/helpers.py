@@ -72,3 +72,15 @@ def compare_batch(ctx, engine, trace, records, base=0, check_state=True):
             exp = np.stack([trace.record(int(i)) for i in mem])
             np.testing.assert_array_equal(grec, exp, err_msg="pending records differ")
     return res, ref
+
+
+def canonical(rows):
+    """Records as the transport form delivers them: bytes behind each field's NUL zeroed
+    (a live sensor zero-fills them anyway, chronos_sensor.py:52/:69)."""
+    out = np.array(rows, dtype=np.uint8, copy=True).reshape(-1, REC)
+    for off, cap in ((4, 16), (20, 256), (276, 10)):
+        f = out[:, off:off + cap]
+        seen_nul = np.cumsum(f == 0, axis=1) > 0
+        f[seen_nul] = 0
+    out[:, 286:288] = 0
+    return out

@@ -136,7 +136,8 @@ def test_sharded_stages_emulated_on_one_gpu():
     from ctypes import c_void_p
 
     import chronos_b200
-    from chronos_b200 import _ffi, tracegen
+    from chronos_b200 import _ffi, sharded, tracegen
+    from helpers import canonical
 
     L = _ffi.lib()
     world = 3
@@ -145,59 +146,62 @@ def test_sharded_stages_emulated_on_one_gpu():
     n = len(rows)
     bounds = [r * n // world for r in range(world + 1)]
     ctxs = [chronos_b200.Context(device=0, max_batch_events=n) for _ in range(world)]
-    sent = []  # per source rank: (records[cnt,288], arrival[cnt], meta[cnt], counts[world])
+    sent = []  # per source rank: (slots[*,16], hdr[cnt], entry counts, slot counts)
     for r in range(world):
         sl = rows[bounds[r]:bounds[r + 1]]
         cap = len(sl)
         d_in = tracegen.DeviceBuffer(0, cap * 288)
         d_in.upload(sl)
-        d_rec, d_arr, d_meta = (tracegen.DeviceBuffer(0, cap * 288), tracegen.DeviceBuffer(0, cap * 8),
-                                tracegen.DeviceBuffer(0, cap))
-        counts = (ctypes.c_uint64 * world)()
-        rc = L.chronos_filter_partition(ctxs[r]._h, c_void_p(d_in.ptr), cap, bounds[r], world, c_void_p(d_rec.ptr),
-                                        c_void_p(d_arr.ptr), c_void_p(d_meta.ptr), cap, counts)
+        d_slots, d_hdr = tracegen.DeviceBuffer(0, cap * 18 * 16), tracegen.DeviceBuffer(0, cap * 8)
+        ec, sc = (ctypes.c_uint64 * world)(), (ctypes.c_uint64 * world)()
+        rc = L.chronos_filter_partition(ctxs[r]._h, c_void_p(d_in.ptr), cap, bounds[r], world, c_void_p(d_slots.ptr),
+                                        cap * 18, c_void_p(d_hdr.ptr), cap, ec, sc)
         ctxs[r]._check(rc)
-        cnt = list(counts)
-        tot = sum(cnt)
-        sent.append((d_rec.download(tot * 288).reshape(-1, 288), d_arr.download(tot * 8).view(np.uint64),
-                     d_meta.download(tot), cnt))
-        for b in (d_in, d_rec, d_arr, d_meta):
+        ec, sc = list(ec), list(sc)
+        sent.append((d_slots.download(sum(sc) * 16).reshape(-1, 16), d_hdr.download(sum(ec) * 8).view(np.uint64), ec, sc))
+        for b in (d_in, d_slots, d_hdr):
             b.free()
-    # survivors of all ranks = oracle survivors
+    # survivors of all ranks = oracle survivors; transport is much smaller than 288 B per survivor
     keep, meta = coracle.classify(rows)
-    all_arr = np.sort(np.concatenate([s[1] for s in sent]))
+    all_arr = np.sort(np.concatenate([s[1] & np.uint64(sharded.HDR_ARRIVAL_MASK) for s in sent]))
     np.testing.assert_array_equal(all_arr, np.nonzero(keep)[0].astype(np.uint64))
+    assert sum(sum(s[3]) for s in sent) * 16 < 0.6 * 288 * len(all_arr)
     merged = []
     for d in range(world):  # route: destination d receives its block from every source, in source order
-        recs, arrs, metas = [], [], []
+        slots, hdrs = [], []
         for r in range(world):
-            rec, arr, met, cnt = sent[r]
-            lo = sum(cnt[:d])
-            recs.append(rec[lo:lo + cnt[d]]); arrs.append(arr[lo:lo + cnt[d]]); metas.append(met[lo:lo + cnt[d]])
-        rec, arr, met = np.concatenate(recs), np.concatenate(arrs), np.concatenate(metas)
-        assert np.all(np.diff(arr.astype(np.int64)) > 0)
-        pid = rec[:, :4].copy().view("<u4").reshape(-1)
-        assert all(chronos_b200.owner_of(int(p), world) == d for p in pid[:200])
-        np.testing.assert_array_equal(met & 0x0F, meta[arr.astype(np.int64)] & 0x0F)
+            sl, hd, ec, sc = sent[r]
+            lo_e, lo_s = sum(ec[:d]), sum(sc[:d])
+            slots.append(sl[lo_s:lo_s + sc[d]]); hdrs.append(hd[lo_e:lo_e + ec[d]])
+        sl, hd = np.concatenate(slots), np.concatenate(hdrs)
+        arr = (hd & np.uint64(sharded.HDR_ARRIVAL_MASK)).astype(np.int64)
+        assert np.all(np.diff(arr) > 0)
+        np.testing.assert_array_equal((hd >> np.uint64(48)) & np.uint64(0x0F), meta[arr] & 0x0F)
         k = len(arr)
-        b_rec, b_arr, b_met = (tracegen.DeviceBuffer(0, max(k, 1) * 288), tracegen.DeviceBuffer(0, max(k, 1) * 8),
-                               tracegen.DeviceBuffer(0, max(k, 1)))
+        b_slots, b_hdr = tracegen.DeviceBuffer(0, max(len(sl), 1) * 16), tracegen.DeviceBuffer(0, max(k, 1) * 8)
         if k:
-            b_rec.upload(rec); b_arr.upload(arr); b_met.upload(met)
-        ctxs[d].submit_survivors_ptr(b_rec.ptr, b_arr.ptr, b_met.ptr, k)
+            b_slots.upload(sl); b_hdr.upload(hd)
+        ctxs[d].submit_survivors_ptr(b_slots.ptr, b_hdr.ptr, k, len(sl))
         res = ctxs[d].fetch(records=True)
+        np.testing.assert_array_equal(res.survivors.astype(np.int64), arr)
+        if k:
+            pid = res.window_records[:, :4].copy().view("<u4").reshape(-1)
+            assert all(chronos_b200.owner_of(int(p), world) == d for p in pid[:200])
         o = 0
         for w in res.windows:
             ln = int(w["len"])
             merged.append((int(w["trigger_idx"]), int(w["pid"]), res.window_records[o:o + ln].copy()))
             o += ln
-        for b in (b_rec, b_arr, b_met):
+        for b in (b_slots, b_hdr):
             b.free()
     merged.sort(key=lambda t: t[0])
     ref = coracle.COracle().feed(rows, 0)
     assert [m[0] for m in merged] == ref["win_trigger"].tolist()
     assert [m[1] for m in merged] == ref["win_pid"].tolist()
-    exp = rows[ref["members"].astype(np.int64)]
-    np.testing.assert_array_equal(np.concatenate([m[2] for m in merged]), exp)
+    # the transport form drops whole chunks behind argv's NUL; junk inside a transported chunk
+    # survives. Both are invisible to the reference (fields are read up to the NUL, :125-130),
+    # so records are compared in canonical form: bytes behind each field's NUL zeroed.
+    exp = canonical(rows[ref["members"].astype(np.int64)])
+    np.testing.assert_array_equal(canonical(np.concatenate([m[2] for m in merged])), exp)
     for c in ctxs:
         c.close()

@@ -54,16 +54,17 @@ def _worker(rank, world, port, out_dir):
         order = np.argsort(owner, kind="stable")
         counts = np.bincount(owner, minlength=world)
         send_records = torch.from_numpy(np.ascontiguousarray(mine[idx][order]).reshape(-1))
-        send_arrival = torch.from_numpy((lo + idx[order]).astype(np.int64))
-        send_meta = torch.from_numpy(np.ascontiguousarray(meta[idx][order]))
+        # header words as on the GPU path; the payload unit here is a whole 288-byte record
+        hdr = sharded.pack_hdr(lo + idx[order], meta[idx][order], np.full(len(idx), 18))
+        send_hdr = torch.from_numpy(hdr.view(np.int64).copy())
         cap = n
         recv_records = torch.empty(cap * REC, dtype=torch.uint8)
-        recv_arrival = torch.empty(cap, dtype=torch.int64)
-        recv_meta = torch.empty(cap, dtype=torch.uint8)
-        n_recv, recv_counts = sharded.exchange(send_records, send_arrival, send_meta, counts, recv_records,
-                                               recv_arrival, recv_meta)
+        recv_hdr = torch.empty(cap, dtype=torch.int64)
+        n_recv, n_units = sharded.exchange(send_records, send_hdr, counts, counts, REC, recv_records, recv_hdr)
+        assert n_units == n_recv
         got = recv_records[: n_recv * REC].numpy().reshape(-1, REC)
-        arr = recv_arrival[:n_recv].numpy()
+        rh = recv_hdr[:n_recv].numpy().view(np.uint64)
+        arr = (rh & np.uint64(sharded.HDR_ARRIVAL_MASK)).astype(np.int64)
         # every received event belongs here, and arrives in global arrival order
         rp = got[:, :4].copy().view("<u4").reshape(-1)
         assert np.all(sharded.owner_of_np(rp, world) == rank)
