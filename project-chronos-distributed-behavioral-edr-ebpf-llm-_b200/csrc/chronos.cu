@@ -52,6 +52,7 @@ struct DeviceScalars {  // one 64-byte block on the device, mirrored in pinned m
 };
 
 constexpr int N_TICKETS = 64;
+constexpr uint32_t COMM_MEMO_SLOTS = 8192;  // device-wide comm memo (insert-only), 192 KB
 
 }  // namespace
 
@@ -75,6 +76,7 @@ struct chronos_ctx {
     DevBuf sp_key, sp_src, sp_meta, sp_ns, tile_count;  // filter's tile-local compaction
     DevBuf surv_pid, surv_ns, ns32, slot_off;            // arrival-ordered pid copy; transport-form bookkeeping
     const uint4 *b_slots = nullptr;                      // transport-form batch (chronos_submit_survivors)
+    DevBuf comm_memo;                                    // second-level comm memo: lock[N] | val[N] | key[N]
     // kill-chain labeller + persistent per-PID table (chain.cuh)
     DevBuf pid_tab, pt_count, chain_pid, chain_idx;
     uint32_t pt_cap = 0;
@@ -415,6 +417,10 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
     fp.out_count = &ds->surv_count;
     fp.key_or = &ds->key_or;
     fp.key_and = &ds->key_and;
+    fp.gm_lock = ptr<uint32_t>(c->comm_memo);
+    fp.gm_val = fp.gm_lock + COMM_MEMO_SLOTS;
+    fp.gm_key = reinterpret_cast<uint4 *>(fp.gm_val + COMM_MEMO_SLOTS);
+    fp.gm_mask = COMM_MEMO_SLOTS - 1;
     CK(cudaEventRecord(c->ev_f0, c->stream));
     if ((rc = launch_filter(c, fp))) return rc;
     CK(cudaEventRecord(c->ev_f1, c->stream));
@@ -804,6 +810,8 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
         if ((rc = ensure(c, c->tickets, N_TICKETS * 4))) return rc;
         if ((rc = ensure(c, c->scalars, sizeof(DeviceScalars)))) return rc;
         if ((rc = ensure(c, c->pt_count, 256))) return rc;
+        if ((rc = ensure(c, c->comm_memo, (size_t)COMM_MEMO_SLOTS * 24))) return rc;
+        CK(cudaMemsetAsync(c->comm_memo.p, 0, (size_t)COMM_MEMO_SLOTS * 24, c->stream));
         CK(cudaMemsetAsync(c->pt_count.p, 0, 256, c->stream));
         return CHRONOS_OK;
     };
@@ -821,7 +829,7 @@ int chronos_destroy(chronos_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->pflag,
-                     &c->entry_out, &c->wsorted, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->ns32, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+                     &c->entry_out, &c->wsorted, &c->comm_memo, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->ns32, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
                      &c->tickets, &c->scalars, &c->scan_status, &c->pack, &c->pack_off};
@@ -1361,6 +1369,10 @@ int chronos_filter_noalloc(int device, void *stream, const void *records, uint64
         fp.out_count = hdr + 2;
         fp.key_or = hdr + 3;
         fp.key_and = hdr + 4;
+        fp.gm_lock = nullptr;
+        fp.gm_val = nullptr;
+        fp.gm_key = nullptr;
+        fp.gm_mask = 0;
         filter_kernel<1><<<std::min<uint32_t>(fp.tile_end, (uint32_t)grid_cap), FILTER_TILE, filter_smem_bytes<1>(), st>>>(fp);
         ScanParams sp;
         sp.data = fp.tile_count;

@@ -47,6 +47,14 @@ struct FilterParams {
     uint32_t *out_count;     // total survivors (atomicAdd, one per CTA)
     uint32_t *key_or;        // OR / AND over survivor pids (radix pass planning)
     uint32_t *key_and;
+    // optional second-level comm memo shared by all CTAs and batches (nullptr: none).
+    // Insert-only: a slot is claimed with a CAS on its lock, its key written, then its value
+    // published with release semantics; a published slot never changes, so a reader that
+    // sees a valid value (acquire) reads a stable key.
+    uint32_t *gm_lock;
+    uint32_t *gm_val;
+    uint4 *gm_key;
+    uint32_t gm_mask;
 };
 
 // ---- needle tests on one 4-byte window `t` (bytes k..k+3) and the byte after it ------
@@ -98,6 +106,11 @@ __device__ __forceinline__ void scan_small_field(uint32_t a0, uint32_t a1, uint3
 __device__ __noinline__ bool utf8_valid_smem(const uint8_t *s, int n) {
     int i = 0;
     while (i < n) {
+        // every field starts 4-byte aligned in the record: skip pure-ASCII words whole
+        if ((i & 3) == 0 && i + 4 <= n && (*reinterpret_cast<const uint32_t *>(s + i) & 0x80808080u) == 0) {
+            i += 4;
+            continue;
+        }
         uint32_t b = s[i];
         if (b < 0x80u) { i++; continue; }
         int need;
@@ -358,7 +371,26 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
             uint32_t cres = S.memo_val[h];
             const bool hit = (cres & CR_VALID) && mk.x == c0 && mk.y == c1 && mk.z == c2 && mk.w == c3;
             const bool miss = alive && !hit;
-            if (miss) cres = comm_classify(w) | CR_VALID;
+            if (miss) {
+                bool done = false;
+                uint32_t g = 0;
+                if (p.gm_val) {
+                    g = ((c0 * 0x85EBCA77u) ^ (c1 * 0xC2B2AE3Du) ^ (c2 * 0x27D4EB2Fu) ^ (c3 * 0x9E3779B1u)) >> 7 & p.gm_mask;
+                    const uint32_t gv = ld_acquire_u32(p.gm_val + g);
+                    if (gv & CR_VALID) {
+                        const uint4 gk = p.gm_key[g];
+                        if (gk.x == c0 && gk.y == c1 && gk.z == c2 && gk.w == c3) { cres = gv; done = true; }
+                    }
+                }
+                if (!done) {
+                    cres = comm_classify(w) | CR_VALID;
+                    if (p.gm_val && atomicCAS(p.gm_lock + g, 0u, 1u) == 0u) {
+                        p.gm_key[g] = make_uint4(c0, c1, c2, c3);
+                        __threadfence();
+                        st_release_u32(p.gm_val + g, cres);
+                    }
+                }
+            }
             {
                 const uint32_t peers = __match_any_sync(FULL, miss ? h : 0x100u + lane);
                 if (miss && (peers & lanemask_lt()) == 0) {
@@ -378,12 +410,22 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
                 }
             }
             if (live) {
+                // which of the chunks 1..4 holds argv's end? (cheap: zero-byte masks only) ...
+                int qe = 0;
 #pragma unroll
                 for (int q = 1; q <= SHORT_CHUNKS; q++) {
-                    if (alen < 0) {
-                        int pos = 0;
-                        if (argv_chunk_end(v4, q, pos, hi)) alen = pos;
+                    if (qe == 0) {
+                        uint4 v = v4[q];
+                        if (q == 1) v.x = 0x01010101u;
+                        if ((zero_bytes(v.x) | zero_bytes(v.y) | zero_bytes(v.z) | zero_bytes(v.w)) != 0) qe = q;
+                        else hi |= v.x | v.y | v.z | v.w;
                     }
+                }
+                // ... then the exact position once, whatever chunk each lane ended in
+                if (qe) {
+                    int pos = 0;
+                    argv_chunk_end(v4, qe, pos, hi);
+                    alen = pos;
                 }
             }
         }

@@ -22,14 +22,14 @@ for it in range(6):
     dist.barrier(); torch.cuda.synchronize()
     t0 = time.perf_counter()
     r.ctx.reset()
-    sc = r.filter_partition(r.rec_ptr, r.n, r.first)
+    ec, sc = r.filter_partition(r.rec_ptr, r.n, r.first)
     t1 = time.perf_counter()
-    n_recv, _ = sharded.exchange(r.send_records, r.send_arrival, r.send_meta, sc, r.recv_records, r.recv_arrival, r.recv_meta)
+    n_recv, n_slots = sharded.exchange(r.send_slots, r.send_hdr, ec, sc, sharded.SLOT_BYTES, r.recv_slots, r.recv_hdr)
     torch.cuda.current_stream().synchronize()
     t2 = time.perf_counter()
-    r.ctx.submit_survivors_ptr(r.recv_records.data_ptr(), r.recv_arrival.data_ptr(), r.recv_meta.data_ptr(), n_recv)
+    r.ctx.submit_survivors_ptr(r.recv_slots.data_ptr(), r.recv_hdr.data_ptr(), n_recv, n_slots)
     c = r.ctx.fetch_counts()
     t3 = time.perf_counter()
     if rank == 0:
-        print(f"it{it}: stage1 {1e3*(t1-t0):.3f} ms  exchange {1e3*(t2-t1):.3f} ms  stage2 {1e3*(t3-t2):.3f} ms  sent {int(sc.sum())} recv {n_recv} filter_ms {r.ctx.last_timing()[1]:.3f}", flush=True)
+        print(f"it{it}: stage1 {1e3*(t1-t0):.3f} ms  exchange {1e3*(t2-t1):.3f} ms  stage2 {1e3*(t3-t2):.3f} ms  sent {int(ec.sum())} entries {int(sc.sum())*16/1e6:.0f} MB recv {n_recv} filter_ms {r.ctx.last_timing()[1]:.3f}", flush=True)
 dist.destroy_process_group()
