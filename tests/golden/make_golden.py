@@ -39,6 +39,9 @@ def run(records, with_prompts):
     }
     if with_prompts:
         res["prompts"] = out["prompts"]
+        banner = "[+] CHRONOS: LIVE. Stateful Monitoring Active.\n"  # chronos_sensor.py:159
+        so = out["stdout"]
+        res["stdout_after_banner"] = so[so.index(banner) + len(banner):]
     return buf, res
 
 

@@ -205,3 +205,38 @@ def test_sharded_stages_emulated_on_one_gpu():
     np.testing.assert_array_equal(canonical(np.concatenate([m[2] for m in merged])), exp)
     for c in ctxs:
         c.close()
+
+
+def test_sensor_drop_in_reproduces_reference_stdout_and_prompts():
+    """GpuSensor (print_event / process_memory / analyze_sequence surface) against what the
+    unmodified chronos_sensor.py printed and POSTed for the same records (golden fixtures;
+    the stub LLM answers like oracle/ref_shim.py's)."""
+    import ctypes
+
+    from chronos_b200 import sensor
+    from test_oracle_golden import fixture_records, load
+
+    for name in ("screenshot_kat.json", "adversarial.json"):
+        data, ref = fixture_records(name)
+        lines, posts = [], []
+
+        class Resp:
+            def json(self):
+                return {"response": '{"risk_score": 0, "verdict": "SAFE", "reason": "stub"}'}
+
+        def post(url, json=None, timeout=None):
+            posts.append(json["prompt"])
+            return Resp()
+
+        out = lambda s: lines.append(s)  # noqa: E731
+        s = sensor.GpuSensor(sensor.default_analyze_sequence("http://x:11434/api/generate", post=post, out=out),
+                             device=0, batch_events=7, out=out)
+        buf = ctypes.create_string_buffer(data, len(data))
+        for i in range(len(data) // 288):  # the way BCC would call it
+            s.print_event(0, ctypes.c_void_p(ctypes.addressof(buf) + 288 * i), 288)
+        pm = s.process_memory
+        assert posts == ref["prompts"]
+        assert pm == {int(k): v for k, v in ref["process_memory"].items()}
+        # everything the unmodified script printed after its banner (:143-155), byte for byte
+        assert "\n".join(lines) + "\n" == ref["stdout_after_banner"]
+        s.close()
