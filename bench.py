@@ -329,7 +329,7 @@ def run_gpu_arm(args, rank, world, local_rank):
                        "l2": "input per step (2.88 GB+) exceeds the 126 MB L2; no flush needed",
                        "timing": "torch CUDA events on the library stream around all K steps, max over ranks"},
             "roofline": {"bound": "hbm", "kernel": "filter_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": TRAFFIC_NCU, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": TRAFFIC_NCU if (world == 1 and n == 10_000_000) else None, "peak_source": peak_src,
                          "kernel_ms": f_ms, "algorithmic_bytes_per_launch": alg_bytes,
                          "pipeline": {"algorithmic_bytes_per_gpu": pipe_bytes, "ms_per_step": ms_per_step,
                                       "achieved": pipe_bytes / (ms_per_step / 1e3) / 1e9,
@@ -349,8 +349,9 @@ def run_gpu_arm(args, rank, world, local_rank):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum of filter_kernel for one launch of the N=1
-# workload, from the committed `ncu --set full` capture (profiles/); None until captured.
-TRAFFIC_NCU = None
+# workload (10 M events), from the committed `ncu --set full` capture
+# (profiles/r01_filter_ncu_raw.csv: 2.917522 GB read + 43.226 MB written).
+TRAFFIC_NCU = 2_960_748_112
 
 
 class SingleGpuRunner:
