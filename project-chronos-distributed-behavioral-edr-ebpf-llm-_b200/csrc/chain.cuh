@@ -5,48 +5,57 @@
 // state of the kill-chain DFA per PID (the extension described in window.cuh), which must
 // survive window flushes and batches.
 //
-// Open addressing, u64 slots: bit 63 valid | bits 33:32 DFA state | low 32 bits pid. The host
-// keeps it at most half full (ensure_pid_table in chronos.cu).
+// Open addressing, u64 slots: bit 63 valid | bits 47:40 epoch | bits 33:32 DFA state | low 32
+// bits pid. The host keeps it at most half full (ensure_pid_table in chronos.cu).
 #pragma once
 #include "common.cuh"
 
 namespace chronos {
 
 constexpr uint64_t PT_VALID = 1ull << 63;
+__host__ __device__ __forceinline__ uint64_t pt_make(uint32_t epoch, uint32_t dfa, uint32_t pid) {
+    return PT_VALID | ((uint64_t)(epoch & 0xFFu) << 40) | ((uint64_t)(dfa & 3u) << 32) | pid;
+}
+__device__ __forceinline__ bool pt_live(uint64_t v, uint32_t epoch) {
+    return (v & PT_VALID) && (uint32_t)((v >> 40) & 0xFFu) == epoch;
+}
 
-// returns the slot index of pid, inserting {pid, state 0} if absent (count++ on insert)
-__device__ __forceinline__ uint32_t pt_find_or_insert(uint64_t *tab, uint32_t mask, uint32_t pid, uint32_t *count) {
+// Slot index of pid, inserting {pid, state 0} if absent (count++ on insert). Slots written
+// under an older epoch count as empty: chronos_reset only bumps the epoch.
+__device__ __forceinline__ uint32_t pt_find_or_insert(uint64_t *tab, uint32_t mask, uint32_t epoch, uint32_t pid,
+                                                      uint32_t *count) {
     uint32_t i = hash32(pid) & mask;
     while (true) {
         uint64_t v = ld_relaxed_u64(tab + i);
-        if (v == 0) {
-            const uint64_t mine = PT_VALID | pid;
-            const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long *>(tab + i), 0ull, (unsigned long long)mine);
-            if (old == 0) {
+        while (!pt_live(v, epoch)) {
+            const uint64_t old = atomicCAS(reinterpret_cast<unsigned long long *>(tab + i), (unsigned long long)v,
+                                           (unsigned long long)pt_make(epoch, 0, pid));
+            if (old == v) {
                 atomicAdd(count, 1u);
                 return i;
             }
-            v = old;
+            v = old;  // somebody else took the slot: look at what is there now
         }
         if ((uint32_t)v == pid) return i;
         i = (i + 1) & mask;
     }
 }
 
-__global__ void pt_rehash_kernel(const uint64_t *old_tab, uint32_t old_cap, uint64_t *new_tab, uint32_t new_mask) {
+__global__ void pt_rehash_kernel(const uint64_t *old_tab, uint32_t old_cap, uint64_t *new_tab, uint32_t new_mask,
+                                 uint32_t epoch) {
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < old_cap; k += gridDim.x * blockDim.x) {
         const uint64_t v = old_tab[k];
-        if (!(v & PT_VALID)) continue;
+        if (!pt_live(v, epoch)) continue;
         uint32_t i = hash32((uint32_t)v) & new_mask;
         while (atomicCAS(reinterpret_cast<unsigned long long *>(new_tab + i), 0ull, (unsigned long long)v) != 0ull)
             i = (i + 1) & new_mask;
     }
 }
 
-__global__ void pt_dump_kernel(const uint64_t *tab, uint32_t cap, uint32_t *out, uint32_t *n_out) {
+__global__ void pt_dump_kernel(const uint64_t *tab, uint32_t cap, uint32_t epoch, uint32_t *out, uint32_t *n_out) {
     for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < cap; k += gridDim.x * blockDim.x) {
         const uint64_t v = tab[k];
-        if (v & PT_VALID) out[atomicAdd(n_out, 1u)] = (uint32_t)v;
+        if (pt_live(v, epoch)) out[atomicAdd(n_out, 1u)] = (uint32_t)v;
     }
 }
 

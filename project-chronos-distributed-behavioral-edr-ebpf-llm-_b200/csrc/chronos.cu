@@ -52,6 +52,7 @@ struct DeviceScalars {  // one 64-byte block on the device, mirrored in pinned m
 };
 
 constexpr int N_TICKETS = 64;
+constexpr uint32_t RADIX_TILE_KEYS = 4096;  // keys per radix tile in plan mode
 constexpr uint32_t COMM_MEMO_SLOTS = 8192;  // device-wide comm memo (insert-only), 192 KB
 
 }  // namespace
@@ -80,6 +81,10 @@ struct chronos_ctx {
     // kill-chain labeller + persistent per-PID table (chain.cuh)
     DevBuf pid_tab, pt_count, chain_pid, chain_idx;
     uint32_t pt_cap = 0;
+    uint32_t pt_epoch = 1;
+    DevBuf plan;                 // device-resident Plan of the batch in flight
+    Plan *h_plan = nullptr;      // pinned copy read at fetch
+    uint64_t b_Mmax = 0;         // P + n: what the buffers of the batch in flight are sized for
     uint32_t *h_pt_count = nullptr;  // pinned
     uint64_t n_pids_seen = 0, b_chains = 0;
     DevBuf surv_arrival;  // only for chronos_submit_survivors
@@ -118,6 +123,9 @@ namespace {
 
 const char *g_static_err = "chronos: invalid context";
 
+// CHRONOS_DEBUG_SYNC=1: wait after every stage so that a device fault names the stage that raised it
+int dbg_sync(chronos_ctx *c, const char *what);
+
 void mark(chronos_ctx *c, const char *name) {
     if (!c->trace || c->n_tev >= 12) return;
     if (!c->tev[c->n_tev]) cudaEventCreate(&c->tev[c->n_tev]);
@@ -142,6 +150,15 @@ int fail(chronos_ctx *c, int code, const char *fmt, ...) {
             return fail(c, e__ == cudaErrorMemoryAllocation ? CHRONOS_E_NOMEM : CHRONOS_E_CUDA,       \
                         "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
     } while (0)
+
+int dbg_sync(chronos_ctx *c, const char *what) {
+    static const bool on = getenv("CHRONOS_DEBUG_SYNC") != nullptr;
+    if (!on) return CHRONOS_OK;
+    cudaError_t e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream2);
+    if (e != cudaSuccess) return fail(c, CHRONOS_E_CUDA, "after %s: %s", what, cudaGetErrorString(e));
+    return CHRONOS_OK;
+}
 
 int ensure(chronos_ctx *c, DevBuf &b, size_t bytes) {
     if (bytes <= b.bytes && b.p) return CHRONOS_OK;
@@ -202,6 +219,8 @@ __global__ void fold_keys_kernel(const uint32_t *keys, uint32_t n, uint32_t *k_o
     }
 }
 
+__global__ void set_u32_kernel(uint32_t *p, uint32_t v) { *p = v; }
+
 __global__ void init_scalars_kernel(DeviceScalars *s) {
     s->surv_count = 0;
     s->key_or = 0;
@@ -209,6 +228,43 @@ __global__ void init_scalars_kernel(DeviceScalars *s) {
     s->n_windows = 0;
     s->n_pending = 0;
     s->n_chains = 0;
+}
+
+// Sizes of the batch, decided on the device once the filter's survivor count is there
+// (no host round trip): radix pass plan over the bits in which the pids differ, tilings,
+// and where the sorted arrays will end up after n_passes ping-pong passes.
+__global__ void plan_kernel(const DeviceScalars *s, uint32_t P, uint32_t m_max, const uint32_t *keyA,
+                            const uint32_t *keyB, const uint32_t *valA, const uint32_t *valB, Plan *pl) {
+    const uint32_t S = s->surv_count;
+    uint32_t M = P + S;
+    pl->overflow = M > m_max ? 1u : 0u;
+    if (M > m_max) M = m_max;  // never run past the buffers; the host reports the overflow
+    pl->S = M - P;
+    pl->P = P;
+    pl->M = M;
+    const uint32_t diff = s->key_or ^ s->key_and;
+    uint32_t passes = 0;
+    if (M >= 2 && diff != 0) {
+        const int lo = __ffs((int)diff) - 1, hi = 32 - __clz((int)diff);
+        const int bits = hi - lo;
+        passes = (uint32_t)(bits + 7) / 8;
+        const int per = (bits + (int)passes - 1) / (int)passes;
+        int sft = lo;
+        for (uint32_t i = 0; i < passes; i++) {
+            const int b = min(per, hi - sft);
+            pl->shift[i] = (uint32_t)sft;
+            pl->mask[i] = (1u << b) - 1u;
+            sft += b;
+        }
+    }
+    pl->n_passes = passes;
+    pl->tile_keys = RADIX_TILE_KEYS;
+    pl->n_tiles = (M + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS;
+    pl->table_len = RADIX_BINS * pl->n_tiles;
+    pl->tiles_m = (M + WIN_TILE - 1) / WIN_TILE;
+    pl->tiles_s = (pl->S + WIN_TILE - 1) / WIN_TILE;
+    pl->skey = (passes & 1u) ? keyB : keyA;
+    pl->sval = (passes & 1u) ? valB : valA;
 }
 
 // Stage 2 of the sharded path, step 1: split the header words of the received entries
@@ -343,7 +399,8 @@ int launch_filter(chronos_ctx *c, const FilterParams &fp) {
 }
 
 // exclusive scan in place (device array of n u32) on the context's stream
-int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n) {
+// (n_dev != nullptr: the real count lives on the device, n is only its upper bound)
+int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_dev = nullptr) {
     if (n == 0) return CHRONOS_OK;
     const uint32_t n_tiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
     int rc;
@@ -355,6 +412,7 @@ int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n) {
     ScanParams sp;
     sp.data = data;
     sp.n = (uint32_t)n;
+    sp.n_ptr = n_dev;
     sp.ticket = ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
     sp.status = ptr<uint64_t>(c->scan_status);
     sp.epoch = ++c->scan_epoch;
@@ -363,30 +421,6 @@ int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n) {
     CK(cudaGetLastError());
     c->launches++;
     return CHRONOS_OK;
-}
-
-struct PassPlan {
-    int n = 0;
-    uint32_t shift[4], mask[4];
-};
-
-PassPlan plan_passes(uint32_t k_or, uint32_t k_and, uint64_t M) {
-    PassPlan pl;
-    uint32_t diff = k_or ^ k_and;
-    if (M < 2 || diff == 0) return pl;
-    int lo = __builtin_ctz(diff), hi = 32 - __builtin_clz(diff);
-    int bits = hi - lo;
-    int passes = (bits + 7) / 8;
-    int per = (bits + passes - 1) / passes;
-    int s = lo;
-    for (int i = 0; i < passes; i++) {
-        int b = std::min(per, hi - s);
-        pl.shift[i] = (uint32_t)s;
-        pl.mask[i] = (1u << b) - 1u;
-        s += b;
-    }
-    pl.n = passes;
-    return pl;
 }
 
 // filter + cross-tile compaction: dense, arrival-ordered survivors (pid -> out_key,
@@ -422,11 +456,14 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
     fp.gm_key = reinterpret_cast<uint4 *>(fp.gm_val + COMM_MEMO_SLOTS);
     fp.gm_mask = COMM_MEMO_SLOTS - 1;
     CK(cudaEventRecord(c->ev_f0, c->stream));
+    if ((rc = dbg_sync(c, "begin_batch"))) return rc;
     if ((rc = launch_filter(c, fp))) return rc;
     CK(cudaEventRecord(c->ev_f1, c->stream));
+    if ((rc = dbg_sync(c, "filter_kernel"))) return rc;
     c->filter_timed = true;
     // cross-tile prefix + dense, arrival-ordered survivor arrays
     if ((rc = launch_scan(c, ptr<uint32_t>(c->tile_count), fp.tile_end))) return rc;
+    if ((rc = dbg_sync(c, "tile-count scan"))) return rc;
     CompactParams cp;
     cp.tile_off = ptr<uint32_t>(c->tile_count);
     cp.sp_key = fp.sp_key;
@@ -445,6 +482,7 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
                         c->stream>>>(cp);
     CK(cudaGetLastError());
     c->launches += 1;
+    if ((rc = dbg_sync(c, "filter + scan + compact"))) return rc;
     return CHRONOS_OK;
 }
 
@@ -464,7 +502,7 @@ int ensure_pid_table(chronos_ctx *c, uint64_t M) {
     CK(cudaMemsetAsync(fresh.p, 0, cap * 8, c->stream));
     if (c->pt_cap && c->n_pids_seen) {
         pt_rehash_kernel<<<(unsigned)std::min<uint64_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
-            ptr<uint64_t>(c->pid_tab), c->pt_cap, static_cast<uint64_t *>(fresh.p), (uint32_t)cap - 1);
+            ptr<uint64_t>(c->pid_tab), c->pt_cap, static_cast<uint64_t *>(fresh.p), (uint32_t)cap - 1, c->pt_epoch);
         CK(cudaGetLastError());
         c->launches++;
     }
@@ -475,104 +513,83 @@ int ensure_pid_table(chronos_ctx *c, uint64_t M) {
     return CHRONOS_OK;
 }
 
-// Everything after the survivors are known on the device (keyA[P..P+S), surv_src, surv_meta).
+// Everything after the survivors are known ON THE DEVICE (keyA[P..P+S), surv_src, surv_meta,
+// scalars.surv_count / key_or / key_and). Nothing here waits for the GPU: buffers are sized
+// for the worst case M = P + n, grids are upper bounds, extents come from the device plan.
 int run_window_stage(chronos_ctx *c) {
     const uint64_t P = c->b_P;
+    const uint64_t Mmax = c->b_Mmax;  // P + n
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    // the one mid-pipeline read-back: survivor count + pid bit spread
+    Plan *plan = ptr<Plan>(c->plan);
     mark(c, "filter+compact done");
-    CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaEventRecord(c->ev_filter, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    const uint64_t S = c->h_scalars->surv_count;
-    const uint64_t M = P + S;
-    c->b_S = S;
-    c->b_M = M;
     const int cur = c->cur, prev = cur ^ 1;
-    c->sorted_key = ptr<uint32_t>(c->keyA);
-    c->sorted_val = nullptr;
-    if (M == 0) {
-        c->h_scalars->n_windows = 0;
-        c->h_scalars->n_pending = 0;
-        c->h_scalars->n_chains = 0;
-        c->pend_cap[cur] = 0;
+    const uint64_t Smax = Mmax - P;
+    if (Mmax >= (1ull << VAL_ID_BITS))
+        return fail(c, CHRONOS_E_CAPACITY, "more than 2^27 grouped entries possible (%llu)", (unsigned long long)Mmax);
+    int rc;
+    if ((rc = ensure(c, c->arena[cur], (Mmax + 1) * CH_REC_BYTES))) return rc;
+    if ((rc = ensure(c, c->pend_key[cur], (Mmax + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->pend_slot[cur], (Mmax + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->pend_arrival[cur], (Mmax + 1) * 8))) return rc;
+    if ((rc = ensure(c, c->pend_meta[cur], Mmax + 1))) return rc;
+    c->pend_cap[cur] = Mmax;
+    if ((rc = ensure(c, c->pflag, (Mmax + 4) * 4))) return rc;
+    if ((rc = ensure(c, c->entry_out, (Smax + 4) * 4))) return rc;
+    if ((rc = ensure(c, c->wsorted, (Smax / 2 + 1) * sizeof(WinSorted)))) return rc;
+    if ((rc = ensure(c, c->windows, (Smax / 2 + 1) * sizeof(chronos_window)))) return rc;
+    if ((rc = ensure(c, c->chain_pid, (Smax + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->chain_idx, (Smax + 1) * 8))) return rc;
+    if ((rc = ensure_pid_table(c, Mmax))) return rc;
+    const uint32_t max_rtiles = (uint32_t)((Mmax + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS);
+    if ((rc = ensure(c, c->radix_table, (size_t)RADIX_BINS * std::max(max_rtiles, 1u) * 4))) return rc;
+
+    plan_kernel<<<1, 1, 0, c->stream>>>(ds, (uint32_t)P, (uint32_t)Mmax, ptr<uint32_t>(c->keyA), ptr<uint32_t>(c->keyB),
+                                        ptr<uint32_t>(c->valA), ptr<uint32_t>(c->valB), plan);
+    c->launches++;
+    if ((rc = dbg_sync(c, "plan_kernel"))) return rc;
+    if (Mmax == 0) {
+        CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(c->h_plan, plan, sizeof(Plan), cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(c->h_pt_count, c->pt_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaEventRecord(c->ev_end, c->stream));
         return CHRONOS_OK;
     }
-    if (M >= (1ull << VAL_ID_BITS)) return fail(c, CHRONOS_E_CAPACITY, "more than 2^27 grouped entries (%llu)", (unsigned long long)M);
 
-    int rc;
-    if ((rc = ensure(c, c->arena[cur], M * CH_REC_BYTES))) return rc;
-    if ((rc = ensure(c, c->pend_key[cur], M * 4))) return rc;
-    if ((rc = ensure(c, c->pend_slot[cur], M * 4))) return rc;
-    if ((rc = ensure(c, c->pend_arrival[cur], M * 8))) return rc;
-    if ((rc = ensure(c, c->pend_meta[cur], M))) return rc;
-    c->pend_cap[cur] = M;
-    if ((rc = ensure(c, c->pflag, (M + 4) * 4))) return rc;
-    if ((rc = ensure(c, c->entry_out, (S + 4) * 4))) return rc;
-    if ((rc = ensure(c, c->wsorted, (S / 2 + 1) * sizeof(WinSorted)))) return rc;
-    if ((rc = ensure(c, c->windows, (S / 2 + 1) * sizeof(chronos_window)))) return rc;
-    if ((rc = ensure(c, c->chain_pid, (S + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->chain_idx, (S + 1) * 8))) return rc;
-    if ((rc = ensure_pid_table(c, M))) return rc;
-
-    mark(c, "host sync + sizing done");
-    // ---- stable sort by pid -----------------------------------------------------------
-    PassPlan pl = plan_passes(c->h_scalars->key_or, c->h_scalars->key_and, M);
-    uint32_t *kin = ptr<uint32_t>(c->keyA), *kout = ptr<uint32_t>(c->keyB);
-    uint32_t *vin = nullptr, *vout = ptr<uint32_t>(c->valA);
-    uint32_t *vspare = ptr<uint32_t>(c->valB);
-    if (pl.n > 0) {
-        uint32_t tile_keys = 4096;
-        while ((M + tile_keys - 1) / tile_keys > 1024) tile_keys *= 2;
-        const uint32_t n_tiles = (uint32_t)((M + tile_keys - 1) / tile_keys);
-        if ((rc = ensure(c, c->radix_table, (size_t)RADIX_BINS * n_tiles * 4))) return rc;
-        for (int i = 0; i < pl.n; i++) {
-            RadixParams rp;
-            rp.keys_in = kin;
-            rp.vals_in = vin;
-            rp.meta_lo = P ? ptr<uint8_t>(c->pend_meta[prev]) + (c->pend_cap[prev] - P) : nullptr;
-            rp.meta_hi = ptr<uint8_t>(c->surv_meta);
-            rp.split = (uint32_t)P;
-            rp.keys_out = kout;
-            rp.vals_out = vout;
-            rp.table = ptr<uint32_t>(c->radix_table);
-            rp.n = (uint32_t)M;
-            rp.tile_keys = tile_keys;
-            rp.n_tiles = n_tiles;
-            rp.shift = pl.shift[i];
-            rp.mask = pl.mask[i];
-            radix_hist<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
-            if ((rc = launch_scan(c, rp.table, (uint64_t)RADIX_BINS * n_tiles))) return rc;
-            radix_scatter<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
-            CK(cudaGetLastError());
+    // ---- stable sort by pid: sort values first (entry id | class bits), then up to 4 passes ----
+    const uint8_t *meta_lo = P ? ptr<uint8_t>(c->pend_meta[prev]) + (c->pend_cap[prev] - P) : nullptr;
+    synth_values_kernel<<<(unsigned)std::min<uint64_t>((Mmax + 255) / 256, 2048), 256, 0, c->stream>>>(
+        ptr<uint32_t>(c->valA), (uint32_t)Mmax, meta_lo, ptr<uint8_t>(c->surv_meta), (uint32_t)P, plan);
+    c->launches++;
+    if ((rc = dbg_sync(c, "synth_values"))) return rc;
+    {
+        RadixParams rp;
+        memset(&rp, 0, sizeof(rp));
+        rp.plan = plan;
+        rp.keyA = ptr<uint32_t>(c->keyA);
+        rp.keyB = ptr<uint32_t>(c->keyB);
+        rp.valA = ptr<uint32_t>(c->valA);
+        rp.valB = ptr<uint32_t>(c->valB);
+        rp.table = ptr<uint32_t>(c->radix_table);
+        for (int i = 0; i < 4; i++) {  // passes beyond plan->n_passes return at once
+            rp.pass = i;
+            radix_hist<<<max_rtiles, RADIX_THREADS, 0, c->stream>>>(rp);
+            if ((rc = dbg_sync(c, "radix_hist"))) return rc;
+            if ((rc = launch_scan(c, rp.table, (uint64_t)RADIX_BINS * max_rtiles, &plan->table_len))) return rc;
+            if ((rc = dbg_sync(c, "radix scan"))) return rc;
+            radix_scatter<<<max_rtiles, RADIX_THREADS, 0, c->stream>>>(rp);
+            if ((rc = dbg_sync(c, "radix_scatter"))) return rc;
             c->launches += 2;
-            std::swap(kin, kout);
-            uint32_t *nv = (vin == nullptr) ? vspare : vin;
-            vin = vout;
-            vout = nv;
         }
-        c->sorted_key = kin;
-        c->sorted_val = vin;
-    } else {
-        // all keys equal (or a single entry): identity permutation
-        uint32_t *v = ptr<uint32_t>(c->valA);
-        synth_values_kernel<<<(unsigned)std::min<uint64_t>((M + 255) / 256, 2048), 256, 0, c->stream>>>(
-            v, (uint32_t)M, P ? ptr<uint8_t>(c->pend_meta[prev]) + (c->pend_cap[prev] - P) : nullptr,
-            ptr<uint8_t>(c->surv_meta), (uint32_t)P);
         CK(cudaGetLastError());
-        c->launches++;
-        c->sorted_key = kin;
-        c->sorted_val = v;
     }
-
     mark(c, "sort done");
+
     // ---- records into the grouped arena ----------------------------------------------
     {
         GatherParams g;
-        g.sval = c->sorted_val;
-        g.M = (uint32_t)M;
-        g.P = (uint32_t)P;
+        memset(&g, 0, sizeof(g));
+        g.plan = plan;
         g.surv_src = ptr<uint32_t>(c->surv_src);
         g.batch = c->b_records;
         const uint64_t pc = c->pend_cap[prev];
@@ -582,25 +599,22 @@ int run_window_stage(chronos_ctx *c) {
         g.slots = c->b_slots;
         g.slot_off = c->b_slots ? ptr<uint32_t>(c->slot_off) : nullptr;
         g.slot_ns = c->b_slots ? ptr<uint8_t>(c->surv_ns) : nullptr;
-        // bandwidth-bound copy on a second stream; it runs while the host enqueues the window
-        // scans and shares the GPU with them as far as registers allow
-        uint32_t blocks = (uint32_t)std::min<uint64_t>((M + 127) / 128, (uint64_t)c->sm_count * 8);
+        // bandwidth-bound copy on a second stream; it runs while the host enqueues the window scans
+        uint32_t blocks = (uint32_t)std::min<uint64_t>((Mmax + 127) / 128, (uint64_t)c->sm_count * 8);
         CK(cudaEventRecord(c->ev_sorted, c->stream));
         CK(cudaStreamWaitEvent(c->stream2, c->ev_sorted, 0));
         gather_records<<<blocks, 256, 0, c->stream2>>>(g);
         CK(cudaGetLastError());
         CK(cudaEventRecord(c->ev_gathered, c->stream2));
         c->launches++;
+        if ((rc = dbg_sync(c, "gather_records"))) return rc;
     }
 
     // ---- window automaton + chain labeller -------------------------------------------------
     {
         WinParams w;
         memset(&w, 0, sizeof(w));
-        w.skey = c->sorted_key;
-        w.sval = c->sorted_val;
-        w.M = (uint32_t)M;
-        w.P = (uint32_t)P;
+        w.plan = plan;
         w.surv_src = ptr<uint32_t>(c->surv_src);
         w.surv_arrival = c->b_explicit_arrival ? ptr<uint64_t>(c->surv_arrival) : nullptr;
         w.base_arrival = c->b_base;
@@ -609,12 +623,13 @@ int run_window_stage(chronos_ctx *c) {
         w.surv_pid = ptr<uint32_t>(c->surv_pid);
         w.pid_tab = ptr<uint64_t>(c->pid_tab);
         w.pid_mask = c->pt_cap - 1;
+        w.pid_epoch = c->pt_epoch;
         w.pid_count = ptr<uint32_t>(c->pt_count);
         w.pflag = ptr<uint32_t>(c->pflag);
         w.entry_out = ptr<uint32_t>(c->entry_out);
         w.wsorted = ptr<WinSorted>(c->wsorted);
         w.n_windows = &ds->n_windows;
-        w.pend_cap = (uint32_t)M;
+        w.pend_cap = (uint32_t)Mmax;
         w.npend_key = ptr<uint32_t>(c->pend_key[cur]);
         w.npend_slot = ptr<uint32_t>(c->pend_slot[cur]);
         w.npend_arrival = ptr<uint64_t>(c->pend_arrival[cur]);
@@ -624,30 +639,31 @@ int run_window_stage(chronos_ctx *c) {
         w.chain_pid = ptr<uint32_t>(c->chain_pid);
         w.chain_idx = ptr<uint64_t>(c->chain_idx);
         w.n_chains = &ds->n_chains;
-        const uint32_t tiles_m = (uint32_t)((M + WIN_TILE - 1) / WIN_TILE);
-        const uint32_t tiles_s = (uint32_t)((S + WIN_TILE - 1) / WIN_TILE);
+        const uint32_t tiles_m = (uint32_t)((Mmax + WIN_TILE - 1) / WIN_TILE);  // upper bounds
+        const uint32_t tiles_s = (uint32_t)((Smax + WIN_TILE - 1) / WIN_TILE);
         uint64_t *st = ptr<uint64_t>(c->status);
         uint32_t *tk = ptr<uint32_t>(c->tickets);
-        const uint32_t cap_blocks = (uint32_t)c->sm_count * 4;
+        const uint32_t cap_blocks = (uint32_t)c->sm_count * 2;
         w.ticket = tk + 60;
         w.status = st;                              // 5 words per tile
-        group_forward<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
+        group_forward<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, c->stream>>>(w);
+        if ((rc = dbg_sync(c, "group_forward"))) return rc;
         w.ticket = tk + 61;
         w.status = st + 5 * (size_t)tiles_m;        // 2 words per tile
-        window_reverse<<<std::min(tiles_m, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
-        c->launches += 2;
-        if (S > 0) {
-            w.ticket = tk + 62;
-            w.status = st + 7 * (size_t)tiles_m;    // 1 word per tile
-            emit_ordered<<<std::min(tiles_s, cap_blocks), WIN_THREADS, 0, c->stream>>>(w);
-            c->launches++;
-        }
+        window_reverse<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, c->stream>>>(w);
+        if ((rc = dbg_sync(c, "window_reverse"))) return rc;
+        w.ticket = tk + 62;
+        w.status = st + 7 * (size_t)tiles_m;        // 1 word per tile
+        emit_ordered<<<std::max(1u, std::min(tiles_s, cap_blocks)), WIN_THREADS, 0, c->stream>>>(w);
+        c->launches += 3;
         CK(cudaGetLastError());
+        if ((rc = dbg_sync(c, "emit_ordered"))) return rc;
     }
     mark(c, "window kernels done");
     CK(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
     mark(c, "gather joined");
     CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(c->h_plan, plan, sizeof(Plan), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(c->h_pt_count, c->pt_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaEventRecord(c->ev_end, c->stream));
     return CHRONOS_OK;
@@ -680,6 +696,7 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
     c->scan_slot = 0;
     c->filter_timed = false;
     const uint64_t ecap = P + n;
+    c->b_Mmax = ecap;
     int rc;
     if ((rc = ensure(c, c->keyA, (ecap + 1) * 4))) return rc;
     if ((rc = ensure(c, c->keyB, (ecap + 1) * 4))) return rc;
@@ -712,9 +729,12 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
 
 int finish_batch(chronos_ctx *c) {
     CK(cudaStreamSynchronize(c->stream));
+    c->b_S = c->h_plan->S;
+    c->b_M = c->h_plan->M;
     c->b_W = c->b_M ? c->h_scalars->n_windows : 0;
     c->n_pending = c->b_M ? c->h_scalars->n_pending : 0;
     c->b_chains = c->b_M ? c->h_scalars->n_chains : 0;
+    if (c->h_plan->overflow) return fail(c, CHRONOS_E_CAPACITY, "more survivors than the batch was sized for");
     c->n_pids_seen = *c->h_pt_count;
     cudaEventElapsedTime(&c->t_total, c->ev_start, c->ev_end);
     if (c->trace) {
@@ -806,10 +826,13 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
         CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_scalars), sizeof(DeviceScalars)));
         CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_pt_count), 64));
         *c->h_pt_count = 0;
+        CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_plan), sizeof(Plan)));
+        memset(c->h_plan, 0, sizeof(Plan));
         int rc;
         if ((rc = ensure(c, c->tickets, N_TICKETS * 4))) return rc;
         if ((rc = ensure(c, c->scalars, sizeof(DeviceScalars)))) return rc;
         if ((rc = ensure(c, c->pt_count, 256))) return rc;
+        if ((rc = ensure(c, c->plan, sizeof(Plan)))) return rc;
         if ((rc = ensure(c, c->comm_memo, (size_t)COMM_MEMO_SLOTS * 24))) return rc;
         CK(cudaMemsetAsync(c->comm_memo.p, 0, (size_t)COMM_MEMO_SLOTS * 24, c->stream));
         CK(cudaMemsetAsync(c->pt_count.p, 0, 256, c->stream));
@@ -829,13 +852,14 @@ int chronos_destroy(chronos_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->pflag,
-                     &c->entry_out, &c->wsorted, &c->comm_memo, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->ns32, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+                     &c->entry_out, &c->wsorted, &c->plan, &c->comm_memo, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->ns32, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
                      &c->tickets, &c->scalars, &c->scan_status, &c->pack, &c->pack_off};
     for (DevBuf *b : all) release(*b);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->h_pt_count) cudaFreeHost(c->h_pt_count);
+    if (c->h_plan) cudaFreeHost(c->h_plan);
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_filter) cudaEventDestroy(c->ev_filter);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -902,9 +926,8 @@ int chronos_submit_survivors(chronos_ctx *c, const void *slots, const uint64_t *
                                                           ptr<uint32_t>(c->surv_src), &ds->key_or, &ds->key_and);
         CK(cudaGetLastError());
         c->launches += 2;
-        c->h_scalars->pad[0] = (uint32_t)n;  // pinned: stays valid until the copy has run
-        CK(cudaMemcpyAsync(&ds->surv_count, &c->h_scalars->pad[0], 4, cudaMemcpyHostToDevice, c->stream));
-        CK(cudaStreamSynchronize(c->stream));
+        set_u32_kernel<<<1, 1, 0, c->stream>>>(&ds->surv_count, (uint32_t)n);
+        c->launches++;
     }
     if ((rc = run_window_stage(c))) return rc;
     c->phase = chronos_ctx::SUBMITTED;
@@ -1060,7 +1083,7 @@ int chronos_state_pids(chronos_ctx *c, uint32_t *pid, uint64_t cap) {
     uint32_t *cnt = ptr<uint32_t>(c->pack_off);
     CK(cudaMemsetAsync(cnt, 0, 4, c->stream));
     pt_dump_kernel<<<(unsigned)std::min<uint32_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
-        ptr<uint64_t>(c->pid_tab), c->pt_cap, ptr<uint32_t>(c->pack), cnt);
+        ptr<uint64_t>(c->pid_tab), c->pt_cap, c->pt_epoch, ptr<uint32_t>(c->pack), cnt);
     CK(cudaGetLastError());
     CK(cudaMemcpyAsync(pid, c->pack.p, K * 4, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
@@ -1098,7 +1121,12 @@ int chronos_reset(chronos_ctx *c) {
     c->n_pending = 0;
     c->n_pids_seen = 0;
     *c->h_pt_count = 0;
-    if (c->pt_cap) CK(cudaMemsetAsync(c->pid_tab.p, 0, (size_t)c->pt_cap * 8, c->stream));
+    // slots written under an older epoch count as empty: a reset costs nothing on the device
+    c->pt_epoch = (c->pt_epoch + 1) & 0xFFu;
+    if (c->pt_epoch == 0) {  // tags wrapped: really clear the table once every 255 resets
+        c->pt_epoch = 1;
+        if (c->pt_cap) CK(cudaMemsetAsync(c->pid_tab.p, 0, (size_t)c->pt_cap * 8, c->stream));
+    }
     CK(cudaMemsetAsync(c->pt_count.p, 0, 256, c->stream));
     c->phase = chronos_ctx::IDLE;
     return CHRONOS_OK;
@@ -1175,6 +1203,7 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
         const uint32_t n_tiles = (uint32_t)((S + tile_keys - 1) / tile_keys);
         if ((rc = ensure(c, c->radix_table, (size_t)RADIX_BINS * n_tiles * 4))) return rc;
         RadixParams rp;
+        memset(&rp, 0, sizeof(rp));  // explicit mode: no plan
         rp.keys_in = owner;
         rp.vals_in = nullptr;
         rp.meta_lo = nullptr;
@@ -1377,6 +1406,7 @@ int chronos_filter_noalloc(int device, void *stream, const void *records, uint64
         ScanParams sp;
         sp.data = fp.tile_count;
         sp.n = fp.tile_end;
+        sp.n_ptr = nullptr;
         sp.ticket = hdr + 1;
         sp.status = reinterpret_cast<uint64_t *>(base + noalloc::OFF_STATUS);
         sp.epoch = 1;  // the status words were just zeroed, tag 0 means "not written yet"

@@ -97,6 +97,20 @@ __device__ __forceinline__ uint32_t lanemask_lt() {
     return m;
 }
 
+// Device-resident sizes of the batch in flight, written by plan_kernel once the survivor
+// count is known ON THE DEVICE. Every kernel after the filter reads its extents from here
+// and is launched with an upper-bound grid, so a submit needs no host round trip.
+struct Plan {
+    uint32_t S, P, M;          // survivors of this batch, carried-in pending entries, M = P + S
+    uint32_t n_passes;         // radix passes actually needed (pids differ only in some bits)
+    uint32_t shift[4], mask[4];
+    uint32_t tile_keys, n_tiles, table_len;  // radix tiling of M
+    uint32_t tiles_m, tiles_s;               // window tiling of M and of S
+    uint32_t overflow;         // set when M exceeds what the buffers were sized for
+    const uint32_t *skey;      // where the sorted (pid, value) arrays ended up
+    const uint32_t *sval;
+};
+
 // owner rank of a pid for PID-hash sharding (also exported through the C ABI)
 __host__ __device__ __forceinline__ uint32_t hash32(uint32_t x) {
     x ^= x >> 16;

@@ -252,6 +252,7 @@ __device__ __forceinline__ typename F::State fn_lookback(uint64_t *status, uint3
 __device__ __forceinline__ uint32_t lookback_count(uint64_t *status, uint32_t tile, uint32_t agg, int lane) {
     if (tile == 0) {
         if (lane == 0) st_relaxed_u64(status, (ST_PREFIX << 62) | agg);
+        __syncwarp();
         return 0;
     }
     if (lane == 0) st_relaxed_u64(status + tile, (ST_AGG << 62) | agg);
@@ -275,6 +276,7 @@ __device__ __forceinline__ uint32_t lookback_count(uint64_t *status, uint32_t ti
         look -= 32;
     }
     if (lane == 0) st_relaxed_u64(status + tile, (ST_PREFIX << 62) | (uint64_t)(excl + agg));
+    __syncwarp();  // reconverge before the caller's __syncthreads() (see fn_lookback)
     return excl;
 }
 
@@ -283,6 +285,7 @@ __device__ __forceinline__ uint2 lookback_count2(uint64_t *status, uint32_t tile
     const uint64_t agg = ((uint64_t)a << 31) | b;
     if (tile == 0) {
         if (lane == 0) st_relaxed_u64(status, (ST_PREFIX << 62) | agg);
+        __syncwarp();
         return make_uint2(0u, 0u);
     }
     if (lane == 0) st_relaxed_u64(status + tile, (ST_AGG << 62) | agg);
@@ -306,6 +309,7 @@ __device__ __forceinline__ uint2 lookback_count2(uint64_t *status, uint32_t tile
         look -= 32;
     }
     if (lane == 0) st_relaxed_u64(status + tile, (ST_PREFIX << 62) | ((excl + agg) & ~(3ull << 62)));
+    __syncwarp();
     return make_uint2((uint32_t)((excl >> 31) & 0x7fffffffu), (uint32_t)(excl & 0x7fffffffu));
 }
 

@@ -20,6 +20,12 @@ constexpr int RADIX_THREADS = 256;
 constexpr int RADIX_WARPS = RADIX_THREADS / 32;
 
 struct RadixParams {
+    // plan mode (plan != nullptr): pass `pass` of the batch's sort; reads set A when the pass
+    // index is even and set B when it is odd, writes the other; extents come from the plan
+    const Plan *plan;
+    int pass;
+    uint32_t *keyA, *keyB, *valA, *valB;
+    // explicit mode (plan == nullptr)
     const uint32_t *keys_in;
     const uint32_t *vals_in;  // nullptr => value = index | class bits << 27 (see synth_value)
     const uint8_t *meta_lo;   // class bits of entries [0, split) (carried-in pending), may be nullptr
@@ -46,22 +52,57 @@ __device__ __forceinline__ uint32_t synth_value(const uint8_t *meta_lo, const ui
     return i | (m << 27);
 }
 
-__global__ void synth_values_kernel(uint32_t *v, uint32_t n, const uint8_t *meta_lo, const uint8_t *meta_hi, uint32_t split) {
+__global__ void synth_values_kernel(uint32_t *v, uint32_t n, const uint8_t *meta_lo, const uint8_t *meta_hi, uint32_t split,
+                                    const Plan *plan) {
+    if (plan) n = plan->M;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
         v[i] = synth_value(meta_lo, meta_hi, split, i);
 }
 
+// One radix pass resolved to plain values (plan mode reads the device plan; explicit mode the
+// parameter struct). active == false: this pass or this tile has nothing to do.
+struct RadixView {
+    const uint32_t *keys_in, *vals_in;
+    uint32_t *keys_out, *vals_out;
+    uint32_t n, tile_keys, n_tiles, shift, mask;
+    bool active;
+};
+__device__ __forceinline__ RadixView radix_view(const RadixParams &p) {
+    RadixView v;
+    if (!p.plan) {
+        v.keys_in = p.keys_in; v.vals_in = p.vals_in; v.keys_out = p.keys_out; v.vals_out = p.vals_out;
+        v.n = p.n; v.tile_keys = p.tile_keys; v.n_tiles = p.n_tiles; v.shift = p.shift; v.mask = p.mask;
+        v.active = blockIdx.x < p.n_tiles;
+        return v;
+    }
+    const Plan &pl = *p.plan;
+    const bool odd = p.pass & 1;
+    v.keys_in = odd ? p.keyB : p.keyA;
+    v.vals_in = odd ? p.valB : p.valA;
+    v.keys_out = odd ? p.keyA : p.keyB;
+    v.vals_out = odd ? p.valA : p.valB;
+    v.n = pl.M;
+    v.tile_keys = pl.tile_keys;
+    v.n_tiles = pl.n_tiles;
+    v.shift = pl.shift[p.pass & 3];
+    v.mask = pl.mask[p.pass & 3];
+    v.active = (uint32_t)p.pass < pl.n_passes && blockIdx.x < pl.n_tiles;
+    return v;
+}
+
 __global__ void __launch_bounds__(RADIX_THREADS) radix_hist(const RadixParams p) {
     __shared__ uint32_t h[RADIX_BINS];
+    const RadixView v = radix_view(p);
+    if (!v.active) return;
     const uint32_t tile = blockIdx.x;
     h[threadIdx.x] = 0;
     __syncthreads();
-    const uint32_t lo = tile * p.tile_keys;
-    const uint32_t hi = min(p.n, lo + p.tile_keys);
+    const uint32_t lo = tile * v.tile_keys;
+    const uint32_t hi = min(v.n, lo + v.tile_keys);
     for (uint32_t i = lo + threadIdx.x; i < hi; i += RADIX_THREADS)
-        atomicAdd(&h[(p.keys_in[i] >> p.shift) & p.mask], 1u);
+        atomicAdd(&h[(v.keys_in[i] >> v.shift) & v.mask], 1u);
     __syncthreads();
-    p.table[(size_t)threadIdx.x * p.n_tiles + tile] = h[threadIdx.x];
+    p.table[(size_t)threadIdx.x * v.n_tiles + tile] = h[threadIdx.x];
 }
 
 // Exclusive scan of n counters in place: persistent CTAs, 4096 counters per tile, chained
@@ -74,6 +115,7 @@ constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 struct ScanParams {
     uint32_t *data;
     uint32_t n;
+    const uint32_t *n_ptr;  // optional: the count lives on the device (overrides n)
     uint32_t *ticket;   // zeroed counter
     uint64_t *status;   // ceil(n / SCAN_TILE) words, any content from older epochs
     uint32_t epoch;     // > 0, unique per launch sharing `status`
@@ -84,6 +126,7 @@ __device__ __forceinline__ uint32_t lookback_count_epoch(uint64_t *status, uint3
     const uint64_t tag = (uint64_t)epoch << 34;
     if (tile == 0) {
         if (lane == 0) st_relaxed_u64(status, tag | (ST_PREFIX << 32) | agg);
+        __syncwarp();
         return 0;
     }
     if (lane == 0) st_relaxed_u64(status + tile, tag | (ST_AGG << 32) | agg);
@@ -107,14 +150,16 @@ __device__ __forceinline__ uint32_t lookback_count_epoch(uint64_t *status, uint3
         look -= 32;
     }
     if (lane == 0) st_relaxed_u64(status + tile, tag | (ST_PREFIX << 32) | (uint64_t)(excl + agg));
+    __syncwarp();  // reconverge before the caller's __syncthreads()
     return excl;
 }
 
 __global__ void __launch_bounds__(SCAN_THREADS) scan_exclusive_u32(const ScanParams p) {
     __shared__ uint32_t warp_sums[SCAN_THREADS / 32];
     __shared__ uint32_t s_tile, s_base;
+    const uint32_t n = p.n_ptr ? *p.n_ptr : p.n;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t n_tiles = (p.n + SCAN_TILE - 1) / SCAN_TILE;
+    const uint32_t n_tiles = (n + SCAN_TILE - 1) / SCAN_TILE;
     while (true) {
         __syncthreads();
         if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
@@ -123,13 +168,13 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_exclusive_u32(const ScanPar
         if (tile >= n_tiles) break;
         const uint32_t i0 = tile * SCAN_TILE + tid * SCAN_ITEMS;
         uint32_t v[SCAN_ITEMS];
-        if (i0 + SCAN_ITEMS <= p.n) {
+        if (i0 + SCAN_ITEMS <= n) {
             const uint4 a = *reinterpret_cast<const uint4 *>(p.data + i0);
             const uint4 b = *reinterpret_cast<const uint4 *>(p.data + i0 + 4);
             v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
         } else {
 #pragma unroll
-            for (int k = 0; k < SCAN_ITEMS; k++) v[k] = (i0 + k < p.n) ? p.data[i0 + k] : 0u;
+            for (int k = 0; k < SCAN_ITEMS; k++) v[k] = (i0 + k < n) ? p.data[i0 + k] : 0u;
         }
         uint32_t sum = 0;
 #pragma unroll
@@ -152,6 +197,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_exclusive_u32(const ScanPar
             if (lane < SCAN_THREADS / 32) warp_sums[lane] = winc - w;
             const uint32_t tot = __shfl_sync(0xffffffffu, winc, 31);
             const uint32_t excl = lookback_count_epoch(p.status, tile, tot, lane, p.epoch);
+            __syncwarp();
             if (lane == 0) s_base = excl;
         }
         __syncthreads();
@@ -162,34 +208,36 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_exclusive_u32(const ScanPar
             o[k] = run;
             run += v[k];
         }
-        if (i0 + SCAN_ITEMS <= p.n) {
+        if (i0 + SCAN_ITEMS <= n) {
             *reinterpret_cast<uint4 *>(p.data + i0) = make_uint4(o[0], o[1], o[2], o[3]);
             *reinterpret_cast<uint4 *>(p.data + i0 + 4) = make_uint4(o[4], o[5], o[6], o[7]);
         } else {
 #pragma unroll
             for (int k = 0; k < SCAN_ITEMS; k++)
-                if (i0 + k < p.n) p.data[i0 + k] = o[k];
+                if (i0 + k < n) p.data[i0 + k] = o[k];
         }
     }
 }
 
 __global__ void __launch_bounds__(RADIX_THREADS) radix_scatter(const RadixParams p) {
     __shared__ uint32_t whist[RADIX_WARPS][RADIX_BINS];
+    const RadixView v = radix_view(p);
+    if (!v.active) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t tile = blockIdx.x;
     for (int i = tid; i < RADIX_WARPS * RADIX_BINS; i += RADIX_THREADS) (&whist[0][0])[i] = 0;
     __syncthreads();
-    const uint32_t t_lo = tile * p.tile_keys;
-    const uint32_t t_hi = min(p.n, t_lo + p.tile_keys);
-    const uint32_t sub = p.tile_keys / RADIX_WARPS;  // multiple of 32
+    const uint32_t t_lo = tile * v.tile_keys;
+    const uint32_t t_hi = min(v.n, t_lo + v.tile_keys);
+    const uint32_t sub = v.tile_keys / RADIX_WARPS;  // multiple of 32
     const uint32_t w_lo = min(t_hi, t_lo + warp * sub);
     const uint32_t w_hi = min(t_hi, w_lo + sub);
     // 1) per-warp digit counts over the warp's contiguous sub-range
-    for (uint32_t i = w_lo + lane; i < w_hi; i += 32) atomicAdd(&whist[warp][(p.keys_in[i] >> p.shift) & p.mask], 1u);
+    for (uint32_t i = w_lo + lane; i < w_hi; i += 32) atomicAdd(&whist[warp][(v.keys_in[i] >> v.shift) & v.mask], 1u);
     __syncthreads();
     // 2) digit d: running base over warps, seeded with the global offset of (d, tile)
     {
-        uint32_t run = p.table[(size_t)tid * p.n_tiles + tile];
+        uint32_t run = p.table[(size_t)tid * v.n_tiles + tile];
 #pragma unroll
         for (int w = 0; w < RADIX_WARPS; w++) {
             uint32_t c = whist[w][tid];
@@ -204,8 +252,8 @@ __global__ void __launch_bounds__(RADIX_THREADS) radix_scatter(const RadixParams
         const bool valid = i < w_hi;
         uint32_t key = 0, d = RADIX_BINS;  // invalid lanes form their own group
         if (valid) {
-            key = p.keys_in[i];
-            d = (key >> p.shift) & p.mask;
+            key = v.keys_in[i];
+            d = (key >> v.shift) & v.mask;
         }
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const uint32_t before = __popc(peers & lanemask_lt());
@@ -216,8 +264,8 @@ __global__ void __launch_bounds__(RADIX_THREADS) radix_scatter(const RadixParams
         __syncwarp();
         if (valid) {
             const uint32_t dst = base + before;
-            p.keys_out[dst] = key;
-            p.vals_out[dst] = p.vals_in ? p.vals_in[i] : synth_value(p.meta_lo, p.meta_hi, p.split, i);
+            v.keys_out[dst] = key;
+            v.vals_out[dst] = v.vals_in ? v.vals_in[i] : synth_value(p.meta_lo, p.meta_hi, p.split, i);
         }
     }
 }

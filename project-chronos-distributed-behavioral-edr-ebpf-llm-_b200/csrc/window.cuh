@@ -56,6 +56,7 @@ struct WinParams {
     const uint32_t *skey;   // M sorted pids
     const uint32_t *sval;   // M values: entry id | meta << 27; ids [0,P) carried-in pending, [P,M) survivors
     uint32_t M, P;
+    const Plan *plan;               // when set, skey / sval / M / P are taken from it on the device
     const uint32_t *surv_src;       // S batch-local record index
     const uint64_t *surv_arrival;   // S explicit arrival indices, or nullptr => base_arrival + surv_src
     uint64_t base_arrival;
@@ -64,6 +65,7 @@ struct WinParams {
     // per-PID table (chain.cuh)
     uint64_t *pid_tab;
     uint32_t pid_mask;
+    uint32_t pid_epoch;
     uint32_t *pid_count;
     // forward outputs
     uint32_t *pflag;                // M
@@ -87,9 +89,12 @@ struct WinParams {
     uint64_t *status;               // look-back words for this kernel
 };
 
-__device__ __forceinline__ uint64_t win_arrival_of(const WinParams &p, uint32_t e) {
-    if (e < p.P) return p.pend_arrival[e];
-    const uint32_t j = e - p.P;
+// M, P and the sorted arrays are resolved into plain locals at the top of every kernel.
+// (Patching a by-value copy of the parameter struct from the plan did not work: nvcc 12.9
+// kept reading the ORIGINAL skey pointer out of the parameter bank)
+__device__ __forceinline__ uint64_t win_arrival_of(const WinParams &p, uint32_t P, uint32_t e) {
+    if (e < P) return p.pend_arrival[e];
+    const uint32_t j = e - P;
     return p.surv_arrival ? p.surv_arrival[j] : p.base_arrival + p.surv_src[j];
 }
 
@@ -111,11 +116,14 @@ __device__ __forceinline__ Fn3 chain_event(uint32_t meta) {
 // counter a = windows flushed so far. Chain DFA: counter a = chain-complete events so far.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) {
+    const uint32_t M = p.plan ? p.plan->M : p.M, P = p.plan ? p.plan->P : p.P;
+    const uint32_t *const skey = p.plan ? p.plan->skey : p.skey;
+    const uint32_t *const sval = p.plan ? p.plan->sval : p.sval;
     __shared__ FnG warp_tot[WIN_THREADS / 32];
     __shared__ uint32_t s_tile;
     __shared__ StG s_in;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t n_tiles = (p.M + WIN_TILE - 1) / WIN_TILE;
+    const uint32_t n_tiles = (M + WIN_TILE - 1) / WIN_TILE;
     while (true) {
         __syncthreads();
         if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
@@ -125,17 +133,17 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
         const uint32_t p0 = tile * WIN_TILE + tid * WIN_ITEMS;
         uint32_t key[WIN_ITEMS], val[WIN_ITEMS];
         uint8_t kind[WIN_ITEMS];  // bit0 head, bits 2:1 the PID's stored DFA state at a head
-        uint32_t prevk = (p0 > 0 && p0 - 1 < p.M) ? p.skey[p0 - 1] : 0;
+        uint32_t prevk = (p0 > 0 && p0 - 1 < M) ? skey[p0 - 1] : 0;
         FnG f = FnG::identity();
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t pos = p0 + k;
             key[k] = 0; val[k] = 0; kind[k] = 0;
-            if (pos < p.M) {
-                key[k] = p.skey[pos];
-                val[k] = p.sval[pos];
+            if (pos < M) {
+                key[k] = skey[pos];
+                val[k] = sval[pos];
                 const uint32_t meta = val[k] >> VAL_ID_BITS;
-                const bool carried = (val[k] & VAL_ID_MASK) < p.P;
+                const bool carried = (val[k] & VAL_ID_MASK) < P;
                 const bool head = (pos == 0) || key[k] != prevk;
                 const bool trig = (meta & META_TRIG) != 0;  // carried entries were stored without it
                 prevk = key[k];
@@ -149,7 +157,7 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
                 e.c = carried ? Fn3{0x24u, {cm, cm, cm}} : chain_event(meta);
                 uint32_t kd = head ? 1u : 0u;
                 if (head) {  // the PID's stored DFA state replaces whatever is carried over
-                    const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, key[k], p.pid_count);
+                    const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, p.pid_epoch, key[k], p.pid_count);
                     const uint32_t d0 = (uint32_t)(ld_relaxed_u64(p.pid_tab + slot) >> 32) & 3u;
                     kd |= d0 << 1;
                     e.c = Fn3::constant(Fn3::o(e.c, d0), Fn3::av(e.c, d0));
@@ -174,9 +182,9 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t pos = p0 + k;
             pf[k] = 0;
-            if (pos >= p.M) continue;
+            if (pos >= M) continue;
             const uint32_t meta = val[k] >> VAL_ID_BITS, e = val[k] & VAL_ID_MASK;
-            const bool carried = e < p.P, head = kind[k] & 1u, trig = (meta & META_TRIG) != 0;
+            const bool carried = e < P, head = kind[k] & 1u, trig = (meta & META_TRIG) != 0;
             // ---- flush automaton
             bool fl = false;
             uint32_t wi = EO_NONE;
@@ -198,23 +206,23 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
                 if (st.c.s == 2u) { if (meta & META_EXEC) { m = true; st.c.s = 0; st.c.a++; } }
                 else if (st.c.s == 1u) { if (meta & META_CHMOD) st.c.s = 2; }
                 else if (meta & META_CURL) st.c.s = 1;
-                p.entry_out[e - p.P] = wi | (m ? EO_MATCH : 0u);
+                p.entry_out[e - P] = wi | (m ? EO_MATCH : 0u);
             }
             pf[k] = (fl ? PF_FLUSH : 0u) | (m ? PF_MATCH : 0u) | (st.c.a << 2);
-            const bool tail = (pos + 1 == p.M) || p.skey[pos + 1] != key[k];
+            const bool tail = (pos + 1 == M) || skey[pos + 1] != key[k];
             if (tail) {  // the PID's DFA state after this batch
-                const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, key[k], p.pid_count);
-                st_relaxed_u64(p.pid_tab + slot, PT_VALID | ((uint64_t)st.c.s << 32) | key[k]);
+                const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, p.pid_epoch, key[k], p.pid_count);
+                st_relaxed_u64(p.pid_tab + slot, pt_make(p.pid_epoch, st.c.s, key[k]));
             }
         }
-        if (p0 + WIN_ITEMS <= p.M) {
+        if (p0 + WIN_ITEMS <= M) {
             uint4 *dst = reinterpret_cast<uint4 *>(p.pflag + p0);
 #pragma unroll
             for (int k = 0; k < WIN_ITEMS; k += 4) dst[k / 4] = make_uint4(pf[k], pf[k + 1], pf[k + 2], pf[k + 3]);
         } else {
 #pragma unroll
             for (int k = 0; k < WIN_ITEMS; k++)
-                if (p0 + k < p.M) p.pflag[p0 + k] = pf[k];
+                if (p0 + k < M) p.pflag[p0 + k] = pf[k];
         }
     }
 }
@@ -224,11 +232,14 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
 // O=1 (open: reaches its PID's end unflushed => stays in process_memory).
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p) {
+    const uint32_t M = p.plan ? p.plan->M : p.M, P = p.plan ? p.plan->P : p.P;
+    const uint32_t *const skey = p.plan ? p.plan->skey : p.skey;
+    const uint32_t *const sval = p.plan ? p.plan->sval : p.sval;
     __shared__ Fn2 warp_tot[WIN_THREADS / 32];
     __shared__ uint32_t s_tile;
     __shared__ St2 s_in;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t n_tiles = (p.M + WIN_TILE - 1) / WIN_TILE;
+    const uint32_t n_tiles = (M + WIN_TILE - 1) / WIN_TILE;
     while (true) {
         __syncthreads();
         if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
@@ -240,15 +251,15 @@ __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p)
         uint8_t kd[WIN_ITEMS];  // bit0 setter, bit1 flush, bit2 chain match
         uint32_t nextk = 0;     // key at pos+1
         bool have_next = false;
-        if (q0 > 0 && q0 <= p.M) { nextk = p.skey[p.M - q0]; have_next = true; }
+        if (q0 > 0 && q0 <= M) { nextk = skey[M - q0]; have_next = true; }
         Fn2 f = Fn2::identity();
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t q = q0 + k;
             key[k] = 0; kd[k] = 0;
-            if (q < p.M) {
-                const uint32_t pos = p.M - 1 - q;
-                key[k] = p.skey[pos];
+            if (q < M) {
+                const uint32_t pos = M - 1 - q;
+                key[k] = skey[pos];
                 const uint32_t pfl = p.pflag[pos];
                 const bool fl = (pfl & PF_FLUSH) != 0;
                 const bool tail = !have_next || key[k] != nextk;
@@ -276,16 +287,16 @@ __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p)
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t q = q0 + k;
-            if (q >= p.M) break;
-            const uint32_t pos = p.M - 1 - q;
+            if (q >= M) break;
+            const uint32_t pos = M - 1 - q;
             if (kd[k] & 1u) st.s = (kd[k] & 2u) ? 0u : 1u;
             if (st.s == 1u) {
                 const uint32_t slot = p.pend_cap - 1u - st.a;
                 st.a++;
-                const uint32_t v = p.sval[pos];
+                const uint32_t v = sval[pos];
                 p.npend_key[slot] = key[k];
                 p.npend_slot[slot] = pos;
-                p.npend_arrival[slot] = win_arrival_of(p, v & VAL_ID_MASK);
+                p.npend_arrival[slot] = win_arrival_of(p, P, v & VAL_ID_MASK);
                 // stored without the trigger bit (a pending event never triggers again), with
                 // the chain mark if it completed a chain, for the label of its future window
                 p.npend_meta[slot] = (uint8_t)(((v >> VAL_ID_BITS) & ~META_TRIG) | ((kd[k] & 4u) ? META_CHAIN : 0u));
@@ -299,10 +310,11 @@ __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p)
 // IS arrival order: windows by trigger arrival (:143-147) and chain matches by arrival.
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) {
+    const uint32_t M = p.plan ? p.plan->M : p.M, P = p.plan ? p.plan->P : p.P;
     __shared__ uint32_t warp_w[WIN_THREADS / 32], warp_c[WIN_THREADS / 32];
     __shared__ uint32_t s_tile, s_base_w, s_base_c;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t S = p.M - p.P;
+    const uint32_t S = M - P;
     const uint32_t n_tiles = (S + WIN_TILE - 1) / WIN_TILE;
     while (true) {
         __syncthreads();
@@ -361,7 +373,7 @@ __global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) {
             if (wi != EO_NONE) {
                 const WinSorted d = p.wsorted[wi];
                 chronos_window o;
-                o.trigger_idx = win_arrival_of(p, d.trig_entry);
+                o.trigger_idx = win_arrival_of(p, P, d.trig_entry);
                 o.start = d.start;
                 o.len = d.len;
                 o.pid = d.pid;
@@ -397,25 +409,28 @@ struct GatherParams {
     const uint4 *slots;
     const uint32_t *slot_off;
     const uint8_t *slot_ns;
+    const Plan *plan;            // when set, sval / M / P are taken from it on the device
 };
 
 __global__ void __launch_bounds__(256) gather_records(const GatherParams g) {
+    const uint32_t gM = g.plan ? g.plan->M : g.M, gP = g.plan ? g.plan->P : g.P;
+    const uint32_t *const gsval = g.plan ? g.plan->sval : g.sval;
     const int lane = threadIdx.x & 31;
     const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
     constexpr uint32_t GROUP = 16;  // records per warp step: 16*18 = 288 chunks = 9 per lane
-    for (uint32_t base = warp_global * GROUP; base < g.M; base += n_warps * GROUP) {
-        const uint32_t cnt = min(GROUP, g.M - base);
+    for (uint32_t base = warp_global * GROUP; base < gM; base += n_warps * GROUP) {
+        const uint32_t cnt = min(GROUP, gM - base);
         // lane r (< cnt) resolves the source of record base+r
         const uint8_t *src = nullptr;
         uint32_t ns = 0;  // 0: plain 288-byte record at src; else transport form of ns slots
         if ((uint32_t)lane < cnt) {
-            const uint32_t e = g.sval[base + lane] & VAL_ID_MASK;
-            if (e < g.P) src = g.prev_arena + (size_t)g.pend_slot[e] * CH_REC_BYTES;
+            const uint32_t e = gsval[base + lane] & VAL_ID_MASK;
+            if (e < gP) src = g.prev_arena + (size_t)g.pend_slot[e] * CH_REC_BYTES;
             else if (g.slots) {
-                src = reinterpret_cast<const uint8_t *>(g.slots + g.slot_off[e - g.P]);
-                ns = g.slot_ns[e - g.P];
-            } else src = g.batch + (size_t)g.surv_src[e - g.P] * CH_REC_BYTES;
+                src = reinterpret_cast<const uint8_t *>(g.slots + g.slot_off[e - gP]);
+                ns = g.slot_ns[e - gP];
+            } else src = g.batch + (size_t)g.surv_src[e - gP] * CH_REC_BYTES;
         }
         uint4 *dst = reinterpret_cast<uint4 *>(g.arena + (size_t)base * CH_REC_BYTES);
 #pragma unroll
