@@ -154,7 +154,8 @@ uint32_t chronos_owner_of(uint32_t pid, uint32_t world);
  *              are not transported (a live sensor zero-fills them, chronos_sensor.py:52/:69;
  *              the receiver restores zeros), which cuts the NVLink volume about 3.5x.
  * entry_counts_host[world] / slot_counts_host[world] receive the per-destination counts
- * (this call waits for the GPU). Destination d's data starts at the running sums. */
+ * (this call waits for the GPU). Destination d's data starts at the running sums.
+ * world <= CHRONOS_EXCHANGE_MAX_WORLD. */
 int chronos_filter_partition(chronos_ctx *ctx, const void *records, uint64_t n, uint64_t base_arrival_index,
                              uint32_t world, void *send_slots, uint64_t cap_slots, uint64_t *send_hdr,
                              uint64_t cap_entries, uint64_t *entry_counts_host, uint64_t *slot_counts_host);
@@ -164,6 +165,50 @@ int chronos_filter_partition(chronos_ctx *ctx, const void *records, uint64_t n, 
  * arrival order). Results are fetched with the calls above. */
 int chronos_submit_survivors(chronos_ctx *ctx, const void *slots, const uint64_t *hdr, uint64_t n_entries,
                              uint64_t n_slots);
+
+/* ---- direct exchange: survivors go straight into the owner's memory over NVLink -------------
+ *
+ * The two calls above leave the all-to-all to the host (torch.distributed / NCCL). On one
+ * NVSwitch box the repartition can skip that: every rank owns a RECEIVE WINDOW in its HBM,
+ * peers map it (CUDA IPC between processes, plain pointers inside one process), and the
+ * pack kernel of stage 1 writes each survivor into its owner's window while it computes the
+ * partition; the last thread block to finish publishes the per-source counts and raises a
+ * flag the owner's stage 2 waits on. No staging buffer, no count exchange, no host round
+ * trip: chronos_filter_exchange + chronos_submit_exchanged only enqueue work; the first wait
+ * is chronos_fetch. No reference counterpart (the reference is one process on one host).
+ *
+ * Protocol, identical on every rank and every step:
+ *   chronos_exchange_create   once; all ranks with the same world and capacities
+ *   (exchange the window pointers or IPC handles, e.g. with an all-gather)
+ *   chronos_exchange_connect  once
+ *   per step: chronos_filter_exchange(slice) ; chronos_submit_exchanged() ; chronos_fetch(...)
+ * Every rank must take part in every step (an empty slice is fine): stage 2 waits for the
+ * flag of every source rank and gives up with CHRONOS_E_STATE after the timeout (20 s unless
+ * chronos_exchange_set_timeout changed it). A (source, owner) pair that exceeds the capacities
+ * makes both ends report CHRONOS_E_CAPACITY at fetch; nothing is truncated silently.
+ * Ranks must not destroy their context while peers may still send (barrier first). */
+#define CHRONOS_IPC_HANDLE_BYTES 64
+#define CHRONOS_EXCHANGE_MAX_WORLD 16
+
+/* Allocate this rank's receive window: room for `cap_entries_per_peer` survivors and
+ * `cap_slots_per_peer` 16-byte transport slots (0 = 8 per entry) from EACH source rank,
+ * twice (two steps in flight). world * cap_entries_per_peer must not exceed the context's
+ * max_batch_events. window_out (optional) receives the device address, ipc_handle_out
+ * (optional, CHRONOS_IPC_HANDLE_BYTES) the handle another process opens it with. */
+int chronos_exchange_create(chronos_ctx *ctx, uint32_t world, uint32_t rank, uint64_t cap_entries_per_peer,
+                            uint64_t cap_slots_per_peer, void **window_out, uint8_t *ipc_handle_out);
+/* Addresses of the peers' windows: peer_windows[world] (device pointers valid in THIS process
+ * and reachable from this GPU; entries may be NULL) and/or peer_ipc_handles
+ * [world * CHRONOS_IPC_HANDLE_BYTES] for ranks in other processes. The own rank is skipped. */
+int chronos_exchange_connect(chronos_ctx *ctx, void *const *peer_windows, const uint8_t *peer_ipc_handles);
+/* Stage 1: filter the slice (host or device pointer, as chronos_submit) and deliver every
+ * survivor to owner = chronos_owner_of(pid, world). Asynchronous. */
+int chronos_filter_exchange(chronos_ctx *ctx, const void *records, uint64_t n, uint64_t base_arrival_index);
+/* Stage 2: wait (on the GPU) for all sources of this step, then grouping + window logic on
+ * what arrived, in source-rank order = global arrival order. Asynchronous; results with
+ * chronos_fetch and the copy calls. */
+int chronos_submit_exchanged(chronos_ctx *ctx);
+int chronos_exchange_set_timeout(chronos_ctx *ctx, double seconds);
 
 /* ---- allocation-free filtering ------------------------------------------------------------ */
 

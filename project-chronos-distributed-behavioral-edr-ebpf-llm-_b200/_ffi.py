@@ -42,6 +42,8 @@ class TracegenCfg(Structure):
 
 
 # every symbol include/chronos.h declares: name -> (restype, argtypes)
+IPC_HANDLE_BYTES = 64
+
 SIGNATURES = {
     "chronos_device_ok": (c_int, [c_int]),
     "chronos_create": (c_int, [c_int, c_uint64, POINTER(c_void_p)]),
@@ -65,6 +67,11 @@ SIGNATURES = {
     "chronos_filter_partition": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64, c_uint32, c_void_p, c_uint64,
                                          c_void_p, c_uint64, c_void_p, c_void_p]),
     "chronos_submit_survivors": (c_int, [c_void_p, c_void_p, c_void_p, c_uint64, c_uint64]),
+    "chronos_exchange_create": (c_int, [c_void_p, c_uint32, c_uint32, c_uint64, c_uint64, POINTER(c_void_p), c_void_p]),
+    "chronos_exchange_connect": (c_int, [c_void_p, c_void_p, c_void_p]),
+    "chronos_filter_exchange": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64]),
+    "chronos_submit_exchanged": (c_int, [c_void_p]),
+    "chronos_exchange_set_timeout": (c_int, [c_void_p, ctypes.c_double]),
     "chronos_filter_noalloc": (c_int, [c_int, c_void_p, c_void_p, c_uint64, c_void_p, c_void_p, c_void_p, c_void_p,
                                        c_char_p, c_uint64]),
     "chronos_tracegen_host": (c_int, [POINTER(TracegenCfg), c_void_p, c_uint64, c_uint64, c_void_p]),

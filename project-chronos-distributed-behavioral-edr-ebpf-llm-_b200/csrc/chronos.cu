@@ -31,6 +31,7 @@
 #include "chain.cuh"
 #include "fnscan.cuh"
 #include "window.cuh"
+#include "exchange.cuh"
 
 using namespace chronos;
 
@@ -48,7 +49,8 @@ struct DeviceScalars {  // one 64-byte block on the device, mirrored in pinned m
     uint32_t n_windows;
     uint32_t n_pending;
     uint32_t n_chains;
-    uint32_t pad[10];
+    uint32_t xchg_err;  // XERR_* bits of the exchange (exchange.cuh); cleared by stage 1, not per batch
+    uint32_t pad[9];
 };
 
 constexpr int N_TICKETS = 64;
@@ -101,6 +103,18 @@ struct chronos_ctx {
     DeviceScalars *h_scalars = nullptr;  // pinned
     DevBuf pack;                         // scratch for chronos_copy_window_records / chronos_state
     DevBuf pack_off;
+
+    // direct exchange over peer memory (exchange.cuh)
+    DevBuf x_window, x_totals;
+    XchgLayout x_L = {};
+    bool x_created = false, x_connected = false, x_sent = false, b_exchanged = false;
+    uint8_t *x_peer[XCHG_MAX_WORLD] = {nullptr};
+    bool x_opened[XCHG_MAX_WORLD] = {false};
+    uint32_t x_epoch = 0;
+    uint64_t x_launches = 0;
+    bool x_filter_timed = false;  // stage 1 of this step ran the filter (non-empty slice)
+    uint64_t x_timeout_ns = 20ull * 1000000000ull;
+    cudaEvent_t ev_x0 = nullptr;
 
     // last batch
     enum { IDLE, SUBMITTED, FETCHED } phase = IDLE;
@@ -323,30 +337,6 @@ __global__ void pack_windows_kernel(const uint8_t *arena, const chronos_window *
         const uint32_t chunks = win[w].len * CH_REC_CHUNKS;
         for (uint32_t ch = lane; ch < chunks; ch += 32) d[ch] = s[ch];
     }
-}
-
-// owner rank of every survivor + per-owner entry and slot counts (shared-memory histograms)
-__global__ void owner_keys_kernel(const uint32_t *pid, const uint8_t *ns, uint32_t n, uint32_t world, uint32_t *owner,
-                                  uint32_t *entry_counts, uint32_t *slot_counts) {
-    __shared__ uint32_t h[64], hs[64];
-    if (threadIdx.x < 64) { h[threadIdx.x] = 0; hs[threadIdx.x] = 0; }
-    __syncthreads();
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t o = hash32(pid[i]) % world;
-        owner[i] = o;
-        atomicAdd(&h[o], 1u);
-        atomicAdd(&hs[o], (uint32_t)ns[i]);
-    }
-    __syncthreads();
-    if (threadIdx.x < world && h[threadIdx.x]) {
-        atomicAdd(&entry_counts[threadIdx.x], h[threadIdx.x]);
-        atomicAdd(&slot_counts[threadIdx.x], hs[threadIdx.x]);
-    }
-}
-
-// slot counts in stream order: ns32[i] = ns[perm[i]]
-__global__ void permute_ns_kernel(const uint32_t *perm, const uint8_t *ns, uint32_t n, uint32_t *ns32) {
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) ns32[i] = ns[perm[i]];
 }
 
 __global__ void add_base_kernel(const uint32_t *src, uint32_t n, uint64_t base, uint64_t *out) {
@@ -707,7 +697,7 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
     const size_t sw = status_words(n, P);
     if ((rc = ensure(c, c->status, sw * 8))) return rc;
     CK(cudaEventRecord(c->ev_start, c->stream));
-    c->n_tev = 0;
+    if (!c->x_sent) c->n_tev = 0;  // (stage 2 of an exchange step keeps the marks of its stage 1)
     mark(c, "start");
     CK(cudaMemsetAsync(c->status.p, 0, sw * 8, c->stream));
     CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
@@ -736,7 +726,18 @@ int finish_batch(chronos_ctx *c) {
     c->b_chains = c->b_M ? c->h_scalars->n_chains : 0;
     if (c->h_plan->overflow) return fail(c, CHRONOS_E_CAPACITY, "more survivors than the batch was sized for");
     c->n_pids_seen = *c->h_pt_count;
-    cudaEventElapsedTime(&c->t_total, c->ev_start, c->ev_end);
+    if (c->b_exchanged) {
+        c->b_n = c->b_S;  // the upper bound the buffers were sized for is of no interest to the caller
+        const uint32_t xe = c->h_scalars->xchg_err;
+        c->phase = chronos_ctx::FETCHED;
+        if (xe & XERR_TIMEOUT)
+            return fail(c, CHRONOS_E_STATE, "exchange: a peer rank did not deliver its survivors within %.0f s",
+                        (double)c->x_timeout_ns * 1e-9);
+        if (xe & (XERR_OVERFLOW | XERR_PEER_OVERFLOW))
+            return fail(c, CHRONOS_E_CAPACITY, "exchange: survivors for one owner rank exceed the window (%u entries / %u slots per peer)",
+                        c->x_L.cap_e, c->x_L.cap_s);
+    }
+    cudaEventElapsedTime(&c->t_total, c->b_exchanged ? c->ev_x0 : c->ev_start, c->ev_end);
     if (c->trace) {
         for (int i = 1; i < c->n_tev; i++) {
             float ms = 0;
@@ -746,7 +747,7 @@ int finish_batch(chronos_ctx *c) {
     }
     cudaEventElapsedTime(&c->t_filter, c->ev_start, c->ev_filter);
     // (a stage-2-only batch keeps the filter time measured by chronos_filter_partition)
-    if (c->filter_timed) cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
+    if (c->filter_timed || (c->b_exchanged && c->x_filter_timed)) cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
     cudaGetLastError();
     c->phase = chronos_ctx::FETCHED;
     return CHRONOS_OK;
@@ -857,6 +858,11 @@ int chronos_destroy(chronos_ctx *c) {
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
                      &c->tickets, &c->scalars, &c->scan_status, &c->pack, &c->pack_off};
     for (DevBuf *b : all) release(*b);
+    for (int d = 0; d < XCHG_MAX_WORLD; d++)
+        if (c->x_opened[d] && c->x_peer[d]) cudaIpcCloseMemHandle(c->x_peer[d]);
+    release(c->x_window);
+    release(c->x_totals);
+    if (c->ev_x0) cudaEventDestroy(c->ev_x0);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->h_pt_count) cudaFreeHost(c->h_pt_count);
     if (c->h_plan) cudaFreeHost(c->h_plan);
@@ -893,6 +899,7 @@ int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t bas
     c->b_records = d_recs;
     c->b_slots = nullptr;
     c->b_explicit_arrival = false;
+    c->b_exchanged = false;
     if (n && (rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA) + c->b_P))) return rc;
     if ((rc = run_window_stage(c))) return rc;
     c->phase = chronos_ctx::SUBMITTED;
@@ -910,6 +917,7 @@ int chronos_submit_survivors(chronos_ctx *c, const void *slots, const uint64_t *
     c->b_records = nullptr;
     c->b_slots = static_cast<const uint4 *>(slots);
     c->b_explicit_arrival = true;
+    c->b_exchanged = false;
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     if (n) {
         if ((rc = ensure(c, c->surv_arrival, n * 8))) return rc;
@@ -1142,11 +1150,75 @@ void *chronos_stream(chronos_ctx *c) { return c ? (void *)c->stream : nullptr; }
 
 uint32_t chronos_owner_of(uint32_t pid, uint32_t world) { return world ? hash32(pid) % world : 0; }
 
+// Stage 1 of the sharded path up to the dense survivor arrays (surv_pid / surv_src / surv_meta /
+// surv_ns, count in scalars.surv_count). The per-PID state of the context is not touched.
+static int stage1_filter(chronos_ctx *c, const void *records, uint64_t n, const uint8_t **d_recs_out) {
+    int rc;
+    const uint8_t *d_recs = nullptr;
+    if (n == 0) {
+        // an empty slice still takes part in the exchange (zero counts, flag raised)
+    } else if (is_device_pointer(records)) {
+        if ((uintptr_t)records & 15) return fail(c, CHRONOS_E_ARG, "device records pointer must be 16-byte aligned");
+        d_recs = static_cast<const uint8_t *>(records);
+    } else {
+        if ((rc = ensure(c, c->d_batch, n * CH_REC_BYTES))) return rc;
+        CK(cudaMemcpyAsync(c->d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, c->stream));
+        d_recs = ptr<uint8_t>(c->d_batch);
+    }
+    c->launches = 0;
+    c->scan_slot = 0;
+    c->n_tev = 0;
+    if ((rc = ensure(c, c->keyA, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
+    if ((rc = ensure(c, c->x_totals, 256))) return rc;
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
+    init_scalars_kernel<<<1, 1, 0, c->stream>>>(ds);
+    set_u32_kernel<<<1, 1, 0, c->stream>>>(&ds->xchg_err, 0u);
+    c->launches += 2;
+    mark(c, "stage 1 start");
+    if (n && (rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA)))) return rc;
+    mark(c, "filter + compact");
+    *d_recs_out = d_recs;
+    return CHRONOS_OK;
+}
+
+// Partition of the survivors by owner rank: xchg_hist -> scan -> xchg_pack (exchange.cuh).
+static int stage1_partition(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint64_t base, XchgPackParams &pk) {
+    int rc;
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    const uint32_t W = pk.world;
+    const uint32_t T = (uint32_t)std::max<uint64_t>((n + XCHG_TILE - 1) / XCHG_TILE, 1);
+    const uint64_t table_len = (uint64_t)2 * W * T + 1;
+    if ((rc = ensure(c, c->radix_table, table_len * 4))) return rc;
+    uint32_t *table = ptr<uint32_t>(c->radix_table);
+    xchg_hist<<<T, XCHG_THREADS, 0, c->stream>>>(ptr<uint32_t>(c->surv_pid), ptr<uint8_t>(c->surv_ns), &ds->surv_count, W, table);
+    if ((rc = launch_scan(c, table, table_len))) return rc;
+    pk.pid = ptr<uint32_t>(c->surv_pid);
+    pk.surv_src = ptr<uint32_t>(c->surv_src);
+    pk.surv_meta = ptr<uint8_t>(c->surv_meta);
+    pk.surv_ns = ptr<uint8_t>(c->surv_ns);
+    pk.n_ptr = &ds->surv_count;
+    pk.batch = d_recs;
+    pk.base_arrival = base;
+    pk.table = table;
+    pk.totals = ptr<uint32_t>(c->x_totals);
+    pk.err = &ds->xchg_err;
+    pk.done = ptr<uint32_t>(c->tickets) + 58;
+    mark(c, "owner histogram + scan");
+    xchg_pack<<<T, XCHG_THREADS, 0, c->stream>>>(pk);
+    CK(cudaGetLastError());
+    mark(c, "pack into owners' windows");
+    c->launches += 2;
+    return CHRONOS_OK;
+}
+
 int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, uint64_t base_arrival_index,
                              uint32_t world, void *send_slots, uint64_t cap_slots, uint64_t *send_hdr,
                              uint64_t cap_entries, uint64_t *entry_counts_host, uint64_t *slot_counts_host) {
-    if (!c || !entry_counts_host || !slot_counts_host || world == 0 || world > 64)
-        return c ? fail(c, CHRONOS_E_ARG, "bad argument") : CHRONOS_E_ARG;
+    if (!c || !entry_counts_host || !slot_counts_host || world == 0 || world > XCHG_MAX_WORLD)
+        return c ? fail(c, CHRONOS_E_ARG, "bad argument (world must be 1..%d)", XCHG_MAX_WORLD) : CHRONOS_E_ARG;
     if (n && (!records || !send_slots || !send_hdr)) return fail(c, CHRONOS_E_ARG, "NULL argument");
     CK(cudaSetDevice(c->device));
     if (c->phase == chronos_ctx::SUBMITTED) {
@@ -1158,102 +1230,183 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
     for (uint32_t d = 0; d < world; d++) entry_counts_host[d] = slot_counts_host[d] = 0;
     if (!n) return CHRONOS_OK;
     int rc;
-    const uint8_t *d_recs;
-    if (is_device_pointer(records)) {
-        if ((uintptr_t)records & 15) return fail(c, CHRONOS_E_ARG, "device records pointer must be 16-byte aligned");
-        d_recs = static_cast<const uint8_t *>(records);
-    } else {
-        if ((rc = ensure(c, c->d_batch, n * CH_REC_BYTES))) return rc;
-        CK(cudaMemcpyAsync(c->d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, c->stream));
-        d_recs = ptr<uint8_t>(c->d_batch);
-    }
-    // scratch only: the per-PID state of this context is not touched by stage 1
-    c->launches = 0;
-    c->scan_slot = 0;
-    c->n_tev = 0;
-    if ((rc = ensure(c, c->keyA, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->keyB, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->valA, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->valB, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
-    if ((rc = ensure(c, c->ns32, (n + 8) * 4))) return rc;
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    const uint8_t *d_recs = nullptr;
     CK(cudaEventRecord(c->ev_start, c->stream));
-    CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
-    init_scalars_kernel<<<1, 1, 0, c->stream>>>(ds);
-    c->launches++;
-    if ((rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA)))) return rc;
+    if ((rc = stage1_filter(c, records, n, &d_recs))) return rc;
+    XchgPackParams pk;
+    memset(&pk, 0, sizeof(pk));
+    pk.world = world;
+    pk.direct = false;
+    pk.send_slots = static_cast<uint4 *>(send_slots);
+    pk.send_hdr = send_hdr;
+    pk.cap_entries = cap_entries;
+    pk.cap_slots = cap_slots;
+    if ((rc = stage1_partition(c, d_recs, n, base_arrival_index, pk))) return rc;
+    uint32_t hc[2 * XCHG_MAX_WORLD];
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    CK(cudaMemcpyAsync(hc, c->x_totals.p, sizeof(hc), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaEventRecord(c->ev_end, c->stream));
     CK(cudaStreamSynchronize(c->stream));
-    const uint64_t S = c->h_scalars->surv_count;
-    if (S > cap_entries) return fail(c, CHRONOS_E_CAPACITY, "%llu survivors do not fit the header buffer (%llu)",
-                                     (unsigned long long)S, (unsigned long long)cap_entries);
-    if (S) {
-        // stable counting sort by owner rank = one radix pass over the owner keys
-        uint32_t *owner = ptr<uint32_t>(c->valB);
-        if ((rc = ensure(c, c->pack_off, 1024))) return rc;
-        uint32_t *ocount = ptr<uint32_t>(c->pack_off);  // [0,64) entries per owner, [64,128) slots per owner
-        CK(cudaMemsetAsync(ocount, 0, 512, c->stream));
-        const unsigned blocks = (unsigned)std::min<uint64_t>((S + 255) / 256, 2048);
-        owner_keys_kernel<<<blocks, 256, 0, c->stream>>>(ptr<uint32_t>(c->keyA), ptr<uint8_t>(c->surv_ns), (uint32_t)S,
-                                                         world, owner, ocount, ocount + 64);
-        uint32_t tile_keys = 4096;
-        while ((S + tile_keys - 1) / tile_keys > 1024) tile_keys *= 2;
-        const uint32_t n_tiles = (uint32_t)((S + tile_keys - 1) / tile_keys);
-        if ((rc = ensure(c, c->radix_table, (size_t)RADIX_BINS * n_tiles * 4))) return rc;
-        RadixParams rp;
-        memset(&rp, 0, sizeof(rp));  // explicit mode: no plan
-        rp.keys_in = owner;
-        rp.vals_in = nullptr;
-        rp.meta_lo = nullptr;
-        rp.meta_hi = nullptr;
-        rp.split = 0;
-        rp.keys_out = ptr<uint32_t>(c->keyB);
-        rp.vals_out = ptr<uint32_t>(c->valA);  // permutation: survivors in (owner, arrival) order
-        rp.table = ptr<uint32_t>(c->radix_table);
-        rp.n = (uint32_t)S;
-        rp.tile_keys = tile_keys;
-        rp.n_tiles = n_tiles;
-        rp.shift = 0;
-        rp.mask = 0xFFu;
-        radix_hist<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
-        if ((rc = launch_scan(c, rp.table, (uint64_t)RADIX_BINS * n_tiles))) return rc;
-        radix_scatter<<<n_tiles, RADIX_THREADS, 0, c->stream>>>(rp);
-        // slot offsets of the transport stream, then the pack itself
-        permute_ns_kernel<<<blocks, 256, 0, c->stream>>>(rp.vals_out, ptr<uint8_t>(c->surv_ns), (uint32_t)S,
-                                                         ptr<uint32_t>(c->ns32));
-        if ((rc = launch_scan(c, ptr<uint32_t>(c->ns32), S))) return rc;
-        uint32_t hc[128];
-        CK(cudaMemcpyAsync(hc, ocount, 512, cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaStreamSynchronize(c->stream));
-        uint64_t tot_slots = 0;
-        for (uint32_t d = 0; d < world; d++) {
-            entry_counts_host[d] = hc[d];
-            slot_counts_host[d] = hc[64 + d];
-            tot_slots += hc[64 + d];
-        }
-        if (tot_slots > cap_slots) return fail(c, CHRONOS_E_CAPACITY, "%llu transport slots do not fit the send buffer (%llu)",
-                                               (unsigned long long)tot_slots, (unsigned long long)cap_slots);
-        PackParams pk;
-        pk.perm = rp.vals_out;
-        pk.surv_src = ptr<uint32_t>(c->surv_src);
-        pk.surv_meta = ptr<uint8_t>(c->surv_meta);
-        pk.surv_ns = ptr<uint8_t>(c->surv_ns);
-        pk.off = ptr<uint32_t>(c->ns32);
-        pk.batch = d_recs;
-        pk.base_arrival = base_arrival_index;
-        pk.S = (uint32_t)S;
-        pk.slots = static_cast<uint4 *>(send_slots);
-        pk.hdr = send_hdr;
-        pack_transport<<<(unsigned)std::min<uint64_t>((S + 255) / 256, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(pk);
-        CK(cudaGetLastError());
-        c->launches += 5;
-        CK(cudaEventRecord(c->ev_end, c->stream));
-        CK(cudaStreamSynchronize(c->stream));
+    uint64_t tot_e = 0, tot_s = 0;
+    for (uint32_t d = 0; d < world; d++) {
+        entry_counts_host[d] = hc[d];
+        slot_counts_host[d] = hc[XCHG_MAX_WORLD + d];
+        tot_e += hc[d];
+        tot_s += hc[XCHG_MAX_WORLD + d];
     }
     cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
     cudaGetLastError();
+    if (c->h_scalars->xchg_err & XERR_OVERFLOW)
+        return fail(c, CHRONOS_E_CAPACITY, "%llu survivors / %llu transport slots do not fit the send buffers (%llu / %llu)",
+                    (unsigned long long)tot_e, (unsigned long long)tot_s, (unsigned long long)cap_entries,
+                    (unsigned long long)cap_slots);
+    return CHRONOS_OK;
+}
+
+// ---- direct exchange over peer memory ---------------------------------------------------------
+int chronos_exchange_create(chronos_ctx *c, uint32_t world, uint32_t rank, uint64_t cap_entries_per_peer,
+                            uint64_t cap_slots_per_peer, void **window_out, uint8_t *ipc_handle_out) {
+    if (!c) return CHRONOS_E_ARG;
+    if (world == 0 || world > XCHG_MAX_WORLD || rank >= world || cap_entries_per_peer == 0)
+        return fail(c, CHRONOS_E_ARG, "bad argument (world must be 1..%d, rank < world)", XCHG_MAX_WORLD);
+    if (c->x_created) return fail(c, CHRONOS_E_STATE, "exchange window already created");
+    if (cap_slots_per_peer == 0) cap_slots_per_peer = cap_entries_per_peer * 8;
+    if (cap_slots_per_peer < 3 * cap_entries_per_peer) cap_slots_per_peer = 3 * cap_entries_per_peer;
+    if ((uint64_t)world * cap_slots_per_peer >= (1ull << 32) || (uint64_t)world * cap_entries_per_peer > c->max_batch)
+        return fail(c, CHRONOS_E_CAPACITY, "world x capacity per peer too large (entries must fit max_batch_events %llu)",
+                    (unsigned long long)c->max_batch);
+    CK(cudaSetDevice(c->device));
+    c->x_L = xchg_layout(world, rank, (uint32_t)cap_entries_per_peer, (uint32_t)cap_slots_per_peer);
+    int rc;
+    if ((rc = ensure(c, c->x_window, 2 * c->x_L.half_bytes))) return rc;
+    if ((rc = ensure(c, c->x_totals, 256))) return rc;
+    CK(cudaMemsetAsync(c->x_window.p, 0, 2 * c->x_L.half_bytes, c->stream));
+    CK(cudaStreamSynchronize(c->stream));  // peers may write as soon as they hold the address
+    if (!c->ev_x0) CK(cudaEventCreate(&c->ev_x0));
+    if (ipc_handle_out) {
+        cudaIpcMemHandle_t h;
+        static_assert(sizeof(h) == CHRONOS_IPC_HANDLE_BYTES, "IPC handle size");
+        CK(cudaIpcGetMemHandle(&h, c->x_window.p));
+        memcpy(ipc_handle_out, &h, sizeof(h));
+    }
+    if (window_out) *window_out = c->x_window.p;
+    for (int d = 0; d < XCHG_MAX_WORLD; d++) { c->x_peer[d] = nullptr; c->x_opened[d] = false; }
+    c->x_peer[rank] = ptr<uint8_t>(c->x_window);
+    c->x_created = true;
+    c->x_connected = (world == 1);
+    c->x_epoch = 0;
+    c->x_sent = false;
+    return CHRONOS_OK;
+}
+
+int chronos_exchange_connect(chronos_ctx *c, void *const *peer_windows, const uint8_t *peer_ipc_handles) {
+    if (!c) return CHRONOS_E_ARG;
+    if (!c->x_created) return fail(c, CHRONOS_E_STATE, "call chronos_exchange_create first");
+    if (!peer_windows && !peer_ipc_handles && c->x_L.world > 1) return fail(c, CHRONOS_E_ARG, "no peer addresses given");
+    CK(cudaSetDevice(c->device));
+    for (uint32_t d = 0; d < c->x_L.world; d++) {
+        if (d == c->x_L.rank || c->x_peer[d]) continue;
+        if (peer_windows && peer_windows[d]) {
+            c->x_peer[d] = static_cast<uint8_t *>(peer_windows[d]);
+            continue;
+        }
+        if (!peer_ipc_handles) return fail(c, CHRONOS_E_ARG, "no address for rank %u", d);
+        cudaIpcMemHandle_t h;
+        memcpy(&h, peer_ipc_handles + (size_t)d * CHRONOS_IPC_HANDLE_BYTES, sizeof(h));
+        void *p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) {
+            cudaGetLastError();
+            return fail(c, CHRONOS_E_CUDA, "cudaIpcOpenMemHandle for rank %u failed: %s", d, cudaGetErrorString(e));
+        }
+        c->x_peer[d] = static_cast<uint8_t *>(p);
+        c->x_opened[d] = true;
+    }
+    c->x_connected = true;
+    return CHRONOS_OK;
+}
+
+int chronos_filter_exchange(chronos_ctx *c, const void *records, uint64_t n, uint64_t base_arrival_index) {
+    if (!c) return CHRONOS_E_ARG;
+    if (!c->x_connected) return fail(c, CHRONOS_E_STATE, "exchange not connected");
+    if (c->x_sent) return fail(c, CHRONOS_E_STATE, "previous exchange not consumed: call chronos_submit_exchanged");
+    if (n && !records) return fail(c, CHRONOS_E_ARG, "records is NULL");
+    CK(cudaSetDevice(c->device));
+    if (c->phase == chronos_ctx::SUBMITTED) {
+        int rc0 = finish_batch(c);
+        if (rc0) return rc0;
+    }
+    if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
+                                      (unsigned long long)n, (unsigned long long)c->max_batch);
+    int rc;
+    const uint8_t *d_recs = nullptr;
+    CK(cudaEventRecord(c->ev_x0, c->stream));
+    if ((rc = stage1_filter(c, records, n, &d_recs))) return rc;
+    XchgPackParams pk;
+    memset(&pk, 0, sizeof(pk));
+    pk.world = c->x_L.world;
+    pk.direct = true;
+    pk.L = c->x_L;
+    pk.epoch = c->x_epoch + 1;
+    for (uint32_t d = 0; d < c->x_L.world; d++) pk.peer[d] = c->x_peer[d];
+    if ((rc = stage1_partition(c, d_recs, n, base_arrival_index, pk))) return rc;
+    c->x_epoch++;
+    c->x_sent = true;
+    c->x_launches = c->launches;
+    c->x_filter_timed = n != 0;
+    return CHRONOS_OK;
+}
+
+int chronos_submit_exchanged(chronos_ctx *c) {
+    if (!c) return CHRONOS_E_ARG;
+    if (!c->x_sent) return fail(c, CHRONOS_E_STATE, "nothing sent: call chronos_filter_exchange first");
+    const XchgLayout &L = c->x_L;
+    const uint64_t n_max = (uint64_t)L.world * L.cap_e;
+    const uint64_t stage1_launches = c->x_launches;
+    int rc = begin_batch(c, n_max, 0);
+    if (rc) return rc;
+    c->launches += stage1_launches;
+    const uint8_t *hb = ptr<uint8_t>(c->x_window) + (size_t)(c->x_epoch & 1u) * L.half_bytes;
+    c->b_records = nullptr;
+    c->b_slots = reinterpret_cast<const uint4 *>(hb + L.off_slots);
+    c->b_explicit_arrival = true;
+    c->b_exchanged = true;
+    c->x_sent = false;
+    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    if ((rc = ensure(c, c->surv_arrival, n_max * 8))) return rc;
+    if ((rc = ensure(c, c->surv_pid, (n_max + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_ns, n_max + 1))) return rc;
+    if ((rc = ensure(c, c->slot_off, (n_max + 8) * 4))) return rc;
+    XchgUnpackParams u;
+    memset(&u, 0, sizeof(u));
+    u.window = ptr<uint8_t>(c->x_window);
+    u.L = L;
+    u.epoch = c->x_epoch;
+    u.timeout_ns = c->x_timeout_ns;
+    u.arrival = ptr<uint64_t>(c->surv_arrival);
+    u.meta = ptr<uint8_t>(c->surv_meta);
+    u.ns = ptr<uint8_t>(c->surv_ns);
+    u.slot_off = ptr<uint32_t>(c->slot_off);
+    u.key = ptr<uint32_t>(c->keyA) + c->b_P;
+    u.pid_copy = ptr<uint32_t>(c->surv_pid);
+    u.src = ptr<uint32_t>(c->surv_src);
+    u.n_out = &ds->surv_count;
+    u.k_or = &ds->key_or;
+    u.k_and = &ds->key_and;
+    u.err = &ds->xchg_err;
+    u.n_cap = (uint32_t)n_max;
+    xchg_unpack<<<(unsigned)std::min<uint64_t>((n_max + 255) / 256, (uint64_t)c->sm_count * 4), 256, 0, c->stream>>>(u);
+    CK(cudaGetLastError());
+    c->launches++;
+    if ((rc = run_window_stage(c))) return rc;
+    c->phase = chronos_ctx::SUBMITTED;
+    return CHRONOS_OK;
+}
+
+int chronos_exchange_set_timeout(chronos_ctx *c, double seconds) {
+    if (!c || !(seconds > 0)) return CHRONOS_E_ARG;
+    c->x_timeout_ns = (uint64_t)(seconds * 1e9);
     return CHRONOS_OK;
 }
 

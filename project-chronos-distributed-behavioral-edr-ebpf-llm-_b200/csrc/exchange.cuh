@@ -1,0 +1,349 @@
+// exchange.cuh -- repartition of survivors by owner rank, sender and receiver.
+//
+// process_memory is keyed by pid and PIDs never interact (chronos_sensor.py:105, :138, :142,
+// :157), so the window logic shards by owner = hash32(pid) % world. Every rank filters a
+// contiguous slice of the arrival-ordered batch; its survivors then travel to their owners
+// in the transport form (filter.cuh transport_slots): one header word
+// (arrival 48 bits | META << 48 | slot count << 56) and 3..18 16-byte slots per survivor.
+//
+// The partition is one stable counting pass over the survivors (arrival order is kept inside
+// every owner's stream, which is all the reference's semantics need, :18-23 has no timestamp):
+//   xchg_hist   per tile of XCHG_TILE survivors: entries and slots per owner
+//   scan        exclusive scan of that table (sort.cuh)
+//   xchg_pack   stable ranks inside the tile, then the headers and slots are written
+//               STRAIGHT INTO THE OWNER'S RECEIVE WINDOW over NVLink (peer pointers), and the
+//               last CTA to finish publishes the counts and raises this rank's flag there.
+// There is no staging buffer, no count exchange and no host round trip on that path; the same
+// kernel can instead write one local stream ordered by (owner, arrival) for a host-driven
+// all-to-all (chronos_filter_partition).
+//
+// Receive window of a rank (one allocation, exported with cudaIpcGetMemHandle), two halves
+// used alternately (epoch & 1); per half:
+//   ctrl   u32 entries[16] | u32 slots[16] | u32 flag[16]      (one word per SOURCE rank)
+//   hdr    world x cap_e u64      region s = what source rank s sent, arrival order
+//   off    world x cap_e u32      first slot of the entry, relative to region s
+//   slots  world x cap_s uint4
+// Why two halves are enough: a rank packs step k+1 only after its own stage 2 of step k, which
+// waited for every peer's flag of step k; a peer raises that flag after ITS stage 2 of step
+// k-1 (stream order), the last reader of the half that step k+1 overwrites.
+#pragma once
+#include "common.cuh"
+
+namespace chronos {
+
+constexpr int XCHG_MAX_WORLD = 16;
+constexpr uint32_t XCHG_TILE = 2048;
+constexpr uint32_t XCHG_THREADS = 256;
+constexpr uint32_t XCHG_WARPS = XCHG_THREADS / 32;
+constexpr uint32_t XCHG_OVERFLOW = 0xFFFFFFFFu;
+constexpr uint32_t XCHG_CTRL_BYTES = 256;
+constexpr uint32_t XERR_OVERFLOW = 1u, XERR_TIMEOUT = 2u, XERR_PEER_OVERFLOW = 4u;
+
+struct XchgLayout {
+    uint32_t world, rank;
+    uint32_t cap_e, cap_s;  // per (source, owner) pair: entries, slots
+    uint64_t off_hdr, off_off, off_slots, half_bytes;
+};
+__host__ __device__ inline uint64_t xchg_align(uint64_t v) { return (v + 255) & ~255ull; }
+__host__ __device__ inline XchgLayout xchg_layout(uint32_t world, uint32_t rank, uint32_t cap_e, uint32_t cap_s) {
+    XchgLayout L;
+    L.world = world; L.rank = rank; L.cap_e = cap_e; L.cap_s = cap_s;
+    L.off_hdr = XCHG_CTRL_BYTES;
+    L.off_off = L.off_hdr + xchg_align((uint64_t)world * cap_e * 8);
+    L.off_slots = L.off_off + xchg_align((uint64_t)world * cap_e * 4);
+    L.half_bytes = L.off_slots + xchg_align((uint64_t)world * cap_s * 16);
+    return L;
+}
+
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint64_t global_timer_ns() {
+    uint64_t t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// ---------------------------------------------------------------------------------------
+// per tile: how many entries / transport slots go to each owner.
+// table is owner-major with row stride T (the grid size, an upper bound of the tile count):
+// rows [0, W) entries, rows [W, 2W) slots, and one closing element table[2W*T] so that the
+// exclusive scan leaves the grand total there.
+// ---------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(XCHG_THREADS) xchg_hist(const uint32_t *pid, const uint8_t *ns, const uint32_t *n_ptr,
+                                                         uint32_t world, uint32_t *table) {
+    __shared__ uint32_t he[XCHG_MAX_WORLD], hs[XCHG_MAX_WORLD];
+    const uint32_t T = gridDim.x, tile = blockIdx.x, S = *n_ptr;
+    if (threadIdx.x < XCHG_MAX_WORLD) { he[threadIdx.x] = 0; hs[threadIdx.x] = 0; }
+    __syncthreads();
+    const uint32_t lo = min(S, tile * XCHG_TILE), hi = min(S, lo + XCHG_TILE);
+    for (uint32_t i = lo + threadIdx.x; i < hi; i += XCHG_THREADS) {
+        const uint32_t o = hash32(pid[i]) % world;
+        atomicAdd(&he[o], 1u);
+        atomicAdd(&hs[o], (uint32_t)ns[i]);
+    }
+    __syncthreads();
+    if (threadIdx.x < world) {
+        table[(size_t)threadIdx.x * T + tile] = he[threadIdx.x];
+        table[(size_t)(world + threadIdx.x) * T + tile] = hs[threadIdx.x];
+    }
+    if (tile == 0 && threadIdx.x == 0) table[(size_t)2 * world * T] = 0;
+}
+
+struct XchgPackParams {
+    // survivors of this rank, arrival order
+    const uint32_t *pid, *surv_src;
+    const uint8_t *surv_meta, *surv_ns;
+    const uint32_t *n_ptr;
+    const uint8_t *batch;         // the slice's records (device)
+    uint64_t base_arrival;
+    const uint32_t *table;        // scanned
+    uint32_t world;
+    // direct mode: peer[d] = base of owner d's receive window (nullptr => local mode)
+    uint8_t *peer[XCHG_MAX_WORLD];
+    XchgLayout L;
+    uint32_t epoch;
+    // local mode: one stream ordered by (owner, arrival)
+    uint4 *send_slots;
+    uint64_t *send_hdr;
+    uint64_t cap_entries, cap_slots;
+    // both: per-owner totals for the host (entries[16] | slots[16]), error bits, CTA counter
+    uint32_t *totals;
+    uint32_t *err;
+    uint32_t *done;
+    bool direct;
+};
+
+__global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g) {
+    __shared__ uint32_t rs_e[XCHG_MAX_WORLD + 1], rs_s[XCHG_MAX_WORLD + 1];  // row starts = per-owner stream starts
+    __shared__ uint32_t wb_e[XCHG_WARPS][XCHG_MAX_WORLD], wb_s[XCHG_WARPS][XCHG_MAX_WORLD];
+    __shared__ uint32_t s_skip, s_last;
+    const uint32_t T = gridDim.x, tile = blockIdx.x, W = g.world, S = *g.n_ptr;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid <= (int)W) {
+        rs_e[tid] = g.table[(size_t)tid * T];
+        rs_s[tid] = g.table[(size_t)(W + tid) * T];
+    }
+    for (int i = tid; i < (int)(XCHG_WARPS * XCHG_MAX_WORLD); i += XCHG_THREADS) {
+        (&wb_e[0][0])[i] = 0;
+        (&wb_s[0][0])[i] = 0;
+    }
+    if (tid == 0) s_skip = 0;
+    __syncthreads();
+    // owners whose stream does not fit are skipped as a whole (reported, never truncated)
+    if (tid < (int)W) {
+        const uint32_t te = rs_e[tid + 1] - rs_e[tid], ts = rs_s[tid + 1] - rs_s[tid];
+        const bool over = g.direct ? (te > g.L.cap_e || ts > g.L.cap_s)
+                                   : ((uint64_t)rs_e[W] > g.cap_entries || (uint64_t)(rs_s[W] - rs_s[0]) > g.cap_slots);
+        if (over) atomicOr(&s_skip, 1u << tid);
+    }
+    const uint32_t t_lo = min(S, tile * XCHG_TILE), t_hi = min(S, t_lo + XCHG_TILE);
+    constexpr uint32_t SUB = XCHG_TILE / XCHG_WARPS;  // contiguous sub-range of a warp
+    const uint32_t w_lo = min(t_hi, t_lo + warp * SUB), w_hi = min(t_hi, w_lo + SUB);
+    // 1) per-warp counts
+    for (uint32_t i = w_lo + lane; i < w_hi; i += 32) {
+        const uint32_t o = hash32(g.pid[i]) % W;
+        atomicAdd(&wb_e[warp][o], 1u);
+        atomicAdd(&wb_s[warp][o], (uint32_t)g.surv_ns[i]);
+    }
+    __syncthreads();
+    // 2) owner d: running base over the warps, seeded with this tile's offset inside d's stream
+    if (tid < (int)W) {
+        uint32_t re = g.table[(size_t)tid * T + tile], rsl = g.table[(size_t)(W + tid) * T + tile];
+        if (g.direct) { re -= rs_e[tid]; rsl -= rs_s[tid]; }   // relative to the (source, owner) region
+        else rsl -= rs_s[0];                                   // slot rows come after the entry rows in the scan
+#pragma unroll
+        for (int w = 0; w < (int)XCHG_WARPS; w++) {
+            const uint32_t ce = wb_e[w][tid], cs = wb_s[w][tid];
+            wb_e[w][tid] = re; wb_s[w][tid] = rsl;
+            re += ce; rsl += cs;
+        }
+    }
+    __syncthreads();
+    const uint32_t skip = s_skip;
+    const uint32_t half = g.epoch & 1u;
+    // 3) stable placement, 32 survivors per step
+    for (uint32_t i0 = w_lo; i0 < w_hi; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const bool valid = i < w_hi;
+        uint32_t o = 0xFFu, ns = 0, rec = 0;
+        if (valid) {
+            o = hash32(g.pid[i]) % W;
+            ns = g.surv_ns[i];
+            rec = g.surv_src[i];
+        }
+        uint32_t rank_e = 0, pre_s = 0, grp_e = 0, grp_s = 0;
+#pragma unroll
+        for (int l = 0; l < 32; l++) {
+            const uint32_t ol = __shfl_sync(0xffffffffu, o, l), nl = __shfl_sync(0xffffffffu, ns, l);
+            if (ol == o) {
+                grp_e++; grp_s += nl;
+                if (l < lane) { rank_e++; pre_s += nl; }
+            }
+        }
+        uint32_t be = 0, bs = 0;
+        if (valid) { be = wb_e[warp][o]; bs = wb_s[warp][o]; }
+        __syncwarp();
+        if (valid && rank_e == 0) { wb_e[warp][o] = be + grp_e; wb_s[warp][o] = bs + grp_s; }
+        __syncwarp();
+        const bool live = valid && !((skip >> o) & 1u);
+        uint4 *dst = nullptr;  // first slot of this entry at its destination
+        const uint4 *src = nullptr;
+        if (live) {
+            const uint32_t e_idx = be + rank_e, s_idx = bs + pre_s;
+            const uint64_t hdr = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)g.surv_meta[i] << 48) | ((uint64_t)ns << 56);
+            src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
+            if (g.direct) {
+                uint8_t *hb = g.peer[o] + (size_t)half * g.L.half_bytes;
+                const size_t re = (size_t)g.L.rank * g.L.cap_e + e_idx;
+                reinterpret_cast<uint64_t *>(hb + g.L.off_hdr)[re] = hdr;
+                reinterpret_cast<uint32_t *>(hb + g.L.off_off)[re] = s_idx;
+                dst = reinterpret_cast<uint4 *>(hb + g.L.off_slots) + (size_t)g.L.rank * g.L.cap_s + s_idx;
+            } else {
+                g.send_hdr[e_idx] = hdr;
+                dst = g.send_slots + s_idx;
+            }
+        }
+        const uint32_t cnt = live ? ns : 0u;
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        const uint32_t excl = incl - cnt, total = __shfl_sync(0xffffffffu, incl, 31);
+        for (uint32_t b0 = 0; b0 < total; b0 += 32) {
+            const uint32_t k = b0 + lane;
+            int sidx = 0;  // lane that owns slot k (shuffle binary search, as in filter.cuh phase B2)
+#pragma unroll
+            for (int step = 16; step >= 1; step >>= 1) {
+                const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
+                if (vv <= k) sidx += step;
+            }
+            const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
+            const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
+            const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)dst, sidx);
+            if (k < total) {
+                const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
+                const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
+                reinterpret_cast<uint4 *>((uintptr_t)dp)[sl] = reinterpret_cast<const uint4 *>((uintptr_t)sp)[ch];
+            }
+        }
+    }
+    // 4) the last CTA to finish publishes counts and flag
+    __threadfence_system();
+    __syncthreads();
+    if (tid == 0) s_last = (atomicAdd(g.done, 1u) == T - 1) ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence_system();
+    if (tid < (int)W) {
+        const uint32_t te = rs_e[tid + 1] - rs_e[tid], ts = rs_s[tid + 1] - rs_s[tid];
+        const bool over = (skip >> tid) & 1u;
+        g.totals[tid] = te;
+        g.totals[XCHG_MAX_WORLD + tid] = ts;
+        if (over) atomicOr(g.err, XERR_OVERFLOW);
+        if (g.direct) {
+            uint32_t *ctrl = reinterpret_cast<uint32_t *>(g.peer[tid] + (size_t)half * g.L.half_bytes);
+            ctrl[g.L.rank] = over ? XCHG_OVERFLOW : te;
+            ctrl[XCHG_MAX_WORLD + g.L.rank] = over ? 0u : ts;
+            __threadfence_system();
+            st_release_sys_u32(ctrl + 2 * XCHG_MAX_WORLD + g.L.rank, g.epoch);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// receiver: wait for every source's flag, then turn the regions of this half into the dense,
+// source-ordered (= arrival-ordered) entry arrays the window stage reads.
+// ---------------------------------------------------------------------------------------
+struct XchgUnpackParams {
+    const uint8_t *window;   // this rank's receive window
+    XchgLayout L;
+    uint32_t epoch;
+    uint64_t timeout_ns;
+    // outputs, one per received entry j
+    uint64_t *arrival;
+    uint8_t *meta, *ns;
+    uint32_t *slot_off;      // index of the entry's first slot in the half's slot area
+    uint32_t *key, *pid_copy, *src;
+    uint32_t *n_out, *k_or, *k_and, *err;
+    uint32_t n_cap;          // capacity of the output arrays
+};
+
+__global__ void __launch_bounds__(256) xchg_unpack(const XchgUnpackParams g) {
+    __shared__ uint32_t es[XCHG_MAX_WORLD + 1];
+    __shared__ uint32_t s_err;
+    const uint32_t W = g.L.world, half = g.epoch & 1u;
+    const uint8_t *hb = g.window + (size_t)half * g.L.half_bytes;
+    const uint32_t *ctrl = reinterpret_cast<const uint32_t *>(hb);
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        uint32_t e = 0, bad = 0;
+        if (lane < (int)W) {
+            const uint64_t t0 = global_timer_ns();
+            while (ld_acquire_sys_u32(ctrl + 2 * XCHG_MAX_WORLD + lane) != g.epoch) {
+                if (global_timer_ns() - t0 > g.timeout_ns) { bad = XERR_TIMEOUT; break; }
+                __nanosleep(200);
+            }
+            if (!bad) {
+                e = ctrl[lane];
+                if (e == XCHG_OVERFLOW) { e = 0; bad = XERR_PEER_OVERFLOW; }
+                else if (e > g.L.cap_e) { e = 0; bad = XERR_PEER_OVERFLOW; }
+            }
+        }
+        bad = __reduce_or_sync(0xffffffffu, bad);
+        if (bad & XERR_TIMEOUT) e = 0;  // nothing of this step is trusted
+        uint32_t incl = e;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane <= (int)W) es[lane] = incl - e;  // es[W] = total
+        if (lane == 0) s_err = bad;
+    }
+    __syncthreads();
+    uint32_t total = es[W];
+    if (total > g.n_cap) total = g.n_cap;  // cannot happen when the context was sized for world * cap_e
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        *g.n_out = total;
+        if (s_err) atomicOr(g.err, s_err);
+    }
+    const uint64_t *hdr = reinterpret_cast<const uint64_t *>(hb + g.L.off_hdr);
+    const uint32_t *off = reinterpret_cast<const uint32_t *>(hb + g.L.off_off);
+    const uint4 *slots = reinterpret_cast<const uint4 *>(hb + g.L.off_slots);
+    uint32_t o = 0, a = 0xffffffffu;
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < total; j += gridDim.x * blockDim.x) {
+        uint32_t s = 0;
+#pragma unroll
+        for (int k = 1; k < XCHG_MAX_WORLD; k++)
+            if (k < (int)W && j >= es[k]) s = k;
+        const size_t r = (size_t)s * g.L.cap_e + (j - es[s]);
+        const uint64_t h = hdr[r];
+        const uint32_t so = s * g.L.cap_s + off[r];
+        const uint32_t k = reinterpret_cast<const uint32_t *>(slots + so)[0];  // pid = first word of slot 0
+        g.arrival[j] = h & 0xFFFFFFFFFFFFull;
+        g.meta[j] = (uint8_t)(h >> 48);
+        g.ns[j] = (uint8_t)(h >> 56);
+        g.slot_off[j] = so;
+        g.key[j] = k;
+        g.pid_copy[j] = k;
+        g.src[j] = j;
+        o |= k;
+        a &= k;
+    }
+    o = __reduce_or_sync(0xffffffffu, o);
+    a = __reduce_and_sync(0xffffffffu, a);
+    if ((threadIdx.x & 31) == 0 && (o | ~a)) {
+        atomicOr(g.k_or, o);
+        atomicAnd(g.k_and, a);
+    }
+}
+
+}  // namespace chronos

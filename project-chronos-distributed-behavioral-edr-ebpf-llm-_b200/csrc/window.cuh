@@ -455,64 +455,4 @@ __global__ void __launch_bounds__(256) gather_records(const GatherParams g) {
     }
 }
 
-// Sender side of the transport form: entry i of the (owner, arrival)-ordered stream is
-// survivor perm[i]; its needed chunks go to slots [off[i], off[i]+ns) and its header word
-// (arrival 48 bits | meta << 48 | ns << 56) to hdr[i]. One lane per entry resolves the
-// source, then the warp copies the 16-byte slots of its 32 entries cooperatively.
-struct PackParams {
-    const uint32_t *perm;      // S
-    const uint32_t *surv_src;  // S
-    const uint8_t *surv_meta;  // S
-    const uint8_t *surv_ns;    // S
-    const uint32_t *off;       // S: exclusive scan of ns in stream order
-    const uint8_t *batch;
-    uint64_t base_arrival;
-    uint32_t S;
-    uint4 *slots;
-    uint64_t *hdr;
-};
-
-__global__ void __launch_bounds__(256) pack_transport(const PackParams g) {
-    const int lane = threadIdx.x & 31;
-    const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
-    for (uint32_t base = warp_global * 32; base < g.S; base += n_warps * 32) {
-        const uint32_t i = base + lane;
-        const uint4 *src = nullptr;
-        uint32_t ns = 0, off = 0;
-        if (i < g.S) {
-            const uint32_t j = g.perm[i];
-            const uint32_t rec = g.surv_src[j];
-            src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
-            ns = g.surv_ns[j];
-            off = g.off[i];
-            g.hdr[i] = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)g.surv_meta[j] << 48) | ((uint64_t)ns << 56);
-        }
-        uint32_t incl = ns;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += t;
-        }
-        const uint32_t excl = incl - ns, total = __shfl_sync(0xffffffffu, incl, 31);
-        const uint32_t first_off = __shfl_sync(0xffffffffu, off, 0);
-        for (uint32_t b0 = 0; b0 < total; b0 += 32) {
-            const uint32_t k = b0 + lane;
-            int sidx = 0;  // owner lane of slot k (see filter.cuh phase B2)
-#pragma unroll
-            for (int step = 16; step >= 1; step >>= 1) {
-                const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
-                if (vv <= k) sidx += step;
-            }
-            const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
-            const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
-            if (k < total) {
-                const uint32_t sl = k - ex;  // slot within the entry
-                const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
-                g.slots[first_off + k] = reinterpret_cast<const uint4 *>((uintptr_t)sp)[ch];
-            }
-        }
-    }
-}
-
 }  // namespace chronos

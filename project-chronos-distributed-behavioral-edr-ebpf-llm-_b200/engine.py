@@ -96,6 +96,43 @@ class Context:
         self._check(self._L.chronos_submit_survivors(self._h, c_void_p(int(slots_ptr)), c_void_p(int(hdr_ptr)),
                                                      int(n_entries), int(n_slots)))
 
+    # ---- direct exchange (include/chronos.h, "direct exchange") -----------------------------
+    def exchange_create(self, world, rank, cap_entries_per_peer, cap_slots_per_peer=0):
+        """Allocate this rank's receive window. Returns (device address, 64-byte IPC handle)."""
+        win = c_void_p()
+        handle = (ctypes.c_uint8 * _ffi.IPC_HANDLE_BYTES)()
+        self._check(self._L.chronos_exchange_create(self._h, int(world), int(rank), int(cap_entries_per_peer),
+                                                    int(cap_slots_per_peer), byref(win), handle))
+        return int(win.value), bytes(handle)
+
+    def exchange_connect(self, world, windows=None, handles=None):
+        """windows: per-rank device addresses usable in this process (or None entries);
+        handles: per-rank 64-byte IPC handles of windows owned by other processes."""
+        wp = hp = None
+        if windows is not None:
+            wp = (c_void_p * world)(*[c_void_p(w) if w else c_void_p() for w in windows])
+        if handles is not None:
+            blob = b"".join(bytes(h) for h in handles)
+            assert len(blob) == world * _ffi.IPC_HANDLE_BYTES
+            hp = (ctypes.c_uint8 * len(blob)).from_buffer_copy(blob)
+        self._check(self._L.chronos_exchange_connect(self._h, wp, hp))
+
+    def filter_exchange_ptr(self, ptr, n, base_arrival_index=0):
+        """Stage 1: filter n records at ptr (host or device) and deliver the survivors to their owners."""
+        self._check(self._L.chronos_filter_exchange(self._h, c_void_p(int(ptr)), int(n), int(base_arrival_index)))
+
+    def filter_exchange(self, records, base_arrival_index=0):
+        a = as_record_bytes(records)
+        self._keep = a
+        self.filter_exchange_ptr(a.ctypes.data if a.size else 0, a.size // RECORD_BYTES, base_arrival_index)
+
+    def submit_exchanged(self):
+        """Stage 2 on what the peers delivered for this step."""
+        self._check(self._L.chronos_submit_exchanged(self._h))
+
+    def exchange_set_timeout(self, seconds):
+        self._check(self._L.chronos_exchange_set_timeout(self._h, float(seconds)))
+
     # ---- results -----------------------------------------------------------------------
     def fetch_counts(self):
         c = _ffi.Counts()

@@ -9,7 +9,9 @@ slices are contiguous and ordered, that is global arrival order, which is all th
 reference's semantics need (there is no timestamp in struct data_t, :18-23).
 
 `exchange()` is plain torch.distributed host logic and works on any backend/device (the
-CPU tests run it over gloo); `ShardedRunner` binds it to the CUDA stages of the C ABI.
+CPU tests run it over gloo); `ShardedRunner` binds it to the CUDA stages of the C ABI, or --
+on one NVSwitch box -- skips it: stage 1 then writes the survivors directly into the owners'
+HBM (csrc/exchange.cuh).
 """
 import ctypes
 from ctypes import c_void_p
@@ -80,22 +82,64 @@ def exchange(send_payload, send_hdr, entry_counts, unit_counts, unit_bytes, recv
 
 
 class ShardedRunner:
-    """One rank of the sharded pipeline: CUDA stage 1 -> all-to-all (NCCL) -> CUDA stage 2."""
+    """One rank of the sharded pipeline.
 
-    def __init__(self, rec_ptr, n, first, device, rank, world, cap=None):
+    mode "direct": CUDA stage 1 writes the survivors straight into the owners' receive
+    windows over NVLink (chronos_filter_exchange / chronos_submit_exchanged), nothing but
+    kernel launches on the host. mode "nccl": stage 1 packs per owner into a send buffer,
+    torch.distributed.all_to_all_single moves it, stage 2 runs on what arrived. "auto" takes
+    "direct" when every rank could map every peer's window (CUDA IPC), else "nccl"."""
+
+    def __init__(self, rec_ptr, n, first, device, rank, world, cap=None, mode="auto", cap_entries_per_peer=None):
         self.rec_ptr, self.n, self.first = int(rec_ptr), int(n), int(first)
         self.device, self.rank, self.world = int(device), int(rank), int(world)
         self.cap = int(cap or max(n // 2, 1024))   # survivors per rank, sent or received
         self.cap_slots = self.cap * 8              # 16-byte transport slots (3..18 per survivor)
-        self.ctx = Context(device=self.device, max_batch_events=max(self.n, self.cap))
-        dev = torch.device("cuda", self.device)
-        self.send_slots = torch.empty(self.cap_slots * SLOT_BYTES, dtype=torch.uint8, device=dev)
-        self.send_hdr = torch.empty(self.cap, dtype=torch.int64, device=dev)
-        self.recv_slots = torch.empty(self.cap_slots * SLOT_BYTES, dtype=torch.uint8, device=dev)
-        self.recv_hdr = torch.empty(self.cap, dtype=torch.int64, device=dev)
-        self._ec = (ctypes.c_uint64 * self.world)()
-        self._sc = (ctypes.c_uint64 * self.world)()
+        self.cap_pair = int(cap_entries_per_peer or max(self.cap // self.world, 1024))
+        self.ctx = Context(device=self.device, max_batch_events=max(self.n, self.cap, self.cap_pair * self.world))
         self._L = _ffi.lib()
+        self.mode = "nccl"
+        if mode in ("auto", "direct"):
+            ok = self._connect_direct()
+            if ok:
+                self.mode = "direct"
+            elif mode == "direct":
+                raise _ffi.ChronosError(_ffi.E_STATE, "direct exchange unavailable: " + self._direct_error)
+        if self.mode == "nccl":
+            dev = torch.device("cuda", self.device)
+            self.send_slots = torch.empty(self.cap_slots * SLOT_BYTES, dtype=torch.uint8, device=dev)
+            self.send_hdr = torch.empty(self.cap, dtype=torch.int64, device=dev)
+            self.recv_slots = torch.empty(self.cap_slots * SLOT_BYTES, dtype=torch.uint8, device=dev)
+            self.recv_hdr = torch.empty(self.cap, dtype=torch.int64, device=dev)
+            self._ec = (ctypes.c_uint64 * self.world)()
+            self._sc = (ctypes.c_uint64 * self.world)()
+
+    def _connect_direct(self):
+        """Create the receive window, all-gather the IPC handles, map the peers. Collective:
+        every rank gets the same answer."""
+        self._direct_error = ""
+        dev = torch.device("cuda", self.device)
+        ok = 1
+        handle = bytes(_ffi.IPC_HANDLE_BYTES)
+        try:
+            _, handle = self.ctx.exchange_create(self.world, self.rank, self.cap_pair)
+        except _ffi.ChronosError as e:
+            ok, self._direct_error = 0, str(e)
+        mine = torch.tensor(list(handle), dtype=torch.uint8, device=dev)
+        everyone = torch.empty(self.world * _ffi.IPC_HANDLE_BYTES, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(everyone, mine)
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 1:
+            blob = bytes(everyone.cpu().numpy().tobytes())
+            hs = [blob[i * _ffi.IPC_HANDLE_BYTES:(i + 1) * _ffi.IPC_HANDLE_BYTES] for i in range(self.world)]
+            try:
+                self.ctx.exchange_connect(self.world, handles=hs)
+            except _ffi.ChronosError as e:
+                ok, self._direct_error = 0, str(e)
+            flag = torch.tensor([ok], dtype=torch.int32, device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        return int(flag.item()) == 1
 
     def stream_ptr(self):
         return int(self._L.chronos_stream(self.ctx._h))
@@ -110,6 +154,13 @@ class ShardedRunner:
     def step(self, reset=True):
         if reset:
             self.ctx.reset()  # benchmark steps repeat the same batch on a fresh process_memory
+        if self.mode == "direct":
+            self.ctx.filter_exchange_ptr(self.rec_ptr, self.n, self.first)  # only enqueues
+            self.ctx.submit_exchanged()                                     # only enqueues
+            c = self.ctx.fetch_counts()
+            t, f = self.ctx.last_timing()
+            c.update(gpu_ms=t, filter_ms=f, launches=self.ctx.last_launches(), n_received=c["n_survivors"])
+            return c
         ec, sc = self.filter_partition(self.rec_ptr, self.n, self.first)  # waits for stage 1
         launches = self.ctx.last_launches()
         n_recv, n_slots = exchange(self.send_slots, self.send_hdr, ec, sc, SLOT_BYTES, self.recv_slots, self.recv_hdr)
@@ -152,5 +203,8 @@ class ShardedRunner:
         total = n * self.world
         return {"value": total / dt, "unit": "events/s", "h2d_bytes_per_step": n * RECORD_BYTES * self.world,
                 "d2h_bytes_per_step": int(d2h) * self.world, "ms_per_step": 1e3 * dt, "steps": steps,
-                "path": "per rank: chronos_filter_partition(pinned host slice) -> all_to_all -> "
-                        "chronos_submit_survivors -> copy_windows/window_records"}
+                "path": ("per rank: chronos_filter_exchange(pinned host slice, survivors written into the owners' "
+                         "windows over NVLink) -> chronos_submit_exchanged -> copy_windows/window_records")
+                if self.mode == "direct" else
+                        ("per rank: chronos_filter_partition(pinned host slice) -> all_to_all -> "
+                         "chronos_submit_survivors -> copy_windows/window_records")}
