@@ -302,7 +302,7 @@ def run_gpu_arm(args, rank, world, local_rank):
     value = total_events / (ms_per_step / 1e3)
 
     # ---- end-to-end through the public host API with pinned host buffers -------------------
-    e2e = runner.e2e(max(1, min(args.steps, 5)), barrier, dist)
+    e2e = runner.e2e(max(1, min(args.steps, 10)), barrier, dist)
 
     # ---- CPU baseline on a bounded sample (rank 0, N=1 only) -------------------------------
     cpu = None
@@ -313,6 +313,10 @@ def run_gpu_arm(args, rank, world, local_rank):
         rate, secs, kind, what = cpu_reference_rate(rows, cores)
         cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
                "sample": f"first {n_sample} events of the workload in {secs:.2f}s, partitioned by pid over {cores} processes; {what}"}
+
+    streaming = None
+    if rank == 0 and world == 1 and not args.no_stream:
+        streaming = stream_latency(chronos_b200, device)
 
     if rank == 0:
         f_ms = float(np.mean(filt_ms))
@@ -338,6 +342,7 @@ def run_gpu_arm(args, rank, world, local_rank):
                                       "library_event_ms": float(np.mean(step_ms))}},
             "cpu_baseline": cpu,
             "e2e": e2e,
+            "streaming": streaming,
             "gpu_launches": launches,
             "clocks": clocks,
             "wall_ms_per_step": 1e3 * t_wall / args.steps,
@@ -374,6 +379,10 @@ class SingleGpuRunner:
         return c
 
     def e2e(self, steps, barrier, dist):
+        """The same step through the public host API: the batch starts in pinned HOST memory
+        (H2D inside submit) and survivors, windows and the windows' records end in pinned host
+        memory. The download of step k runs on its own stream while step k+1's batch comes up
+        (chronos_download_begin); every download has completed before the clock stops."""
         from chronos_b200 import _ffi
 
         L = _ffi.lib()
@@ -385,31 +394,80 @@ class SingleGpuRunner:
         self.ctx.reset()
         self.ctx.submit_ptr(host.ptr, n, 0)
         c = self.ctx.fetch_counts()
-        S, W = c["n_survivors"], c["n_windows"]
-        r_idx, r_meta, r_win = Pinned(S * 8), Pinned(S), Pinned(W * 32)
-        r_rec = Pinned(S * REC)
-        h = self.ctx._h
+        cap = (c["n_survivors"] * (9 + REC) + c["n_windows"] * 32 + 4096 + 255) // 256 * 256
+        out = [Pinned(cap), Pinned(cap)]
         barrier()
         t0 = time.perf_counter()
-        for _ in range(steps):
+        lay = None
+        for k in range(steps):
             ts = time.perf_counter()
             self.ctx.reset()
             self.ctx.submit_ptr(host.ptr, n, 0)          # H2D of the whole batch inside
             c = self.ctx.fetch_counts()
-            assert L.chronos_copy_survivors(h, ctypes.c_void_p(r_idx.ptr), ctypes.c_void_p(r_meta.ptr), S) == 0
-            assert L.chronos_copy_windows(h, ctypes.c_void_p(r_win.ptr), W) == 0
-            assert L.chronos_copy_window_records(h, ctypes.c_void_p(r_rec.ptr), S) == 0
+            lay = self.ctx.download_begin(out[k & 1].ptr, cap)
             if os.environ.get("CHRONOS_BENCH_DEBUG"):
                 print(f"e2e step {1e3 * (time.perf_counter() - ts):.2f} ms", file=sys.stderr, flush=True)
+        self.ctx.download_wait()
         barrier()
         dt = (time.perf_counter() - t0) / steps
-        win = np.frombuffer(r_win.array[:W * 32], dtype=self.mod.WINDOW_DTYPE)
-        d2h = S * 9 + W * 32 + int(win["len"].sum()) * REC + 64
-        for p in (host, r_idx, r_meta, r_win, r_rec):
+        # the last download must be what the blocking calls return
+        idx, meta, win, rec = self.ctx.parse_download(out[(steps - 1) & 1].array, lay)
+        assert len(idx) == c["n_survivors"] and len(win) == c["n_windows"] and int(win["len"].sum()) == len(rec)
+        assert np.all(np.diff(win["trigger_idx"].astype(np.int64)) > 0) and np.all(np.diff(idx.astype(np.int64)) > 0)
+        d2h = lay["total_bytes"]
+        for p in [host] + out:
             p.free()
         return {"value": n / dt, "unit": UNIT, "h2d_bytes_per_step": n * REC, "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": 1e3 * dt, "steps": steps,
-                "path": "Context.submit(pinned host records) -> fetch -> copy_survivors/windows/window_records"}
+                "path": "Context.submit(pinned host records) -> fetch -> download_begin(pinned host results: survivors, "
+                        "windows, window records); the download of step k overlaps the upload of step k+1, all "
+                        "downloads complete inside the timed region"}
+
+
+def stream_latency(chronos_b200, device, batches=1000, batch_events=65_536, ring=64, warm=50):
+    """BASELINE.json configs[4]: a stream of 64K-event micro-batches through ONE context whose
+    per-PID state persists (process_memory, chronos_sensor.py:105); per-batch latency of
+    submit -> fetch, wall clock around the blocking calls. Two legs: batch already in HBM, and
+    batch in pinned host memory with the windows and their records read back (18.9 MB up)."""
+    from chronos_b200 import _ffi, tracegen
+
+    L = _ffi.lib()
+    spec = tracegen.WORKLOADS["stream_64k"]
+    dev = tracegen.generate_device(spec, device=device, first=0, n=ring * batch_events)
+    host = Pinned(ring * batch_events * REC)
+    assert L.chronos_memcpy_d2h(device, ctypes.c_void_p(host.ptr), ctypes.c_void_p(dev.ptr), ring * batch_events * REC) == 0
+    r_win, r_rec = Pinned(batch_events * 32), Pinned(batch_events * REC)
+    out = {"workload": "configs[4]: 64K-event micro-batches, persistent per-PID state (stream_64k)",
+           "batch_events": batch_events, "batches": batches, "batch_bytes": batch_events * REC,
+           "clock": "host wall clock around submit..fetch (blocking), one batch in flight"}
+    for leg in ("device_resident", "host_buffers"):
+        ctx = chronos_b200.Context(device=device, max_batch_events=batch_events)
+        lat, windows, survivors = [], 0, 0
+        for i in range(warm + batches):
+            slot = i % ring
+            src = (dev.ptr if leg == "device_resident" else host.ptr) + slot * batch_events * REC
+            t0 = time.perf_counter()
+            ctx.submit_ptr(src, batch_events, i * batch_events)
+            c = ctx.fetch_counts()
+            if leg == "host_buffers":
+                W, S = c["n_windows"], c["n_survivors"]
+                if W:
+                    ctx._check(L.chronos_copy_windows(ctx._h, ctypes.c_void_p(r_win.ptr), W))
+                    ctx._check(L.chronos_copy_window_records(ctx._h, ctypes.c_void_p(r_rec.ptr), batch_events))
+            t1 = time.perf_counter()
+            if i >= warm:
+                lat.append(1e3 * (t1 - t0))
+                windows += c["n_windows"]
+                survivors += c["n_survivors"]
+        a = np.array(lat)
+        out[leg] = {"p50_ms": float(np.percentile(a, 50)), "p99_ms": float(np.percentile(a, 99)), "mean_ms": float(a.mean()),
+                    "min_ms": float(a.min()), "max_ms": float(a.max()), "events_per_s": batch_events / (a.mean() / 1e3),
+                    "survivors": survivors, "windows": windows, "pending_at_end": c["n_pending"]}
+        ctx.close()
+    for b in (host, r_win, r_rec):
+        b.free()
+    dev.free()
+    return out
 
 
 def main():
@@ -420,6 +478,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--events", type=int, default=0, help="override events per GPU (testing only)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-stream", action="store_true", help="skip the configs[4] micro-batch latency leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

@@ -166,6 +166,29 @@ int chronos_filter_partition(chronos_ctx *ctx, const void *records, uint64_t n, 
 int chronos_submit_survivors(chronos_ctx *ctx, const void *slots, const uint64_t *hdr, uint64_t n_entries,
                              uint64_t n_slots);
 
+/* ---- asynchronous download of the results ------------------------------------------------
+ *
+ * The chronos_copy_* calls block. A replay loop that wants the PCIe link busy in both
+ * directions (results of batch k going down while batch k+1 comes up) uses these two
+ * instead: chronos_download_begin gathers survivors, windows and the windows' records of the
+ * FETCHED batch into one device staging buffer and starts ONE device-to-host copy on a
+ * separate stream; it returns at once and the context is free for the next chronos_submit.
+ * host_dst should be pinned memory (chronos_host_alloc_pinned); with pageable memory the copy
+ * still works but is staged by the driver. Two downloads may be in flight; a third call waits
+ * for the oldest. The data is complete after chronos_download_wait. No reference counterpart
+ * (the reference prints each window as it flushes, chronos_sensor.py:143-155). */
+typedef struct chronos_download {
+    uint64_t n_survivors, n_windows, n_window_records;
+    uint64_t off_survivor_idx;    /* u64[n_survivors]  global arrival index, ascending */
+    uint64_t off_survivor_meta;   /* u8[n_survivors]   CHRONOS_META_* bits */
+    uint64_t off_windows;         /* chronos_window[n_windows], ascending trigger arrival */
+    uint64_t off_window_records;  /* 288 B x n_window_records, window after window */
+    uint64_t total_bytes;         /* what host_dst must hold */
+} chronos_download;
+/* cap_bytes too small: CHRONOS_E_ARG, and *out still tells the size needed. */
+int chronos_download_begin(chronos_ctx *ctx, void *host_dst, uint64_t cap_bytes, chronos_download *out);
+int chronos_download_wait(chronos_ctx *ctx);
+
 /* ---- direct exchange: survivors go straight into the owner's memory over NVLink -------------
  *
  * The two calls above leave the all-to-all to the host (torch.distributed / NCCL). On one

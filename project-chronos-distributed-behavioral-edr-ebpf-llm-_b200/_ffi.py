@@ -44,6 +44,13 @@ class TracegenCfg(Structure):
 # every symbol include/chronos.h declares: name -> (restype, argtypes)
 IPC_HANDLE_BYTES = 64
 
+
+class Download(Structure):
+    _fields_ = [("n_survivors", c_uint64), ("n_windows", c_uint64), ("n_window_records", c_uint64),
+                ("off_survivor_idx", c_uint64), ("off_survivor_meta", c_uint64), ("off_windows", c_uint64),
+                ("off_window_records", c_uint64), ("total_bytes", c_uint64)]
+
+
 SIGNATURES = {
     "chronos_device_ok": (c_int, [c_int]),
     "chronos_create": (c_int, [c_int, c_uint64, POINTER(c_void_p)]),
@@ -67,6 +74,8 @@ SIGNATURES = {
     "chronos_filter_partition": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64, c_uint32, c_void_p, c_uint64,
                                          c_void_p, c_uint64, c_void_p, c_void_p]),
     "chronos_submit_survivors": (c_int, [c_void_p, c_void_p, c_void_p, c_uint64, c_uint64]),
+    "chronos_download_begin": (c_int, [c_void_p, c_void_p, c_uint64, POINTER(Download)]),
+    "chronos_download_wait": (c_int, [c_void_p]),
     "chronos_exchange_create": (c_int, [c_void_p, c_uint32, c_uint32, c_uint64, c_uint64, POINTER(c_void_p), c_void_p]),
     "chronos_exchange_connect": (c_int, [c_void_p, c_void_p, c_void_p]),
     "chronos_filter_exchange": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64]),

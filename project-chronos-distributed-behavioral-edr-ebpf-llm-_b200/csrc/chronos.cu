@@ -115,6 +115,12 @@ struct chronos_ctx {
     bool x_filter_timed = false;  // stage 1 of this step ran the filter (non-empty slice)
     uint64_t x_timeout_ns = 20ull * 1000000000ull;
     cudaEvent_t ev_x0 = nullptr;
+    // asynchronous result download (chronos_download_begin)
+    cudaStream_t dl_stream = nullptr;
+    cudaEvent_t dl_ready = nullptr, dl_done[2] = {nullptr, nullptr};
+    DevBuf dl_stage[2];
+    bool dl_inflight[2] = {false, false};
+    int dl_k = 0;
 
     // last batch
     enum { IDLE, SUBMITTED, FETCHED } phase = IDLE;
@@ -327,7 +333,12 @@ __global__ void pack_by_slot_kernel(const uint8_t *arena, const uint32_t *slot, 
 }
 
 // one warp per window: packed[off[w] ..] = arena[start .. start+len)
-__global__ void pack_windows_kernel(const uint8_t *arena, const chronos_window *win, const uint64_t *off, uint32_t nw,
+__global__ void window_len_kernel(const chronos_window *win, uint32_t nw, uint32_t *len) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nw; i += gridDim.x * blockDim.x) len[i] = win[i].len;
+}
+
+// records of every window, window after window (off = exclusive scan of the window lengths)
+__global__ void pack_windows_kernel(const uint8_t *arena, const chronos_window *win, const uint32_t *off, uint32_t nw,
                                     uint8_t *dst) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
@@ -390,7 +401,7 @@ int launch_filter(chronos_ctx *c, const FilterParams &fp) {
 
 // exclusive scan in place (device array of n u32) on the context's stream
 // (n_dev != nullptr: the real count lives on the device, n is only its upper bound)
-int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_dev = nullptr) {
+int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_dev = nullptr, int own_ticket = -1) {
     if (n == 0) return CHRONOS_OK;
     const uint32_t n_tiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
     int rc;
@@ -398,12 +409,13 @@ int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_de
     if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_tiles * 8, 4096)))) return rc;
     if (c->scan_status.p != before || c->scan_epoch == 0)  // fresh memory or wrapped epoch: tag 0 = "never"
         CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, c->stream));
-    if (c->scan_slot >= 48) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
+    if (own_ticket < 0 && c->scan_slot >= 48) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
+    if (own_ticket >= 0) CK(cudaMemsetAsync(ptr<uint32_t>(c->tickets) + own_ticket, 0, 4, c->stream));
     ScanParams sp;
     sp.data = data;
     sp.n = (uint32_t)n;
     sp.n_ptr = n_dev;
-    sp.ticket = ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
+    sp.ticket = own_ticket >= 0 ? ptr<uint32_t>(c->tickets) + own_ticket : ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
     sp.status = ptr<uint64_t>(c->scan_status);
     sp.epoch = ++c->scan_epoch;
     if (c->scan_epoch >= (1u << 29)) c->scan_epoch = 0;  // re-zero on the next call
@@ -862,6 +874,15 @@ int chronos_destroy(chronos_ctx *c) {
         if (c->x_opened[d] && c->x_peer[d]) cudaIpcCloseMemHandle(c->x_peer[d]);
     release(c->x_window);
     release(c->x_totals);
+    if (c->dl_stream) {
+        cudaStreamSynchronize(c->dl_stream);
+        cudaStreamDestroy(c->dl_stream);
+        cudaEventDestroy(c->dl_ready);
+        cudaEventDestroy(c->dl_done[0]);
+        cudaEventDestroy(c->dl_done[1]);
+    }
+    release(c->dl_stage[0]);
+    release(c->dl_stage[1]);
     if (c->ev_x0) cudaEventDestroy(c->ev_x0);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
     if (c->h_pt_count) cudaFreeHost(c->h_pt_count);
@@ -1010,31 +1031,97 @@ int chronos_copy_arena(chronos_ctx *c, void *dst, uint64_t cap_records) {
     return CHRONOS_OK;
 }
 
+// records of all windows of the fetched batch, window after window, into a DEVICE buffer
+// (every grouped entry is in a window or pending, so the total is known without a read-back)
+static int pack_window_records(chronos_ctx *c, uint8_t *dst_dev) {
+    const uint64_t W = c->b_W;
+    if (!W) return CHRONOS_OK;
+    int rc;
+    if ((rc = ensure(c, c->pack_off, (W + 8) * 4))) return rc;
+    const unsigned blocks = (unsigned)std::min<uint64_t>((W + 255) / 256, 2048);
+    window_len_kernel<<<blocks, 256, 0, c->stream>>>(ptr<chronos_window>(c->windows), (uint32_t)W, ptr<uint32_t>(c->pack_off));
+    if ((rc = launch_scan(c, ptr<uint32_t>(c->pack_off), W, nullptr, 56))) return rc;
+    pack_windows_kernel<<<(unsigned)std::min<uint64_t>((W + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
+        ptr<uint8_t>(c->arena[c->cur]), ptr<chronos_window>(c->windows), ptr<uint32_t>(c->pack_off), (uint32_t)W, dst_dev);
+    CK(cudaGetLastError());
+    return CHRONOS_OK;
+}
+
 int chronos_copy_window_records(chronos_ctx *c, void *dst, uint64_t cap_records) {
     int rc = need_fetched(c);
     if (rc) return rc;
-    const uint64_t W = c->b_W;
-    if (!W) return CHRONOS_OK;
-    std::vector<chronos_window> win(W);
-    CK(cudaMemcpyAsync(win.data(), c->windows.p, W * sizeof(chronos_window), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
-    std::vector<uint64_t> off(W);
-    uint64_t tot = 0;
-    for (uint64_t i = 0; i < W; i++) {
-        off[i] = tot;
-        tot += win[i].len;
-    }
+    const uint64_t tot = c->b_M - c->n_pending;  // grouped entries that left in a window
+    if (!c->b_W) return CHRONOS_OK;
     if (cap_records < tot || !dst) return fail(c, CHRONOS_E_ARG, "window record buffer too small (%llu < %llu)",
                                                (unsigned long long)cap_records, (unsigned long long)tot);
     if ((rc = ensure(c, c->pack, tot * CH_REC_BYTES))) return rc;
-    if ((rc = ensure(c, c->pack_off, W * 8))) return rc;
-    CK(cudaMemcpyAsync(c->pack_off.p, off.data(), W * 8, cudaMemcpyHostToDevice, c->stream));
-    pack_windows_kernel<<<(unsigned)std::min<uint64_t>((W + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
-        ptr<uint8_t>(c->arena[c->cur]), ptr<chronos_window>(c->windows), ptr<uint64_t>(c->pack_off), (uint32_t)W,
-        ptr<uint8_t>(c->pack));
-    CK(cudaGetLastError());
+    if ((rc = pack_window_records(c, ptr<uint8_t>(c->pack)))) return rc;
     CK(cudaMemcpyAsync(dst, c->pack.p, tot * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
+    return CHRONOS_OK;
+}
+
+// ---- asynchronous download of a fetched batch's results ---------------------------------------
+int chronos_download_begin(chronos_ctx *c, void *host_dst, uint64_t cap_bytes, chronos_download *out) {
+    int rc = need_fetched(c);
+    if (rc) return rc;
+    if (!out) return fail(c, CHRONOS_E_ARG, "out is NULL");
+    auto al = [](uint64_t v) { return (v + 255) & ~255ull; };
+    const uint64_t S = c->b_S, W = c->b_W, R = c->b_W ? c->b_M - c->n_pending : 0;
+    memset(out, 0, sizeof(*out));
+    out->n_survivors = S;
+    out->n_windows = W;
+    out->n_window_records = R;
+    out->off_survivor_idx = 0;
+    out->off_survivor_meta = al(S * 8);
+    out->off_windows = out->off_survivor_meta + al(S);
+    out->off_window_records = out->off_windows + al(W * sizeof(chronos_window));
+    out->total_bytes = out->off_window_records + R * CH_REC_BYTES;
+    if (out->total_bytes == 0) return CHRONOS_OK;
+    if (!host_dst || cap_bytes < out->total_bytes)
+        return fail(c, CHRONOS_E_ARG, "download buffer too small (%llu < %llu bytes)", (unsigned long long)cap_bytes,
+                    (unsigned long long)out->total_bytes);
+    if (!c->dl_stream) {
+        CK(cudaStreamCreateWithFlags(&c->dl_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&c->dl_ready, cudaEventDisableTiming));
+        for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&c->dl_done[k], cudaEventDisableTiming));
+    }
+    const int k = c->dl_k;
+    if (c->dl_inflight[k]) {  // the copy started two calls ago still reads this staging buffer
+        CK(cudaEventSynchronize(c->dl_done[k]));
+        c->dl_inflight[k] = false;
+    }
+    if ((rc = ensure(c, c->dl_stage[k], out->total_bytes))) return rc;
+    uint8_t *st = ptr<uint8_t>(c->dl_stage[k]);
+    if (S) {
+        if (c->b_explicit_arrival) {
+            CK(cudaMemcpyAsync(st + out->off_survivor_idx, c->surv_arrival.p, S * 8, cudaMemcpyDeviceToDevice, c->stream));
+        } else {
+            add_base_kernel<<<(unsigned)std::min<uint64_t>((S + 255) / 256, 2048), 256, 0, c->stream>>>(
+                ptr<uint32_t>(c->surv_src), (uint32_t)S, c->b_base, reinterpret_cast<uint64_t *>(st + out->off_survivor_idx));
+            CK(cudaGetLastError());
+        }
+        CK(cudaMemcpyAsync(st + out->off_survivor_meta, c->surv_meta.p, S, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    if (W) {
+        CK(cudaMemcpyAsync(st + out->off_windows, c->windows.p, W * sizeof(chronos_window), cudaMemcpyDeviceToDevice, c->stream));
+        if ((rc = pack_window_records(c, st + out->off_window_records))) return rc;
+    }
+    CK(cudaEventRecord(c->dl_ready, c->stream));
+    CK(cudaStreamWaitEvent(c->dl_stream, c->dl_ready, 0));
+    CK(cudaMemcpyAsync(host_dst, st, out->total_bytes, cudaMemcpyDeviceToHost, c->dl_stream));
+    CK(cudaEventRecord(c->dl_done[k], c->dl_stream));
+    c->dl_inflight[k] = true;
+    c->dl_k ^= 1;
+    return CHRONOS_OK;
+}
+
+int chronos_download_wait(chronos_ctx *c) {
+    if (!c) return CHRONOS_E_ARG;
+    if (!c->dl_stream) return CHRONOS_OK;
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->dl_stream));
+    c->dl_inflight[0] = c->dl_inflight[1] = false;
     return CHRONOS_OK;
 }
 

@@ -96,6 +96,28 @@ class Context:
         self._check(self._L.chronos_submit_survivors(self._h, c_void_p(int(slots_ptr)), c_void_p(int(hdr_ptr)),
                                                      int(n_entries), int(n_slots)))
 
+    # ---- asynchronous download ------------------------------------------------------------
+    def download_begin(self, host_ptr, cap_bytes):
+        """Start one device-to-host copy of the fetched batch's survivors, windows and window
+        records into (pinned) host memory at host_ptr; returns the layout as a dict. The data
+        is complete after download_wait(); the context can take the next submit meanwhile."""
+        d = _ffi.Download()
+        self._check(self._L.chronos_download_begin(self._h, c_void_p(int(host_ptr)), int(cap_bytes), byref(d)))
+        return {k: int(getattr(d, k)) for k, _ in _ffi.Download._fields_}
+
+    def download_wait(self):
+        self._check(self._L.chronos_download_wait(self._h))
+
+    @staticmethod
+    def parse_download(buf, layout):
+        """Views into a completed download (buf: uint8 array over the host buffer)."""
+        S, W, R = layout["n_survivors"], layout["n_windows"], layout["n_window_records"]
+        idx = buf[layout["off_survivor_idx"]:layout["off_survivor_idx"] + 8 * S].view("<u8")
+        meta = buf[layout["off_survivor_meta"]:layout["off_survivor_meta"] + S]
+        win = buf[layout["off_windows"]:layout["off_windows"] + 32 * W].view(WINDOW_DTYPE)
+        rec = buf[layout["off_window_records"]:layout["off_window_records"] + RECORD_BYTES * R].reshape(-1, RECORD_BYTES)
+        return idx, meta, win, rec
+
     # ---- direct exchange (include/chronos.h, "direct exchange") -----------------------------
     def exchange_create(self, world, rank, cap_entries_per_peer, cap_slots_per_peer=0):
         """Allocate this rank's receive window. Returns (device address, 64-byte IPC handle)."""

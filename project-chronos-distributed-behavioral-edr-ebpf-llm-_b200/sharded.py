@@ -174,7 +174,8 @@ class ShardedRunner:
 
     def e2e(self, steps, barrier, dist_mod):
         """Same step, but the slice starts in pinned HOST memory (H2D inside the timed region)
-        and the windows + their records are read back to the host."""
+        and survivors, windows and window records are read back to pinned host memory; the
+        download of step k overlaps the upload of step k+1 (chronos_download_begin)."""
         import time
 
         L = self._L
@@ -184,27 +185,29 @@ class ShardedRunner:
         assert L.chronos_memcpy_d2h(self.device, p, c_void_p(self.rec_ptr), n * RECORD_BYTES) == 0
         dev_ptr, self.rec_ptr = self.rec_ptr, p.value
         c = self.step()
-        W, S = c["n_windows"], c["n_survivors"]
-        win = np.zeros(max(W, 1) * 32, dtype=np.uint8)
-        rec = np.zeros((max(S, 1), RECORD_BYTES), dtype=np.uint8)
+        cap = ((c["n_survivors"] * 2 + 4096) * (9 + RECORD_BYTES + 32) + 255) // 256 * 256
+        outs = []
+        for _ in range(2):
+            q = c_void_p()
+            assert L.chronos_host_alloc_pinned(cap, ctypes.byref(q)) == 0
+            outs.append(q)
         barrier()
         t0 = time.perf_counter()
         d2h = 0
-        for _ in range(steps):
+        for k in range(steps):
             c = self.step()
-            W = c["n_windows"]
-            self.ctx._check(L.chronos_copy_windows(self.ctx._h, win.ctypes.data, max(W, 1)))
-            self.ctx._check(L.chronos_copy_window_records(self.ctx._h, rec.ctypes.data, max(S, 1)))
-            d2h = W * 32 + int(np.frombuffer(win[:W * 32], dtype="<u4").reshape(-1, 8)[:, 4].sum()) * RECORD_BYTES
+            d2h = self.ctx.download_begin(outs[k & 1].value, cap)["total_bytes"]
+        self.ctx.download_wait()
         barrier()
         dt = (time.perf_counter() - t0) / steps
         self.rec_ptr = dev_ptr
         L.chronos_host_free_pinned(p)
+        for q in outs:
+            L.chronos_host_free_pinned(q)
         total = n * self.world
+        how = ("chronos_filter_exchange(pinned host slice, survivors written into the owners' windows over NVLink) -> "
+               "chronos_submit_exchanged" if self.mode == "direct" else
+               "chronos_filter_partition(pinned host slice) -> all_to_all -> chronos_submit_survivors")
         return {"value": total / dt, "unit": "events/s", "h2d_bytes_per_step": n * RECORD_BYTES * self.world,
                 "d2h_bytes_per_step": int(d2h) * self.world, "ms_per_step": 1e3 * dt, "steps": steps,
-                "path": ("per rank: chronos_filter_exchange(pinned host slice, survivors written into the owners' "
-                         "windows over NVLink) -> chronos_submit_exchanged -> copy_windows/window_records")
-                if self.mode == "direct" else
-                        ("per rank: chronos_filter_partition(pinned host slice) -> all_to_all -> "
-                         "chronos_submit_survivors -> copy_windows/window_records")}
+                "path": "per rank: " + how + " -> fetch -> download_begin(pinned host results), overlapped with the next upload"}

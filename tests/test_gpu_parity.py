@@ -240,3 +240,41 @@ def test_sensor_drop_in_reproduces_reference_stdout_and_prompts():
         # everything the unmodified script printed after its banner (:143-155), byte for byte
         assert "\n".join(lines) + "\n" == ref["stdout_after_banner"]
         s.close()
+
+
+def test_async_download_equals_blocking_copies(ctx):
+    """chronos_download_begin/_wait deliver exactly what the blocking copy calls return, also
+    with two downloads in flight while the context already works on the next batch."""
+    import ctypes
+
+    from chronos_b200 import _ffi, tracegen
+
+    L = _ffi.lib()
+    rows = tracegen.generate_host(tracegen.WORKLOADS["stream_64k"], n=60_000)
+    thirds = [rows[0:20_000], rows[20_000:40_000], rows[40_000:60_000]]
+    cap = 20_000 * (288 + 9 + 32) * 2
+    bufs = []
+    for _ in range(3):
+        p = ctypes.c_void_p()
+        assert L.chronos_host_alloc_pinned(cap, ctypes.byref(p)) == 0
+        bufs.append(p)
+    ctx.reset()
+    expect, layouts = [], []
+    for k, part in enumerate(thirds):
+        ctx.submit(part, k * 20_000)
+        res = ctx.fetch(records=True)                        # blocking reference copies
+        expect.append(res)
+        layouts.append(ctx.download_begin(bufs[k].value, cap))   # and the same batch asynchronously
+    ctx.download_wait()
+    for k in range(3):
+        arr = np.ctypeslib.as_array((ctypes.c_uint8 * cap).from_address(bufs[k].value))
+        idx, meta, win, rec = ctx.parse_download(arr, layouts[k])
+        np.testing.assert_array_equal(idx, expect[k].survivors)
+        np.testing.assert_array_equal(meta, expect[k].survivor_meta)
+        assert win.tobytes() == expect[k].windows.tobytes()
+        np.testing.assert_array_equal(rec, expect[k].window_records)
+        assert layouts[k]["n_windows"] > 100
+    with pytest.raises(_ffi.ChronosError):
+        ctx.download_begin(bufs[0].value, 16)                # too small: reported, nothing written
+    for p in bufs:
+        L.chronos_host_free_pinned(p)
