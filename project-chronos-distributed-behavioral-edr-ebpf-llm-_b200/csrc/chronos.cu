@@ -50,11 +50,16 @@ struct DeviceScalars {  // one 64-byte block on the device, mirrored in pinned m
     uint32_t n_pending;
     uint32_t n_chains;
     uint32_t xchg_err;  // XERR_* bits of the exchange (exchange.cuh); cleared by stage 1, not per batch
-    uint32_t pad[9];
+    uint32_t n_pids_seen;  // copy of the per-PID table's count at the end of the batch
+    uint32_t pad[8];
 };
+static_assert(sizeof(DeviceScalars) == 64, "DeviceScalars layout");
+// the Plan of the batch in flight lives right behind the scalars: ONE copy brings both back
+constexpr size_t RESULT_BLOCK_BYTES = 64 + ((sizeof(Plan) + 63) / 64) * 64;
 
 constexpr int N_TICKETS = 64;
-constexpr uint32_t RADIX_TILE_KEYS = 4096;  // keys per radix tile in plan mode
+// ticket counters followed by the global digit histograms of the sort (sort.cuh), cleared together
+constexpr size_t TICKET_BYTES = (N_TICKETS + RADIX_MAX_PASSES * RADIX_BINS) * 4;
 constexpr uint32_t COMM_MEMO_SLOTS = 8192;  // device-wide comm memo (insert-only), 192 KB
 
 }  // namespace
@@ -84,10 +89,8 @@ struct chronos_ctx {
     DevBuf pid_tab, pt_count, chain_pid, chain_idx;
     uint32_t pt_cap = 0;
     uint32_t pt_epoch = 1;
-    DevBuf plan;                 // device-resident Plan of the batch in flight
-    Plan *h_plan = nullptr;      // pinned copy read at fetch
+    Plan *h_plan = nullptr;      // pinned copy of the batch's device Plan, read at fetch (behind h_scalars)
     uint64_t b_Mmax = 0;         // P + n: what the buffers of the batch in flight are sized for
-    uint32_t *h_pt_count = nullptr;  // pinned
     uint64_t n_pids_seen = 0, b_chains = 0;
     DevBuf surv_arrival;  // only for chronos_submit_survivors
     // double-buffered persistent state
@@ -97,8 +100,8 @@ struct chronos_ctx {
     int cur = 0;                    // index written by the batch in flight / last fetched
     uint64_t n_pending = 0;         // entries pending after the last fetched batch (in buffer `cur`)
     // scheduling scratch
-    DevBuf status, tickets, scalars, scan_status;
-    uint32_t scan_epoch = 0;
+    DevBuf status, tickets, scalars, scan_status, sweep_status;
+    uint32_t scan_epoch = 0, sweep_epoch = 0;
     int scan_slot = 0;  // next free ticket counter for scans in this batch
     DeviceScalars *h_scalars = nullptr;  // pinned
     DevBuf pack;                         // scratch for chronos_copy_window_records / chronos_state
@@ -241,50 +244,16 @@ __global__ void fold_keys_kernel(const uint32_t *keys, uint32_t n, uint32_t *k_o
 
 __global__ void set_u32_kernel(uint32_t *p, uint32_t v) { *p = v; }
 
-__global__ void init_scalars_kernel(DeviceScalars *s) {
+// start of a batch: scalars to their neutral values, ticket counters and digit histograms to 0
+__global__ void init_scalars_kernel(DeviceScalars *s, uint32_t *tickets) {
+    for (uint32_t i = threadIdx.x; i < TICKET_BYTES / 4; i += blockDim.x) tickets[i] = 0;
+    if (threadIdx.x) return;
     s->surv_count = 0;
     s->key_or = 0;
     s->key_and = 0xffffffffu;
     s->n_windows = 0;
     s->n_pending = 0;
     s->n_chains = 0;
-}
-
-// Sizes of the batch, decided on the device once the filter's survivor count is there
-// (no host round trip): radix pass plan over the bits in which the pids differ, tilings,
-// and where the sorted arrays will end up after n_passes ping-pong passes.
-__global__ void plan_kernel(const DeviceScalars *s, uint32_t P, uint32_t m_max, const uint32_t *keyA,
-                            const uint32_t *keyB, const uint32_t *valA, const uint32_t *valB, Plan *pl) {
-    const uint32_t S = s->surv_count;
-    uint32_t M = P + S;
-    pl->overflow = M > m_max ? 1u : 0u;
-    if (M > m_max) M = m_max;  // never run past the buffers; the host reports the overflow
-    pl->S = M - P;
-    pl->P = P;
-    pl->M = M;
-    const uint32_t diff = s->key_or ^ s->key_and;
-    uint32_t passes = 0;
-    if (M >= 2 && diff != 0) {
-        const int lo = __ffs((int)diff) - 1, hi = 32 - __clz((int)diff);
-        const int bits = hi - lo;
-        passes = (uint32_t)(bits + 7) / 8;
-        const int per = (bits + (int)passes - 1) / (int)passes;
-        int sft = lo;
-        for (uint32_t i = 0; i < passes; i++) {
-            const int b = min(per, hi - sft);
-            pl->shift[i] = (uint32_t)sft;
-            pl->mask[i] = (1u << b) - 1u;
-            sft += b;
-        }
-    }
-    pl->n_passes = passes;
-    pl->tile_keys = RADIX_TILE_KEYS;
-    pl->n_tiles = (M + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS;
-    pl->table_len = RADIX_BINS * pl->n_tiles;
-    pl->tiles_m = (M + WIN_TILE - 1) / WIN_TILE;
-    pl->tiles_s = (pl->S + WIN_TILE - 1) / WIN_TILE;
-    pl->skey = (passes & 1u) ? keyB : keyA;
-    pl->sval = (passes & 1u) ? valB : valA;
 }
 
 // Stage 2 of the sharded path, step 1: split the header words of the received entries
@@ -409,7 +378,7 @@ int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_de
     if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_tiles * 8, 4096)))) return rc;
     if (c->scan_status.p != before || c->scan_epoch == 0)  // fresh memory or wrapped epoch: tag 0 = "never"
         CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, c->stream));
-    if (own_ticket < 0 && c->scan_slot >= 48) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
+    if (own_ticket < 0 && c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
     if (own_ticket >= 0) CK(cudaMemsetAsync(ptr<uint32_t>(c->tickets) + own_ticket, 0, 4, c->stream));
     ScanParams sp;
     sp.data = data;
@@ -463,27 +432,35 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
     CK(cudaEventRecord(c->ev_f1, c->stream));
     if ((rc = dbg_sync(c, "filter_kernel"))) return rc;
     c->filter_timed = true;
-    // cross-tile prefix + dense, arrival-ordered survivor arrays
-    if ((rc = launch_scan(c, ptr<uint32_t>(c->tile_count), fp.tile_end))) return rc;
-    if ((rc = dbg_sync(c, "tile-count scan"))) return rc;
-    CompactParams cp;
-    cp.tile_off = ptr<uint32_t>(c->tile_count);
-    cp.sp_key = fp.sp_key;
-    cp.sp_src = fp.sp_src;
-    cp.sp_meta = fp.sp_meta;
-    cp.sp_ns = fp.sp_ns;
-    cp.out_key = out_key;
-    cp.out_src = ptr<uint32_t>(c->surv_src);
-    cp.out_meta = ptr<uint8_t>(c->surv_meta);
-    cp.out_ns = ptr<uint8_t>(c->surv_ns);
-    cp.out_pid = ptr<uint32_t>(c->surv_pid);
-    cp.n_tiles = fp.tile_end;
-    cp.tile = (uint32_t)TILE;
-    cp.total = &ds->surv_count;
-    compact_survivors<<<(unsigned)std::min<uint32_t>((fp.tile_end + 255) / 256, (uint32_t)c->sm_count * 8), 256, 0,
-                        c->stream>>>(cp);
-    CK(cudaGetLastError());
-    c->launches += 1;
+    // cross-tile prefix + dense, arrival-ordered survivor arrays, one kernel
+    {
+        const uint32_t n_chunks = (fp.tile_end + CS_CHUNK - 1) / CS_CHUNK;
+        const void *before = c->scan_status.p;
+        if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_chunks * 8, 4096)))) return rc;
+        if (c->scan_status.p != before || c->scan_epoch == 0)
+            CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, c->stream));
+        if (c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
+        CompactScanParams cp;
+        cp.tile_count = ptr<uint32_t>(c->tile_count);
+        cp.n_tiles = fp.tile_end;
+        cp.tile = (uint32_t)TILE;
+        cp.sp_key = fp.sp_key;
+        cp.sp_src = fp.sp_src;
+        cp.sp_meta = fp.sp_meta;
+        cp.sp_ns = fp.sp_ns;
+        cp.out_key = out_key;
+        cp.out_src = ptr<uint32_t>(c->surv_src);
+        cp.out_meta = ptr<uint8_t>(c->surv_meta);
+        cp.out_ns = ptr<uint8_t>(c->surv_ns);
+        cp.out_pid = ptr<uint32_t>(c->surv_pid);
+        cp.ticket = ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
+        cp.status = ptr<uint64_t>(c->scan_status);
+        cp.epoch = ++c->scan_epoch;
+        if (c->scan_epoch >= (1u << 29)) c->scan_epoch = 0;
+        compact_scan<<<std::max(1u, std::min<uint32_t>(n_chunks, (uint32_t)c->sm_count * 4)), CS_THREADS, 0, c->stream>>>(cp);
+        CK(cudaGetLastError());
+        c->launches += 1;
+    }
     if ((rc = dbg_sync(c, "filter + scan + compact"))) return rc;
     return CHRONOS_OK;
 }
@@ -522,7 +499,7 @@ int run_window_stage(chronos_ctx *c) {
     const uint64_t P = c->b_P;
     const uint64_t Mmax = c->b_Mmax;  // P + n
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    Plan *plan = ptr<Plan>(c->plan);
+    Plan *plan = reinterpret_cast<Plan *>(ptr<uint8_t>(c->scalars) + 64);
     mark(c, "filter+compact done");
     CK(cudaEventRecord(c->ev_filter, c->stream));
     const int cur = c->cur, prev = cur ^ 1;
@@ -544,44 +521,50 @@ int run_window_stage(chronos_ctx *c) {
     if ((rc = ensure(c, c->chain_idx, (Smax + 1) * 8))) return rc;
     if ((rc = ensure_pid_table(c, Mmax))) return rc;
     const uint32_t max_rtiles = (uint32_t)((Mmax + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS);
-    if ((rc = ensure(c, c->radix_table, (size_t)RADIX_BINS * std::max(max_rtiles, 1u) * 4))) return rc;
 
-    plan_kernel<<<1, 1, 0, c->stream>>>(ds, (uint32_t)P, (uint32_t)Mmax, ptr<uint32_t>(c->keyA), ptr<uint32_t>(c->keyB),
-                                        ptr<uint32_t>(c->valA), ptr<uint32_t>(c->valB), plan);
+    // ---- stable sort by pid: plan + global digit histograms, then one kernel per pass --------
+    SortParams sp;
+    memset(&sp, 0, sizeof(sp));
+    sp.plan = plan;
+    sp.in.surv_count = &ds->surv_count;
+    sp.in.key_or = &ds->key_or;
+    sp.in.key_and = &ds->key_and;
+    sp.in.P = (uint32_t)P;
+    sp.in.m_max = (uint32_t)Mmax;
+    sp.in.win_tile = WIN_TILE;
+    sp.keyA = ptr<uint32_t>(c->keyA);
+    sp.keyB = ptr<uint32_t>(c->keyB);
+    sp.valA = ptr<uint32_t>(c->valA);
+    sp.valB = ptr<uint32_t>(c->valB);
+    sp.meta_lo = P ? ptr<uint8_t>(c->pend_meta[prev]) + (c->pend_cap[prev] - P) : nullptr;
+    sp.meta_hi = ptr<uint8_t>(c->surv_meta);
+    sp.ghist = ptr<uint32_t>(c->tickets) + N_TICKETS;  // zeroed with the tickets
+    {
+        const void *before = c->sweep_status.p;
+        const size_t need = std::max<size_t>((size_t)max_rtiles, 1) * RADIX_BINS * 8;
+        if ((rc = ensure(c, c->sweep_status, need))) return rc;
+        if (c->sweep_status.p != before || c->sweep_epoch == 0)  // fresh memory or wrapped epoch: tag 0 = "never"
+            CK(cudaMemsetAsync(c->sweep_status.p, 0, c->sweep_status.bytes, c->stream));
+    }
+    sp.status = ptr<uint64_t>(c->sweep_status);
+    const unsigned sort_blocks = std::max(1u, std::min(max_rtiles, (uint32_t)c->sm_count * 4));
+    sort_prepare<<<sort_blocks, RADIX_THREADS, 0, c->stream>>>(sp);
     c->launches++;
-    if ((rc = dbg_sync(c, "plan_kernel"))) return rc;
-    if (Mmax == 0) {
-        CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaMemcpyAsync(c->h_plan, plan, sizeof(Plan), cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaMemcpyAsync(c->h_pt_count, c->pt_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
+    if ((rc = dbg_sync(c, "sort_prepare"))) return rc;
+    if (Mmax == 0) {  // nothing pending, nothing submitted: only the (empty) counts go back
+        CK(cudaMemcpyAsync(c->h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, c->stream));
         CK(cudaEventRecord(c->ev_end, c->stream));
         return CHRONOS_OK;
     }
-
-    // ---- stable sort by pid: sort values first (entry id | class bits), then up to 4 passes ----
-    const uint8_t *meta_lo = P ? ptr<uint8_t>(c->pend_meta[prev]) + (c->pend_cap[prev] - P) : nullptr;
-    synth_values_kernel<<<(unsigned)std::min<uint64_t>((Mmax + 255) / 256, 2048), 256, 0, c->stream>>>(
-        ptr<uint32_t>(c->valA), (uint32_t)Mmax, meta_lo, ptr<uint8_t>(c->surv_meta), (uint32_t)P, plan);
-    c->launches++;
-    if ((rc = dbg_sync(c, "synth_values"))) return rc;
     {
-        RadixParams rp;
-        memset(&rp, 0, sizeof(rp));
-        rp.plan = plan;
-        rp.keyA = ptr<uint32_t>(c->keyA);
-        rp.keyB = ptr<uint32_t>(c->keyB);
-        rp.valA = ptr<uint32_t>(c->valA);
-        rp.valB = ptr<uint32_t>(c->valB);
-        rp.table = ptr<uint32_t>(c->radix_table);
-        for (int i = 0; i < 4; i++) {  // passes beyond plan->n_passes return at once
-            rp.pass = i;
-            radix_hist<<<max_rtiles, RADIX_THREADS, 0, c->stream>>>(rp);
-            if ((rc = dbg_sync(c, "radix_hist"))) return rc;
-            if ((rc = launch_scan(c, rp.table, (uint64_t)RADIX_BINS * max_rtiles, &plan->table_len))) return rc;
-            if ((rc = dbg_sync(c, "radix scan"))) return rc;
-            radix_scatter<<<max_rtiles, RADIX_THREADS, 0, c->stream>>>(rp);
-            if ((rc = dbg_sync(c, "radix_scatter"))) return rc;
-            c->launches += 2;
+        for (int i = 0; i < RADIX_MAX_PASSES; i++) {  // passes beyond plan->n_passes return at once
+            sp.pass = i;
+            sp.ticket = ptr<uint32_t>(c->tickets) + 40 + i;
+            sp.epoch = ++c->sweep_epoch;
+            if (c->sweep_epoch >= (1u << 29)) c->sweep_epoch = 0;  // re-zero on the next batch
+            onesweep_pass<<<sort_blocks, RADIX_THREADS, 0, c->stream>>>(sp);
+            c->launches++;
+            if ((rc = dbg_sync(c, "onesweep_pass"))) return rc;
         }
         CK(cudaGetLastError());
     }
@@ -627,6 +610,7 @@ int run_window_stage(chronos_ctx *c) {
         w.pid_mask = c->pt_cap - 1;
         w.pid_epoch = c->pt_epoch;
         w.pid_count = ptr<uint32_t>(c->pt_count);
+        w.n_pids_out = &ds->n_pids_seen;
         w.pflag = ptr<uint32_t>(c->pflag);
         w.entry_out = ptr<uint32_t>(c->entry_out);
         w.wsorted = ptr<WinSorted>(c->wsorted);
@@ -664,9 +648,7 @@ int run_window_stage(chronos_ctx *c) {
     mark(c, "window kernels done");
     CK(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
     mark(c, "gather joined");
-    CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaMemcpyAsync(c->h_plan, plan, sizeof(Plan), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaMemcpyAsync(c->h_pt_count, c->pt_count.p, 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(c->h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaEventRecord(c->ev_end, c->stream));
     return CHRONOS_OK;
 }
@@ -712,8 +694,7 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
     if (!c->x_sent) c->n_tev = 0;  // (stage 2 of an exchange step keeps the marks of its stage 1)
     mark(c, "start");
     CK(cudaMemsetAsync(c->status.p, 0, sw * 8, c->stream));
-    CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
-    init_scalars_kernel<<<1, 1, 0, c->stream>>>(ptr<DeviceScalars>(c->scalars));
+    init_scalars_kernel<<<1, 256, 0, c->stream>>>(ptr<DeviceScalars>(c->scalars), ptr<uint32_t>(c->tickets));
     c->launches++;
     if (P) {
         const int prev = c->cur ^ 1;
@@ -737,7 +718,7 @@ int finish_batch(chronos_ctx *c) {
     c->n_pending = c->b_M ? c->h_scalars->n_pending : 0;
     c->b_chains = c->b_M ? c->h_scalars->n_chains : 0;
     if (c->h_plan->overflow) return fail(c, CHRONOS_E_CAPACITY, "more survivors than the batch was sized for");
-    c->n_pids_seen = *c->h_pt_count;
+    c->n_pids_seen = c->b_M ? c->h_scalars->n_pids_seen : c->n_pids_seen;
     if (c->b_exchanged) {
         c->b_n = c->b_S;  // the upper bound the buffers were sized for is of no interest to the caller
         const uint32_t xe = c->h_scalars->xchg_err;
@@ -836,16 +817,13 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
         CK(cudaEventCreate(&c->ev_end));
         CK(cudaEventCreate(&c->ev_f0));
         CK(cudaEventCreate(&c->ev_f1));
-        CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_scalars), sizeof(DeviceScalars)));
-        CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_pt_count), 64));
-        *c->h_pt_count = 0;
-        CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_plan), sizeof(Plan)));
-        memset(c->h_plan, 0, sizeof(Plan));
+        CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_scalars), RESULT_BLOCK_BYTES));
+        memset(c->h_scalars, 0, RESULT_BLOCK_BYTES);
+        c->h_plan = reinterpret_cast<Plan *>(reinterpret_cast<uint8_t *>(c->h_scalars) + 64);
         int rc;
-        if ((rc = ensure(c, c->tickets, N_TICKETS * 4))) return rc;
-        if ((rc = ensure(c, c->scalars, sizeof(DeviceScalars)))) return rc;
+        if ((rc = ensure(c, c->tickets, TICKET_BYTES))) return rc;
+        if ((rc = ensure(c, c->scalars, RESULT_BLOCK_BYTES))) return rc;
         if ((rc = ensure(c, c->pt_count, 256))) return rc;
-        if ((rc = ensure(c, c->plan, sizeof(Plan)))) return rc;
         if ((rc = ensure(c, c->comm_memo, (size_t)COMM_MEMO_SLOTS * 24))) return rc;
         CK(cudaMemsetAsync(c->comm_memo.p, 0, (size_t)COMM_MEMO_SLOTS * 24, c->stream));
         CK(cudaMemsetAsync(c->pt_count.p, 0, 256, c->stream));
@@ -865,10 +843,10 @@ int chronos_destroy(chronos_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->pflag,
-                     &c->entry_out, &c->wsorted, &c->plan, &c->comm_memo, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->ns32, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+                     &c->entry_out, &c->wsorted, &c->comm_memo, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->ns32, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
-                     &c->tickets, &c->scalars, &c->scan_status, &c->pack, &c->pack_off};
+                     &c->tickets, &c->scalars, &c->scan_status, &c->sweep_status, &c->pack, &c->pack_off};
     for (DevBuf *b : all) release(*b);
     for (int d = 0; d < XCHG_MAX_WORLD; d++)
         if (c->x_opened[d] && c->x_peer[d]) cudaIpcCloseMemHandle(c->x_peer[d]);
@@ -885,8 +863,6 @@ int chronos_destroy(chronos_ctx *c) {
     release(c->dl_stage[1]);
     if (c->ev_x0) cudaEventDestroy(c->ev_x0);
     if (c->h_scalars) cudaFreeHost(c->h_scalars);
-    if (c->h_pt_count) cudaFreeHost(c->h_pt_count);
-    if (c->h_plan) cudaFreeHost(c->h_plan);
     if (c->ev_start) cudaEventDestroy(c->ev_start);
     if (c->ev_filter) cudaEventDestroy(c->ev_filter);
     if (c->ev_end) cudaEventDestroy(c->ev_end);
@@ -1215,7 +1191,6 @@ int chronos_reset(chronos_ctx *c) {
     CK(cudaStreamSynchronize(c->stream));
     c->n_pending = 0;
     c->n_pids_seen = 0;
-    *c->h_pt_count = 0;
     // slots written under an older epoch count as empty: a reset costs nothing on the device
     c->pt_epoch = (c->pt_epoch + 1) & 0xFFu;
     if (c->pt_epoch == 0) {  // tags wrapped: really clear the table once every 255 resets
@@ -1260,8 +1235,7 @@ static int stage1_filter(chronos_ctx *c, const void *records, uint64_t n, const 
     if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
     if ((rc = ensure(c, c->x_totals, 256))) return rc;
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    CK(cudaMemsetAsync(c->tickets.p, 0, N_TICKETS * 4, c->stream));
-    init_scalars_kernel<<<1, 1, 0, c->stream>>>(ds);
+    init_scalars_kernel<<<1, 256, 0, c->stream>>>(ds, ptr<uint32_t>(c->tickets));
     set_u32_kernel<<<1, 1, 0, c->stream>>>(&ds->xchg_err, 0u);
     c->launches += 2;
     mark(c, "stage 1 start");

@@ -28,6 +28,7 @@
 //       applies the exclusive scan of the per-tile counts, so CTAs never wait on each other.
 #pragma once
 #include "common.cuh"
+#include "sort.cuh"  // lookback_count_epoch
 
 namespace chronos {
 
@@ -560,6 +561,120 @@ __global__ void __launch_bounds__(256) compact_survivors(const CompactParams c) 
             c.out_meta[lo + j] = c.sp_meta[base + j];
             if (c.out_ns) c.out_ns[lo + j] = c.sp_ns[base + j];
             if (c.out_pid) c.out_pid[lo + j] = c.sp_key[base + j];
+        }
+    }
+}
+
+// The same step in ONE kernel for the batch pipeline: a chunk of CS_CHUNK filter tiles per
+// CTA iteration -- scan of the tile counts inside the chunk, chunk base by decoupled look-back
+// (sort.cuh lookback_count_epoch), then every thread places survivors by output position
+// (binary search of the position in the chunk's offsets), so the writes are coalesced.
+constexpr int CS_THREADS = 256;
+constexpr int CS_ITEMS = 4;
+constexpr int CS_CHUNK = CS_THREADS * CS_ITEMS;
+static_assert(CS_CHUNK == 1024, "the position search below is unrolled for 2^10 tiles");
+
+struct CompactScanParams {
+    const uint32_t *tile_count;  // survivors per filter tile (filter_kernel), left untouched
+    uint32_t n_tiles;
+    uint32_t tile;               // records (= slots) per filter tile
+    const uint32_t *sp_key, *sp_src;
+    const uint8_t *sp_meta, *sp_ns;
+    uint32_t *out_key, *out_src, *out_pid;
+    uint8_t *out_meta, *out_ns;
+    uint32_t *ticket;            // zeroed
+    uint64_t *status;            // ceil(n_tiles / CS_CHUNK) epoch-tagged words
+    uint32_t epoch;
+};
+
+__global__ void __launch_bounds__(CS_THREADS) compact_scan(const CompactScanParams p) {
+    __shared__ uint32_t off[CS_CHUNK + 1];
+    __shared__ uint32_t warp_sums[CS_THREADS / 32];
+    __shared__ uint32_t s_chunk, s_base;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t n_chunks = (p.n_tiles + CS_CHUNK - 1) / CS_CHUNK;
+    while (true) {
+        __syncthreads();
+        if (tid == 0) s_chunk = atomicAdd(p.ticket, 1u);
+        __syncthreads();
+        const uint32_t chunk = s_chunk;
+        if (chunk >= n_chunks) break;
+        const uint32_t t0 = chunk * CS_CHUNK + tid * CS_ITEMS;
+        uint32_t v[CS_ITEMS];
+        if (t0 + CS_ITEMS <= p.n_tiles) {
+            const uint4 a = *reinterpret_cast<const uint4 *>(p.tile_count + t0);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w;
+        } else {
+#pragma unroll
+            for (int k = 0; k < CS_ITEMS; k++) v[k] = (t0 + k < p.n_tiles) ? p.tile_count[t0 + k] : 0u;
+        }
+        const uint32_t sum = v[0] + v[1] + v[2] + v[3];
+        uint32_t inc = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        if (lane == 31) warp_sums[warp] = inc;
+        __syncthreads();
+        uint32_t before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < CS_THREADS / 32; w++) {
+            const uint32_t ws = warp_sums[w];
+            if (w < warp) before += ws;
+            total += ws;
+        }
+        uint32_t run = before + inc - sum;
+#pragma unroll
+        for (int k = 0; k < CS_ITEMS; k++) {
+            off[tid * CS_ITEMS + k] = run;
+            run += v[k];
+        }
+        if (tid == CS_THREADS - 1) off[CS_CHUNK] = total;
+        if (warp == 0) {
+            const uint32_t b = lookback_count_epoch(p.status, chunk, total, lane, p.epoch);
+            if (lane == 0) s_base = b;
+        }
+        __syncthreads();
+        const uint32_t base = s_base;
+        const size_t slot0 = (size_t)chunk * CS_CHUNK * p.tile;
+        // four independent positions per thread and step: the search and the four loads of one
+        // position are a dependent chain, so the chains are interleaved
+        constexpr int CS_ILP = 4;
+        for (uint32_t j0 = tid; j0 < total; j0 += CS_ILP * CS_THREADS) {
+            size_t src[CS_ILP];
+            uint32_t k[CS_ILP], sr[CS_ILP];
+            uint8_t me[CS_ILP], nn[CS_ILP];
+#pragma unroll
+            for (int u = 0; u < CS_ILP; u++) {
+                const uint32_t j = min(j0 + u * CS_THREADS, total - 1);
+                uint32_t lo = 0, hi = CS_CHUNK;  // off[lo] <= j < off[hi]
+#pragma unroll
+                for (int it = 0; it < 10; it++) {  // CS_CHUNK = 1024 = 2^10
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (off[mid] <= j) lo = mid; else hi = mid;
+                }
+                src[u] = slot0 + (size_t)lo * p.tile + (j - off[lo]);
+            }
+#pragma unroll
+            for (int u = 0; u < CS_ILP; u++) {
+                k[u] = p.sp_key[src[u]];
+                sr[u] = p.sp_src[src[u]];
+                me[u] = p.sp_meta[src[u]];
+                nn[u] = p.sp_ns[src[u]];
+            }
+#pragma unroll
+            for (int u = 0; u < CS_ILP; u++) {
+                const uint32_t j = j0 + u * CS_THREADS;
+                if (j < total) {
+                    const uint32_t dst = base + j;
+                    p.out_key[dst] = k[u];
+                    p.out_pid[dst] = k[u];
+                    p.out_src[dst] = sr[u];
+                    p.out_meta[dst] = me[u];
+                    p.out_ns[dst] = nn[u];
+                }
+            }
         }
     }
 }

@@ -5,11 +5,13 @@
 // has no timestamp (:18-23), so stability on pid alone is what preserves arrival order.
 //
 // LSD radix sort, <=8-bit digits, only over the bit range in which the keys actually
-// differ (planned on the host from the OR/AND the filter kernel folded). One pass =
-//   radix_hist    per-tile digit histograms            (digit-major table)
-//   scan_exclusive_u32  exclusive scan of the table     (look-back, multi-CTA)
-//   radix_scatter stable scatter: per-warp sub-ranges, __match_any_sync ranking
-// Values are entry ids; pass 0 synthesises them (iota) instead of reading them.
+// differ (planned ON THE DEVICE from the OR/AND the filter kernel folded):
+//   sort_prepare   the plan + the global digit histogram of every pass, one read of the keys
+//   onesweep_pass  one kernel per pass: per-tile digit counts, per-digit decoupled look-back
+//                  across tiles, stable scatter (per-warp sub-ranges, __match_any_sync ranking)
+// Values are entry ids; pass 0 synthesises them (iota | class bits) instead of reading them.
+// scan_exclusive_u32 (bottom of this file) is the stand-alone exclusive scan used by the
+// compaction and the exchange.
 #pragma once
 #include "common.cuh"
 
@@ -19,27 +21,8 @@ constexpr int RADIX_BINS = 256;
 constexpr int RADIX_THREADS = 256;
 constexpr int RADIX_WARPS = RADIX_THREADS / 32;
 
-struct RadixParams {
-    // plan mode (plan != nullptr): pass `pass` of the batch's sort; reads set A when the pass
-    // index is even and set B when it is odd, writes the other; extents come from the plan
-    const Plan *plan;
-    int pass;
-    uint32_t *keyA, *keyB, *valA, *valB;
-    // explicit mode (plan == nullptr)
-    const uint32_t *keys_in;
-    const uint32_t *vals_in;  // nullptr => value = index | class bits << 27 (see synth_value)
-    const uint8_t *meta_lo;   // class bits of entries [0, split) (carried-in pending), may be nullptr
-    const uint8_t *meta_hi;   // class bits of entries [split, n) (this batch's survivors), may be nullptr
-    uint32_t split;
-    uint32_t *keys_out;
-    uint32_t *vals_out;
-    uint32_t *table;          // RADIX_BINS * n_tiles counters, digit-major
-    uint32_t n;
-    uint32_t tile_keys;       // keys per tile (multiple of RADIX_WARPS*32)
-    uint32_t n_tiles;
-    uint32_t shift;
-    uint32_t mask;            // (1<<bits)-1
-};
+constexpr uint32_t RADIX_TILE_KEYS = 4096;  // keys per tile (multiple of RADIX_WARPS*32)
+constexpr int RADIX_MAX_PASSES = 4;
 
 // Pass 0 synthesises the sort values instead of reading them: the entry id in the low 27
 // bits and the event's class bits (CHRONOS_META_*) above, so that the kernels after the
@@ -52,57 +35,198 @@ __device__ __forceinline__ uint32_t synth_value(const uint8_t *meta_lo, const ui
     return i | (m << 27);
 }
 
-__global__ void synth_values_kernel(uint32_t *v, uint32_t n, const uint8_t *meta_lo, const uint8_t *meta_hi, uint32_t split,
-                                    const Plan *plan) {
-    if (plan) n = plan->M;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
-        v[i] = synth_value(meta_lo, meta_hi, split, i);
-}
-
-// One radix pass resolved to plain values (plan mode reads the device plan; explicit mode the
-// parameter struct). active == false: this pass or this tile has nothing to do.
-struct RadixView {
-    const uint32_t *keys_in, *vals_in;
-    uint32_t *keys_out, *vals_out;
-    uint32_t n, tile_keys, n_tiles, shift, mask;
-    bool active;
+// What the filter stage leaves on the device for the planner.
+struct SortInputs {
+    const uint32_t *surv_count, *key_or, *key_and;  // scalars of the batch in flight
+    uint32_t P, m_max, win_tile;
 };
-__device__ __forceinline__ RadixView radix_view(const RadixParams &p) {
-    RadixView v;
-    if (!p.plan) {
-        v.keys_in = p.keys_in; v.vals_in = p.vals_in; v.keys_out = p.keys_out; v.vals_out = p.vals_out;
-        v.n = p.n; v.tile_keys = p.tile_keys; v.n_tiles = p.n_tiles; v.shift = p.shift; v.mask = p.mask;
-        v.active = blockIdx.x < p.n_tiles;
-        return v;
+
+struct SortParams {
+    Plan *plan;               // written by sort_prepare (block 0), read by everything after it
+    SortInputs in;
+    uint32_t *keyA, *keyB, *valA, *valB;   // pass i reads set A when i is even, set B when odd
+    const uint8_t *meta_lo;   // class bits of entries [0, P) (carried-in pending), may be nullptr
+    const uint8_t *meta_hi;   // class bits of entries [P, M) (this batch's survivors)
+    uint32_t *ghist;          // RADIX_MAX_PASSES x RADIX_BINS global digit counts, zeroed per batch
+    int pass;                 // onesweep_pass only
+    uint32_t *ticket;         // zeroed per batch, one per pass
+    uint64_t *status;         // look-back words: one per (tile, digit); epoch-tagged, never cleared
+    uint32_t epoch;           // unique per onesweep_pass launch
+};
+
+// Sizes of the batch, decided on the device once the survivor count is there (no host round
+// trip): radix passes over the bits in which the pids differ, tilings, and where the sorted
+// arrays end up after n_passes ping-pong passes.
+__device__ __forceinline__ void make_plan(const SortParams &p, Plan &pl) {
+    const uint32_t S = *p.in.surv_count, P = p.in.P;
+    uint32_t M = P + S;
+    pl.overflow = M > p.in.m_max ? 1u : 0u;
+    if (M > p.in.m_max) M = p.in.m_max;  // never run past the buffers; the host reports the overflow
+    pl.S = M - P;
+    pl.P = P;
+    pl.M = M;
+    const uint32_t diff = *p.in.key_or ^ *p.in.key_and;
+    uint32_t passes = 0;
+    for (int i = 0; i < RADIX_MAX_PASSES; i++) { pl.shift[i] = 0; pl.mask[i] = 0; }
+    if (M >= 2 && diff != 0) {
+        const int lo = __ffs((int)diff) - 1, hi = 32 - __clz((int)diff);
+        const int bits = hi - lo;
+        passes = (uint32_t)(bits + 7) / 8;
+        const int per = (bits + (int)passes - 1) / (int)passes;
+        int sft = lo;
+        for (uint32_t i = 0; i < passes; i++) {
+            const int b = min(per, hi - sft);
+            pl.shift[i] = (uint32_t)sft;
+            pl.mask[i] = (1u << b) - 1u;
+            sft += b;
+        }
     }
-    const Plan &pl = *p.plan;
-    const bool odd = p.pass & 1;
-    v.keys_in = odd ? p.keyB : p.keyA;
-    v.vals_in = odd ? p.valB : p.valA;
-    v.keys_out = odd ? p.keyA : p.keyB;
-    v.vals_out = odd ? p.valA : p.valB;
-    v.n = pl.M;
-    v.tile_keys = pl.tile_keys;
-    v.n_tiles = pl.n_tiles;
-    v.shift = pl.shift[p.pass & 3];
-    v.mask = pl.mask[p.pass & 3];
-    v.active = (uint32_t)p.pass < pl.n_passes && blockIdx.x < pl.n_tiles;
-    return v;
+    pl.n_passes = passes;
+    pl.tile_keys = RADIX_TILE_KEYS;
+    pl.n_tiles = (M + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS;
+    pl.table_len = 0;
+    pl.tiles_m = (M + p.in.win_tile - 1) / p.in.win_tile;
+    pl.tiles_s = (pl.S + p.in.win_tile - 1) / p.in.win_tile;
+    pl.skey = (passes & 1u) ? p.keyB : p.keyA;
+    pl.sval = (passes & 1u) ? p.valB : p.valA;
 }
 
-__global__ void __launch_bounds__(RADIX_THREADS) radix_hist(const RadixParams p) {
-    __shared__ uint32_t h[RADIX_BINS];
-    const RadixView v = radix_view(p);
-    if (!v.active) return;
-    const uint32_t tile = blockIdx.x;
-    h[threadIdx.x] = 0;
+// Kernel 1 of the sort: the plan, and the GLOBAL digit histogram of every pass in one read of
+// the keys (the passes then need no histogram kernel and no table scan of their own).
+__global__ void __launch_bounds__(RADIX_THREADS) sort_prepare(const SortParams p) {
+    __shared__ Plan pl;
+    __shared__ uint32_t h[RADIX_MAX_PASSES][RADIX_BINS];
+    if (threadIdx.x == 0) {
+        make_plan(p, pl);
+        if (blockIdx.x == 0) *p.plan = pl;
+    }
+    for (int i = threadIdx.x; i < RADIX_MAX_PASSES * RADIX_BINS; i += RADIX_THREADS) (&h[0][0])[i] = 0;
     __syncthreads();
-    const uint32_t lo = tile * v.tile_keys;
-    const uint32_t hi = min(v.n, lo + v.tile_keys);
-    for (uint32_t i = lo + threadIdx.x; i < hi; i += RADIX_THREADS)
-        atomicAdd(&h[(v.keys_in[i] >> v.shift) & v.mask], 1u);
+    const uint32_t M = pl.M, np = pl.n_passes;
+    if (np == 0) {  // nothing to sort: the "sorted" values are the synthesised ones, in place
+        for (uint32_t i = blockIdx.x * RADIX_THREADS + threadIdx.x; i < M; i += gridDim.x * RADIX_THREADS)
+            p.valA[i] = synth_value(p.meta_lo, p.meta_hi, pl.P, i);
+        return;
+    }
+    for (uint32_t i = blockIdx.x * RADIX_THREADS + threadIdx.x; i < M; i += gridDim.x * RADIX_THREADS) {
+        const uint32_t k = p.keyA[i];
+        for (uint32_t q = 0; q < np; q++) atomicAdd(&h[q][(k >> pl.shift[q]) & pl.mask[q]], 1u);
+    }
     __syncthreads();
-    p.table[(size_t)threadIdx.x * v.n_tiles + tile] = h[threadIdx.x];
+    for (uint32_t q = 0; q < np; q++) {
+        const uint32_t c = h[q][threadIdx.x];
+        if (c) atomicAdd(&p.ghist[q * RADIX_BINS + threadIdx.x], c);
+    }
+}
+
+// Kernel 2..: one radix pass in ONE kernel. Tiles are taken in ticket order; a tile counts its
+// digits, publishes the counts, learns how many keys with the same digit precede it from its
+// predecessors' status words (decoupled look-back, one chain per digit = one per thread) and
+// scatters: stable, because a tile's keys go behind those of every earlier tile and the
+// placement inside the tile is in index order.
+// status word: [63:34] epoch | [33:32] ST_* | [31:0] count
+__global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams p) {
+    __shared__ uint32_t whist[RADIX_WARPS][RADIX_BINS];
+    __shared__ uint32_t gbase[RADIX_BINS];
+    __shared__ uint32_t warp_tot[RADIX_WARPS];
+    __shared__ uint32_t s_tile;
+    const Plan &pl = *p.plan;
+    if ((uint32_t)p.pass >= pl.n_passes) return;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const bool odd = p.pass & 1;
+    const uint32_t *keys_in = odd ? p.keyB : p.keyA;
+    const uint32_t *vals_in = p.pass == 0 ? nullptr : (odd ? p.valB : p.valA);
+    uint32_t *keys_out = odd ? p.keyA : p.keyB;
+    uint32_t *vals_out = odd ? p.valA : p.valB;
+    const uint32_t n = pl.M, n_tiles = pl.n_tiles, shift = pl.shift[p.pass], mask = pl.mask[p.pass], split = pl.P;
+    const uint64_t tag = (uint64_t)p.epoch << 34;
+    {   // where digit d starts in the output: exclusive scan of the global digit counts
+        const uint32_t c = p.ghist[p.pass * RADIX_BINS + tid];
+        uint32_t inc = c;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, d);
+            if (lane >= d) inc += t;
+        }
+        if (lane == 31) warp_tot[warp] = inc;
+        __syncthreads();
+        uint32_t before = 0;
+#pragma unroll
+        for (int w = 0; w < RADIX_WARPS; w++)
+            if (w < warp) before += warp_tot[w];
+        gbase[tid] = before + inc - c;
+    }
+    while (true) {
+        __syncthreads();
+        if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
+        for (int i = tid; i < RADIX_WARPS * RADIX_BINS; i += RADIX_THREADS) (&whist[0][0])[i] = 0;
+        __syncthreads();
+        const uint32_t tile = s_tile;
+        if (tile >= n_tiles) break;
+        const uint32_t t_lo = tile * RADIX_TILE_KEYS;
+        const uint32_t t_hi = min(n, t_lo + RADIX_TILE_KEYS);
+        constexpr uint32_t sub = RADIX_TILE_KEYS / RADIX_WARPS;  // multiple of 32
+        const uint32_t w_lo = min(t_hi, t_lo + warp * sub);
+        const uint32_t w_hi = min(t_hi, w_lo + sub);
+        // 1) per-warp digit counts over the warp's contiguous sub-range
+        for (uint32_t i = w_lo + lane; i < w_hi; i += 32) atomicAdd(&whist[warp][(keys_in[i] >> shift) & mask], 1u);
+        __syncthreads();
+        // 2) digit d = tid: tile total, published; keys of digit d in earlier tiles by look-back
+        uint32_t total = 0;
+#pragma unroll
+        for (int w = 0; w < RADIX_WARPS; w++) total += whist[w][tid];
+        uint64_t *st = p.status + (size_t)tile * RADIX_BINS + tid;
+        uint32_t excl = 0;
+        if (tile == 0) {
+            st_relaxed_u64(st, tag | (ST_PREFIX << 32) | total);
+        } else {
+            st_relaxed_u64(st, tag | (ST_AGG << 32) | total);
+            const uint64_t *q = st - RADIX_BINS;
+            while (true) {
+                uint64_t v;
+                do {
+                    v = ld_relaxed_u64(q);
+                } while ((v >> 34) != p.epoch || ((v >> 32) & 3u) == ST_NONE);
+                excl += (uint32_t)v;
+                if (((v >> 32) & 3u) == ST_PREFIX) break;
+                q -= RADIX_BINS;
+            }
+            st_relaxed_u64(st, tag | (ST_PREFIX << 32) | (uint64_t)(excl + total));
+        }
+        __syncwarp();  // the chains of a warp's 32 digits end at different depths
+        {
+            uint32_t run = gbase[tid] + excl;
+#pragma unroll
+            for (int w = 0; w < RADIX_WARPS; w++) {
+                const uint32_t c = whist[w][tid];
+                whist[w][tid] = run;
+                run += c;
+            }
+        }
+        __syncthreads();
+        // 3) stable placement, 32 keys per step, in index order
+        for (uint32_t i0 = w_lo; i0 < w_hi; i0 += 32) {
+            const uint32_t i = i0 + lane;
+            const bool valid = i < w_hi;
+            uint32_t key = 0, d = RADIX_BINS;  // invalid lanes form their own group
+            if (valid) {
+                key = keys_in[i];
+                d = (key >> shift) & mask;
+            }
+            const uint32_t peers = __match_any_sync(0xffffffffu, d);
+            const uint32_t before = __popc(peers & lanemask_lt());
+            uint32_t base = 0;
+            if (valid) base = whist[warp][d];
+            __syncwarp();
+            if (valid && before == 0) whist[warp][d] = base + __popc(peers);
+            __syncwarp();
+            if (valid) {
+                const uint32_t dst = base + before;
+                keys_out[dst] = key;
+                vals_out[dst] = vals_in ? vals_in[i] : synth_value(p.meta_lo, p.meta_hi, split, i);
+            }
+        }
+    }
 }
 
 // Exclusive scan of n counters in place: persistent CTAs, 4096 counters per tile, chained
@@ -215,57 +339,6 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_exclusive_u32(const ScanPar
 #pragma unroll
             for (int k = 0; k < SCAN_ITEMS; k++)
                 if (i0 + k < n) p.data[i0 + k] = o[k];
-        }
-    }
-}
-
-__global__ void __launch_bounds__(RADIX_THREADS) radix_scatter(const RadixParams p) {
-    __shared__ uint32_t whist[RADIX_WARPS][RADIX_BINS];
-    const RadixView v = radix_view(p);
-    if (!v.active) return;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t tile = blockIdx.x;
-    for (int i = tid; i < RADIX_WARPS * RADIX_BINS; i += RADIX_THREADS) (&whist[0][0])[i] = 0;
-    __syncthreads();
-    const uint32_t t_lo = tile * v.tile_keys;
-    const uint32_t t_hi = min(v.n, t_lo + v.tile_keys);
-    const uint32_t sub = v.tile_keys / RADIX_WARPS;  // multiple of 32
-    const uint32_t w_lo = min(t_hi, t_lo + warp * sub);
-    const uint32_t w_hi = min(t_hi, w_lo + sub);
-    // 1) per-warp digit counts over the warp's contiguous sub-range
-    for (uint32_t i = w_lo + lane; i < w_hi; i += 32) atomicAdd(&whist[warp][(v.keys_in[i] >> v.shift) & v.mask], 1u);
-    __syncthreads();
-    // 2) digit d: running base over warps, seeded with the global offset of (d, tile)
-    {
-        uint32_t run = p.table[(size_t)tid * v.n_tiles + tile];
-#pragma unroll
-        for (int w = 0; w < RADIX_WARPS; w++) {
-            uint32_t c = whist[w][tid];
-            whist[w][tid] = run;
-            run += c;
-        }
-    }
-    __syncthreads();
-    // 3) stable placement, 32 keys per step, in index order
-    for (uint32_t i0 = w_lo; i0 < w_hi; i0 += 32) {
-        const uint32_t i = i0 + lane;
-        const bool valid = i < w_hi;
-        uint32_t key = 0, d = RADIX_BINS;  // invalid lanes form their own group
-        if (valid) {
-            key = v.keys_in[i];
-            d = (key >> v.shift) & v.mask;
-        }
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
-        const uint32_t before = __popc(peers & lanemask_lt());
-        uint32_t base = 0;
-        if (valid) base = whist[warp][d];
-        __syncwarp();
-        if (valid && before == 0) whist[warp][d] = base + __popc(peers);
-        __syncwarp();
-        if (valid) {
-            const uint32_t dst = base + before;
-            v.keys_out[dst] = key;
-            v.vals_out[dst] = v.vals_in ? v.vals_in[i] : synth_value(p.meta_lo, p.meta_hi, p.split, i);
         }
     }
 }
