@@ -217,22 +217,35 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
             if (lane >= d) incl += t;
         }
         const uint32_t excl = incl - cnt, total = __shfl_sync(0xffffffffu, incl, 31);
-        for (uint32_t b0 = 0; b0 < total; b0 += 32) {
-            const uint32_t k = b0 + lane;
-            int sidx = 0;  // lane that owns slot k (shuffle binary search, as in filter.cuh phase B2)
+        // the warp copies the slots of its 32 entries cooperatively, 4 x 32 slots per step with
+        // all four loads issued before the first store
+        for (uint32_t b0 = 0; b0 < total; b0 += 128) {
+            uint4 v[4];
+            uint4 *dq[4];
 #pragma unroll
-            for (int step = 16; step >= 1; step >>= 1) {
-                const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
-                if (vv <= k) sidx += step;
+            for (int u = 0; u < 4; u++) {
+                const uint32_t k = b0 + u * 32 + lane;
+                int sidx = 0;  // lane that owns slot k (shuffle binary search, as in filter.cuh phase B2)
+#pragma unroll
+                for (int step = 16; step >= 1; step >>= 1) {
+                    const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
+                    if (vv <= k) sidx += step;
+                }
+                const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
+                const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
+                const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)dst, sidx);
+                dq[u] = nullptr;
+                v[u] = make_uint4(0u, 0u, 0u, 0u);
+                if (k < total) {
+                    const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
+                    const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
+                    v[u] = __ldg(reinterpret_cast<const uint4 *>((uintptr_t)sp) + ch);
+                    dq[u] = reinterpret_cast<uint4 *>((uintptr_t)dp) + sl;
+                }
             }
-            const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
-            const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
-            const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)dst, sidx);
-            if (k < total) {
-                const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
-                const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
-                reinterpret_cast<uint4 *>((uintptr_t)dp)[sl] = reinterpret_cast<const uint4 *>((uintptr_t)sp)[ch];
-            }
+#pragma unroll
+            for (int u = 0; u < 4; u++)
+                if (dq[u]) *dq[u] = v[u];
         }
     }
     // 4) the last CTA to finish publishes counts and flag

@@ -136,6 +136,7 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
         uint8_t kind[WIN_ITEMS];  // bit0 head, bits 2:1 the PID's stored DFA state at a head
         uint32_t prevk = (p0 > 0 && p0 - 1 < M) ? skey[p0 - 1] : 0;
         FnG f = FnG::identity();
+        uint32_t new_pids = 0;  // PIDs this thread inserted into the per-PID table
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t pos = p0 + k;
@@ -158,7 +159,7 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
                 e.c = carried ? Fn3{0x24u, {cm, cm, cm}} : chain_event(meta);
                 uint32_t kd = head ? 1u : 0u;
                 if (head) {  // the PID's stored DFA state replaces whatever is carried over
-                    const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, p.pid_epoch, key[k], p.pid_count);
+                    const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, p.pid_epoch, key[k], new_pids);
                     const uint32_t d0 = (uint32_t)(ld_relaxed_u64(p.pid_tab + slot) >> 32) & 3u;
                     kd |= d0 << 1;
                     e.c = Fn3::constant(Fn3::o(e.c, d0), Fn3::av(e.c, d0));
@@ -178,6 +179,7 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
         }
         __syncthreads();
         StG st = FnG::apply(excl, s_in);
+        uint32_t stored_dfa = NONE32;  // what the table holds for the current group, if its head is ours
         uint32_t pf[WIN_ITEMS];
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
@@ -199,7 +201,10 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
                 p.wsorted[wi] = WinSorted{key[k], e, st.w.b, pos - st.w.b + 1};
             }
             // ---- chain DFA
-            if (head) st.c.s = (kind[k] >> 1) & 3u;
+            if (head) {
+                st.c.s = (kind[k] >> 1) & 3u;
+                stored_dfa = st.c.s;
+            }
             bool m = false;
             if (carried) {
                 st.c.a += (meta & META_CHAIN) ? 1u : 0u;
@@ -211,11 +216,19 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
             }
             pf[k] = (fl ? PF_FLUSH : 0u) | (m ? PF_MATCH : 0u) | (st.c.a << 2);
             const bool tail = (pos + 1 == M) || skey[pos + 1] != key[k];
-            if (tail) {  // the PID's DFA state after this batch
-                const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, p.pid_epoch, key[k], p.pid_count);
-                st_relaxed_u64(p.pid_tab + slot, pt_make(p.pid_epoch, st.c.s, key[k]));
+            if (tail) {
+                // the PID's DFA state after this batch. Only chain events move it, so when this
+                // thread also saw the group's head and the state is what the table already
+                // holds, there is nothing to write and no second probe.
+                if (stored_dfa != st.c.s) {
+                    const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, p.pid_epoch, key[k], new_pids);
+                    st_relaxed_u64(p.pid_tab + slot, pt_make(p.pid_epoch, st.c.s, key[k]));
+                }
+                stored_dfa = NONE32;
             }
         }
+        new_pids = __reduce_add_sync(0xffffffffu, new_pids);
+        if (lane == 0 && new_pids) atomicAdd(p.pid_count, new_pids);
         if (p0 + WIN_ITEMS <= M) {
             uint4 *dst = reinterpret_cast<uint4 *>(p.pflag + p0);
 #pragma unroll
