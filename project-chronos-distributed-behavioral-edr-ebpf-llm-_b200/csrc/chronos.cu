@@ -1254,8 +1254,12 @@ static int stage1_partition(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, u
     const uint64_t table_len = (uint64_t)2 * W * T + 1;
     if ((rc = ensure(c, c->radix_table, table_len * 4))) return rc;
     uint32_t *table = ptr<uint32_t>(c->radix_table);
-    xchg_hist<<<T, XCHG_THREADS, 0, c->stream>>>(ptr<uint32_t>(c->surv_pid), ptr<uint8_t>(c->surv_ns), &ds->surv_count, W, table);
+    // persistent CTAs: the tile count is an upper bound (the survivor count stays on the device)
+    const unsigned xblocks = std::min<uint32_t>(T, (uint32_t)c->sm_count * 4);
+    xchg_hist<<<xblocks, XCHG_THREADS, 0, c->stream>>>(ptr<uint32_t>(c->surv_pid), ptr<uint8_t>(c->surv_ns), &ds->surv_count, W, T, table);
+    if ((rc = dbg_sync(c, "xchg_hist"))) return rc;
     if ((rc = launch_scan(c, table, table_len))) return rc;
+    if ((rc = dbg_sync(c, "owner table scan"))) return rc;
     pk.pid = ptr<uint32_t>(c->surv_pid);
     pk.surv_src = ptr<uint32_t>(c->surv_src);
     pk.surv_meta = ptr<uint8_t>(c->surv_meta);
@@ -1268,8 +1272,10 @@ static int stage1_partition(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, u
     pk.err = &ds->xchg_err;
     pk.done = ptr<uint32_t>(c->tickets) + 58;
     mark(c, "owner histogram + scan");
-    xchg_pack<<<T, XCHG_THREADS, 0, c->stream>>>(pk);
+    pk.T = T;
+    xchg_pack<<<xblocks, XCHG_THREADS, 0, c->stream>>>(pk);
     CK(cudaGetLastError());
+    if ((rc = dbg_sync(c, "xchg_pack"))) return rc;
     mark(c, "pack into owners' windows");
     c->launches += 2;
     return CHRONOS_OK;

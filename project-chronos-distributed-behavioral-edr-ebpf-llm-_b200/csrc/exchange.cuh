@@ -32,7 +32,7 @@
 namespace chronos {
 
 constexpr int XCHG_MAX_WORLD = 16;
-constexpr uint32_t XCHG_TILE = 2048;
+constexpr uint32_t XCHG_TILE = 1024;
 constexpr uint32_t XCHG_THREADS = 256;
 constexpr uint32_t XCHG_WARPS = XCHG_THREADS / 32;
 constexpr uint32_t XCHG_OVERFLOW = 0xFFFFFFFFu;
@@ -71,28 +71,36 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
 
 // ---------------------------------------------------------------------------------------
 // per tile: how many entries / transport slots go to each owner.
-// table is owner-major with row stride T (the grid size, an upper bound of the tile count):
+// table is owner-major with row stride T (an upper bound of the tile count, known to the host):
 // rows [0, W) entries, rows [W, 2W) slots, and one closing element table[2W*T] so that the
-// exclusive scan leaves the grand total there.
+// exclusive scan leaves the grand total there. Persistent CTAs; tiles past the survivors get
+// zeros (the scan runs over the whole table).
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(XCHG_THREADS) xchg_hist(const uint32_t *pid, const uint8_t *ns, const uint32_t *n_ptr,
-                                                         uint32_t world, uint32_t *table) {
+                                                         uint32_t world, uint32_t T, uint32_t *table) {
     __shared__ uint32_t he[XCHG_MAX_WORLD], hs[XCHG_MAX_WORLD];
-    const uint32_t T = gridDim.x, tile = blockIdx.x, S = *n_ptr;
-    if (threadIdx.x < XCHG_MAX_WORLD) { he[threadIdx.x] = 0; hs[threadIdx.x] = 0; }
-    __syncthreads();
-    const uint32_t lo = min(S, tile * XCHG_TILE), hi = min(S, lo + XCHG_TILE);
-    for (uint32_t i = lo + threadIdx.x; i < hi; i += XCHG_THREADS) {
-        const uint32_t o = hash32(pid[i]) % world;
-        atomicAdd(&he[o], 1u);
-        atomicAdd(&hs[o], (uint32_t)ns[i]);
+    const uint32_t S = *n_ptr;
+    const uint32_t used = (S + XCHG_TILE - 1) / XCHG_TILE;
+    if (blockIdx.x == 0 && threadIdx.x == 0) table[(size_t)2 * world * T] = 0;
+    // columns of tiles that hold no survivor: zeros
+    for (uint32_t i = blockIdx.x * XCHG_THREADS + threadIdx.x; i < T * 2 * world; i += gridDim.x * XCHG_THREADS)
+        if (i % T >= used) table[i] = 0;
+    for (uint32_t tile = blockIdx.x; tile < used; tile += gridDim.x) {
+        __syncthreads();
+        if (threadIdx.x < XCHG_MAX_WORLD) { he[threadIdx.x] = 0; hs[threadIdx.x] = 0; }
+        __syncthreads();
+        const uint32_t lo = tile * XCHG_TILE, hi = min(S, lo + XCHG_TILE);
+        for (uint32_t i = lo + threadIdx.x; i < hi; i += XCHG_THREADS) {
+            const uint32_t o = hash32(pid[i]) % world;
+            atomicAdd(&he[o], 1u);
+            atomicAdd(&hs[o], (uint32_t)ns[i]);
+        }
+        __syncthreads();
+        if (threadIdx.x < world) {
+            table[(size_t)threadIdx.x * T + tile] = he[threadIdx.x];
+            table[(size_t)(world + threadIdx.x) * T + tile] = hs[threadIdx.x];
+        }
     }
-    __syncthreads();
-    if (threadIdx.x < world) {
-        table[(size_t)threadIdx.x * T + tile] = he[threadIdx.x];
-        table[(size_t)(world + threadIdx.x) * T + tile] = hs[threadIdx.x];
-    }
-    if (tile == 0 && threadIdx.x == 0) table[(size_t)2 * world * T] = 0;
 }
 
 struct XchgPackParams {
@@ -103,6 +111,7 @@ struct XchgPackParams {
     const uint8_t *batch;         // the slice's records (device)
     uint64_t base_arrival;
     const uint32_t *table;        // scanned
+    uint32_t T;                   // row stride of the table
     uint32_t world;
     // direct mode: peer[d] = base of owner d's receive window (nullptr => local mode)
     uint8_t *peer[XCHG_MAX_WORLD];
@@ -119,19 +128,20 @@ struct XchgPackParams {
     bool direct;
 };
 
+constexpr uint32_t XCHG_SUB = XCHG_TILE / XCHG_WARPS;   // contiguous sub-range of a warp
+constexpr int XCHG_STEPS = XCHG_SUB / 32;               // 32 survivors per step
+
 __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g) {
     __shared__ uint32_t rs_e[XCHG_MAX_WORLD + 1], rs_s[XCHG_MAX_WORLD + 1];  // row starts = per-owner stream starts
     __shared__ uint32_t wb_e[XCHG_WARPS][XCHG_MAX_WORLD], wb_s[XCHG_WARPS][XCHG_MAX_WORLD];
+    __shared__ uint32_t sh_ns[XCHG_WARPS][32];
     __shared__ uint32_t s_skip, s_last;
-    const uint32_t T = gridDim.x, tile = blockIdx.x, W = g.world, S = *g.n_ptr;
+    const uint32_t T = g.T, W = g.world, S = *g.n_ptr;
+    const uint32_t used = (S + XCHG_TILE - 1) / XCHG_TILE;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid <= (int)W) {
         rs_e[tid] = g.table[(size_t)tid * T];
         rs_s[tid] = g.table[(size_t)(W + tid) * T];
-    }
-    for (int i = tid; i < (int)(XCHG_WARPS * XCHG_MAX_WORLD); i += XCHG_THREADS) {
-        (&wb_e[0][0])[i] = 0;
-        (&wb_s[0][0])[i] = 0;
     }
     if (tid == 0) s_skip = 0;
     __syncthreads();
@@ -142,116 +152,149 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
                                    : ((uint64_t)rs_e[W] > g.cap_entries || (uint64_t)(rs_s[W] - rs_s[0]) > g.cap_slots);
         if (over) atomicOr(&s_skip, 1u << tid);
     }
-    const uint32_t t_lo = min(S, tile * XCHG_TILE), t_hi = min(S, t_lo + XCHG_TILE);
-    constexpr uint32_t SUB = XCHG_TILE / XCHG_WARPS;  // contiguous sub-range of a warp
-    const uint32_t w_lo = min(t_hi, t_lo + warp * SUB), w_hi = min(t_hi, w_lo + SUB);
-    // 1) per-warp counts
-    for (uint32_t i = w_lo + lane; i < w_hi; i += 32) {
-        const uint32_t o = hash32(g.pid[i]) % W;
-        atomicAdd(&wb_e[warp][o], 1u);
-        atomicAdd(&wb_s[warp][o], (uint32_t)g.surv_ns[i]);
-    }
-    __syncthreads();
-    // 2) owner d: running base over the warps, seeded with this tile's offset inside d's stream
-    if (tid < (int)W) {
-        uint32_t re = g.table[(size_t)tid * T + tile], rsl = g.table[(size_t)(W + tid) * T + tile];
-        if (g.direct) { re -= rs_e[tid]; rsl -= rs_s[tid]; }   // relative to the (source, owner) region
-        else rsl -= rs_s[0];                                   // slot rows come after the entry rows in the scan
-#pragma unroll
-        for (int w = 0; w < (int)XCHG_WARPS; w++) {
-            const uint32_t ce = wb_e[w][tid], cs = wb_s[w][tid];
-            wb_e[w][tid] = re; wb_s[w][tid] = rsl;
-            re += ce; rsl += cs;
-        }
-    }
     __syncthreads();
     const uint32_t skip = s_skip;
     const uint32_t half = g.epoch & 1u;
-    // 3) stable placement, 32 survivors per step
-    for (uint32_t i0 = w_lo; i0 < w_hi; i0 += 32) {
-        const uint32_t i = i0 + lane;
-        const bool valid = i < w_hi;
-        uint32_t o = 0xFFu, ns = 0, rec = 0;
-        if (valid) {
-            o = hash32(g.pid[i]) % W;
-            ns = g.surv_ns[i];
-            rec = g.surv_src[i];
+    for (uint32_t tile = blockIdx.x; tile < used; tile += gridDim.x) {
+        __syncwarp();  // (the copy loop below ends in predicated stores: reconverge before the barrier)
+        __syncthreads();
+        for (int i = tid; i < (int)(XCHG_WARPS * XCHG_MAX_WORLD); i += XCHG_THREADS) {
+            (&wb_e[0][0])[i] = 0;
+            (&wb_s[0][0])[i] = 0;
         }
-        uint32_t rank_e = 0, pre_s = 0, grp_e = 0, grp_s = 0;
+        __syncthreads();
+        const uint32_t t_lo = tile * XCHG_TILE, t_hi = min(S, t_lo + XCHG_TILE);
+        const uint32_t w_lo = min(t_hi, t_lo + warp * XCHG_SUB), w_hi = min(t_hi, w_lo + XCHG_SUB);
+        // 1) this warp's survivors, all steps at once (the loads of the later steps are in
+        //    flight while the first step is placed), and the per-warp counts per owner
+        uint32_t ow[XCHG_STEPS], nsv[XCHG_STEPS], recv[XCHG_STEPS], metav[XCHG_STEPS];
 #pragma unroll
-        for (int l = 0; l < 32; l++) {
-            const uint32_t ol = __shfl_sync(0xffffffffu, o, l), nl = __shfl_sync(0xffffffffu, ns, l);
-            if (ol == o) {
-                grp_e++; grp_s += nl;
-                if (l < lane) { rank_e++; pre_s += nl; }
+        for (int q = 0; q < XCHG_STEPS; q++) {
+            const uint32_t i = w_lo + q * 32 + lane;
+            ow[q] = 0xFFu; nsv[q] = 0; recv[q] = 0; metav[q] = 0;
+            if (i < w_hi) {
+                ow[q] = hash32(g.pid[i]) % W;
+                nsv[q] = g.surv_ns[i];
+                recv[q] = g.surv_src[i];
+                metav[q] = g.surv_meta[i];
             }
         }
-        uint32_t be = 0, bs = 0;
-        if (valid) { be = wb_e[warp][o]; bs = wb_s[warp][o]; }
+#pragma unroll
+        for (int q = 0; q < XCHG_STEPS; q++) {
+            if (ow[q] != 0xFFu) {
+                atomicAdd(&wb_e[warp][ow[q]], 1u);
+                atomicAdd(&wb_s[warp][ow[q]], nsv[q]);
+            }
+        }
         __syncwarp();
-        if (valid && rank_e == 0) { wb_e[warp][o] = be + grp_e; wb_s[warp][o] = bs + grp_s; }
+        __syncthreads();
+        // 2) owner d: running base over the warps, seeded with this tile's offset inside d's stream
+        if (tid < (int)W) {
+            uint32_t re = g.table[(size_t)tid * T + tile], rsl = g.table[(size_t)(W + tid) * T + tile];
+            if (g.direct) { re -= rs_e[tid]; rsl -= rs_s[tid]; }   // relative to the (source, owner) region
+            else rsl -= rs_s[0];                                   // slot rows come after the entry rows in the scan
+#pragma unroll
+            for (int w = 0; w < (int)XCHG_WARPS; w++) {
+                const uint32_t ce = wb_e[w][tid], cs = wb_s[w][tid];
+                wb_e[w][tid] = re; wb_s[w][tid] = rsl;
+                re += ce; rsl += cs;
+            }
+        }
         __syncwarp();
-        const bool live = valid && !((skip >> o) & 1u);
-        uint4 *dst = nullptr;  // first slot of this entry at its destination
-        const uint4 *src = nullptr;
-        if (live) {
-            const uint32_t e_idx = be + rank_e, s_idx = bs + pre_s;
-            const uint64_t hdr = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)g.surv_meta[i] << 48) | ((uint64_t)ns << 56);
-            src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
-            if (g.direct) {
-                uint8_t *hb = g.peer[o] + (size_t)half * g.L.half_bytes;
-                const size_t re = (size_t)g.L.rank * g.L.cap_e + e_idx;
-                reinterpret_cast<uint64_t *>(hb + g.L.off_hdr)[re] = hdr;
-                reinterpret_cast<uint32_t *>(hb + g.L.off_off)[re] = s_idx;
-                dst = reinterpret_cast<uint4 *>(hb + g.L.off_slots) + (size_t)g.L.rank * g.L.cap_s + s_idx;
-            } else {
-                g.send_hdr[e_idx] = hdr;
-                dst = g.send_slots + s_idx;
+        __syncthreads();
+        // 3) stable placement, 32 survivors per step (every step is executed by the whole warp;
+        //    lanes past the end carry owner 0xFF and nothing to copy)
+#pragma unroll
+        for (int q = 0; q < XCHG_STEPS; q++) {
+            const uint32_t o = ow[q], ns = nsv[q], rec = recv[q];
+            const bool valid = o != 0xFFu;
+            // rank among the lanes with the same owner, and the slots those lanes hold
+            const uint32_t peers = __match_any_sync(0xffffffffu, o);
+            const uint32_t lower = peers & lanemask_lt();
+            const uint32_t rank_e = __popc(lower);
+            sh_ns[warp][lane] = ns;
+            __syncwarp();
+            uint32_t pre_s = 0;
+            for (uint32_t m = lower; m; m &= m - 1) pre_s += sh_ns[warp][__ffs((int)m) - 1];
+            uint32_t be = 0, bs = 0;
+            if (valid) { be = wb_e[warp][o]; bs = wb_s[warp][o]; }
+            __syncwarp();
+            if (valid && (peers >> lane) == 1u) {  // highest lane of its group: it knows the group totals
+                wb_e[warp][o] = be + rank_e + 1;
+                wb_s[warp][o] = bs + pre_s + ns;
             }
-        }
-        const uint32_t cnt = live ? ns : 0u;
-        uint32_t incl = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += t;
-        }
-        const uint32_t excl = incl - cnt, total = __shfl_sync(0xffffffffu, incl, 31);
-        // the warp copies the slots of its 32 entries cooperatively, 4 x 32 slots per step with
-        // all four loads issued before the first store
-        for (uint32_t b0 = 0; b0 < total; b0 += 128) {
-            uint4 v[4];
-            uint4 *dq[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const uint32_t k = b0 + u * 32 + lane;
-                int sidx = 0;  // lane that owns slot k (shuffle binary search, as in filter.cuh phase B2)
-#pragma unroll
-                for (int step = 16; step >= 1; step >>= 1) {
-                    const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
-                    if (vv <= k) sidx += step;
-                }
-                const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
-                const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
-                const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)dst, sidx);
-                dq[u] = nullptr;
-                v[u] = make_uint4(0u, 0u, 0u, 0u);
-                if (k < total) {
-                    const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
-                    const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
-                    v[u] = __ldg(reinterpret_cast<const uint4 *>((uintptr_t)sp) + ch);
-                    dq[u] = reinterpret_cast<uint4 *>((uintptr_t)dp) + sl;
+            __syncwarp();
+            const bool live = valid && !((skip >> (o & 31u)) & 1u);
+            uint4 *dst = nullptr;  // first slot of this entry at its destination
+            const uint4 *src = nullptr;
+            if (live) {
+                const uint32_t e_idx = be + rank_e, s_idx = bs + pre_s;
+                const uint64_t hdr = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)metav[q] << 48) | ((uint64_t)ns << 56);
+                src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
+                if (g.direct) {
+                    uint8_t *hb = g.peer[o] + (size_t)half * g.L.half_bytes;
+                    const size_t re = (size_t)g.L.rank * g.L.cap_e + e_idx;
+                    reinterpret_cast<uint64_t *>(hb + g.L.off_hdr)[re] = hdr;
+                    reinterpret_cast<uint32_t *>(hb + g.L.off_off)[re] = s_idx;
+                    dst = reinterpret_cast<uint4 *>(hb + g.L.off_slots) + (size_t)g.L.rank * g.L.cap_s + s_idx;
+                } else {
+                    g.send_hdr[e_idx] = hdr;
+                    dst = g.send_slots + s_idx;
                 }
             }
+            __syncwarp();
+            const uint32_t cnt = live ? ns : 0u;
+            uint32_t incl = cnt;
 #pragma unroll
-            for (int u = 0; u < 4; u++)
-                if (dq[u]) *dq[u] = v[u];
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+                if (lane >= d) incl += t;
+            }
+            const uint32_t excl = incl - cnt, total = __shfl_sync(0xffffffffu, incl, 31);
+            // the warp copies the slots of its 32 entries cooperatively, 4 x 32 slots per step
+            // with all four loads issued before the first store
+            for (uint32_t b0 = 0; b0 < total; b0 += 128) {
+                uint4 v[4];
+                uint4 *dq[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t k = b0 + u * 32 + lane;
+                    int sidx = 0;  // lane that owns slot k (shuffle binary search, as in filter.cuh phase B2)
+#pragma unroll
+                    for (int step = 16; step >= 1; step >>= 1) {
+                        const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
+                        if (vv <= k) sidx += step;
+                    }
+                    sidx &= 31;
+                    const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
+                    const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
+                    const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)dst, sidx);
+                    dq[u] = nullptr;
+                    v[u] = make_uint4(0u, 0u, 0u, 0u);
+                    if (k < total) {
+                        const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
+                        const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
+                        v[u] = __ldg(reinterpret_cast<const uint4 *>((uintptr_t)sp) + ch);
+                        dq[u] = reinterpret_cast<uint4 *>((uintptr_t)dp) + sl;
+                    }
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if (dq[u]) *dq[u] = v[u];
+                __syncwarp();
+            }
         }
     }
-    // 4) the last CTA to finish publishes counts and flag
-    __threadfence_system();
+    // 4) the last CTA to finish publishes counts and flag. One system-scope fence per CTA, by
+    //    the thread that then counts the CTA in: the block barrier orders every thread's
+    //    stores before it (the pattern of a grid barrier); a fence per thread made this
+    //    kernel membar-bound.
+    __syncwarp();
     __syncthreads();
-    if (tid == 0) s_last = (atomicAdd(g.done, 1u) == T - 1) ? 1u : 0u;
+    if (tid == 0) {
+        __threadfence_system();
+        s_last = (atomicAdd(g.done, 1u) == gridDim.x - 1) ? 1u : 0u;
+    }
     __syncthreads();
     if (!s_last) return;
     __threadfence_system();
