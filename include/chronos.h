@@ -166,6 +166,22 @@ int chronos_filter_partition(chronos_ctx *ctx, const void *records, uint64_t n, 
 int chronos_submit_survivors(chronos_ctx *ctx, const void *slots, const uint64_t *hdr, uint64_t n_entries,
                              uint64_t n_slots);
 
+/* ---- checkpoint of the per-PID state -----------------------------------
+ *
+ * Everything a context carries from one batch to the next -- the pending per-PID lists with
+ * their records (process_memory, chronos_sensor.py:105), the set of PIDs seen (its keys,
+ * including lists emptied at :157) and the chain labeller's per-PID state -- as one
+ * little-endian blob in HOST memory: a 64-byte header ("CHRNCKP1", version, counts), the PID
+ * entries sorted by pid, then pid / arrival index / META bits / 288-byte record of every
+ * pending entry. A context that loads the blob continues exactly where the saved one was
+ * (same windows, same final state). The reference has no counterpart: its state dies with
+ * the process. Not allowed between chronos_submit and chronos_fetch. */
+int chronos_checkpoint_bytes(chronos_ctx *ctx, uint64_t *bytes);
+int chronos_checkpoint_save(chronos_ctx *ctx, void *dst, uint64_t cap_bytes);
+/* Replaces the context's state (an implicit chronos_reset first). Malformed or truncated
+ * input: CHRONOS_E_ARG and the state is left reset or untouched, never half loaded. */
+int chronos_checkpoint_load(chronos_ctx *ctx, const void *src, uint64_t bytes);
+
 /* ---- asynchronous download of the results ------------------------------------------------
  *
  * The chronos_copy_* calls block. A replay loop that wants the PCIe link busy in both

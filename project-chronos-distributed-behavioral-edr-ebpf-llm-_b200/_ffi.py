@@ -74,6 +74,9 @@ SIGNATURES = {
     "chronos_filter_partition": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64, c_uint32, c_void_p, c_uint64,
                                          c_void_p, c_uint64, c_void_p, c_void_p]),
     "chronos_submit_survivors": (c_int, [c_void_p, c_void_p, c_void_p, c_uint64, c_uint64]),
+    "chronos_checkpoint_bytes": (c_int, [c_void_p, POINTER(c_uint64)]),
+    "chronos_checkpoint_save": (c_int, [c_void_p, c_void_p, c_uint64]),
+    "chronos_checkpoint_load": (c_int, [c_void_p, c_void_p, c_uint64]),
     "chronos_download_begin": (c_int, [c_void_p, c_void_p, c_uint64, POINTER(Download)]),
     "chronos_download_wait": (c_int, [c_void_p]),
     "chronos_exchange_create": (c_int, [c_void_p, c_uint32, c_uint32, c_uint64, c_uint64, POINTER(c_void_p), c_void_p]),

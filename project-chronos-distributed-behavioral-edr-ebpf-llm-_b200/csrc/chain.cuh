@@ -70,4 +70,22 @@ __global__ void pt_dump_kernel(const uint64_t *tab, uint32_t cap, uint32_t epoch
     }
 }
 
+// checkpoint: every live entry as (dfa << 32 | pid), any order
+__global__ void pt_dump64_kernel(const uint64_t *tab, uint32_t cap, uint32_t epoch, uint64_t *out, uint32_t *n_out) {
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < cap; k += gridDim.x * blockDim.x) {
+        const uint64_t v = tab[k];
+        if (pt_live(v, epoch)) out[atomicAdd(n_out, 1u)] = v & 0x3FFFFFFFFull;
+    }
+}
+
+// checkpoint: entries (dfa << 32 | pid) back into an empty table
+__global__ void pt_load_kernel(uint64_t *tab, uint32_t mask, uint32_t epoch, const uint64_t *in, uint32_t n) {
+    for (uint32_t k = blockIdx.x * blockDim.x + threadIdx.x; k < n; k += gridDim.x * blockDim.x) {
+        const uint64_t e = in[k];
+        uint32_t inserted = 0;
+        const uint32_t slot = pt_find_or_insert(tab, mask, epoch, (uint32_t)e, inserted);
+        st_relaxed_u64(tab + slot, pt_make(epoch, (uint32_t)(e >> 32) & 3u, (uint32_t)e));
+    }
+}
+
 }  // namespace chronos

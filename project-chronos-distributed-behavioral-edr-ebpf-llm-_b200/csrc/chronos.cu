@@ -1161,6 +1161,146 @@ int chronos_state_pids(chronos_ctx *c, uint32_t *pid, uint64_t cap) {
     return CHRONOS_OK;
 }
 
+// ---- checkpoint of the per-PID state ----------------------------------------------------------
+namespace {
+struct CkptHeader {
+    char magic[8];
+    uint32_t version, record_bytes;
+    uint64_t n_pending, n_pids;
+    uint64_t reserved[4];
+};
+static_assert(sizeof(CkptHeader) == 64, "checkpoint header");
+const char CKPT_MAGIC[8] = {'C', 'H', 'R', 'N', 'C', 'K', 'P', '1'};
+inline uint64_t al8(uint64_t v) { return (v + 7) & ~7ull; }
+struct CkptLayout { uint64_t off_tab, off_pid, off_arr, off_meta, off_rec, total; };
+CkptLayout ckpt_layout(uint64_t P, uint64_t K) {
+    CkptLayout L;
+    L.off_tab = sizeof(CkptHeader);
+    L.off_pid = L.off_tab + K * 8;
+    L.off_arr = L.off_pid + al8(P * 4);
+    L.off_meta = L.off_arr + P * 8;
+    L.off_rec = L.off_meta + al8(P);
+    L.total = L.off_rec + P * CH_REC_BYTES;
+    return L;
+}
+__global__ void iota_u32_kernel(uint32_t *p, uint32_t n) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) p[i] = i;
+}
+}  // namespace
+
+int chronos_checkpoint_bytes(chronos_ctx *c, uint64_t *bytes) {
+    if (!c || !bytes) return CHRONOS_E_ARG;
+    if (c->phase == chronos_ctx::SUBMITTED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    *bytes = ckpt_layout(c->n_pending, c->n_pids_seen).total;
+    return CHRONOS_OK;
+}
+
+int chronos_checkpoint_save(chronos_ctx *c, void *dst, uint64_t cap) {
+    if (!c || !dst) return CHRONOS_E_ARG;
+    if (c->phase == chronos_ctx::SUBMITTED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    CK(cudaSetDevice(c->device));
+    const uint64_t P = c->n_pending, K = c->n_pids_seen;
+    const CkptLayout L = ckpt_layout(P, K);
+    if (cap < L.total) return fail(c, CHRONOS_E_ARG, "checkpoint buffer too small (%llu < %llu)", (unsigned long long)cap,
+                                   (unsigned long long)L.total);
+    uint8_t *out = static_cast<uint8_t *>(dst);
+    memset(out, 0, L.off_pid);
+    CkptHeader h;
+    memset(&h, 0, sizeof(h));
+    memcpy(h.magic, CKPT_MAGIC, 8);
+    h.version = 1;
+    h.record_bytes = CH_REC_BYTES;
+    h.n_pending = P;
+    h.n_pids = K;
+    memcpy(out, &h, sizeof(h));
+    int rc;
+    if (K) {
+        if ((rc = ensure(c, c->pack, K * 8 + 256))) return rc;
+        if ((rc = ensure(c, c->pack_off, 256))) return rc;
+        uint32_t *cnt = ptr<uint32_t>(c->pack_off);
+        CK(cudaMemsetAsync(cnt, 0, 4, c->stream));
+        pt_dump64_kernel<<<(unsigned)std::min<uint32_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
+            ptr<uint64_t>(c->pid_tab), c->pt_cap, c->pt_epoch, ptr<uint64_t>(c->pack), cnt);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(out + L.off_tab, c->pack.p, K * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        uint64_t *e = reinterpret_cast<uint64_t *>(out + L.off_tab);
+        std::sort(e, e + K, [](uint64_t a, uint64_t b) { return (uint32_t)a < (uint32_t)b; });  // by pid: files compare equal
+    }
+    if (P) {
+        memset(out + L.off_pid, 0, L.off_arr - L.off_pid);
+        memset(out + L.off_meta, 0, L.off_rec - L.off_meta);
+        const int cur = c->cur;
+        const uint64_t pc = c->pend_cap[cur];
+        CK(cudaMemcpyAsync(out + L.off_pid, ptr<uint32_t>(c->pend_key[cur]) + (pc - P), P * 4, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(out + L.off_arr, ptr<uint64_t>(c->pend_arrival[cur]) + (pc - P), P * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(out + L.off_meta, ptr<uint8_t>(c->pend_meta[cur]) + (pc - P), P, cudaMemcpyDeviceToHost, c->stream));
+        if ((rc = ensure(c, c->pack, P * CH_REC_BYTES))) return rc;
+        pack_by_slot_kernel<<<(unsigned)std::min<uint64_t>((P + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
+            ptr<uint8_t>(c->arena[cur]), ptr<uint32_t>(c->pend_slot[cur]) + (pc - P), (uint32_t)P, ptr<uint8_t>(c->pack));
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(out + L.off_rec, c->pack.p, P * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+    }
+    return CHRONOS_OK;
+}
+
+int chronos_checkpoint_load(chronos_ctx *c, const void *src, uint64_t bytes) {
+    if (!c || !src) return CHRONOS_E_ARG;
+    if (bytes < sizeof(CkptHeader)) return fail(c, CHRONOS_E_ARG, "not a checkpoint (too short)");
+    const uint8_t *in = static_cast<const uint8_t *>(src);
+    CkptHeader h;
+    memcpy(&h, in, sizeof(h));
+    if (memcmp(h.magic, CKPT_MAGIC, 8) != 0 || h.version != 1 || h.record_bytes != CH_REC_BYTES)
+        return fail(c, CHRONOS_E_ARG, "not a version-1 checkpoint of 288-byte records");
+    const uint64_t P = h.n_pending, K = h.n_pids;
+    if (P >= (1ull << VAL_ID_BITS) || K >= (1ull << 31)) return fail(c, CHRONOS_E_CAPACITY, "checkpoint too large");
+    const CkptLayout L = ckpt_layout(P, K);
+    if (bytes < L.total) return fail(c, CHRONOS_E_ARG, "checkpoint truncated (%llu < %llu bytes)", (unsigned long long)bytes,
+                                     (unsigned long long)L.total);
+    // the pending list must be what window_reverse would have written: ascending pid, ascending
+    // arrival inside a pid; every pending pid must be in the key set
+    const uint32_t *ppid = reinterpret_cast<const uint32_t *>(in + L.off_pid);
+    const uint64_t *parr = reinterpret_cast<const uint64_t *>(in + L.off_arr);
+    for (uint64_t i = 1; i < P; i++)
+        if (ppid[i] < ppid[i - 1] || (ppid[i] == ppid[i - 1] && parr[i] <= parr[i - 1]))
+            return fail(c, CHRONOS_E_ARG, "checkpoint: pending entry %llu out of order", (unsigned long long)i);
+    int rc = chronos_reset(c);
+    if (rc) return rc;
+    if (K) {
+        if ((rc = ensure_pid_table(c, K))) return rc;
+        if ((rc = ensure(c, c->pack, K * 8))) return rc;
+        CK(cudaMemcpyAsync(c->pack.p, in + L.off_tab, K * 8, cudaMemcpyHostToDevice, c->stream));
+        pt_load_kernel<<<(unsigned)std::min<uint64_t>((K + 255) / 256, 2048), 256, 0, c->stream>>>(
+            ptr<uint64_t>(c->pid_tab), c->pt_cap - 1, c->pt_epoch, ptr<uint64_t>(c->pack), (uint32_t)K);
+        CK(cudaGetLastError());
+        const uint32_t k32 = (uint32_t)K;
+        CK(cudaMemcpyAsync(c->pt_count.p, &k32, 4, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+    }
+    const int cur = c->cur;
+    if (P) {
+        if ((rc = ensure(c, c->arena[cur], (P + 1) * CH_REC_BYTES))) return rc;
+        if ((rc = ensure(c, c->pend_key[cur], (P + 1) * 4))) return rc;
+        if ((rc = ensure(c, c->pend_slot[cur], (P + 1) * 4))) return rc;
+        if ((rc = ensure(c, c->pend_arrival[cur], (P + 1) * 8))) return rc;
+        if ((rc = ensure(c, c->pend_meta[cur], P + 1))) return rc;
+        c->pend_cap[cur] = P;  // right-aligned in a layout of exactly P entries
+        CK(cudaMemcpyAsync(c->pend_key[cur].p, ppid, P * 4, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->pend_arrival[cur].p, parr, P * 8, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->pend_meta[cur].p, in + L.off_meta, P, cudaMemcpyHostToDevice, c->stream));
+        CK(cudaMemcpyAsync(c->arena[cur].p, in + L.off_rec, P * CH_REC_BYTES, cudaMemcpyHostToDevice, c->stream));
+        iota_u32_kernel<<<(unsigned)std::min<uint64_t>((P + 255) / 256, 2048), 256, 0, c->stream>>>(
+            ptr<uint32_t>(c->pend_slot[cur]), (uint32_t)P);
+        CK(cudaGetLastError());
+        CK(cudaStreamSynchronize(c->stream));
+    }
+    c->n_pending = P;
+    c->n_pids_seen = K;
+    c->phase = chronos_ctx::IDLE;
+    return CHRONOS_OK;
+}
+
 int chronos_get_device_view(chronos_ctx *c, chronos_device_view *out) {
     int rc = need_fetched(c);
     if (rc) return rc;

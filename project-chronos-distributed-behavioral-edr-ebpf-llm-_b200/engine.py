@@ -96,6 +96,20 @@ class Context:
         self._check(self._L.chronos_submit_survivors(self._h, c_void_p(int(slots_ptr)), c_void_p(int(hdr_ptr)),
                                                      int(n_entries), int(n_slots)))
 
+    # ---- checkpoint ------------------------------------------------------------------------
+    def checkpoint_save(self):
+        """The whole carried state (pending lists with records, PIDs seen, chain states) as bytes."""
+        n = c_uint64()
+        self._check(self._L.chronos_checkpoint_bytes(self._h, byref(n)))
+        buf = np.zeros(max(int(n.value), 1), dtype=np.uint8)
+        self._check(self._L.chronos_checkpoint_save(self._h, buf.ctypes.data, buf.size))
+        return buf[:int(n.value)].tobytes()
+
+    def checkpoint_load(self, blob):
+        """Replace this context's state with a saved one; the next submit continues the stream."""
+        a = np.frombuffer(blob, dtype=np.uint8)
+        self._check(self._L.chronos_checkpoint_load(self._h, a.ctypes.data, a.size))
+
     # ---- asynchronous download ------------------------------------------------------------
     def download_begin(self, host_ptr, cap_bytes):
         """Start one device-to-host copy of the fetched batch's survivors, windows and window
