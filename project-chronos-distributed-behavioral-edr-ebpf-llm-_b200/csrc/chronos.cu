@@ -370,16 +370,18 @@ int launch_filter(chronos_ctx *c, const FilterParams &fp) {
 
 // exclusive scan in place (device array of n u32) on the context's stream
 // (n_dev != nullptr: the real count lives on the device, n is only its upper bound)
-int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_dev = nullptr, int own_ticket = -1) {
+int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_dev = nullptr, int own_ticket = -1,
+                cudaStream_t stream = nullptr) {
     if (n == 0) return CHRONOS_OK;
+    if (!stream) stream = c->stream;
     const uint32_t n_tiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
     int rc;
     const void *before = c->scan_status.p;
     if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_tiles * 8, 4096)))) return rc;
     if (c->scan_status.p != before || c->scan_epoch == 0)  // fresh memory or wrapped epoch: tag 0 = "never"
-        CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, c->stream));
+        CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, stream));
     if (own_ticket < 0 && c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
-    if (own_ticket >= 0) CK(cudaMemsetAsync(ptr<uint32_t>(c->tickets) + own_ticket, 0, 4, c->stream));
+    if (own_ticket >= 0) CK(cudaMemsetAsync(ptr<uint32_t>(c->tickets) + own_ticket, 0, 4, stream));
     ScanParams sp;
     sp.data = data;
     sp.n = (uint32_t)n;
@@ -388,7 +390,7 @@ int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_de
     sp.status = ptr<uint64_t>(c->scan_status);
     sp.epoch = ++c->scan_epoch;
     if (c->scan_epoch >= (1u << 29)) c->scan_epoch = 0;  // re-zero on the next call
-    scan_exclusive_u32<<<std::min<uint32_t>(n_tiles, (uint32_t)c->sm_count * 2), SCAN_THREADS, 0, c->stream>>>(sp);
+    scan_exclusive_u32<<<std::min<uint32_t>(n_tiles, (uint32_t)c->sm_count * 2), SCAN_THREADS, 0, stream>>>(sp);
     CK(cudaGetLastError());
     c->launches++;
     return CHRONOS_OK;
@@ -396,11 +398,11 @@ int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_de
 
 // filter + cross-tile compaction: dense, arrival-ordered survivors (pid -> out_key,
 // batch-local index -> surv_src, META bits -> surv_meta, count -> scalars.surv_count)
-int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t *out_key) {
+// Buffers and parameters of the filter for a batch of n records (no launch).
+int filter_setup(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, FilterParams &fp) {
     int rc;
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     const int TILE = filter_tile_size(c);
-    FilterParams fp;
     fp.recs = d_recs;
     fp.n = n;
     fp.tile_begin = 0;
@@ -413,7 +415,7 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
     if ((rc = ensure(c, c->sp_ns, slots))) return rc;
     if ((rc = ensure(c, c->surv_pid, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->surv_ns, n + 1))) return rc;
-    if ((rc = ensure(c, c->tile_count, ((uint64_t)fp.tile_end + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->tile_count, ((uint64_t)fp.tile_end + 4) * 4))) return rc;
     fp.tile_count = ptr<uint32_t>(c->tile_count);
     fp.sp_key = ptr<uint32_t>(c->sp_key);
     fp.sp_src = ptr<uint32_t>(c->sp_src);
@@ -426,41 +428,60 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
     fp.gm_val = fp.gm_lock + COMM_MEMO_SLOTS;
     fp.gm_key = reinterpret_cast<uint4 *>(fp.gm_val + COMM_MEMO_SLOTS);
     fp.gm_mask = COMM_MEMO_SLOTS - 1;
+    return CHRONOS_OK;
+}
+
+// Cross-tile prefix + dense, arrival-ordered survivor arrays for the filter tiles
+// [tile_begin, tile_end), one kernel on `stream`. base_ptr / total_out: see CompactScanParams.
+int launch_compact(chronos_ctx *c, const FilterParams &fp, uint32_t tile_begin, uint32_t tile_end, uint32_t *out_key,
+                   cudaStream_t stream, const uint32_t *base_ptr, uint32_t *total_out) {
+    int rc;
+    const uint32_t n_tiles = tile_end - tile_begin;
+    const uint32_t n_chunks = (n_tiles + CS_CHUNK - 1) / CS_CHUNK;
+    const void *before = c->scan_status.p;
+    if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_chunks * 8, 4096)))) return rc;
+    if (c->scan_status.p != before || c->scan_epoch == 0)
+        CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, stream));
+    if (c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
+    CompactScanParams cp;
+    cp.tile_count = fp.tile_count;
+    cp.tile_begin = tile_begin;
+    cp.n_tiles = n_tiles;
+    cp.base_ptr = base_ptr;
+    cp.total_out = total_out;
+    cp.tile = (uint32_t)filter_tile_size(c);
+    cp.sp_key = fp.sp_key;
+    cp.sp_src = fp.sp_src;
+    cp.sp_meta = fp.sp_meta;
+    cp.sp_ns = fp.sp_ns;
+    cp.out_key = out_key;
+    cp.out_src = ptr<uint32_t>(c->surv_src);
+    cp.out_meta = ptr<uint8_t>(c->surv_meta);
+    cp.out_ns = ptr<uint8_t>(c->surv_ns);
+    cp.out_pid = ptr<uint32_t>(c->surv_pid);
+    cp.ticket = ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
+    cp.status = ptr<uint64_t>(c->scan_status);
+    cp.epoch = ++c->scan_epoch;
+    if (c->scan_epoch >= (1u << 29)) c->scan_epoch = 0;
+    compact_scan<<<std::max(1u, std::min<uint32_t>(n_chunks, (uint32_t)c->sm_count * 4)), CS_THREADS, 0, stream>>>(cp);
+    CK(cudaGetLastError());
+    c->launches += 1;
+    return CHRONOS_OK;
+}
+
+// filter + cross-tile compaction: dense, arrival-ordered survivors (pid -> out_key,
+// batch-local index -> surv_src, META bits -> surv_meta, count -> scalars.surv_count)
+int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t *out_key) {
+    int rc;
+    FilterParams fp;
+    if ((rc = filter_setup(c, d_recs, n, fp))) return rc;
     CK(cudaEventRecord(c->ev_f0, c->stream));
     if ((rc = dbg_sync(c, "begin_batch"))) return rc;
     if ((rc = launch_filter(c, fp))) return rc;
     CK(cudaEventRecord(c->ev_f1, c->stream));
     if ((rc = dbg_sync(c, "filter_kernel"))) return rc;
     c->filter_timed = true;
-    // cross-tile prefix + dense, arrival-ordered survivor arrays, one kernel
-    {
-        const uint32_t n_chunks = (fp.tile_end + CS_CHUNK - 1) / CS_CHUNK;
-        const void *before = c->scan_status.p;
-        if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_chunks * 8, 4096)))) return rc;
-        if (c->scan_status.p != before || c->scan_epoch == 0)
-            CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, c->stream));
-        if (c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
-        CompactScanParams cp;
-        cp.tile_count = ptr<uint32_t>(c->tile_count);
-        cp.n_tiles = fp.tile_end;
-        cp.tile = (uint32_t)TILE;
-        cp.sp_key = fp.sp_key;
-        cp.sp_src = fp.sp_src;
-        cp.sp_meta = fp.sp_meta;
-        cp.sp_ns = fp.sp_ns;
-        cp.out_key = out_key;
-        cp.out_src = ptr<uint32_t>(c->surv_src);
-        cp.out_meta = ptr<uint8_t>(c->surv_meta);
-        cp.out_ns = ptr<uint8_t>(c->surv_ns);
-        cp.out_pid = ptr<uint32_t>(c->surv_pid);
-        cp.ticket = ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
-        cp.status = ptr<uint64_t>(c->scan_status);
-        cp.epoch = ++c->scan_epoch;
-        if (c->scan_epoch >= (1u << 29)) c->scan_epoch = 0;
-        compact_scan<<<std::max(1u, std::min<uint32_t>(n_chunks, (uint32_t)c->sm_count * 4)), CS_THREADS, 0, c->stream>>>(cp);
-        CK(cudaGetLastError());
-        c->launches += 1;
-    }
+    if ((rc = launch_compact(c, fp, 0, fp.tile_end, out_key, c->stream, nullptr, nullptr))) return rc;
     if ((rc = dbg_sync(c, "filter + scan + compact"))) return rc;
     return CHRONOS_OK;
 }
@@ -1352,9 +1373,14 @@ void *chronos_stream(chronos_ctx *c) { return c ? (void *)c->stream : nullptr; }
 
 uint32_t chronos_owner_of(uint32_t pid, uint32_t world) { return world ? hash32(pid) % world : 0; }
 
-// Stage 1 of the sharded path up to the dense survivor arrays (surv_pid / surv_src / surv_meta /
-// surv_ns, count in scalars.surv_count). The per-PID state of the context is not touched.
-static int stage1_filter(chronos_ctx *c, const void *records, uint64_t n, const uint8_t **d_recs_out) {
+// Stage 1 of the sharded path: filter the slice, partition the survivors by owner rank and
+// deliver them (pk.direct: into the owners' windows; else into the caller's send buffers).
+// The slice can be cut into `chunks` tile ranges: while the filter works on chunk k+1 on the
+// main stream, chunk k is compacted, counted and packed on the second stream (off by default,
+// see below). The per-PID state of the context is not touched.
+//   device words in x_totals: [0,32) per-owner totals for the host, [32,64) per-owner bases of
+//   the step (direct mode), [64] survivors before the current chunk, [65] survivors of the chunk
+static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base, XchgPackParams &pk, int chunks) {
     int rc;
     const uint8_t *d_recs = nullptr;
     if (n == 0) {
@@ -1373,51 +1399,95 @@ static int stage1_filter(chronos_ctx *c, const void *records, uint64_t n, const 
     if ((rc = ensure(c, c->keyA, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
-    if ((rc = ensure(c, c->x_totals, 256))) return rc;
+    if ((rc = ensure(c, c->surv_pid, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->surv_ns, n + 1))) return rc;
+    if ((rc = ensure(c, c->x_totals, 512))) return rc;
+    uint32_t *xs = ptr<uint32_t>(c->x_totals);
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    CK(cudaMemsetAsync(xs, 0, 512, c->stream));
     init_scalars_kernel<<<1, 256, 0, c->stream>>>(ds, ptr<uint32_t>(c->tickets));
     set_u32_kernel<<<1, 1, 0, c->stream>>>(&ds->xchg_err, 0u);
     c->launches += 2;
     mark(c, "stage 1 start");
-    if (n && (rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA)))) return rc;
-    mark(c, "filter + compact");
-    *d_recs_out = d_recs;
-    return CHRONOS_OK;
-}
 
-// Partition of the survivors by owner rank: xchg_hist -> scan -> xchg_pack (exchange.cuh).
-static int stage1_partition(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint64_t base, XchgPackParams &pk) {
-    int rc;
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     const uint32_t W = pk.world;
-    const uint32_t T = (uint32_t)std::max<uint64_t>((n + XCHG_TILE - 1) / XCHG_TILE, 1);
+    const int TILE = filter_tile_size(c);
+    const uint32_t tiles_all = (uint32_t)((n + TILE - 1) / TILE);
+    // chunks <= 0: the default, ONE piece. Measured on 2xB200 with 12.5 M events per rank: cutting
+    // the slice in 2 / 4 pieces so that the delivery of piece k overlaps the filter of piece k+1
+    // makes stage 1 slower, 0.80 -> 1.25 / 1.15 ms: the filter needs its ~19 single-warp CTAs per
+    // SM and loses them to the pack kernel (its span grows from 0.60 to 1.07 ms). The pieces stay
+    // available (CHRONOS_XCHG_CHUNKS, at most 4: filter tickets 0..3) and tested.
+    if (chunks <= 0) chunks = 1;
+    if (chunks > 4) chunks = 4;
+    if (chunks < 1 || tiles_all < 1024u * (uint32_t)chunks) chunks = 1;
+    const uint32_t tiles_per_chunk = ((tiles_all + chunks - 1) / chunks + 1023u) & ~1023u;
+    const uint64_t chunk_events = (uint64_t)tiles_per_chunk * TILE;
+    const uint32_t T = (uint32_t)std::max<uint64_t>((std::min<uint64_t>(chunk_events, std::max<uint64_t>(n, 1)) + XCHG_TILE - 1) / XCHG_TILE, 1);
     const uint64_t table_len = (uint64_t)2 * W * T + 1;
     if ((rc = ensure(c, c->radix_table, table_len * 4))) return rc;
     uint32_t *table = ptr<uint32_t>(c->radix_table);
-    // persistent CTAs: the tile count is an upper bound (the survivor count stays on the device)
-    const unsigned xblocks = std::min<uint32_t>(T, (uint32_t)c->sm_count * 4);
-    xchg_hist<<<xblocks, XCHG_THREADS, 0, c->stream>>>(ptr<uint32_t>(c->surv_pid), ptr<uint8_t>(c->surv_ns), &ds->surv_count, W, T, table);
-    if ((rc = dbg_sync(c, "xchg_hist"))) return rc;
-    if ((rc = launch_scan(c, table, table_len))) return rc;
-    if ((rc = dbg_sync(c, "owner table scan"))) return rc;
+    const unsigned xblocks = std::min<uint32_t>(T, (uint32_t)c->sm_count * 4);  // persistent CTAs, T is an upper bound
+
     pk.pid = ptr<uint32_t>(c->surv_pid);
     pk.surv_src = ptr<uint32_t>(c->surv_src);
     pk.surv_meta = ptr<uint8_t>(c->surv_meta);
     pk.surv_ns = ptr<uint8_t>(c->surv_ns);
-    pk.n_ptr = &ds->surv_count;
+    pk.n_ptr = xs + 65;
+    pk.start_ptr = xs + 64;
+    pk.owner_base = pk.direct ? xs + 32 : nullptr;
     pk.batch = d_recs;
     pk.base_arrival = base;
     pk.table = table;
-    pk.totals = ptr<uint32_t>(c->x_totals);
+    pk.T = T;
+    pk.totals = xs;
     pk.err = &ds->xchg_err;
     pk.done = ptr<uint32_t>(c->tickets) + 58;
-    mark(c, "owner histogram + scan");
-    pk.T = T;
-    xchg_pack<<<xblocks, XCHG_THREADS, 0, c->stream>>>(pk);
-    CK(cudaGetLastError());
-    if ((rc = dbg_sync(c, "xchg_pack"))) return rc;
-    mark(c, "pack into owners' windows");
-    c->launches += 2;
+
+    FilterParams fp;
+    memset(&fp, 0, sizeof(fp));
+    if (n && (rc = filter_setup(c, d_recs, n, fp))) return rc;
+    const bool overlap = chunks > 1;
+    cudaStream_t side = overlap ? c->stream2 : c->stream;
+    CK(cudaEventRecord(c->ev_f0, c->stream));
+    for (int k = 0; k < chunks; k++) {
+        const uint32_t tb = std::min<uint32_t>(tiles_all, (uint32_t)k * tiles_per_chunk);
+        const uint32_t te = std::min<uint32_t>(tiles_all, tb + tiles_per_chunk);
+        if (te > tb) {
+            fp.tile_begin = tb;
+            fp.tile_end = te;
+            fp.ticket = ptr<uint32_t>(c->tickets) + k;
+            if ((rc = launch_filter(c, fp))) return rc;
+            if ((rc = dbg_sync(c, "filter_kernel (chunk)"))) return rc;
+        }
+        if (k == chunks - 1) CK(cudaEventRecord(c->ev_f1, c->stream));
+        if (overlap) {
+            CK(cudaEventRecord(c->ev_sorted, c->stream));
+            CK(cudaStreamWaitEvent(side, c->ev_sorted, 0));
+        }
+        if (te > tb) {
+            if ((rc = launch_compact(c, fp, tb, te, ptr<uint32_t>(c->keyA), side, xs + 64, xs + 65))) return rc;
+        } else {
+            set_u32_kernel<<<1, 1, 0, side>>>(xs + 65, 0u);  // nothing in this chunk
+            c->launches++;
+        }
+        if ((rc = dbg_sync(c, "compact_scan (chunk)"))) return rc;
+        xchg_hist<<<xblocks, XCHG_THREADS, 0, side>>>(ptr<uint32_t>(c->surv_pid), ptr<uint8_t>(c->surv_ns), xs + 65, xs + 64, W, T, table);
+        if ((rc = dbg_sync(c, "xchg_hist (chunk)"))) return rc;
+        if ((rc = launch_scan(c, table, table_len, nullptr, -1, side))) return rc;
+        if ((rc = dbg_sync(c, "owner table scan (chunk)"))) return rc;
+        pk.final_chunk = (k == chunks - 1);
+        xchg_pack<<<xblocks, XCHG_THREADS, 0, side>>>(pk);
+        CK(cudaGetLastError());
+        c->launches += 2;
+        if ((rc = dbg_sync(c, "compact + partition (chunk)"))) return rc;
+    }
+    if (overlap) {  // the main stream continues after the last chunk has been delivered
+        CK(cudaEventRecord(c->ev_gathered, side));
+        CK(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
+    }
+    c->x_filter_timed = n != 0;
+    mark(c, "filter, partition and delivery");
     return CHRONOS_OK;
 }
 
@@ -1437,9 +1507,7 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
     for (uint32_t d = 0; d < world; d++) entry_counts_host[d] = slot_counts_host[d] = 0;
     if (!n) return CHRONOS_OK;
     int rc;
-    const uint8_t *d_recs = nullptr;
     CK(cudaEventRecord(c->ev_start, c->stream));
-    if ((rc = stage1_filter(c, records, n, &d_recs))) return rc;
     XchgPackParams pk;
     memset(&pk, 0, sizeof(pk));
     pk.world = world;
@@ -1448,7 +1516,7 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
     pk.send_hdr = send_hdr;
     pk.cap_entries = cap_entries;
     pk.cap_slots = cap_slots;
-    if ((rc = stage1_partition(c, d_recs, n, base_arrival_index, pk))) return rc;
+    if ((rc = stage1(c, records, n, base_arrival_index, pk, 1))) return rc;
     uint32_t hc[2 * XCHG_MAX_WORLD];
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     CK(cudaMemcpyAsync(hc, c->x_totals.p, sizeof(hc), cudaMemcpyDeviceToHost, c->stream));
@@ -1487,7 +1555,7 @@ int chronos_exchange_create(chronos_ctx *c, uint32_t world, uint32_t rank, uint6
     c->x_L = xchg_layout(world, rank, (uint32_t)cap_entries_per_peer, (uint32_t)cap_slots_per_peer);
     int rc;
     if ((rc = ensure(c, c->x_window, 2 * c->x_L.half_bytes))) return rc;
-    if ((rc = ensure(c, c->x_totals, 256))) return rc;
+    if ((rc = ensure(c, c->x_totals, 512))) return rc;
     CK(cudaMemsetAsync(c->x_window.p, 0, 2 * c->x_L.half_bytes, c->stream));
     CK(cudaStreamSynchronize(c->stream));  // peers may write as soon as they hold the address
     if (!c->ev_x0) CK(cudaEventCreate(&c->ev_x0));
@@ -1547,9 +1615,7 @@ int chronos_filter_exchange(chronos_ctx *c, const void *records, uint64_t n, uin
     if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
                                       (unsigned long long)n, (unsigned long long)c->max_batch);
     int rc;
-    const uint8_t *d_recs = nullptr;
     CK(cudaEventRecord(c->ev_x0, c->stream));
-    if ((rc = stage1_filter(c, records, n, &d_recs))) return rc;
     XchgPackParams pk;
     memset(&pk, 0, sizeof(pk));
     pk.world = c->x_L.world;
@@ -1557,11 +1623,11 @@ int chronos_filter_exchange(chronos_ctx *c, const void *records, uint64_t n, uin
     pk.L = c->x_L;
     pk.epoch = c->x_epoch + 1;
     for (uint32_t d = 0; d < c->x_L.world; d++) pk.peer[d] = c->x_peer[d];
-    if ((rc = stage1_partition(c, d_recs, n, base_arrival_index, pk))) return rc;
+    const char *ce = getenv("CHRONOS_XCHG_CHUNKS");  // experiments and tests: force the number of pieces
+    if ((rc = stage1(c, records, n, base_arrival_index, pk, ce ? atoi(ce) : 0))) return rc;
     c->x_epoch++;
     c->x_sent = true;
     c->x_launches = c->launches;
-    c->x_filter_timed = n != 0;
     return CHRONOS_OK;
 }
 

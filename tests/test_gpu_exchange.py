@@ -47,13 +47,18 @@ def _merge(results):
     return merged
 
 
-@pytest.mark.parametrize("world", [1, 2, 3, 8])
-def test_direct_exchange_matches_oracle_over_two_steps(world):
+@pytest.mark.parametrize("world,chunks", [(1, 0), (2, 0), (3, 0), (8, 0), (2, 4), (3, 3), (8, 2)])
+def test_direct_exchange_matches_oracle_over_two_steps(world, chunks, monkeypatch):
+    """chunks > 0 forces stage 1 to cut the slice into that many pieces (filter of piece k+1
+    overlapping the delivery of piece k), which real runs only do for multi-million-event slices."""
     import chronos_b200
     from chronos_b200 import tracegen
 
+    if chunks:
+        monkeypatch.setenv("CHRONOS_XCHG_CHUNKS", str(chunks))
+
     spec = dict(tracegen.WORKLOADS["skewed_zipf_chains"])
-    rows = tracegen.generate_host(spec, n=120_000)
+    rows = tracegen.generate_host(spec, n=120_000 if not chunks else 1_200_000)
     half = len(rows) // 2
     eng = coracle.COracle()
     ctxs = _make_ranks(world, half, cap_pair=half // 2)
