@@ -7,7 +7,7 @@ ROOT = os.path.dirname(HERE)
 SRC_DIR = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libchronos_b200.so")
 SOURCES = ["chronos.cu"]
-HEADERS = ["common.cuh", "filter.cuh", "sort.cuh", "window.cuh", "chain.cuh", "fnscan.cuh", "tracegen.cuh"]
+HEADERS = ["common.cuh", "filter.cuh", "sort.cuh", "window.cuh", "chain.cuh", "fnscan.cuh", "tracegen.cuh", "exchange.cuh"]
 
 
 def _stale():

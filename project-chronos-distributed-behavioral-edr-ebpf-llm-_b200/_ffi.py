@@ -108,7 +108,8 @@ def lib():
             raise ImportError(
                 f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
                 "chronos_b200 has no CPU fallback.")
-        L = ctypes.CDLL(LIB_PATH)
+        # CHRONOS_LIB: a differently tuned build of the same sources (tools/ab_build.sh), experiments only
+        L = ctypes.CDLL(os.environ.get("CHRONOS_LIB") or LIB_PATH)
         for name, (rt, at) in SIGNATURES.items():
             fn = getattr(L, name)
             fn.restype = rt

@@ -2,15 +2,17 @@
 // B200-native CHRONOS hot path. Kernels live in filter.cuh / sort.cuh / window.cuh.
 //
 // Per batch (one perf_buffer_poll() worth of events, chronos_sensor.py:160-162):
-//   filter_kernel      raw records -> arrival-ordered survivors (pid, src index, meta)
-//   radix passes       stable sort of [carried-in pending ++ survivors] by pid
-//   gather_records     every grouped event copied once into the arena
-//   window_forward     flush automaton -> window descriptors
+//   filter_kernel      raw records -> tile-local survivors (pid, src index, meta)
+//   compact_scan       dense, arrival-ordered survivor arrays
+//   sort_prepare + onesweep_pass x4
+//                      stable sort of [carried-in pending ++ survivors] by pid
+//   gather_records     every grouped event copied once into the arena (second stream)
+//   group_forward      flush automaton + chain labeller -> window descriptors
 //   window_reverse     unflushed tails -> next batch's pending list (process_memory)
-//   window_order       windows in trigger-arrival order (the order analyze_sequence
+//   emit_ordered       windows in trigger-arrival order (the order analyze_sequence
 //                      is called in, :143-147)
-// The only host synchronisation inside a submit is the read-back of the survivor count
-// and the pid OR/AND after the filter (sizes every later launch and buffer exactly).
+// A submit only enqueues: extents of everything after the filter live in a device-side plan,
+// grids are upper bounds; the first host wait is chronos_fetch.
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdint.h>
@@ -80,9 +82,9 @@ struct chronos_ctx {
     // batch staging for host-pointer submits
     DevBuf d_batch;
     // entry arrays (capacity in entries = ecap)
-    DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, pflag, entry_out, wsorted, windows, radix_table;
+    DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, pflag, entry_out, wsorted, windows, owner_table;
     DevBuf sp_key, sp_src, sp_meta, sp_ns, tile_count;  // filter's tile-local compaction
-    DevBuf surv_pid, surv_ns, ns32, slot_off;            // arrival-ordered pid copy; transport-form bookkeeping
+    DevBuf surv_pid, surv_ns, slot_off;                  // arrival-ordered pid copy; transport-form bookkeeping
     const uint4 *b_slots = nullptr;                      // transport-form batch (chronos_submit_survivors)
     DevBuf comm_memo;                                    // second-level comm memo: lock[N] | val[N] | key[N]
     // kill-chain labeller + persistent per-PID table (chain.cuh)
@@ -130,7 +132,6 @@ struct chronos_ctx {
     uint64_t b_n = 0, b_base = 0, b_S = 0, b_P = 0, b_M = 0, b_W = 0;
     const uint8_t *b_records = nullptr;  // device pointer of the batch records
     bool b_explicit_arrival = false;
-    const uint32_t *sorted_key = nullptr, *sorted_val = nullptr;
     uint64_t launches = 0;
     float t_total = 0.f, t_filter = 0.f, t_filter_kernel = 0.f;
     bool filter_timed = false;
@@ -650,7 +651,7 @@ int run_window_stage(chronos_ctx *c) {
         const uint32_t tiles_s = (uint32_t)((Smax + WIN_TILE - 1) / WIN_TILE);
         uint64_t *st = ptr<uint64_t>(c->status);
         uint32_t *tk = ptr<uint32_t>(c->tickets);
-        const uint32_t cap_blocks = (uint32_t)c->sm_count * 2;
+        const uint32_t cap_blocks = (uint32_t)c->sm_count * (WIN_ITEMS >= 16 ? 2 : 4);
         w.ticket = tk + 60;
         w.status = st;                              // 5 words per tile
         group_forward<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, c->stream>>>(w);
@@ -864,7 +865,7 @@ int chronos_destroy(chronos_ctx *c) {
     cudaSetDevice(c->device);
     if (c->stream) cudaStreamSynchronize(c->stream);
     DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->pflag,
-                     &c->entry_out, &c->wsorted, &c->comm_memo, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->ns32, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->radix_table, &c->surv_arrival, &c->arena[0],
+                     &c->entry_out, &c->wsorted, &c->comm_memo, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->owner_table, &c->surv_arrival, &c->arena[0],
                      &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
                      &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
                      &c->tickets, &c->scalars, &c->scan_status, &c->sweep_status, &c->pack, &c->pack_off};
@@ -1425,8 +1426,8 @@ static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base
     const uint64_t chunk_events = (uint64_t)tiles_per_chunk * TILE;
     const uint32_t T = (uint32_t)std::max<uint64_t>((std::min<uint64_t>(chunk_events, std::max<uint64_t>(n, 1)) + XCHG_TILE - 1) / XCHG_TILE, 1);
     const uint64_t table_len = (uint64_t)2 * W * T + 1;
-    if ((rc = ensure(c, c->radix_table, table_len * 4))) return rc;
-    uint32_t *table = ptr<uint32_t>(c->radix_table);
+    if ((rc = ensure(c, c->owner_table, table_len * 4))) return rc;
+    uint32_t *table = ptr<uint32_t>(c->owner_table);
     const unsigned xblocks = std::min<uint32_t>(T, (uint32_t)c->sm_count * 4);  // persistent CTAs, T is an upper bound
 
     pk.pid = ptr<uint32_t>(c->surv_pid);

@@ -21,7 +21,10 @@ constexpr int RADIX_BINS = 256;
 constexpr int RADIX_THREADS = 256;
 constexpr int RADIX_WARPS = RADIX_THREADS / 32;
 
-constexpr uint32_t RADIX_TILE_KEYS = 4096;  // keys per tile (multiple of RADIX_WARPS*32)
+#ifndef CHRONOS_RADIX_TILE
+#define CHRONOS_RADIX_TILE 4096
+#endif
+constexpr uint32_t RADIX_TILE_KEYS = CHRONOS_RADIX_TILE;  // keys per tile (multiple of RADIX_WARPS*32)
 constexpr int RADIX_MAX_PASSES = 4;
 
 // Pass 0 synthesises the sort values instead of reading them: the entry id in the low 27

@@ -39,7 +39,10 @@ namespace chronos {
 constexpr int VAL_ID_BITS = 27;
 constexpr uint32_t VAL_ID_MASK = (1u << VAL_ID_BITS) - 1u;
 constexpr int WIN_THREADS = 256;
-constexpr int WIN_ITEMS = 16;
+#ifndef CHRONOS_WIN_ITEMS
+#define CHRONOS_WIN_ITEMS 16
+#endif
+constexpr int WIN_ITEMS = CHRONOS_WIN_ITEMS;
 constexpr int WIN_TILE = WIN_THREADS * WIN_ITEMS;
 // per-position flags written by group_forward: bit0 flush, bit1 chain match, bits 31:2 =
 // inclusive count of chain-complete events up to this position
