@@ -198,7 +198,7 @@ def workload_name(world):
     if world == 1:
         return "configs[1]: 10M synthetic events, 4K PIDs, 256-byte path fields, 1xB200 (uniform_10m_4k)"
     return (f"configs[2]: {12.5 * world:g}M events ({'100M' if world == 8 else 'scaled'}), 1M PIDs, PID-hash sharded "
-            f"across {world}xB200 with all-to-all (sharded_100m_1m)")
+            f"across {world}xB200, survivors repartitioned all-to-all over NVLink (sharded_100m_1m)")
 
 
 # ------------------------------------------------------------------------------------------
@@ -331,7 +331,11 @@ def run_gpu_arm(args, rank, world, local_rank):
             "config": {"workload": workload_name(world), "events_per_gpu": n, "record_bytes": REC,
                        "survivors_rank0": S, "windows_rank0": W, "pending_rank0": last["n_pending"],
                        "l2": "input per step (2.88 GB+) exceeds the 126 MB L2; no flush needed",
-                       "timing": "torch CUDA events on the library stream around all K steps, max over ranks"},
+                       "timing": "torch CUDA events on the library stream around all K steps, max over ranks",
+                       "exchange": (None if world == 1 else
+                                    ("direct: stage 1 writes survivors into the owners' HBM over NVLink (CUDA IPC windows), "
+                                     "stage 2 waits for the peers' flags on the GPU" if getattr(runner, "mode", "") == "direct"
+                                     else "torch.distributed.all_to_all_single (NCCL) of the transport form"))},
             "roofline": {"bound": "hbm", "kernel": "filter_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": TRAFFIC_NCU if (world == 1 and n == 10_000_000) else None, "peak_source": peak_src,
                          "kernel_ms": f_ms, "algorithmic_bytes_per_launch": alg_bytes,
