@@ -311,8 +311,11 @@ def run_gpu_arm(args, rank, world, local_rank):
         n_sample = int(min(n, 1_000_000 * cores))
         rows = dev.download(n_sample * REC).reshape(-1, REC)
         rate, secs, kind, what = cpu_reference_rate(rows, cores)
+        n_one = int(min(n_sample, 500_000))
+        rate1, secs1, _, _ = cpu_reference_rate(rows[:n_one], 1)
         cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
-               "sample": f"first {n_sample} events of the workload in {secs:.2f}s, partitioned by pid over {cores} processes; {what}"}
+               "sample": f"first {n_sample} events of the workload in {secs:.2f}s, partitioned by pid over {cores} processes; {what}",
+               "one_core": {"value": rate1, "unit": UNIT, "sample": f"first {n_one} events in {secs1:.2f}s, one process"}}
 
     streaming = None
     if rank == 0 and world == 1 and not args.no_stream:
@@ -337,13 +340,15 @@ def run_gpu_arm(args, rank, world, local_rank):
                                      "stage 2 waits for the peers' flags on the GPU" if getattr(runner, "mode", "") == "direct"
                                      else "torch.distributed.all_to_all_single (NCCL) of the transport form"))},
             "roofline": {"bound": "hbm", "kernel": "filter_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": TRAFFIC_NCU if (world == 1 and n == 10_000_000) else None, "peak_source": peak_src,
+                         "frac": achieved / peak, "frac_of_8TBs_nominal": achieved / 8000.0, "traffic": TRAFFIC_NCU if (world == 1 and n == 10_000_000) else None, "peak_source": peak_src,
                          "kernel_ms": f_ms, "algorithmic_bytes_per_launch": alg_bytes,
                          "pipeline": {"algorithmic_bytes_per_gpu": pipe_bytes, "ms_per_step": ms_per_step,
                                       "achieved": pipe_bytes / (ms_per_step / 1e3) / 1e9,
                                       "frac": pipe_bytes / (ms_per_step / 1e3) / 1e9 / peak,
                                       "frac_of_8TBs_nominal": pipe_bytes / (ms_per_step / 1e3) / 1e9 / 8000.0,
-                                      "library_event_ms": float(np.mean(step_ms))}},
+                                      "library_event_ms": float(np.mean(step_ms)),
+                                      "library_event_ms_median": float(np.median(step_ms)),
+                                      "library_event_ms_min": float(np.min(step_ms))}},
             "cpu_baseline": cpu,
             "e2e": e2e,
             "streaming": streaming,
