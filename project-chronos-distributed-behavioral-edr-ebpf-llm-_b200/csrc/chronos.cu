@@ -371,10 +371,9 @@ int launch_filter(chronos_ctx *c, const FilterParams &fp) {
 
 // exclusive scan in place (device array of n u32) on the context's stream
 // (n_dev != nullptr: the real count lives on the device, n is only its upper bound)
-int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_dev = nullptr, int own_ticket = -1,
-                cudaStream_t stream = nullptr) {
+int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_dev = nullptr, int own_ticket = -1) {
     if (n == 0) return CHRONOS_OK;
-    if (!stream) stream = c->stream;
+    cudaStream_t stream = c->stream;
     const uint32_t n_tiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
     int rc;
     const void *before = c->scan_status.p;
@@ -432,12 +431,11 @@ int filter_setup(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, FilterParams
     return CHRONOS_OK;
 }
 
-// Cross-tile prefix + dense, arrival-ordered survivor arrays for the filter tiles
-// [tile_begin, tile_end), one kernel on `stream`. base_ptr / total_out: see CompactScanParams.
-int launch_compact(chronos_ctx *c, const FilterParams &fp, uint32_t tile_begin, uint32_t tile_end, uint32_t *out_key,
-                   cudaStream_t stream, const uint32_t *base_ptr, uint32_t *total_out) {
+// Cross-tile prefix + dense, arrival-ordered survivor arrays, one kernel.
+int launch_compact(chronos_ctx *c, const FilterParams &fp, uint32_t *out_key) {
     int rc;
-    const uint32_t n_tiles = tile_end - tile_begin;
+    cudaStream_t stream = c->stream;
+    const uint32_t n_tiles = fp.tile_end;
     const uint32_t n_chunks = (n_tiles + CS_CHUNK - 1) / CS_CHUNK;
     const void *before = c->scan_status.p;
     if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_chunks * 8, 4096)))) return rc;
@@ -446,10 +444,7 @@ int launch_compact(chronos_ctx *c, const FilterParams &fp, uint32_t tile_begin, 
     if (c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
     CompactScanParams cp;
     cp.tile_count = fp.tile_count;
-    cp.tile_begin = tile_begin;
     cp.n_tiles = n_tiles;
-    cp.base_ptr = base_ptr;
-    cp.total_out = total_out;
     cp.tile = (uint32_t)filter_tile_size(c);
     cp.sp_key = fp.sp_key;
     cp.sp_src = fp.sp_src;
@@ -482,7 +477,7 @@ int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t
     CK(cudaEventRecord(c->ev_f1, c->stream));
     if ((rc = dbg_sync(c, "filter_kernel"))) return rc;
     c->filter_timed = true;
-    if ((rc = launch_compact(c, fp, 0, fp.tile_end, out_key, c->stream, nullptr, nullptr))) return rc;
+    if ((rc = launch_compact(c, fp, out_key))) return rc;
     if ((rc = dbg_sync(c, "filter + scan + compact"))) return rc;
     return CHRONOS_OK;
 }
@@ -1375,13 +1370,14 @@ void *chronos_stream(chronos_ctx *c) { return c ? (void *)c->stream : nullptr; }
 uint32_t chronos_owner_of(uint32_t pid, uint32_t world) { return world ? hash32(pid) % world : 0; }
 
 // Stage 1 of the sharded path: filter the slice, partition the survivors by owner rank and
-// deliver them (pk.direct: into the owners' windows; else into the caller's send buffers).
-// The slice can be cut into `chunks` tile ranges: while the filter works on chunk k+1 on the
-// main stream, chunk k is compacted, counted and packed on the second stream (off by default,
-// see below). The per-PID state of the context is not touched.
-//   device words in x_totals: [0,32) per-owner totals for the host, [32,64) per-owner bases of
-//   the step (direct mode), [64] survivors before the current chunk, [65] survivors of the chunk
-static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base, XchgPackParams &pk, int chunks) {
+// deliver them (pk.direct: into the owners' windows; else into the caller's send buffers):
+// filter -> compact_scan -> xchg_hist -> scan -> xchg_pack, all on the main stream. The
+// per-PID state of the context is not touched.
+// (Cutting the slice into pieces so that the delivery of piece k overlaps the filter of piece
+//  k+1 was built and measured on 2xB200, 12.5 M events per rank: stage 1 got SLOWER, 0.80 ->
+//  1.15 ms with four pieces -- the filter loses its ~19 single-warp CTAs per SM to the pack
+//  kernel -- so it was removed again.)
+static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base, XchgPackParams &pk) {
     int rc;
     const uint8_t *d_recs = nullptr;
     if (n == 0) {
@@ -1403,92 +1399,44 @@ static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base
     if ((rc = ensure(c, c->surv_pid, (n + 1) * 4))) return rc;
     if ((rc = ensure(c, c->surv_ns, n + 1))) return rc;
     if ((rc = ensure(c, c->x_totals, 512))) return rc;
-    uint32_t *xs = ptr<uint32_t>(c->x_totals);
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    CK(cudaMemsetAsync(xs, 0, 512, c->stream));
     init_scalars_kernel<<<1, 256, 0, c->stream>>>(ds, ptr<uint32_t>(c->tickets));
     set_u32_kernel<<<1, 1, 0, c->stream>>>(&ds->xchg_err, 0u);
     c->launches += 2;
     mark(c, "stage 1 start");
+    if (n && (rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA)))) return rc;
+    c->x_filter_timed = n != 0;
+    mark(c, "filter + compact");
 
     const uint32_t W = pk.world;
-    const int TILE = filter_tile_size(c);
-    const uint32_t tiles_all = (uint32_t)((n + TILE - 1) / TILE);
-    // chunks <= 0: the default, ONE piece. Measured on 2xB200 with 12.5 M events per rank: cutting
-    // the slice in 2 / 4 pieces so that the delivery of piece k overlaps the filter of piece k+1
-    // makes stage 1 slower, 0.80 -> 1.25 / 1.15 ms: the filter needs its ~19 single-warp CTAs per
-    // SM and loses them to the pack kernel (its span grows from 0.60 to 1.07 ms). The pieces stay
-    // available (CHRONOS_XCHG_CHUNKS, at most 4: filter tickets 0..3) and tested.
-    if (chunks <= 0) chunks = 1;
-    if (chunks > 4) chunks = 4;
-    if (chunks < 1 || tiles_all < 1024u * (uint32_t)chunks) chunks = 1;
-    const uint32_t tiles_per_chunk = ((tiles_all + chunks - 1) / chunks + 1023u) & ~1023u;
-    const uint64_t chunk_events = (uint64_t)tiles_per_chunk * TILE;
-    const uint32_t T = (uint32_t)std::max<uint64_t>((std::min<uint64_t>(chunk_events, std::max<uint64_t>(n, 1)) + XCHG_TILE - 1) / XCHG_TILE, 1);
+    const uint32_t T = (uint32_t)std::max<uint64_t>((n + XCHG_TILE - 1) / XCHG_TILE, 1);  // upper bound of the tile count
     const uint64_t table_len = (uint64_t)2 * W * T + 1;
     if ((rc = ensure(c, c->owner_table, table_len * 4))) return rc;
     uint32_t *table = ptr<uint32_t>(c->owner_table);
-    const unsigned xblocks = std::min<uint32_t>(T, (uint32_t)c->sm_count * 4);  // persistent CTAs, T is an upper bound
-
+    const unsigned xblocks = std::min<uint32_t>(T, (uint32_t)c->sm_count * 4);  // persistent CTAs
+    xchg_hist<<<xblocks, XCHG_THREADS, 0, c->stream>>>(ptr<uint32_t>(c->surv_pid), ptr<uint8_t>(c->surv_ns), &ds->surv_count, W, T,
+                                                     table);
+    if ((rc = dbg_sync(c, "xchg_hist"))) return rc;
+    if ((rc = launch_scan(c, table, table_len))) return rc;
+    if ((rc = dbg_sync(c, "owner table scan"))) return rc;
+    mark(c, "owner histogram + scan");
     pk.pid = ptr<uint32_t>(c->surv_pid);
     pk.surv_src = ptr<uint32_t>(c->surv_src);
     pk.surv_meta = ptr<uint8_t>(c->surv_meta);
     pk.surv_ns = ptr<uint8_t>(c->surv_ns);
-    pk.n_ptr = xs + 65;
-    pk.start_ptr = xs + 64;
-    pk.owner_base = pk.direct ? xs + 32 : nullptr;
+    pk.n_ptr = &ds->surv_count;
     pk.batch = d_recs;
     pk.base_arrival = base;
     pk.table = table;
     pk.T = T;
-    pk.totals = xs;
+    pk.totals = ptr<uint32_t>(c->x_totals);
     pk.err = &ds->xchg_err;
     pk.done = ptr<uint32_t>(c->tickets) + 58;
-
-    FilterParams fp;
-    memset(&fp, 0, sizeof(fp));
-    if (n && (rc = filter_setup(c, d_recs, n, fp))) return rc;
-    const bool overlap = chunks > 1;
-    cudaStream_t side = overlap ? c->stream2 : c->stream;
-    CK(cudaEventRecord(c->ev_f0, c->stream));
-    for (int k = 0; k < chunks; k++) {
-        const uint32_t tb = std::min<uint32_t>(tiles_all, (uint32_t)k * tiles_per_chunk);
-        const uint32_t te = std::min<uint32_t>(tiles_all, tb + tiles_per_chunk);
-        if (te > tb) {
-            fp.tile_begin = tb;
-            fp.tile_end = te;
-            fp.ticket = ptr<uint32_t>(c->tickets) + k;
-            if ((rc = launch_filter(c, fp))) return rc;
-            if ((rc = dbg_sync(c, "filter_kernel (chunk)"))) return rc;
-        }
-        if (k == chunks - 1) CK(cudaEventRecord(c->ev_f1, c->stream));
-        if (overlap) {
-            CK(cudaEventRecord(c->ev_sorted, c->stream));
-            CK(cudaStreamWaitEvent(side, c->ev_sorted, 0));
-        }
-        if (te > tb) {
-            if ((rc = launch_compact(c, fp, tb, te, ptr<uint32_t>(c->keyA), side, xs + 64, xs + 65))) return rc;
-        } else {
-            set_u32_kernel<<<1, 1, 0, side>>>(xs + 65, 0u);  // nothing in this chunk
-            c->launches++;
-        }
-        if ((rc = dbg_sync(c, "compact_scan (chunk)"))) return rc;
-        xchg_hist<<<xblocks, XCHG_THREADS, 0, side>>>(ptr<uint32_t>(c->surv_pid), ptr<uint8_t>(c->surv_ns), xs + 65, xs + 64, W, T, table);
-        if ((rc = dbg_sync(c, "xchg_hist (chunk)"))) return rc;
-        if ((rc = launch_scan(c, table, table_len, nullptr, -1, side))) return rc;
-        if ((rc = dbg_sync(c, "owner table scan (chunk)"))) return rc;
-        pk.final_chunk = (k == chunks - 1);
-        xchg_pack<<<xblocks, XCHG_THREADS, 0, side>>>(pk);
-        CK(cudaGetLastError());
-        c->launches += 2;
-        if ((rc = dbg_sync(c, "compact + partition (chunk)"))) return rc;
-    }
-    if (overlap) {  // the main stream continues after the last chunk has been delivered
-        CK(cudaEventRecord(c->ev_gathered, side));
-        CK(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
-    }
-    c->x_filter_timed = n != 0;
-    mark(c, "filter, partition and delivery");
+    xchg_pack<<<xblocks, XCHG_THREADS, 0, c->stream>>>(pk);
+    CK(cudaGetLastError());
+    c->launches += 2;
+    if ((rc = dbg_sync(c, "xchg_pack"))) return rc;
+    mark(c, "pack into owners' windows");
     return CHRONOS_OK;
 }
 
@@ -1517,7 +1465,7 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
     pk.send_hdr = send_hdr;
     pk.cap_entries = cap_entries;
     pk.cap_slots = cap_slots;
-    if ((rc = stage1(c, records, n, base_arrival_index, pk, 1))) return rc;
+    if ((rc = stage1(c, records, n, base_arrival_index, pk))) return rc;
     uint32_t hc[2 * XCHG_MAX_WORLD];
     DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     CK(cudaMemcpyAsync(hc, c->x_totals.p, sizeof(hc), cudaMemcpyDeviceToHost, c->stream));
@@ -1624,8 +1572,7 @@ int chronos_filter_exchange(chronos_ctx *c, const void *records, uint64_t n, uin
     pk.L = c->x_L;
     pk.epoch = c->x_epoch + 1;
     for (uint32_t d = 0; d < c->x_L.world; d++) pk.peer[d] = c->x_peer[d];
-    const char *ce = getenv("CHRONOS_XCHG_CHUNKS");  // experiments and tests: force the number of pieces
-    if ((rc = stage1(c, records, n, base_arrival_index, pk, ce ? atoi(ce) : 0))) return rc;
+    if ((rc = stage1(c, records, n, base_arrival_index, pk))) return rc;
     c->x_epoch++;
     c->x_sent = true;
     c->x_launches = c->launches;

@@ -76,10 +76,9 @@ __device__ __forceinline__ uint64_t global_timer_ns() {
 // zeros (the scan runs over the whole table).
 // ---------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(XCHG_THREADS) xchg_hist(const uint32_t *pid, const uint8_t *ns, const uint32_t *n_ptr,
-                                                         const uint32_t *start_ptr, uint32_t world, uint32_t T, uint32_t *table) {
+                                                         uint32_t world, uint32_t T, uint32_t *table) {
     __shared__ uint32_t he[XCHG_MAX_WORLD], hs[XCHG_MAX_WORLD];
     const uint32_t S = *n_ptr;
-    if (start_ptr) { pid += *start_ptr; ns += *start_ptr; }  // this launch: survivors [start, start + S)
     const uint32_t used = (S + XCHG_TILE - 1) / XCHG_TILE;
     if (blockIdx.x == 0 && threadIdx.x == 0) table[(size_t)2 * world * T] = 0;
     // columns of tiles that hold no survivor: zeros
@@ -107,12 +106,7 @@ struct XchgPackParams {
     // survivors of this rank, arrival order
     const uint32_t *pid, *surv_src;
     const uint8_t *surv_meta, *surv_ns;
-    const uint32_t *n_ptr;        // survivors handled by this launch ...
-    uint32_t *start_ptr;          // ... starting at this survivor (device scalars; nullptr: 0). The
-                                  // last block advances *start_ptr by *n_ptr for the next chunk.
-    uint32_t *owner_base;         // entries[16] | slots[16] already delivered to every owner by earlier
-                                  // chunks of this step (direct mode; zeroed per step)
-    bool final_chunk;             // publish counts and raise the flag after this launch
+    const uint32_t *n_ptr;        // survivor count (device scalar)
     const uint8_t *batch;         // the slice's records (device)
     uint64_t base_arrival;
     const uint32_t *table;        // scanned
@@ -140,27 +134,20 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
     __shared__ uint32_t rs_e[XCHG_MAX_WORLD + 1], rs_s[XCHG_MAX_WORLD + 1];  // row starts = per-owner stream starts
     __shared__ uint32_t wb_e[XCHG_WARPS][XCHG_MAX_WORLD], wb_s[XCHG_WARPS][XCHG_MAX_WORLD];
     __shared__ uint32_t sh_ns[XCHG_WARPS][32];
-    __shared__ uint32_t ob_e[XCHG_MAX_WORLD], ob_s[XCHG_MAX_WORLD];  // delivered by earlier chunks
     __shared__ uint32_t s_skip, s_last;
     const uint32_t T = g.T, W = g.world, S = *g.n_ptr;
-    const uint32_t start = g.start_ptr ? *g.start_ptr : 0u;
     const uint32_t used = (S + XCHG_TILE - 1) / XCHG_TILE;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid <= (int)W) {
         rs_e[tid] = g.table[(size_t)tid * T];
         rs_s[tid] = g.table[(size_t)(W + tid) * T];
     }
-    if (tid < XCHG_MAX_WORLD) {
-        ob_e[tid] = g.owner_base ? g.owner_base[tid] : 0u;
-        ob_s[tid] = g.owner_base ? g.owner_base[XCHG_MAX_WORLD + tid] : 0u;
-    }
     if (tid == 0) s_skip = 0;
     __syncthreads();
-    // owners whose stream does not fit are skipped as a whole (reported, never truncated);
-    // a chunk that follows an overflowing one overflows as well (the bases keep growing)
+    // owners whose stream does not fit are skipped as a whole (reported, never truncated)
     if (tid < (int)W) {
         const uint32_t te = rs_e[tid + 1] - rs_e[tid], ts = rs_s[tid + 1] - rs_s[tid];
-        const bool over = g.direct ? ((uint64_t)ob_e[tid] + te > g.L.cap_e || (uint64_t)ob_s[tid] + ts > g.L.cap_s)
+        const bool over = g.direct ? (te > g.L.cap_e || ts > g.L.cap_s)
                                    : ((uint64_t)rs_e[W] > g.cap_entries || (uint64_t)(rs_s[W] - rs_s[0]) > g.cap_slots);
         if (over) atomicOr(&s_skip, 1u << tid);
     }
@@ -185,10 +172,10 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
             const uint32_t i = w_lo + q * 32 + lane;
             ow[q] = 0xFFu; nsv[q] = 0; recv[q] = 0; metav[q] = 0;
             if (i < w_hi) {
-                ow[q] = hash32(g.pid[start + i]) % W;
-                nsv[q] = g.surv_ns[start + i];
-                recv[q] = g.surv_src[start + i];
-                metav[q] = g.surv_meta[start + i];
+                ow[q] = hash32(g.pid[i]) % W;
+                nsv[q] = g.surv_ns[i];
+                recv[q] = g.surv_src[i];
+                metav[q] = g.surv_meta[i];
             }
         }
 #pragma unroll
@@ -203,7 +190,7 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
         // 2) owner d: running base over the warps, seeded with this tile's offset inside d's stream
         if (tid < (int)W) {
             uint32_t re = g.table[(size_t)tid * T + tile], rsl = g.table[(size_t)(W + tid) * T + tile];
-            if (g.direct) { re = re - rs_e[tid] + ob_e[tid]; rsl = rsl - rs_s[tid] + ob_s[tid]; }  // position in the (source, owner) region
+            if (g.direct) { re -= rs_e[tid]; rsl -= rs_s[tid]; }   // relative to the (source, owner) region
             else rsl -= rs_s[0];                                   // slot rows come after the entry rows in the scan
 #pragma unroll
             for (int w = 0; w < (int)XCHG_WARPS; w++) {
@@ -309,26 +296,16 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
     __syncthreads();
     if (!s_last) return;
     __threadfence_system();
-    if (tid == 0) {
-        *g.done = 0;  // ready for the next chunk's launch
-        if (g.start_ptr) *g.start_ptr = start + S;
-    }
     if (tid < (int)W) {
         const uint32_t te = rs_e[tid + 1] - rs_e[tid], ts = rs_s[tid + 1] - rs_s[tid];
         const bool over = (skip >> tid) & 1u;
-        const uint32_t sum_e = ob_e[tid] + te, sum_s = ob_s[tid] + ts;  // delivered so far in this step
-        if (g.owner_base) {
-            g.owner_base[tid] = sum_e;
-            g.owner_base[XCHG_MAX_WORLD + tid] = sum_s;
-        }
-        g.totals[tid] = sum_e;
-        g.totals[XCHG_MAX_WORLD + tid] = sum_s;
+        g.totals[tid] = te;
+        g.totals[XCHG_MAX_WORLD + tid] = ts;
         if (over) atomicOr(g.err, XERR_OVERFLOW);
-        const bool any_over = over;  // (an owner that overflowed in an earlier chunk overflows here too: the bases kept growing)
-        if (g.direct && g.final_chunk) {
+        if (g.direct) {
             uint32_t *ctrl = reinterpret_cast<uint32_t *>(g.peer[tid] + (size_t)half * g.L.half_bytes);
-            ctrl[g.L.rank] = any_over ? XCHG_OVERFLOW : sum_e;
-            ctrl[XCHG_MAX_WORLD + g.L.rank] = any_over ? 0u : sum_s;
+            ctrl[g.L.rank] = over ? XCHG_OVERFLOW : te;
+            ctrl[XCHG_MAX_WORLD + g.L.rank] = over ? 0u : ts;
             __threadfence_system();
             st_release_sys_u32(ctrl + 2 * XCHG_MAX_WORLD + g.L.rank, g.epoch);
         }

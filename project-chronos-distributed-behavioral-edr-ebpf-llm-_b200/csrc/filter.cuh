@@ -576,10 +576,7 @@ static_assert(CS_CHUNK == 1024, "the position search below is unrolled for 2^10 
 
 struct CompactScanParams {
     const uint32_t *tile_count;  // survivors per filter tile (filter_kernel), left untouched
-    uint32_t tile_begin;         // this launch compacts tiles [tile_begin, tile_begin + n_tiles) (multiple of 4)
     uint32_t n_tiles;
-    const uint32_t *base_ptr;    // device scalar: survivors of the tiles before tile_begin (nullptr: 0)
-    uint32_t *total_out;         // device scalar: survivors of this launch's tiles (optional)
     uint32_t tile;               // records (= slots) per filter tile
     const uint32_t *sp_key, *sp_src;
     const uint8_t *sp_meta, *sp_ns;
@@ -602,8 +599,8 @@ __global__ void __launch_bounds__(CS_THREADS) compact_scan(const CompactScanPara
         __syncthreads();
         const uint32_t chunk = s_chunk;
         if (chunk >= n_chunks) break;
-        const uint32_t t0 = chunk * CS_CHUNK + tid * CS_ITEMS;  // relative to tile_begin
-        const uint32_t *tc = p.tile_count + p.tile_begin;
+        const uint32_t t0 = chunk * CS_CHUNK + tid * CS_ITEMS;
+        const uint32_t *tc = p.tile_count;
         uint32_t v[CS_ITEMS];
         if (t0 + CS_ITEMS <= p.n_tiles) {
             const uint4 a = *reinterpret_cast<const uint4 *>(tc + t0);
@@ -637,14 +634,11 @@ __global__ void __launch_bounds__(CS_THREADS) compact_scan(const CompactScanPara
         if (tid == CS_THREADS - 1) off[CS_CHUNK] = total;
         if (warp == 0) {
             const uint32_t b = lookback_count_epoch(p.status, chunk, total, lane, p.epoch);
-            if (lane == 0) {
-                s_base = b + (p.base_ptr ? *p.base_ptr : 0u);
-                if (p.total_out && chunk == n_chunks - 1) *p.total_out = b + total;
-            }
+            if (lane == 0) s_base = b;
         }
         __syncthreads();
         const uint32_t base = s_base;
-        const size_t slot0 = ((size_t)p.tile_begin + (size_t)chunk * CS_CHUNK) * p.tile;
+        const size_t slot0 = (size_t)chunk * CS_CHUNK * p.tile;
         // four independent positions per thread and step: the search and the four loads of one
         // position are a dependent chain, so the chains are interleaved
         constexpr int CS_ILP = 4;

@@ -3,6 +3,11 @@ import sys
 
 import pytest
 
+# Before CUDA starts in this process: the exchange tests emulate several ranks with several
+# contexts on ONE GPU, and a rank's stage 2 spins on the GPU for its peers. Streams that share
+# a hardware queue (8 by default) could put a peer's work behind such a spin.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
