@@ -495,14 +495,21 @@ int ensure_pid_table(chronos_ctx *c, uint64_t M) {
     DevBuf fresh;
     int rc;
     if ((rc = ensure(c, fresh, cap * 8))) return rc;
-    CK(cudaMemsetAsync(fresh.p, 0, cap * 8, c->stream));
-    if (c->pt_cap && c->n_pids_seen) {
-        pt_rehash_kernel<<<(unsigned)std::min<uint64_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
-            ptr<uint64_t>(c->pid_tab), c->pt_cap, static_cast<uint64_t *>(fresh.p), (uint32_t)cap - 1, c->pt_epoch);
-        CK(cudaGetLastError());
-        c->launches++;
+    auto grow = [&]() -> int {
+        CK(cudaMemsetAsync(fresh.p, 0, cap * 8, c->stream));
+        if (c->pt_cap && c->n_pids_seen) {
+            pt_rehash_kernel<<<(unsigned)std::min<uint64_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
+                ptr<uint64_t>(c->pid_tab), c->pt_cap, static_cast<uint64_t *>(fresh.p), (uint32_t)cap - 1, c->pt_epoch);
+            CK(cudaGetLastError());
+            c->launches++;
+        }
+        CK(cudaStreamSynchronize(c->stream));
+        return CHRONOS_OK;
+    };
+    if ((rc = grow())) {
+        release(fresh);  // the old table stays in place
+        return rc;
     }
-    CK(cudaStreamSynchronize(c->stream));
     release(c->pid_tab);
     c->pid_tab = fresh;
     c->pt_cap = (uint32_t)cap;

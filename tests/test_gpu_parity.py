@@ -278,3 +278,24 @@ def test_async_download_equals_blocking_copies(ctx):
         ctx.download_begin(bufs[0].value, 16)                # too small: reported, nothing written
     for p in bufs:
         L.chronos_host_free_pinned(p)
+
+
+def test_one_pid_across_many_tiles_and_extreme_pids(ctx):
+    """A single PID whose list spans hundreds of scan tiles (look-back carries one open group
+    across all of them), runs of consecutive triggers, and the pid values 0 and 2^32-1."""
+    rng = np.random.default_rng(11)
+    comms = [b"sh", b"bash", b"sshd", b"cat", b"cron", b"vim"]
+    paths = [b"/tmp/a", b"/tmp/nc", b"/home/u/x.txt", b"/var/log/cat.log", b"", b"/etc/passwd", b"/opt/tool"]
+    n = 300_000
+    one = b"".join(R(77, comms[int(rng.integers(len(comms)))], paths[int(rng.integers(len(paths)))],
+                     b"EXEC" if rng.integers(16) == 0 else b"OPEN") for _ in range(n))
+    ctx.reset()
+    eng, tr = coracle.COracle(), Trace()
+    compare_batch(ctx, eng, tr, one, 0)
+    # long stretch without any trigger, then all triggers: the list only grows, then flushes pairwise
+    quiet = b"".join(R(77, b"vim", b"/home/u/notes", b"OPEN") for _ in range(50_000))
+    loud = b"".join(R(77, b"bash", b"/tmp/x", b"OPEN") for _ in range(50_001))
+    compare_batch(ctx, eng, tr, quiet, n)
+    compare_batch(ctx, eng, tr, loud, n + 50_000)
+    ext = b"".join(R(pid, comms[i % 6], paths[i % 7], b"OPEN") for i in range(4000) for pid in (0, 0xFFFFFFFF, 1, 0x80000000))
+    compare_batch(ctx, eng, tr, ext, n + 100_001)
