@@ -1,0 +1,88 @@
+"""Worker of test_gpu_multiprocess.py: one process per GPU (torchrun), real CUDA IPC windows.
+Every rank builds the same trace, filters its contiguous slice, survivors travel to their
+owners over NVLink, rank 0 merges all windows and compares them with the C oracle."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from chronos_b200 import sharded, tracegen  # noqa: E402
+
+STEPS = [(0, 250_000), (250_000, 400_000)]
+
+
+def run_rank(rank, world, lr, rows):
+    """Both steps on this rank; returns per step (windows, survivors, n_pending) and the mode."""
+    dev = tracegen.DeviceBuffer(lr, 250_000 * 288)
+    runner = sharded.ShardedRunner(dev.ptr, 0, 0, lr, rank, world, cap=200_000, mode="direct",
+                                   cap_entries_per_peer=100_000)
+    out = []
+    for lo, hi in STEPS:
+        n = hi - lo
+        a, b = lo + rank * n // world, lo + (rank + 1) * n // world
+        mine = np.ascontiguousarray(rows[a:b])
+        dev.upload(mine)
+        runner.ctx.filter_exchange_ptr(dev.ptr, len(mine), a)
+        runner.ctx.submit_exchanged()
+        res = runner.ctx.fetch(records=True)
+        wins, o = [], 0
+        for w in res.windows:
+            ln = int(w["len"])
+            wins.append((int(w["trigger_idx"]), int(w["pid"]), int(w["flags"]) & 1,
+                         res.window_records[o:o + ln].tobytes()))
+            o += ln
+        out.append((wins, res.survivors.tolist(), res.counts["n_pending"]))
+    return out, runner
+
+
+def check(rows, per_step):
+    from helpers import canonical
+    from oracle import coracle
+
+    eng = coracle.COracle()
+    ok = True
+    for (lo, hi), gathered in zip(STEPS, per_step):
+        ref = eng.feed(rows[lo:hi], lo)
+        merged = sorted((w for g in gathered for w in g[0]), key=lambda t: t[0])
+        surv = np.sort(np.concatenate([np.asarray(g[1], dtype=np.int64) for g in gathered]))
+        ok &= [m[0] for m in merged] == ref["win_trigger"].tolist()
+        ok &= [m[1] for m in merged] == ref["win_pid"].tolist()
+        ok &= [m[2] for m in merged] == (ref["win_flags"] & 1).tolist()
+        ok &= bool(np.array_equal(surv, np.asarray(ref["survivors"], dtype=np.int64)))
+        got = np.frombuffer(b"".join(m[3] for m in merged), dtype=np.uint8).reshape(-1, 288)
+        ok &= bool(np.array_equal(canonical(got), canonical(rows[ref["members"].astype(np.int64)])))
+        ok &= sum(g[2] for g in gathered) == len(eng.state()[2])
+    return ok
+
+
+def main():
+    rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", lr))
+    rows = tracegen.generate_host(dict(tracegen.WORKLOADS["skewed_zipf_chains"]), n=400_000)
+    mine, runner = run_rank(rank, world, lr, rows)
+    per_step = []
+    for s in range(len(STEPS)):
+        gathered = [None] * world if rank == 0 else None
+        dist.gather_object(mine[s], gathered, dst=0)
+        per_step.append(gathered)
+    ok = True
+    if rank == 0:
+        ok = check(rows, per_step)
+        print("MP_EXCHANGE", "OK" if ok else "MISMATCH", "mode", runner.mode, "windows",
+              sum(len(g[0]) for g in per_step[-1]), flush=True)
+    dist.barrier()
+    runner.ctx.close()
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+
+
+if __name__ == "__main__":
+    main()
