@@ -33,8 +33,10 @@ __host__ __device__ __forceinline__ uint32_t pt_home(uint32_t pid, uint32_t mask
 // total to the table's count ONCE per warp: one atomic per new PID on a single address was the
 // largest cost of group_forward on the 1 M-PID workload). Slots written under an older epoch
 // count as empty: chronos_reset only bumps the epoch.
+// *dfa_out (optional) receives the chain state stored for the pid (0 for a new one), so that
+// the caller does not have to read the slot again.
 __device__ __forceinline__ uint32_t pt_find_or_insert(uint64_t *tab, uint32_t mask, uint32_t epoch, uint32_t pid,
-                                                      uint32_t &inserted) {
+                                                      uint32_t &inserted, uint32_t *dfa_out = nullptr) {
     uint32_t i = pt_home(pid, mask);
     while (true) {
         uint64_t v = ld_relaxed_u64(tab + i);
@@ -43,11 +45,15 @@ __device__ __forceinline__ uint32_t pt_find_or_insert(uint64_t *tab, uint32_t ma
                                            (unsigned long long)pt_make(epoch, 0, pid));
             if (old == v) {
                 inserted++;
+                if (dfa_out) *dfa_out = 0;
                 return i;
             }
             v = old;  // somebody else took the slot: look at what is there now
         }
-        if ((uint32_t)v == pid) return i;
+        if ((uint32_t)v == pid) {
+            if (dfa_out) *dfa_out = (uint32_t)(v >> 32) & 3u;
+            return i;
+        }
         i = (i + 1) & mask;
     }
 }

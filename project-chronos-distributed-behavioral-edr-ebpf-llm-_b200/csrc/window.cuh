@@ -140,6 +140,7 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
         uint32_t prevk = (p0 > 0 && p0 - 1 < M) ? skey[p0 - 1] : 0;
         FnG f = FnG::identity();
         uint32_t new_pids = 0;  // PIDs this thread inserted into the per-PID table
+        // pass 1: keys, values, group heads
 #pragma unroll
         for (int k = 0; k < WIN_ITEMS; k++) {
             const uint32_t pos = p0 + k;
@@ -147,11 +148,37 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
             if (pos < M) {
                 key[k] = skey[pos];
                 val[k] = sval[pos];
+                kind[k] = ((pos == 0) || key[k] != prevk) ? 1u : 0u;
+                prevk = key[k];
+            }
+        }
+        // pass 2: the stored chain state of every head. The home slots of all heads are read
+        // first (independent loads, in flight together); only a miss -- a new PID or a collision
+        // -- takes the probing path.
+        uint64_t home[WIN_ITEMS];
+#pragma unroll
+        for (int k = 0; k < WIN_ITEMS; k++) {
+            home[k] = 0;
+            if (kind[k] & 1u) home[k] = ld_relaxed_u64(p.pid_tab + pt_home(key[k], p.pid_mask));
+        }
+#pragma unroll
+        for (int k = 0; k < WIN_ITEMS; k++) {
+            if (kind[k] & 1u) {
+                uint32_t d0 = 0;
+                if (pt_live(home[k], p.pid_epoch) && (uint32_t)home[k] == key[k]) d0 = (uint32_t)(home[k] >> 32) & 3u;
+                else pt_find_or_insert(p.pid_tab, p.pid_mask, p.pid_epoch, key[k], new_pids, &d0);
+                kind[k] |= (uint8_t)(d0 << 1);
+            }
+        }
+        // pass 3: what the thread's items do to the two automata
+#pragma unroll
+        for (int k = 0; k < WIN_ITEMS; k++) {
+            const uint32_t pos = p0 + k;
+            if (pos < M) {
                 const uint32_t meta = val[k] >> VAL_ID_BITS;
                 const bool carried = (val[k] & VAL_ID_MASK) < P;
-                const bool head = (pos == 0) || key[k] != prevk;
+                const bool head = kind[k] & 1u;
                 const bool trig = (meta & META_TRIG) != 0;  // carried entries were stored without it
-                prevk = key[k];
                 FnG e;
                 if (head) e.w = Fn2{0x3u, {0u, 0u}, {pos, pos}};
                 else if (!trig) e.w = Fn2{0x3u, {0u, 0u}, {pos, NONE32}};
@@ -160,14 +187,10 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
                 // its "completed a chain" mark along for the window label
                 const uint32_t cm = (meta & META_CHAIN) ? 1u : 0u;
                 e.c = carried ? Fn3{0x24u, {cm, cm, cm}} : chain_event(meta);
-                uint32_t kd = head ? 1u : 0u;
                 if (head) {  // the PID's stored DFA state replaces whatever is carried over
-                    const uint32_t slot = pt_find_or_insert(p.pid_tab, p.pid_mask, p.pid_epoch, key[k], new_pids);
-                    const uint32_t d0 = (uint32_t)(ld_relaxed_u64(p.pid_tab + slot) >> 32) & 3u;
-                    kd |= d0 << 1;
+                    const uint32_t d0 = (kind[k] >> 1) & 3u;
                     e.c = Fn3::constant(Fn3::o(e.c, d0), Fn3::av(e.c, d0));
                 }
-                kind[k] = (uint8_t)kd;
                 f = FnG::compose(f, e);
             }
         }
