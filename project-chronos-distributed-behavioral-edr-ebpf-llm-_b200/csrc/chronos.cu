@@ -1439,7 +1439,12 @@ static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base
     pk.totals = ptr<uint32_t>(c->x_totals);
     pk.err = &ds->xchg_err;
     pk.done = ptr<uint32_t>(c->tickets) + 58;
-    xchg_pack<<<xblocks, XCHG_THREADS, 0, c->stream>>>(pk);
+    static bool pack_configured[16] = {false};
+    if (!pack_configured[c->device & 15]) {
+        CK(cudaFuncSetAttribute(xchg_pack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XCHG_PACK_SMEM));
+        pack_configured[c->device & 15] = true;
+    }
+    xchg_pack<<<xblocks, XCHG_THREADS, XCHG_PACK_SMEM, c->stream>>>(pk);
     CK(cudaGetLastError());
     c->launches += 2;
     if ((rc = dbg_sync(c, "xchg_pack"))) return rc;

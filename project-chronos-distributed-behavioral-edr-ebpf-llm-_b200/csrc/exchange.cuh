@@ -128,6 +128,9 @@ struct XchgPackParams {
 };
 
 constexpr uint32_t XCHG_SUB = XCHG_TILE / XCHG_WARPS;   // contiguous sub-range of a warp
+constexpr uint32_t XCHG_STAGE_PER_WARP = 32 * 18 + 32;   // uint4: slots of one step + its descriptors
+constexpr size_t XCHG_PACK_SMEM = (size_t)XCHG_WARPS * XCHG_STAGE_PER_WARP * 16;
+constexpr uint32_t NONE_AT = 0xffffffffu;
 constexpr int XCHG_STEPS = XCHG_SUB / 32;               // 32 survivors per step
 
 __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g) {
@@ -135,6 +138,7 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
     __shared__ uint32_t wb_e[XCHG_WARPS][XCHG_MAX_WORLD], wb_s[XCHG_WARPS][XCHG_MAX_WORLD];
     __shared__ uint32_t sh_ns[XCHG_WARPS][32];
     __shared__ uint32_t s_skip, s_last;
+    extern __shared__ uint4 stage[];  // XCHG_PACK_SMEM bytes
     const uint32_t T = g.T, W = g.world, S = *g.n_ptr;
     const uint32_t used = (S + XCHG_TILE - 1) / XCHG_TILE;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -224,23 +228,52 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
             }
             __syncwarp();
             const bool live = valid && !((skip >> (o & 31u)) & 1u);
-            uint4 *dst = nullptr;  // first slot of this entry at its destination
-            const uint4 *src = nullptr;
-            if (live) {
-                const uint32_t e_idx = be + rank_e, s_idx = bs + pre_s;
-                const uint64_t hdr = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)metav[q] << 48) | ((uint64_t)ns << 56);
-                src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
-                if (g.direct) {
-                    uint8_t *hb = g.peer[o] + (size_t)half * g.L.half_bytes;
-                    const size_t re = (size_t)g.L.rank * g.L.cap_e + e_idx;
-                    reinterpret_cast<uint4 *>(hb + g.L.off_desc)[re] = make_uint4((uint32_t)hdr, (uint32_t)(hdr >> 32), s_idx, 0u);
-                    dst = reinterpret_cast<uint4 *>(hb + g.L.off_slots) + (size_t)g.L.rank * g.L.cap_s + s_idx;
-                } else {
-                    g.send_hdr[e_idx] = hdr;
-                    dst = g.send_slots + s_idx;
+            // ---- owner-major staging in shared memory ----------------------------------------
+            // Written entry by entry, a survivor is an 80-byte fragment at some place in its
+            // owner's window; NVLink moves such scattered fragments at about 375 GB/s, runs of
+            // 128 bytes and more at 660 GB/s (tools/nvlink_probe.cu). All entries a warp step
+            // sends to ONE owner are neighbours at the destination, so the step is staged owner by
+            // owner and every owner's run then leaves with consecutive lanes on consecutive slots.
+            // Lane w keeps the books of owner w: slots / entries of the step, where its run starts
+            // in the staging buffer and where it goes.
+            uint32_t tot_s = 0, tot_e = 0, lower_s = 0, lower_e = 0;
+            uint4 *run_dst = nullptr, *desc_dst = nullptr;
+            for (uint32_t w = 0; w < W; w++) {
+                const bool mine = live && o == w;
+                const uint32_t bal = __ballot_sync(0xffffffffu, mine);
+                const uint32_t ts = __reduce_add_sync(0xffffffffu, mine ? ns : 0u);
+                const int f = bal ? __ffs((int)bal) - 1 : 0;
+                const uint32_t bs_w = __shfl_sync(0xffffffffu, bs, f), be_w = __shfl_sync(0xffffffffu, be, f);
+                if (live && w < o) { lower_s += ts; lower_e += __popc(bal); }
+                if ((uint32_t)lane == w && bal) {
+                    tot_s = ts;
+                    tot_e = __popc(bal);
+                    if (g.direct) {
+                        uint8_t *hb = g.peer[w] + (size_t)half * g.L.half_bytes;
+                        run_dst = reinterpret_cast<uint4 *>(hb + g.L.off_slots) + (size_t)g.L.rank * g.L.cap_s + bs_w;
+                        desc_dst = reinterpret_cast<uint4 *>(hb + g.L.off_desc) + (size_t)g.L.rank * g.L.cap_e + be_w;
+                    } else {
+                        run_dst = g.send_slots + bs_w;
+                    }
                 }
             }
-            __syncwarp();
+            uint32_t end_s = tot_s, end_e = tot_e;  // inclusive scans over the owners
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t1 = __shfl_up_sync(0xffffffffu, end_s, d), t2 = __shfl_up_sync(0xffffffffu, end_e, d);
+                if (lane >= d) { end_s += t1; end_e += t2; }
+            }
+            const uint32_t total = __shfl_sync(0xffffffffu, end_s, 31), n_live = __shfl_sync(0xffffffffu, end_e, 31);
+            uint4 *stg = stage + (size_t)warp * XCHG_STAGE_PER_WARP;  // [0, 576) slots, [576, 608) descriptors
+            const uint32_t my_soff = lower_s + pre_s;                 // first staged slot of this lane's entry
+            const uint4 *src = nullptr;
+            if (live) {
+                const uint64_t hdr = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)metav[q] << 48) | ((uint64_t)ns << 56);
+                src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
+                if (g.direct) stg[576 + lower_e + rank_e] = make_uint4((uint32_t)hdr, (uint32_t)(hdr >> 32), bs + pre_s, 0u);
+                else g.send_hdr[be + rank_e] = hdr;
+            }
+            // the slots of the 32 entries, read cooperatively in lane order (4 x 32 loads in flight)
             const uint32_t cnt = live ? ns : 0u;
             uint32_t incl = cnt;
 #pragma unroll
@@ -248,12 +281,10 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
                 const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
                 if (lane >= d) incl += t;
             }
-            const uint32_t excl = incl - cnt, total = __shfl_sync(0xffffffffu, incl, 31);
-            // the warp copies the slots of its 32 entries cooperatively, 4 x 32 slots per step
-            // with all four loads issued before the first store
+            const uint32_t excl = incl - cnt;
             for (uint32_t b0 = 0; b0 < total; b0 += 128) {
                 uint4 v[4];
-                uint4 *dq[4];
+                uint32_t at[4];
 #pragma unroll
                 for (int u = 0; u < 4; u++) {
                     const uint32_t k = b0 + u * 32 + lane;
@@ -265,22 +296,52 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
                     }
                     sidx &= 31;
                     const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
+                    const uint32_t so = __shfl_sync(0xffffffffu, my_soff, sidx);
                     const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
-                    const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)dst, sidx);
-                    dq[u] = nullptr;
+                    at[u] = NONE_AT;
                     v[u] = make_uint4(0u, 0u, 0u, 0u);
                     if (k < total) {
                         const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
                         const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
                         v[u] = __ldg(reinterpret_cast<const uint4 *>((uintptr_t)sp) + ch);
-                        dq[u] = reinterpret_cast<uint4 *>((uintptr_t)dp) + sl;
+                        at[u] = so + sl;
                     }
                 }
 #pragma unroll
                 for (int u = 0; u < 4; u++)
-                    if (dq[u]) *dq[u] = v[u];
-                __syncwarp();
+                    if (at[u] != NONE_AT) stg[at[u]] = v[u];
             }
+            __syncwarp();
+            // every owner's run leaves with consecutive lanes on consecutive 16-byte slots
+            for (uint32_t j0 = 0; j0 < total; j0 += 128) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const uint32_t j = j0 + u * 32 + lane;
+                    int w = 0;  // owner whose run holds staged slot j: first lane with end_s > j
+#pragma unroll
+                    for (int step = 16; step >= 1; step >>= 1) {
+                        const uint32_t vv = __shfl_sync(0xffffffffu, end_s, w + step - 1);
+                        if (vv <= j) w += step;
+                    }
+                    w &= 31;
+                    const uint32_t st = __shfl_sync(0xffffffffu, end_s - tot_s, w);
+                    const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)run_dst, w);
+                    if (j < total) reinterpret_cast<uint4 *>((uintptr_t)dp)[j - st] = stg[j];
+                }
+            }
+            if (g.direct) {  // descriptors: at most 32 per step, same owner-major order
+                int w = 0;
+#pragma unroll
+                for (int step = 16; step >= 1; step >>= 1) {
+                    const uint32_t vv = __shfl_sync(0xffffffffu, end_e, w + step - 1);
+                    if (vv <= (uint32_t)lane) w += step;
+                }
+                w &= 31;
+                const uint32_t st = __shfl_sync(0xffffffffu, end_e - tot_e, w);
+                const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)desc_dst, w);
+                if ((uint32_t)lane < n_live) reinterpret_cast<uint4 *>((uintptr_t)dp)[lane - st] = stg[576 + lane];
+            }
+            __syncwarp();  // the staging buffer is reused by the next step
         }
     }
     // 4) the last CTA to finish publishes counts and flag. One system-scope fence per CTA, by
