@@ -80,9 +80,18 @@ typedef struct chronos_device_view {
 int chronos_device_ok(int device);
 
 /* Replaces: module start-up + `process_memory = defaultdict(list)`
- * (chronos_sensor.py:100-105).  Allocates all device state for batches of up to
- * max_batch_events records on `device`. */
+ * (chronos_sensor.py:100-105).  Allocates ALL device memory the context needs for batches of
+ * up to max_batch_events records (< 2^27) on top of up to max_pending_events events pending in
+ * process_memory: two buffer sets (arena, pending lists, survivor and window arrays), the
+ * sort / scan temporaries and the per-PID table.  A submit allocates nothing, with two
+ * documented exceptions: the first submit from HOST memory creates the upload staging buffer
+ * (max_batch_events x 288 bytes per buffer set), and a context whose pending lists outgrow
+ * max_pending_events is re-sized once by the submit that finds out (it waits for the GPU, the
+ * state is kept).  process_memory itself is unbounded in the reference (:105); the one hard
+ * limit here is pending + one batch < 2^27 events.  chronos_create uses
+ * max_pending_events = max(max_batch_events, 65536). */
 int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out);
+int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pending_events, chronos_ctx **out);
 
 /* Replaces: process exit (chronos_sensor.py:163). */
 int chronos_destroy(chronos_ctx *ctx);
@@ -99,12 +108,19 @@ const char *chronos_last_error(const chronos_ctx *ctx);
  * (chronos_sensor.py:124-142, :157, :160-162) preceded by the openat hook's filter
  * (:74-92).  `records` = n*288 bytes in arrival order, host or device memory (detected;
  * device pointers must be 16-byte aligned); record i has global arrival index
- * base_arrival_index + i.  Work is queued on the context's stream; per-PID state
- * carries over from earlier submits.  A submit while results of the previous one are
- * still unfetched discards those results (state is kept). */
+ * base_arrival_index + i (all arrival indices must stay below 2^48).  Work is only
+ * queued; per-PID state carries over from earlier submits.
+ * TWO batches may be in flight: a submit while the previous batch is unfetched starts
+ * its filter stage beside that batch's window stage (the stages of one batch never
+ * overlap, and window stages run in submit order), and chronos_fetch then returns the
+ * batches in submit order.  A third submit drops the results of the oldest unfetched
+ * batch (its effect on the state is kept).  `records` in device memory must stay
+ * valid until the batch has been fetched.  A submit that is refused (CHRONOS_E_ARG,
+ * CHRONOS_E_CAPACITY, CHRONOS_E_NOMEM) leaves the context exactly as it was. */
 int chronos_submit(chronos_ctx *ctx, const void *records, uint64_t n, uint64_t base_arrival_index);
 
-/* Waits for the submitted batch and returns its counts. */
+/* Waits for the oldest batch not fetched yet and returns its counts; the copy calls below
+ * then refer to that batch until the next chronos_fetch. */
 int chronos_fetch(chronos_ctx *ctx, chronos_counts *out);
 
 /* Copies to host memory, after chronos_fetch.  cap_* are capacities in elements; the
@@ -315,6 +331,10 @@ int chronos_memcpy_h2d(int device, void *dst_dev, const void *src_host, uint64_t
 int chronos_memcpy_d2h(int device, void *dst_host, const void *src_dev, uint64_t bytes);
 /* Writes `bytes` of a scratch device buffer, to evict the 126 MB L2 between timed runs. */
 int chronos_flush_l2(int device);
+/* cudaDeviceSynchronize for ctypes-only callers. */
+int chronos_device_synchronize(int device);
+/* cudaMemGetInfo for ctypes-only callers (tests use it to show that submits allocate nothing). */
+int chronos_device_mem_info(int device, uint64_t *free_bytes, uint64_t *total_bytes);
 
 #ifdef __cplusplus
 }

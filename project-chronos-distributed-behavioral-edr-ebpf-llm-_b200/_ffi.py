@@ -54,6 +54,7 @@ class Download(Structure):
 SIGNATURES = {
     "chronos_device_ok": (c_int, [c_int]),
     "chronos_create": (c_int, [c_int, c_uint64, POINTER(c_void_p)]),
+    "chronos_create_sized": (c_int, [c_int, c_uint64, c_uint64, POINTER(c_void_p)]),
     "chronos_destroy": (c_int, [c_void_p]),
     "chronos_reset": (c_int, [c_void_p]),
     "chronos_last_error": (c_char_p, [c_void_p]),
@@ -95,6 +96,8 @@ SIGNATURES = {
     "chronos_memcpy_h2d": (c_int, [c_int, c_void_p, c_void_p, c_uint64]),
     "chronos_memcpy_d2h": (c_int, [c_int, c_void_p, c_void_p, c_uint64]),
     "chronos_flush_l2": (c_int, [c_int]),
+    "chronos_device_synchronize": (c_int, [c_int]),
+    "chronos_device_mem_info": (c_int, [c_int, POINTER(c_uint64), POINTER(c_uint64)]),
 }
 
 _lib = None

@@ -2,17 +2,22 @@
 // B200-native CHRONOS hot path. Kernels live in filter.cuh / sort.cuh / window.cuh.
 //
 // Per batch (one perf_buffer_poll() worth of events, chronos_sensor.py:160-162):
-//   filter_kernel      raw records -> tile-local survivors (pid, src index, meta)
-//   compact_scan       dense, arrival-ordered survivor arrays
-//   sort_prepare + onesweep_pass x4
-//                      stable sort of [carried-in pending ++ survivors] by pid
-//   gather_records     every grouped event copied once into the arena (second stream)
-//   group_forward      flush automaton + chain labeller -> window descriptors
-//   window_reverse     unflushed tails -> next batch's pending list (process_memory)
-//   emit_ordered       windows in trigger-arrival order (the order analyze_sequence
-//                      is called in, :143-147)
-// A submit only enqueues: extents of everything after the filter live in a device-side plan,
-// grids are upper bounds; the first host wait is chronos_fetch.
+//   stage 1 (needs nothing from earlier batches)
+//     filter_kernel      raw records -> tile-local survivors (pid, src index, meta)
+//     compact_scan       dense, arrival-ordered survivor arrays
+//   tail (reads and writes the per-PID state, so tails run one after the other)
+//     sort_prepare + onesweep_pass
+//                        stable sort of [carried-in pending ++ survivors] by pid
+//     gather_records     every grouped event copied once into the arena (own stream)
+//     group_forward      flush automaton + chain labeller -> window descriptors
+//     window_reverse     unflushed tails -> next batch's pending list (process_memory)
+//     emit_ordered       windows in trigger-arrival order (the order analyze_sequence
+//                        is called in, :143-147)
+// A submit only enqueues: extents of everything after the filter -- including the number of
+// pending entries the previous batch left -- live on the device (Plan, Carry), grids are upper
+// bounds; the first host wait is chronos_fetch. Two batches may be in flight: the context
+// keeps two buffer sets, and stage 1 of batch k+1 runs beside the tail of batch k.
+// All device memory for batches of up to max_batch_events is allocated by chronos_create.
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdint.h>
@@ -56,63 +61,103 @@ struct DeviceScalars {  // one 64-byte block on the device, mirrored in pinned m
     uint32_t pad[8];
 };
 static_assert(sizeof(DeviceScalars) == 64, "DeviceScalars layout");
-// the Plan of the batch in flight lives right behind the scalars: ONE copy brings both back
+// the Plan of the batch lives right behind its scalars: ONE copy brings both back
 constexpr size_t RESULT_BLOCK_BYTES = 64 + ((sizeof(Plan) + 63) / 64) * 64;
 
 constexpr int N_TICKETS = 64;
 // ticket counters followed by the global digit histograms of the sort (sort.cuh), cleared together
-constexpr size_t TICKET_BYTES = (N_TICKETS + RADIX_MAX_PASSES * RADIX_BINS) * 4;
+constexpr size_t TICKET_WORDS = N_TICKETS + RADIX_MAX_PASSES * RADIX_BINS;
+constexpr size_t TICKET_BYTES = TICKET_WORDS * 4;
 constexpr uint32_t COMM_MEMO_SLOTS = 8192;  // device-wide comm memo (insert-only), 192 KB
+constexpr uint64_t MAX_GROUPED = (1ull << VAL_ID_BITS) - 1;  // entry ids are 27 bits of the sort value
+constexpr uint64_t MAX_ARRIVAL = 1ull << 48;                  // the transport header keeps 48 bits
+
+int device_sm_count(int device) {
+    static int cached[64] = {0};
+    if (device >= 0 && device < 64 && cached[device]) return cached[device];
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || sms <= 0) {
+        cudaGetLastError();
+        sms = 148;
+    }
+    if (device >= 0 && device < 64) cached[device] = sms;
+    return sms;
+}
+
+// Everything one batch owns: the state it leaves behind (arena + pending lists, read by the
+// next batch), its survivors and results (read by the host after fetch) and its bookkeeping.
+// The context has two of these; batch k uses set k & 1.
+struct BatchSet {
+    DevBuf arena, pend_key, pend_slot, pend_arrival, pend_meta;
+    uint64_t pend_cap = 0;  // entries the right-aligned pending arrays are laid out for
+    uint64_t cap_M = 0;     // grouped entries (pending + survivors) this set has room for
+    uint64_t cap_n = 0;     // raw events of one batch this set has room for
+    DevBuf surv_src, surv_meta, surv_pid, surv_ns, surv_arrival, slot_off;
+    DevBuf windows, chain_pid, chain_idx;
+    DevBuf d_batch;         // upload staging for host-pointer submits (allocated on first use)
+    DevBuf result;          // DeviceScalars + Plan
+    DeviceScalars *h_scalars = nullptr;  // pinned mirror of `result`
+    Plan *h_plan = nullptr;
+    cudaEvent_t ev_start = nullptr, ev_stage1 = nullptr, ev_end = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
+    cudaEvent_t ev_packed = nullptr;  // last read of this set's results by a download
+    enum State { FREE, SUBMITTED, DONE, FETCHED } state = FREE;
+    // the batch
+    uint64_t n = 0, base = 0, P_ub = 0, pids_ub = 0, Mmax = 0;
+    uint64_t S = 0, M = 0, W = 0, chains = 0, pending_after = 0, pids_after = 0, launches = 0, seq = 0;
+    const uint8_t *records = nullptr;  // device pointer of the batch records
+    const uint4 *slots = nullptr;      // transport-form batch (chronos_submit_survivors / exchange)
+    bool explicit_arrival = false, exchanged = false, filter_timed = false, pipelined = false;
+    uint32_t x_epoch = 0;  // exchange step this batch consumed
+    float t_total = 0.f, t_filter = 0.f, t_filter_kernel = 0.f;
+    int rc = CHRONOS_OK;  // outcome found when the batch completed
+};
 
 }  // namespace
 
-struct chronos_ctx;
-namespace {
-void mark(chronos_ctx *c, const char *name);
-}
 struct chronos_ctx {
     int device = 0;
     int sm_count = 0;
-    uint64_t max_batch = 0;
-    cudaStream_t stream = nullptr, stream2 = nullptr;  // stream2: record gather, overlapped with the window scans
-    cudaEvent_t ev_sorted = nullptr, ev_gathered = nullptr;
-    cudaEvent_t ev_start = nullptr, ev_filter = nullptr, ev_end = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
+    uint64_t max_batch = 0, max_pending = 0;
+    // stream: tails (and stage 1 when nothing else is in flight); stream_f: stage 1 of a batch
+    // submitted while the previous one is still running; stream2: record gather; stream3: ordered
+    // emission beside the reverse scan; dl_stream: everything the host asks for after a fetch
+    cudaStream_t stream = nullptr, stream_f = nullptr, stream2 = nullptr, stream3 = nullptr, dl_stream = nullptr;
+    cudaEvent_t ev_sorted = nullptr, ev_gathered = nullptr, ev_fwd = nullptr, ev_emitted = nullptr;
     char err[256] = {0};
 
-    // batch staging for host-pointer submits
-    DevBuf d_batch;
-    // entry arrays (capacity in entries = ecap)
-    DevBuf keyA, keyB, valA, valB, surv_src, surv_meta, pflag, entry_out, wsorted, windows, owner_table;
-    DevBuf sp_key, sp_src, sp_meta, sp_ns, tile_count;  // filter's tile-local compaction
-    DevBuf surv_pid, surv_ns, slot_off;                  // arrival-ordered pid copy; transport-form bookkeeping
-    const uint4 *b_slots = nullptr;                      // transport-form batch (chronos_submit_survivors)
-    DevBuf comm_memo;                                    // second-level comm memo: lock[N] | val[N] | key[N]
-    // kill-chain labeller + persistent per-PID table (chain.cuh)
-    DevBuf pid_tab, pt_count, chain_pid, chain_idx;
+    BatchSet set[2];
+    int last = 0;       // set of the most recently submitted batch (or of the loaded / reset state)
+    int fetched = -1;   // set whose results the copy calls return
+    uint64_t seq = 0;
+    uint64_t n_pending = 0, n_pids_seen = 0;  // exact once every submitted batch has completed
+
+    // shared by all batches
+    DevBuf carry;                                  // Carry: what a batch hands to the next on the device
+    DevBuf keyA, keyB, valA, valB, pflag, entry_out, wsorted;   // tail temporaries
+    DevBuf status, sweep_status;
+    uint64_t cap_M = 0, cap_n = 0;
+    DevBuf sp_key, sp_src, sp_meta, sp_ns, tile_count, scan_status;   // stage-1 temporaries
+    DevBuf tickets_f, tickets_t;
+    DevBuf owner_table;
+    uint64_t owner_table_T = 0;
+    DevBuf comm_memo;                              // second-level comm memo: lock[N] | val[N] | key[N]
+    DevBuf pid_tab, pt_count;                      // persistent per-PID table (chain.cuh)
     uint32_t pt_cap = 0;
     uint32_t pt_epoch = 1;
-    Plan *h_plan = nullptr;      // pinned copy of the batch's device Plan, read at fetch (behind h_scalars)
-    uint64_t b_Mmax = 0;         // P + n: what the buffers of the batch in flight are sized for
-    uint64_t n_pids_seen = 0, b_chains = 0;
-    DevBuf surv_arrival;  // only for chronos_submit_survivors
-    // double-buffered persistent state
-    DevBuf arena[2];
-    DevBuf pend_key[2], pend_slot[2], pend_arrival[2], pend_meta[2];
-    uint64_t pend_cap[2] = {0, 0};  // capacity (entries) the right-aligned arrays were laid out for
-    int cur = 0;                    // index written by the batch in flight / last fetched
-    uint64_t n_pending = 0;         // entries pending after the last fetched batch (in buffer `cur`)
-    // scheduling scratch
-    DevBuf status, tickets, scalars, scan_status, sweep_status;
     uint32_t scan_epoch = 0, sweep_epoch = 0;
-    int scan_slot = 0;  // next free ticket counter for scans in this batch
-    DeviceScalars *h_scalars = nullptr;  // pinned
-    DevBuf pack;                         // scratch for chronos_copy_window_records / chronos_state
-    DevBuf pack_off;
+    int scan_slot = 0;  // next free ticket counter for scans of the stage 1 being enqueued
+    // host-side copies after a fetch
+    DevBuf pack, pack_off, dl_scan_status, dl_ticket;
+    uint32_t dl_scan_epoch = 0;
+    cudaEvent_t dl_ready = nullptr, dl_done[2] = {nullptr, nullptr};
+    DevBuf dl_stage[2];
+    bool dl_inflight[2] = {false, false};
+    int dl_k = 0;
 
     // direct exchange over peer memory (exchange.cuh)
     DevBuf x_window, x_totals;
     XchgLayout x_L = {};
-    bool x_created = false, x_connected = false, x_sent = false, b_exchanged = false;
+    bool x_created = false, x_connected = false, x_sent = false;
     uint8_t *x_peer[XCHG_MAX_WORLD] = {nullptr};
     bool x_opened[XCHG_MAX_WORLD] = {false};
     uint32_t x_epoch = 0;
@@ -120,26 +165,17 @@ struct chronos_ctx {
     bool x_filter_timed = false;  // stage 1 of this step ran the filter (non-empty slice)
     uint64_t x_timeout_ns = 20ull * 1000000000ull;
     cudaEvent_t ev_x0 = nullptr;
-    // asynchronous result download (chronos_download_begin)
-    cudaStream_t dl_stream = nullptr;
-    cudaEvent_t dl_ready = nullptr, dl_done[2] = {nullptr, nullptr};
-    DevBuf dl_stage[2];
-    bool dl_inflight[2] = {false, false};
-    int dl_k = 0;
 
-    // last batch
-    enum { IDLE, SUBMITTED, FETCHED } phase = IDLE;
-    uint64_t b_n = 0, b_base = 0, b_S = 0, b_P = 0, b_M = 0, b_W = 0;
-    const uint8_t *b_records = nullptr;  // device pointer of the batch records
-    bool b_explicit_arrival = false;
-    uint64_t launches = 0;
-    float t_total = 0.f, t_filter = 0.f, t_filter_kernel = 0.f;
-    bool filter_timed = false;
+    uint64_t launches = 0;  // of the submit being enqueued
     int filter_variant = 0;
+    int gather_ctas_per_sm = 0;
+    bool gather_first = true;
+    int prio_lo = 0;
+    bool no_pipeline = false;
     // CHRONOS_TRACE=1: CUDA events between the stages of a submit, printed at fetch
     bool trace = false;
-    cudaEvent_t tev[12] = {nullptr};
-    const char *tname[12] = {nullptr};
+    cudaEvent_t tev[24] = {nullptr};
+    const char *tname[24] = {nullptr};
     int n_tev = 0;
 };
 
@@ -147,13 +183,10 @@ namespace {
 
 const char *g_static_err = "chronos: invalid context";
 
-// CHRONOS_DEBUG_SYNC=1: wait after every stage so that a device fault names the stage that raised it
-int dbg_sync(chronos_ctx *c, const char *what);
-
-void mark(chronos_ctx *c, const char *name) {
-    if (!c->trace || c->n_tev >= 12) return;
+void mark(chronos_ctx *c, const char *name, cudaStream_t st = nullptr) {
+    if (!c->trace || c->n_tev >= 24) return;
     if (!c->tev[c->n_tev]) cudaEventCreate(&c->tev[c->n_tev]);
-    cudaEventRecord(c->tev[c->n_tev], c->stream);
+    cudaEventRecord(c->tev[c->n_tev], st ? st : c->stream);
     c->tname[c->n_tev++] = name;
 }
 
@@ -175,15 +208,16 @@ int fail(chronos_ctx *c, int code, const char *fmt, ...) {
                         "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
     } while (0)
 
+// CHRONOS_DEBUG_SYNC=1: wait after every stage so that a device fault names the stage that raised it
 int dbg_sync(chronos_ctx *c, const char *what) {
     static const bool on = getenv("CHRONOS_DEBUG_SYNC") != nullptr;
     if (!on) return CHRONOS_OK;
-    cudaError_t e = cudaStreamSynchronize(c->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream2);
+    cudaError_t e = cudaDeviceSynchronize();
     if (e != cudaSuccess) return fail(c, CHRONOS_E_CUDA, "after %s: %s", what, cudaGetErrorString(e));
     return CHRONOS_OK;
 }
 
+// grow-only: the buffer is re-allocated when it is too small (contents are NOT kept)
 int ensure(chronos_ctx *c, DevBuf &b, size_t bytes) {
     if (bytes <= b.bytes && b.p) return CHRONOS_OK;
     if (b.p) {
@@ -191,13 +225,8 @@ int ensure(chronos_ctx *c, DevBuf &b, size_t bytes) {
         b.p = nullptr;
         b.bytes = 0;
     }
-    size_t want = std::max<size_t>(bytes + bytes / 8, 256);
+    const size_t want = std::max<size_t>(bytes, 256);
     cudaError_t e = cudaMalloc(&b.p, want);
-    if (e != cudaSuccess) {
-        cudaGetLastError();
-        want = std::max<size_t>(bytes, 256);
-        e = cudaMalloc(&b.p, want);
-    }
     if (e != cudaSuccess) {
         cudaGetLastError();
         b.p = nullptr;
@@ -227,34 +256,46 @@ bool is_device_pointer(const void *p) {
     return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
 }
 
-// ---- small helper kernels ---------------------------------------------------------------
-__global__ void fold_keys_kernel(const uint32_t *keys, uint32_t n, uint32_t *k_or, uint32_t *k_and) {
-    uint32_t o = 0, a = 0xffffffffu;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        uint32_t k = keys[i];
-        o |= k;
-        a &= k;
+// Work the host asks for after a fetch (copies, packing) goes to the main stream while that is
+// idle; when a younger batch is already queued there, to a stream of its own.
+int host_stream(chronos_ctx *c, cudaStream_t *out) {
+    bool busy = false;
+    for (BatchSet &b : c->set) busy |= b.state == BatchSet::SUBMITTED;
+    if (!busy) {
+        *out = c->stream;
+        return CHRONOS_OK;
     }
-    o = __reduce_or_sync(0xffffffffu, o);
-    a = __reduce_and_sync(0xffffffffu, a);
-    if ((threadIdx.x & 31) == 0) {
-        atomicOr(k_or, o);
-        atomicAnd(k_and, a);
-    }
+    if (!c->dl_stream) CK(cudaStreamCreateWithPriority(&c->dl_stream, cudaStreamNonBlocking, c->prio_lo));
+    *out = c->dl_stream;
+    return CHRONOS_OK;
 }
 
+DeviceScalars *dscal(BatchSet &b) { return ptr<DeviceScalars>(b.result); }
+Plan *dplan(BatchSet &b) { return reinterpret_cast<Plan *>(ptr<uint8_t>(b.result) + 64); }
+
+// ---- small helper kernels ---------------------------------------------------------------
 __global__ void set_u32_kernel(uint32_t *p, uint32_t v) { *p = v; }
+__global__ void copy_u32_kernel(uint32_t *dst, const uint32_t *src) { *dst = *src; }
 
 // start of a batch: scalars to their neutral values, ticket counters and digit histograms to 0
-__global__ void init_scalars_kernel(DeviceScalars *s, uint32_t *tickets) {
-    for (uint32_t i = threadIdx.x; i < TICKET_BYTES / 4; i += blockDim.x) tickets[i] = 0;
-    if (threadIdx.x) return;
-    s->surv_count = 0;
-    s->key_or = 0;
-    s->key_and = 0xffffffffu;
-    s->n_windows = 0;
-    s->n_pending = 0;
-    s->n_chains = 0;
+// (what & 1: the stage-1 half, what & 2: the tail half)
+__global__ void init_batch_kernel(DeviceScalars *s, uint32_t *tickets_f, uint32_t *tickets_t, int what) {
+    if (what & 1) {
+        for (uint32_t i = threadIdx.x; i < N_TICKETS; i += blockDim.x) tickets_f[i] = 0;
+        if (threadIdx.x == 0) {
+            s->surv_count = 0;
+            s->key_or = 0;
+            s->key_and = 0xffffffffu;
+        }
+    }
+    if (what & 2) {
+        for (uint32_t i = threadIdx.x; i < TICKET_WORDS; i += blockDim.x) tickets_t[i] = 0;
+        if (threadIdx.x == 0) {
+            s->n_windows = 0;
+            s->n_pending = 0;
+            s->n_chains = 0;
+        }
+    }
 }
 
 // Stage 2 of the sharded path, step 1: split the header words of the received entries
@@ -272,13 +313,12 @@ __global__ void unpack_hdr_kernel(const uint64_t *hdr, uint32_t n, uint64_t *arr
 }
 
 // step 2 (after the scan of the slot counts): the pid is the first word of an entry's slot 0
-__global__ void extract_pid_kernel(const uint4 *slots, const uint32_t *slot_off, uint32_t n, uint32_t *key,
-                                   uint32_t *pid_copy, uint32_t *src, uint32_t *k_or, uint32_t *k_and) {
+__global__ void extract_pid_kernel(const uint4 *slots, const uint32_t *slot_off, uint32_t n, uint32_t *pid_out,
+                                   uint32_t *src, uint32_t *k_or, uint32_t *k_and) {
     uint32_t o = 0, a = 0xffffffffu;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t k = reinterpret_cast<const uint32_t *>(slots + slot_off[i])[0];
-        key[i] = k;
-        pid_copy[i] = k;
+        pid_out[i] = k;
         src[i] = i;
         o |= k;
         a &= k;
@@ -302,7 +342,6 @@ __global__ void pack_by_slot_kernel(const uint8_t *arena, const uint32_t *slot, 
     }
 }
 
-// one warp per window: packed[off[w] ..] = arena[start .. start+len)
 __global__ void window_len_kernel(const chronos_window *win, uint32_t nw, uint32_t *len) {
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < nw; i += gridDim.x * blockDim.x) len[i] = win[i].len;
 }
@@ -340,53 +379,59 @@ __global__ void tracegen_kernel(chronos_tracegen_cfg cfg, const uint64_t *cdf, u
     }
 }
 
+// ---- one-time kernel attributes per device ------------------------------------------------
+std::mutex g_attr_lock;
+bool g_attr_done[64] = {false};
+
+int configure_kernels(chronos_ctx *c) {
+    std::lock_guard<std::mutex> g(g_attr_lock);
+    if (c->device < 64 && g_attr_done[c->device]) return CHRONOS_OK;
+    CK(cudaFuncSetAttribute(filter_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)filter_smem_bytes<1>()));
+    CK(cudaFuncSetAttribute(filter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)filter_smem_bytes<2>()));
+    CK(cudaFuncSetAttribute(xchg_pack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XCHG_PACK_SMEM));
+    CK(cudaFuncSetAttribute(gather_records, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GATHER_SMEM));
+    if (c->device < 64) g_attr_done[c->device] = true;
+    return CHRONOS_OK;
+}
+
 // ---- filter launch ------------------------------------------------------------------------
 template <int NSTAGE>
-int launch_filter_t(chronos_ctx *c, FilterParams fp) {
-    static bool configured[16] = {false};
+int launch_filter_t(chronos_ctx *c, FilterParams fp, cudaStream_t st) {
     auto kern = filter_kernel<NSTAGE>;
     const size_t smem = filter_smem_bytes<NSTAGE>();
-    if (!configured[c->device & 15]) {
-        CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured[c->device & 15] = true;
+    static int per_sm_of[64] = {0};
+    int per_sm = c->device < 64 ? per_sm_of[c->device] : 0;
+    if (per_sm == 0) {
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FILTER_TILE, smem));
+        if (per_sm < 1) return fail(c, CHRONOS_E_CUDA, "filter kernel does not fit on an SM (smem %zu)", smem);
+        if (c->device < 64) per_sm_of[c->device] = per_sm;
     }
-    int per_sm = 0;
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, FILTER_TILE, smem));
-    if (per_sm < 1) return fail(c, CHRONOS_E_CUDA, "filter kernel does not fit on an SM (smem %zu)", smem);
     const uint32_t tiles = fp.tile_end - fp.tile_begin;
     const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(per_sm * c->sm_count));
-    kern<<<grid, FILTER_TILE, smem, c->stream>>>(fp);
+    kern<<<grid, FILTER_TILE, smem, st>>>(fp);
     CK(cudaGetLastError());
     c->launches++;
     return CHRONOS_OK;
 }
 
-int filter_tile_size(const chronos_ctx *) { return FILTER_TILE; }
-
 // CHRONOS_FILTER_VARIANT=2 selects the double-buffered build of the filter (tuning knob)
-int launch_filter(chronos_ctx *c, const FilterParams &fp) {
-    if (c->filter_variant == 2) return launch_filter_t<2>(c, fp);
-    return launch_filter_t<1>(c, fp);
+int launch_filter(chronos_ctx *c, const FilterParams &fp, cudaStream_t st) {
+    if (c->filter_variant == 2) return launch_filter_t<2>(c, fp, st);
+    return launch_filter_t<1>(c, fp, st);
 }
 
-// exclusive scan in place (device array of n u32) on the context's stream
-// (n_dev != nullptr: the real count lives on the device, n is only its upper bound)
-int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_dev = nullptr, int own_ticket = -1) {
+// exclusive scan in place (device array of n u32) as part of the stage 1 being enqueued
+int launch_scan(chronos_ctx *c, cudaStream_t stream, uint32_t *data, uint64_t n) {
     if (n == 0) return CHRONOS_OK;
-    cudaStream_t stream = c->stream;
     const uint32_t n_tiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
-    int rc;
-    const void *before = c->scan_status.p;
-    if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_tiles * 8, 4096)))) return rc;
-    if (c->scan_status.p != before || c->scan_epoch == 0)  // fresh memory or wrapped epoch: tag 0 = "never"
-        CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, stream));
-    if (own_ticket < 0 && c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
-    if (own_ticket >= 0) CK(cudaMemsetAsync(ptr<uint32_t>(c->tickets) + own_ticket, 0, 4, stream));
+    if ((size_t)n_tiles * 8 > c->scan_status.bytes) return fail(c, CHRONOS_E_STATE, "scan of %llu counters exceeds the status buffer", (unsigned long long)n);
+    if (c->scan_epoch == 0) CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, stream));  // tag 0 = "never"
+    if (c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
     ScanParams sp;
     sp.data = data;
     sp.n = (uint32_t)n;
-    sp.n_ptr = n_dev;
-    sp.ticket = own_ticket >= 0 ? ptr<uint32_t>(c->tickets) + own_ticket : ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
+    sp.n_ptr = nullptr;
+    sp.ticket = ptr<uint32_t>(c->tickets_f) + 8 + c->scan_slot++;
     sp.status = ptr<uint64_t>(c->scan_status);
     sp.epoch = ++c->scan_epoch;
     if (c->scan_epoch >= (1u << 29)) c->scan_epoch = 0;  // re-zero on the next call
@@ -396,26 +441,14 @@ int launch_scan(chronos_ctx *c, uint32_t *data, uint64_t n, const uint32_t *n_de
     return CHRONOS_OK;
 }
 
-// filter + cross-tile compaction: dense, arrival-ordered survivors (pid -> out_key,
-// batch-local index -> surv_src, META bits -> surv_meta, count -> scalars.surv_count)
-// Buffers and parameters of the filter for a batch of n records (no launch).
-int filter_setup(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, FilterParams &fp) {
-    int rc;
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    const int TILE = filter_tile_size(c);
+// Parameters of the filter for a batch of n records (no launch); buffers exist since create.
+void filter_setup(chronos_ctx *c, BatchSet &b, const uint8_t *d_recs, uint64_t n, FilterParams &fp) {
+    DeviceScalars *ds = dscal(b);
     fp.recs = d_recs;
     fp.n = n;
     fp.tile_begin = 0;
-    fp.tile_end = (uint32_t)((n + TILE - 1) / TILE);
-    fp.ticket = ptr<uint32_t>(c->tickets);
-    const uint64_t slots = (uint64_t)fp.tile_end * TILE;
-    if ((rc = ensure(c, c->sp_key, slots * 4))) return rc;
-    if ((rc = ensure(c, c->sp_src, slots * 4))) return rc;
-    if ((rc = ensure(c, c->sp_meta, slots))) return rc;
-    if ((rc = ensure(c, c->sp_ns, slots))) return rc;
-    if ((rc = ensure(c, c->surv_pid, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_ns, n + 1))) return rc;
-    if ((rc = ensure(c, c->tile_count, ((uint64_t)fp.tile_end + 4) * 4))) return rc;
+    fp.tile_end = (uint32_t)((n + FILTER_TILE - 1) / FILTER_TILE);
+    fp.ticket = ptr<uint32_t>(c->tickets_f);
     fp.tile_count = ptr<uint32_t>(c->tile_count);
     fp.sp_key = ptr<uint32_t>(c->sp_key);
     fp.sp_src = ptr<uint32_t>(c->sp_src);
@@ -428,34 +461,28 @@ int filter_setup(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, FilterParams
     fp.gm_val = fp.gm_lock + COMM_MEMO_SLOTS;
     fp.gm_key = reinterpret_cast<uint4 *>(fp.gm_val + COMM_MEMO_SLOTS);
     fp.gm_mask = COMM_MEMO_SLOTS - 1;
-    return CHRONOS_OK;
 }
 
-// Cross-tile prefix + dense, arrival-ordered survivor arrays, one kernel.
-int launch_compact(chronos_ctx *c, const FilterParams &fp, uint32_t *out_key) {
-    int rc;
-    cudaStream_t stream = c->stream;
+// Cross-tile prefix + dense, arrival-ordered survivor arrays of the set, one kernel.
+int launch_compact(chronos_ctx *c, BatchSet &b, const FilterParams &fp, cudaStream_t stream) {
     const uint32_t n_tiles = fp.tile_end;
     const uint32_t n_chunks = (n_tiles + CS_CHUNK - 1) / CS_CHUNK;
-    const void *before = c->scan_status.p;
-    if ((rc = ensure(c, c->scan_status, std::max<size_t>((size_t)n_chunks * 8, 4096)))) return rc;
-    if (c->scan_status.p != before || c->scan_epoch == 0)
-        CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, stream));
+    if (c->scan_epoch == 0) CK(cudaMemsetAsync(c->scan_status.p, 0, c->scan_status.bytes, stream));
     if (c->scan_slot >= 32) return fail(c, CHRONOS_E_STATE, "too many scans in one batch");
     CompactScanParams cp;
     cp.tile_count = fp.tile_count;
     cp.n_tiles = n_tiles;
-    cp.tile = (uint32_t)filter_tile_size(c);
+    cp.tile = (uint32_t)FILTER_TILE;
     cp.sp_key = fp.sp_key;
     cp.sp_src = fp.sp_src;
     cp.sp_meta = fp.sp_meta;
     cp.sp_ns = fp.sp_ns;
-    cp.out_key = out_key;
-    cp.out_src = ptr<uint32_t>(c->surv_src);
-    cp.out_meta = ptr<uint8_t>(c->surv_meta);
-    cp.out_ns = ptr<uint8_t>(c->surv_ns);
-    cp.out_pid = ptr<uint32_t>(c->surv_pid);
-    cp.ticket = ptr<uint32_t>(c->tickets) + 8 + c->scan_slot++;
+    cp.out_key = nullptr;
+    cp.out_src = ptr<uint32_t>(b.surv_src);
+    cp.out_meta = ptr<uint8_t>(b.surv_meta);
+    cp.out_ns = ptr<uint8_t>(b.surv_ns);
+    cp.out_pid = ptr<uint32_t>(b.surv_pid);
+    cp.ticket = ptr<uint32_t>(c->tickets_f) + 8 + c->scan_slot++;
     cp.status = ptr<uint64_t>(c->scan_status);
     cp.epoch = ++c->scan_epoch;
     if (c->scan_epoch >= (1u << 29)) c->scan_epoch = 0;
@@ -465,43 +492,129 @@ int launch_compact(chronos_ctx *c, const FilterParams &fp, uint32_t *out_key) {
     return CHRONOS_OK;
 }
 
-// filter + cross-tile compaction: dense, arrival-ordered survivors (pid -> out_key,
+// filter + cross-tile compaction: dense, arrival-ordered survivors of the set (pid -> surv_pid,
 // batch-local index -> surv_src, META bits -> surv_meta, count -> scalars.surv_count)
-int run_filter_stage(chronos_ctx *c, const uint8_t *d_recs, uint64_t n, uint32_t *out_key) {
+int run_filter_stage(chronos_ctx *c, BatchSet &b, const uint8_t *d_recs, uint64_t n, cudaStream_t st) {
     int rc;
     FilterParams fp;
-    if ((rc = filter_setup(c, d_recs, n, fp))) return rc;
-    CK(cudaEventRecord(c->ev_f0, c->stream));
+    filter_setup(c, b, d_recs, n, fp);
+    CK(cudaEventRecord(b.ev_f0, st));
     if ((rc = dbg_sync(c, "begin_batch"))) return rc;
-    if ((rc = launch_filter(c, fp))) return rc;
-    CK(cudaEventRecord(c->ev_f1, c->stream));
+    if ((rc = launch_filter(c, fp, st))) return rc;
+    CK(cudaEventRecord(b.ev_f1, st));
     if ((rc = dbg_sync(c, "filter_kernel"))) return rc;
-    c->filter_timed = true;
-    if ((rc = launch_compact(c, fp, out_key))) return rc;
+    b.filter_timed = true;
+    if ((rc = launch_compact(c, b, fp, st))) return rc;
     if ((rc = dbg_sync(c, "filter + scan + compact"))) return rc;
     return CHRONOS_OK;
 }
 
-int finish_batch(chronos_ctx *c);
+// ---- memory ----------------------------------------------------------------------------------
+// status words needed by the window kernels for M grouped entries
+size_t status_words(uint64_t M) {
+    const uint64_t tiles_m = (M + WIN_TILE - 1) / WIN_TILE;
+    return (size_t)(8 * tiles_m + 64);
+}
+
+// Buffers shared by all batches, for batches of up to n raw events and M grouped entries.
+int reserve_shared(chronos_ctx *c, uint64_t n, uint64_t M) {
+    int rc;
+    n = std::max(n, c->cap_n);
+    M = std::max(M, c->cap_M);
+    if ((rc = ensure(c, c->keyA, (M + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->keyB, (M + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->valA, (M + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->valB, (M + 1) * 4))) return rc;
+    if ((rc = ensure(c, c->pflag, (M + 4) * 4))) return rc;
+    if ((rc = ensure(c, c->entry_out, (n + 4) * 4))) return rc;
+    // a window holds at least two grouped entries and exactly one trigger survivor of its batch
+    if ((rc = ensure(c, c->wsorted, (std::min(n, M / 2) + 1) * sizeof(WinSorted)))) return rc;
+    const size_t sw_before = c->status.bytes;
+    if ((rc = ensure(c, c->status, status_words(M) * 8))) return rc;
+    (void)sw_before;
+    {
+        const uint64_t rtiles = std::max<uint64_t>((M + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS, 1);
+        const void *before = c->sweep_status.p;
+        if ((rc = ensure(c, c->sweep_status, rtiles * RADIX_BINS * 8))) return rc;
+        if (c->sweep_status.p != before) {  // fresh memory: tag 0 = "never written"
+            CK(cudaMemset(c->sweep_status.p, 0, c->sweep_status.bytes));
+            c->sweep_epoch = 0;
+        }
+    }
+    const uint64_t tiles = (n + FILTER_TILE - 1) / FILTER_TILE;
+    const uint64_t slots = tiles * FILTER_TILE;
+    if ((rc = ensure(c, c->sp_key, slots * 4 + 16))) return rc;
+    if ((rc = ensure(c, c->sp_src, slots * 4 + 16))) return rc;
+    if ((rc = ensure(c, c->sp_meta, slots + 16))) return rc;
+    if ((rc = ensure(c, c->sp_ns, slots + 16))) return rc;
+    if ((rc = ensure(c, c->tile_count, (tiles + 4) * 4))) return rc;
+    {
+        // scans of stage 1: tile counts (chunks of CS_CHUNK tiles), slot counts of n entries,
+        // the owner table of an exchange (2 * world * ceil(n / XCHG_TILE) + 1 counters)
+        const uint64_t owner = 2ull * XCHG_MAX_WORLD * ((n + XCHG_TILE - 1) / XCHG_TILE + 1) + 1;
+        const uint64_t words = std::max<uint64_t>({(tiles + CS_CHUNK - 1) / CS_CHUNK, (n + SCAN_TILE - 1) / SCAN_TILE,
+                                                   (owner + SCAN_TILE - 1) / SCAN_TILE, 512});
+        const void *before = c->scan_status.p;
+        if ((rc = ensure(c, c->scan_status, words * 8))) return rc;
+        if (c->scan_status.p != before) {
+            CK(cudaMemset(c->scan_status.p, 0, c->scan_status.bytes));
+            c->scan_epoch = 0;
+        }
+    }
+    c->cap_n = n;
+    c->cap_M = M;
+    return CHRONOS_OK;
+}
+
+// One buffer set, for a batch of up to n raw events on top of carried-in state, M entries in all.
+int reserve_set(chronos_ctx *c, BatchSet &b, uint64_t n, uint64_t M) {
+    int rc;
+    n = std::max(n, b.cap_n);
+    M = std::max(M, b.cap_M);
+    if ((rc = ensure(c, b.arena, (M + 1) * CH_REC_BYTES))) return rc;
+    if ((rc = ensure(c, b.pend_key, (M + 1) * 4))) return rc;
+    if ((rc = ensure(c, b.pend_slot, (M + 1) * 4))) return rc;
+    if ((rc = ensure(c, b.pend_arrival, (M + 1) * 8))) return rc;
+    if ((rc = ensure(c, b.pend_meta, M + 1))) return rc;
+    if ((rc = ensure(c, b.surv_src, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, b.surv_meta, n + 1))) return rc;
+    if ((rc = ensure(c, b.surv_pid, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, b.surv_ns, n + 1))) return rc;
+    if ((rc = ensure(c, b.windows, (std::min(n, M / 2) + 1) * sizeof(chronos_window)))) return rc;
+    if ((rc = ensure(c, b.chain_pid, (n + 1) * 4))) return rc;
+    if ((rc = ensure(c, b.chain_idx, (n + 1) * 8))) return rc;
+    b.cap_n = n;
+    b.cap_M = M;
+    b.pend_cap = M;
+    return CHRONOS_OK;
+}
+
+// arrays only the transport-form submits need (chronos_submit_survivors, the exchange)
+int reserve_transport(chronos_ctx *c, BatchSet &b) {
+    int rc;
+    if ((rc = ensure(c, b.surv_arrival, (b.cap_n + 1) * 8))) return rc;
+    if ((rc = ensure(c, b.slot_off, (b.cap_n + 8) * 4))) return rc;
+    return CHRONOS_OK;
+}
 
 // The per-PID table must stay at most half full: room for every PID seen so far plus one new
-// PID per grouped entry of this batch.
-int ensure_pid_table(chronos_ctx *c, uint64_t M) {
-    const uint64_t need = 2 * (c->n_pids_seen + M) + 64;
+// PID per grouped entry of the batch about to run. Growing it waits for the GPU.
+int ensure_pid_table(chronos_ctx *c, uint64_t pids_ub, uint64_t M) {
+    const uint64_t need = 2 * (pids_ub + M) + 64;
     if (c->pt_cap >= need) return CHRONOS_OK;
     uint64_t cap = 1024;
     while (cap < need) cap <<= 1;
     if (cap > (1ull << 31)) return fail(c, CHRONOS_E_CAPACITY, "per-PID table would need %llu slots", (unsigned long long)cap);
+    CK(cudaDeviceSynchronize());  // batches in flight use the old table
     DevBuf fresh;
     int rc;
     if ((rc = ensure(c, fresh, cap * 8))) return rc;
     auto grow = [&]() -> int {
         CK(cudaMemsetAsync(fresh.p, 0, cap * 8, c->stream));
-        if (c->pt_cap && c->n_pids_seen) {
+        if (c->pt_cap) {
             pt_rehash_kernel<<<(unsigned)std::min<uint64_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
                 ptr<uint64_t>(c->pid_tab), c->pt_cap, static_cast<uint64_t *>(fresh.p), (uint32_t)cap - 1, c->pt_epoch);
             CK(cudaGetLastError());
-            c->launches++;
         }
         CK(cudaStreamSynchronize(c->stream));
         return CHRONOS_OK;
@@ -516,35 +629,41 @@ int ensure_pid_table(chronos_ctx *c, uint64_t M) {
     return CHRONOS_OK;
 }
 
-// Everything after the survivors are known ON THE DEVICE (keyA[P..P+S), surv_src, surv_meta,
-// scalars.surv_count / key_or / key_and). Nothing here waits for the GPU: buffers are sized
-// for the worst case M = P + n, grids are upper bounds, extents come from the device plan.
-int run_window_stage(chronos_ctx *c) {
-    const uint64_t P = c->b_P;
-    const uint64_t Mmax = c->b_Mmax;  // P + n
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    Plan *plan = reinterpret_cast<Plan *>(ptr<uint8_t>(c->scalars) + 64);
+__global__ void set_carry_kernel(Carry *c, uint32_t P, uint32_t k_or, uint32_t k_and) {
+    c->P = P;
+    c->key_or = k_or;
+    c->key_and = k_and;
+}
+
+// (queued on the main stream, ahead of the next batch's tail)
+int set_carry(chronos_ctx *c, uint32_t P, uint32_t k_or, uint32_t k_and) {
+    set_carry_kernel<<<1, 1, 0, c->stream>>>(ptr<Carry>(c->carry), P, k_or, k_and);
+    CK(cudaGetLastError());
+    return CHRONOS_OK;
+}
+
+// ---- the tail -----------------------------------------------------------------------------------
+// Everything after the survivors of set `b` are known ON THE DEVICE (surv_pid / surv_src /
+// surv_meta, scalars.surv_count / key_or / key_and). Nothing here waits for the GPU: buffers are
+// sized for the worst case, grids are upper bounds, extents come from the device plan.
+//
+//   main stream   sort_prepare, passes, group_forward, window_reverse
+//   stream2       gather_records   (after the sort; bandwidth-bound)
+//   stream3       emit_ordered     (after group_forward; independent of window_reverse)
+// The main stream joins both before the result block goes to the host, so the next batch's
+// tail (same stream) starts after everything of this one.
+int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
+    const uint64_t Mmax = b.Mmax;  // upper bound of P + n
+    DeviceScalars *ds = dscal(b);
+    Plan *plan = dplan(b);
+    cudaStream_t st = c->stream;
     mark(c, "filter+compact done");
-    CK(cudaEventRecord(c->ev_filter, c->stream));
-    const int cur = c->cur, prev = cur ^ 1;
-    const uint64_t Smax = Mmax - P;
-    if (Mmax >= (1ull << VAL_ID_BITS))
-        return fail(c, CHRONOS_E_CAPACITY, "more than 2^27 grouped entries possible (%llu)", (unsigned long long)Mmax);
+    const uint64_t Smax = b.n;
     int rc;
-    if ((rc = ensure(c, c->arena[cur], (Mmax + 1) * CH_REC_BYTES))) return rc;
-    if ((rc = ensure(c, c->pend_key[cur], (Mmax + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->pend_slot[cur], (Mmax + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->pend_arrival[cur], (Mmax + 1) * 8))) return rc;
-    if ((rc = ensure(c, c->pend_meta[cur], Mmax + 1))) return rc;
-    c->pend_cap[cur] = Mmax;
-    if ((rc = ensure(c, c->pflag, (Mmax + 4) * 4))) return rc;
-    if ((rc = ensure(c, c->entry_out, (Smax + 4) * 4))) return rc;
-    if ((rc = ensure(c, c->wsorted, (Smax / 2 + 1) * sizeof(WinSorted)))) return rc;
-    if ((rc = ensure(c, c->windows, (Smax / 2 + 1) * sizeof(chronos_window)))) return rc;
-    if ((rc = ensure(c, c->chain_pid, (Smax + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->chain_idx, (Smax + 1) * 8))) return rc;
-    if ((rc = ensure_pid_table(c, Mmax))) return rc;
     const uint32_t max_rtiles = (uint32_t)((Mmax + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS);
+    CK(cudaMemsetAsync(c->status.p, 0, status_words(Mmax) * 8, st));
+    init_batch_kernel<<<1, 256, 0, st>>>(ds, ptr<uint32_t>(c->tickets_f), ptr<uint32_t>(c->tickets_t), 2);
+    c->launches++;
 
     // ---- stable sort by pid: plan + global digit histograms, then one kernel per pass --------
     SortParams sp;
@@ -553,220 +672,315 @@ int run_window_stage(chronos_ctx *c) {
     sp.in.surv_count = &ds->surv_count;
     sp.in.key_or = &ds->key_or;
     sp.in.key_and = &ds->key_and;
-    sp.in.P = (uint32_t)P;
-    sp.in.m_max = (uint32_t)Mmax;
+    sp.in.carry = ptr<Carry>(c->carry);
+    sp.in.m_max = (uint32_t)std::min<uint64_t>(Mmax, std::min(c->cap_M, b.cap_M));
     sp.in.win_tile = WIN_TILE;
     sp.keyA = ptr<uint32_t>(c->keyA);
     sp.keyB = ptr<uint32_t>(c->keyB);
     sp.valA = ptr<uint32_t>(c->valA);
     sp.valB = ptr<uint32_t>(c->valB);
-    sp.meta_lo = P ? ptr<uint8_t>(c->pend_meta[prev]) + (c->pend_cap[prev] - P) : nullptr;
-    sp.meta_hi = ptr<uint8_t>(c->surv_meta);
-    sp.ghist = ptr<uint32_t>(c->tickets) + N_TICKETS;  // zeroed with the tickets
-    {
-        const void *before = c->sweep_status.p;
-        const size_t need = std::max<size_t>((size_t)max_rtiles, 1) * RADIX_BINS * 8;
-        if ((rc = ensure(c, c->sweep_status, need))) return rc;
-        if (c->sweep_status.p != before || c->sweep_epoch == 0)  // fresh memory or wrapped epoch: tag 0 = "never"
-            CK(cudaMemsetAsync(c->sweep_status.p, 0, c->sweep_status.bytes, c->stream));
-    }
+    sp.pend_key = ptr<uint32_t>(prev.pend_key);
+    sp.pend_meta = ptr<uint8_t>(prev.pend_meta);
+    sp.pend_cap = (uint32_t)prev.pend_cap;
+    sp.surv_pid = ptr<uint32_t>(b.surv_pid);
+    sp.surv_meta = ptr<uint8_t>(b.surv_meta);
+    sp.ghist = ptr<uint32_t>(c->tickets_t) + N_TICKETS;  // zeroed with the tickets
+    if (c->sweep_epoch == 0) CK(cudaMemsetAsync(c->sweep_status.p, 0, c->sweep_status.bytes, st));  // wrapped epoch
     sp.status = ptr<uint64_t>(c->sweep_status);
     const unsigned sort_blocks = std::max(1u, std::min(max_rtiles, (uint32_t)c->sm_count * 4));
-    sort_prepare<<<sort_blocks, RADIX_THREADS, 0, c->stream>>>(sp);
+    sort_prepare<<<sort_blocks, RADIX_THREADS, 0, st>>>(sp);
     c->launches++;
     if ((rc = dbg_sync(c, "sort_prepare"))) return rc;
     if (Mmax == 0) {  // nothing pending, nothing submitted: only the (empty) counts go back
-        CK(cudaMemcpyAsync(c->h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaEventRecord(c->ev_end, c->stream));
+        copy_u32_kernel<<<1, 1, 0, st>>>(&ds->n_pids_seen, ptr<uint32_t>(c->pt_count));
+        CK(cudaMemcpyAsync(b.h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(b.ev_end, st));
         return CHRONOS_OK;
     }
-    {
-        for (int i = 0; i < RADIX_MAX_PASSES; i++) {  // passes beyond plan->n_passes return at once
-            sp.pass = i;
-            sp.ticket = ptr<uint32_t>(c->tickets) + 40 + i;
-            sp.epoch = ++c->sweep_epoch;
-            if (c->sweep_epoch >= (1u << 29)) c->sweep_epoch = 0;  // re-zero on the next batch
-            onesweep_pass<<<sort_blocks, RADIX_THREADS, 0, c->stream>>>(sp);
-            c->launches++;
-            if ((rc = dbg_sync(c, "onesweep_pass"))) return rc;
-        }
-        CK(cudaGetLastError());
+    for (int i = 0; i < RADIX_MAX_PASSES; i++) {  // passes beyond plan->n_passes return at once
+        sp.pass = i;
+        sp.ticket = ptr<uint32_t>(c->tickets_t) + 40 + i;
+        sp.epoch = ++c->sweep_epoch;
+        if (c->sweep_epoch >= (1u << 29)) c->sweep_epoch = 0;  // re-zero on the next batch
+        onesweep_pass<<<sort_blocks, RADIX_THREADS, 0, st>>>(sp);
+        c->launches++;
+        if ((rc = dbg_sync(c, "onesweep_pass"))) return rc;
     }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev_sorted, st));
     mark(c, "sort done");
 
-    // ---- records into the grouped arena ----------------------------------------------
-    {
+    WinParams w;
+    memset(&w, 0, sizeof(w));
+    w.plan = plan;
+    w.surv_src = ptr<uint32_t>(b.surv_src);
+    w.surv_arrival = b.explicit_arrival ? ptr<uint64_t>(b.surv_arrival) : nullptr;
+    w.base_arrival = b.base;
+    w.pend_arrival = ptr<uint64_t>(prev.pend_arrival);
+    w.pend_cap_prev = (uint32_t)prev.pend_cap;
+    w.carry = ptr<Carry>(c->carry);
+    w.surv_pid = ptr<uint32_t>(b.surv_pid);
+    w.pid_tab = ptr<uint64_t>(c->pid_tab);
+    w.pid_mask = c->pt_cap - 1;
+    w.pid_epoch = c->pt_epoch;
+    w.pid_count = ptr<uint32_t>(c->pt_count);
+    w.n_pids_out = &ds->n_pids_seen;
+    w.pflag = ptr<uint32_t>(c->pflag);
+    w.entry_out = ptr<uint32_t>(c->entry_out);
+    w.wsorted = ptr<WinSorted>(c->wsorted);
+    w.n_windows = &ds->n_windows;
+    w.pend_cap = (uint32_t)b.pend_cap;
+    w.npend_key = ptr<uint32_t>(b.pend_key);
+    w.npend_slot = ptr<uint32_t>(b.pend_slot);
+    w.npend_arrival = ptr<uint64_t>(b.pend_arrival);
+    w.npend_meta = ptr<uint8_t>(b.pend_meta);
+    w.n_pending = &ds->n_pending;
+    w.windows = ptr<chronos_window>(b.windows);
+    w.chain_pid = ptr<uint32_t>(b.chain_pid);
+    w.chain_idx = ptr<uint64_t>(b.chain_idx);
+    w.n_chains = &ds->n_chains;
+    const uint32_t tiles_m = (uint32_t)((Mmax + WIN_TILE - 1) / WIN_TILE);  // upper bounds
+    const uint32_t tiles_s = (uint32_t)((Smax + WIN_TILE - 1) / WIN_TILE);
+    uint64_t *stw = ptr<uint64_t>(c->status);
+    uint32_t *tk = ptr<uint32_t>(c->tickets_t);
+    const uint32_t cap_blocks = (uint32_t)c->sm_count * (WIN_ITEMS >= 16 ? 2 : 4);
+
+    // ---- records into the grouped arena: a bandwidth-bound copy on its own stream. It keeps
+    // its data in flight in shared memory and takes a bounded number of CTAs per SM, so that the
+    // latency-bound scans find registers and warp slots on every SM beside it (a gather that
+    // fills the SMs, or scans that fill the register file, serialise the two: profiles/README.md).
+    auto launch_gather = [&]() -> int     {
         GatherParams g;
         memset(&g, 0, sizeof(g));
         g.plan = plan;
-        g.surv_src = ptr<uint32_t>(c->surv_src);
-        g.batch = c->b_records;
-        const uint64_t pc = c->pend_cap[prev];
-        g.pend_slot = P ? ptr<uint32_t>(c->pend_slot[prev]) + (pc - P) : nullptr;
-        g.prev_arena = ptr<uint8_t>(c->arena[prev]);
-        g.arena = ptr<uint8_t>(c->arena[cur]);
-        g.slots = c->b_slots;
-        g.slot_off = c->b_slots ? ptr<uint32_t>(c->slot_off) : nullptr;
-        g.slot_ns = c->b_slots ? ptr<uint8_t>(c->surv_ns) : nullptr;
-        // bandwidth-bound copy on a second stream; it runs while the host enqueues the window scans
-        uint32_t blocks = (uint32_t)std::min<uint64_t>((Mmax + 127) / 128, (uint64_t)c->sm_count * 8);
-        CK(cudaEventRecord(c->ev_sorted, c->stream));
+        g.surv_src = ptr<uint32_t>(b.surv_src);
+        g.batch = b.records;
+        g.pend_slot = ptr<uint32_t>(prev.pend_slot);
+        g.pend_cap_prev = (uint32_t)prev.pend_cap;
+        g.prev_arena = ptr<uint8_t>(prev.arena);
+        g.arena = ptr<uint8_t>(b.arena);
+        g.slots = b.slots;
+        g.slot_off = b.slots ? ptr<uint32_t>(b.slot_off) : nullptr;
+        g.slot_ns = b.slots ? ptr<uint8_t>(b.surv_ns) : nullptr;
+        const uint32_t blocks = (uint32_t)std::min<uint64_t>((Mmax + GATHER_WARPS * GATHER_GROUP - 1) / (GATHER_WARPS * GATHER_GROUP),
+                                                             (uint64_t)c->sm_count * (uint64_t)c->gather_ctas_per_sm);
         CK(cudaStreamWaitEvent(c->stream2, c->ev_sorted, 0));
-        gather_records<<<blocks, 256, 0, c->stream2>>>(g);
+        mark(c, "gather starts", c->stream2);
+        gather_records<<<std::max(1u, blocks), GATHER_THREADS, GATHER_SMEM, c->stream2>>>(g);
         CK(cudaGetLastError());
         CK(cudaEventRecord(c->ev_gathered, c->stream2));
+        mark(c, "gather done", c->stream2);
         c->launches++;
         if ((rc = dbg_sync(c, "gather_records"))) return rc;
-    }
+        return CHRONOS_OK;
+    };
+    if (c->gather_first && (rc = launch_gather())) return rc;
 
-    // ---- window automaton + chain labeller -------------------------------------------------
+    // ---- flush automaton + chain labeller ----------------------------------------------------
+    w.ticket = tk + 60;
+    w.status = stw;  // 5 words per tile
+    group_forward<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, st>>>(w);
+    c->launches++;
+    CK(cudaGetLastError());
+    if ((rc = dbg_sync(c, "group_forward"))) return rc;
+    CK(cudaEventRecord(c->ev_fwd, st));
+    mark(c, "group_forward done");
+
+    if (!c->gather_first && (rc = launch_gather())) return rc;
+
+    // ---- windows in arrival order (stream3) beside the reverse scan (main stream) ----------
     {
-        WinParams w;
-        memset(&w, 0, sizeof(w));
-        w.plan = plan;
-        w.surv_src = ptr<uint32_t>(c->surv_src);
-        w.surv_arrival = c->b_explicit_arrival ? ptr<uint64_t>(c->surv_arrival) : nullptr;
-        w.base_arrival = c->b_base;
-        const uint64_t pc = c->pend_cap[prev];
-        w.pend_arrival = P ? ptr<uint64_t>(c->pend_arrival[prev]) + (pc - P) : nullptr;
-        w.surv_pid = ptr<uint32_t>(c->surv_pid);
-        w.pid_tab = ptr<uint64_t>(c->pid_tab);
-        w.pid_mask = c->pt_cap - 1;
-        w.pid_epoch = c->pt_epoch;
-        w.pid_count = ptr<uint32_t>(c->pt_count);
-        w.n_pids_out = &ds->n_pids_seen;
-        w.pflag = ptr<uint32_t>(c->pflag);
-        w.entry_out = ptr<uint32_t>(c->entry_out);
-        w.wsorted = ptr<WinSorted>(c->wsorted);
-        w.n_windows = &ds->n_windows;
-        w.pend_cap = (uint32_t)Mmax;
-        w.npend_key = ptr<uint32_t>(c->pend_key[cur]);
-        w.npend_slot = ptr<uint32_t>(c->pend_slot[cur]);
-        w.npend_arrival = ptr<uint64_t>(c->pend_arrival[cur]);
-        w.npend_meta = ptr<uint8_t>(c->pend_meta[cur]);
-        w.n_pending = &ds->n_pending;
-        w.windows = ptr<chronos_window>(c->windows);
-        w.chain_pid = ptr<uint32_t>(c->chain_pid);
-        w.chain_idx = ptr<uint64_t>(c->chain_idx);
-        w.n_chains = &ds->n_chains;
-        const uint32_t tiles_m = (uint32_t)((Mmax + WIN_TILE - 1) / WIN_TILE);  // upper bounds
-        const uint32_t tiles_s = (uint32_t)((Smax + WIN_TILE - 1) / WIN_TILE);
-        uint64_t *st = ptr<uint64_t>(c->status);
-        uint32_t *tk = ptr<uint32_t>(c->tickets);
-        const uint32_t cap_blocks = (uint32_t)c->sm_count * (WIN_ITEMS >= 16 ? 2 : 4);
-        w.ticket = tk + 60;
-        w.status = st;                              // 5 words per tile
-        group_forward<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, c->stream>>>(w);
-        if ((rc = dbg_sync(c, "group_forward"))) return rc;
-        w.ticket = tk + 61;
-        w.status = st + 5 * (size_t)tiles_m;        // 2 words per tile
-        window_reverse<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, c->stream>>>(w);
-        if ((rc = dbg_sync(c, "window_reverse"))) return rc;
-        w.ticket = tk + 62;
-        w.status = st + 7 * (size_t)tiles_m;        // 1 word per tile
-        emit_ordered<<<std::max(1u, std::min(tiles_s, cap_blocks)), WIN_THREADS, 0, c->stream>>>(w);
-        c->launches += 3;
+        WinParams we = w;
+        we.ticket = tk + 62;
+        we.status = stw + 7 * (size_t)tiles_m;  // 1 word per tile
+        CK(cudaStreamWaitEvent(c->stream3, c->ev_fwd, 0));
+        emit_ordered<<<std::max(1u, std::min(tiles_s, cap_blocks)), WIN_THREADS, 0, c->stream3>>>(we);
         CK(cudaGetLastError());
+        CK(cudaEventRecord(c->ev_emitted, c->stream3));
+        mark(c, "emit_ordered done", c->stream3);
+        c->launches++;
         if ((rc = dbg_sync(c, "emit_ordered"))) return rc;
     }
-    mark(c, "window kernels done");
-    CK(cudaStreamWaitEvent(c->stream, c->ev_gathered, 0));
-    mark(c, "gather joined");
-    CK(cudaMemcpyAsync(c->h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaEventRecord(c->ev_end, c->stream));
-    return CHRONOS_OK;
-}
-
-// status words needed for a batch of n raw records producing at most n survivors on top of P pending
-size_t status_words(uint64_t n, uint64_t P) {
-    const uint64_t M = n + P;
-    const uint64_t tiles_m = (M + WIN_TILE - 1) / WIN_TILE;
-    return (size_t)(8 * tiles_m + 64);
-}
-
-int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base) {
-    CK(cudaSetDevice(c->device));
-    if (c->phase == chronos_ctx::SUBMITTED) {
-        int rc = finish_batch(c);  // results dropped, state kept
-        if (rc) return rc;
-    }
-    if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
-                                      (unsigned long long)n, (unsigned long long)c->max_batch);
-    if (n >= (1ull << 32)) return fail(c, CHRONOS_E_CAPACITY, "batch too large");
-    // the batch in flight writes buffer set cur^1; the previous state stays in cur until fetch
-    const uint64_t P = c->n_pending;
-    c->cur ^= 1;
-    c->b_n = n;
-    c->b_base = base;
-    c->b_P = P;
-    c->b_S = c->b_M = c->b_W = 0;
-    c->launches = 0;
-    c->scan_slot = 0;
-    c->filter_timed = false;
-    const uint64_t ecap = P + n;
-    c->b_Mmax = ecap;
-    int rc;
-    if ((rc = ensure(c, c->keyA, (ecap + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->keyB, (ecap + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->valA, (ecap + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->valB, (ecap + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
-    const size_t sw = status_words(n, P);
-    if ((rc = ensure(c, c->status, sw * 8))) return rc;
-    CK(cudaEventRecord(c->ev_start, c->stream));
-    if (!c->x_sent) c->n_tev = 0;  // (stage 2 of an exchange step keeps the marks of its stage 1)
-    mark(c, "start");
-    CK(cudaMemsetAsync(c->status.p, 0, sw * 8, c->stream));
-    init_scalars_kernel<<<1, 256, 0, c->stream>>>(ptr<DeviceScalars>(c->scalars), ptr<uint32_t>(c->tickets));
+    w.ticket = tk + 61;
+    w.status = stw + 5 * (size_t)tiles_m;  // 2 words per tile
+    window_reverse<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, st>>>(w);
     c->launches++;
-    if (P) {
-        const int prev = c->cur ^ 1;
-        const uint64_t pc = c->pend_cap[prev];
-        const uint32_t *pk = ptr<uint32_t>(c->pend_key[prev]) + (pc - P);
-        CK(cudaMemcpyAsync(c->keyA.p, pk, P * 4, cudaMemcpyDeviceToDevice, c->stream));
-        DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-        fold_keys_kernel<<<(unsigned)std::min<uint64_t>((P + 255) / 256, 1024), 256, 0, c->stream>>>(
-            pk, (uint32_t)P, &ds->key_or, &ds->key_and);
-        c->launches++;
-    }
     CK(cudaGetLastError());
+    if ((rc = dbg_sync(c, "window_reverse"))) return rc;
+    mark(c, "window_reverse done");
+    CK(cudaStreamWaitEvent(st, c->ev_emitted, 0));
+    CK(cudaStreamWaitEvent(st, c->ev_gathered, 0));
+    mark(c, "all joined");
+    CK(cudaMemcpyAsync(b.h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(b.ev_end, st));
     return CHRONOS_OK;
 }
 
-int finish_batch(chronos_ctx *c) {
-    CK(cudaStreamSynchronize(c->stream));
-    c->b_S = c->h_plan->S;
-    c->b_M = c->h_plan->M;
-    c->b_W = c->b_M ? c->h_scalars->n_windows : 0;
-    c->n_pending = c->b_M ? c->h_scalars->n_pending : 0;
-    c->b_chains = c->b_M ? c->h_scalars->n_chains : 0;
-    if (c->h_plan->overflow) return fail(c, CHRONOS_E_CAPACITY, "more survivors than the batch was sized for");
-    c->n_pids_seen = c->b_M ? c->h_scalars->n_pids_seen : c->n_pids_seen;
-    if (c->b_exchanged) {
-        c->b_n = c->b_S;  // the upper bound the buffers were sized for is of no interest to the caller
-        const uint32_t xe = c->h_scalars->xchg_err;
-        c->phase = chronos_ctx::FETCHED;
-        if (xe & XERR_TIMEOUT)
-            return fail(c, CHRONOS_E_STATE, "exchange: a peer rank did not deliver its survivors within %.0f s",
-                        (double)c->x_timeout_ns * 1e-9);
-        if (xe & (XERR_OVERFLOW | XERR_PEER_OVERFLOW))
-            return fail(c, CHRONOS_E_CAPACITY, "exchange: survivors for one owner rank exceed the window (%u entries / %u slots per peer)",
+// ---- batch bookkeeping --------------------------------------------------------------------------
+// Wait for a submitted batch and read its result block: sizes, what it left pending.
+int complete_batch(chronos_ctx *c, BatchSet &b) {
+    if (b.state != BatchSet::SUBMITTED) return CHRONOS_OK;
+    CK(cudaEventSynchronize(b.ev_end));
+    b.state = BatchSet::DONE;
+    b.rc = CHRONOS_OK;
+    const bool any = b.Mmax != 0;  // (else only sort_prepare ran: an empty plan)
+    b.S = b.h_plan->S;
+    b.M = b.h_plan->M;
+    b.W = any && b.M ? b.h_scalars->n_windows : 0;
+    b.chains = any && b.M ? b.h_scalars->n_chains : 0;
+    b.pending_after = any && b.M ? b.h_scalars->n_pending : 0;
+    b.pids_after = b.h_scalars->n_pids_seen;
+    const bool newest = b.seq == c->seq;
+    if (newest) {
+        c->n_pending = b.pending_after;
+        c->n_pids_seen = b.pids_after;
+    } else {  // a younger batch is in flight: what it carries in is now known exactly
+        BatchSet &y = c->set[(&b == &c->set[0]) ? 1 : 0];
+        y.P_ub = std::min(y.P_ub, b.pending_after);
+        y.pids_ub = std::min(y.pids_ub, b.pids_after);
+    }
+    if (any && b.h_plan->overflow)
+        b.rc = fail(c, CHRONOS_E_CAPACITY, "more pending + surviving events than the context has room for (%llu)",
+                    (unsigned long long)std::min(c->cap_M, b.cap_M));
+    if (b.exchanged) {
+        b.n = b.S;  // the upper bound the buffers were sized for is of no interest to the caller
+        const uint32_t xe = b.h_scalars->xchg_err;
+        if (xe & XERR_TIMEOUT) {
+            // which sources are missing: the flag words of this step's half, read back for the message
+            uint32_t flags[XCHG_MAX_WORLD] = {0};
+            const uint8_t *hb = ptr<uint8_t>(c->x_window) + (size_t)(b.x_epoch & 1u) * c->x_L.half_bytes;
+            cudaMemcpy(flags, hb + 2 * XCHG_MAX_WORLD * 4, sizeof(flags), cudaMemcpyDeviceToHost);
+            char miss[96] = {0};
+            size_t o = 0;
+            for (uint32_t d = 0; d < c->x_L.world && o + 8 < sizeof(miss); d++)
+                if (flags[d] != b.x_epoch) o += (size_t)snprintf(miss + o, sizeof(miss) - o, " %u(flag %u)", d, flags[d]);
+            b.rc = fail(c, CHRONOS_E_STATE, "exchange step %u: no delivery within %.0f s from source rank(s)%s",
+                        b.x_epoch, (double)c->x_timeout_ns * 1e-9, miss);
+        }
+        else if (xe & (XERR_OVERFLOW | XERR_PEER_OVERFLOW))
+            b.rc = fail(c, CHRONOS_E_CAPACITY,
+                        "exchange: survivors for one owner rank exceed the window (%u entries / %u slots per peer)",
                         c->x_L.cap_e, c->x_L.cap_s);
     }
-    cudaEventElapsedTime(&c->t_total, c->b_exchanged ? c->ev_x0 : c->ev_start, c->ev_end);
-    if (c->trace) {
-        for (int i = 1; i < c->n_tev; i++) {
+    cudaEventElapsedTime(&b.t_total, b.exchanged ? c->ev_x0 : b.ev_start, b.ev_end);
+    if (c->trace && !b.pipelined) {
+        for (int i = 1; i < c->n_tev; i++) {  // time since the first mark (marks sit on several streams)
             float ms = 0;
-            cudaEventElapsedTime(&ms, c->tev[i - 1], c->tev[i]);
-            fprintf(stderr, "[chronos trace] %-28s %8.3f ms\n", c->tname[i], ms);
+            cudaEventSynchronize(c->tev[i]);
+            cudaEventElapsedTime(&ms, c->tev[0], c->tev[i]);
+            fprintf(stderr, "[chronos trace] %-28s at %8.3f ms\n", c->tname[i], ms);
         }
     }
-    cudaEventElapsedTime(&c->t_filter, c->ev_start, c->ev_filter);
-    // (a stage-2-only batch keeps the filter time measured by chronos_filter_partition)
-    if (c->filter_timed || (c->b_exchanged && c->x_filter_timed)) cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
+    cudaEventElapsedTime(&b.t_filter, b.ev_start, b.ev_stage1);
+    // (a stage-2-only batch keeps the filter time measured by its stage 1)
+    if (b.filter_timed || (b.exchanged && c->x_filter_timed)) cudaEventElapsedTime(&b.t_filter_kernel, b.ev_f0, b.ev_f1);
     cudaGetLastError();
-    c->phase = chronos_ctx::FETCHED;
+    return CHRONOS_OK;
+}
+
+// Upper bounds of what the next batch carries in, from the host's point of view.
+void carried_bounds(chronos_ctx *c, uint64_t &P_ub, uint64_t &pids_ub) {
+    BatchSet &l = c->set[c->last];
+    if (l.state == BatchSet::SUBMITTED) {
+        P_ub = l.P_ub + l.n;
+        pids_ub = l.pids_ub + l.n;
+    } else {
+        P_ub = c->n_pending;
+        pids_ub = c->n_pids_seen;
+    }
+}
+
+// Start of a submit of n events. Everything that can refuse the batch happens BEFORE any state
+// of the context changes: a refused submit leaves process_memory exactly as it was.
+// On success *out is the set the batch runs in and *sf the stream of its stage 1.
+int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base, bool transport, BatchSet **out, cudaStream_t *sf) {
+    CK(cudaSetDevice(c->device));
+    if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
+                                      (unsigned long long)n, (unsigned long long)c->max_batch);
+    if (base >= MAX_ARRIVAL || base + n > MAX_ARRIVAL)
+        return fail(c, CHRONOS_E_ARG, "arrival indices must stay below 2^48");
+    const int t = c->last ^ 1;
+    BatchSet &b = c->set[t], &prev = c->set[c->last];
+    int rc;
+    if (b.state == BatchSet::SUBMITTED) {  // two batches ago, never fetched: its results are dropped
+        if ((rc = complete_batch(c, b))) return rc;
+    }
+    uint64_t P_ub, pids_ub;
+    carried_bounds(c, P_ub, pids_ub);
+    auto short_of = [&](uint64_t M) { return M > MAX_GROUPED || M > c->cap_M || M > b.cap_M || n > c->cap_n || n > b.cap_n; };
+    if (short_of(P_ub + n) && prev.state == BatchSet::SUBMITTED) {
+        // the bound is too coarse: wait for the batch in flight and use the exact count
+        if ((rc = complete_batch(c, prev))) return rc;
+        carried_bounds(c, P_ub, pids_ub);
+    }
+    const uint64_t Mmax = P_ub + n;
+    if (Mmax > MAX_GROUPED)
+        return fail(c, CHRONOS_E_CAPACITY, "%llu pending + %llu new events: more than 2^27 - 1 grouped entries possible",
+                    (unsigned long long)P_ub, (unsigned long long)n);
+    if (short_of(Mmax)) {
+        // The pending lists outgrew what chronos_create reserved: the ONE place where a submit
+        // allocates. Everything in flight finishes first (its results stay fetchable); the shared
+        // temporaries and the set about to be written hold nothing that must survive.
+        if (prev.state == BatchSet::SUBMITTED && (rc = complete_batch(c, prev))) return rc;
+        CK(cudaDeviceSynchronize());
+        const uint64_t want = std::min<uint64_t>(MAX_GROUPED, Mmax + Mmax / 4);
+        if ((rc = reserve_shared(c, c->max_batch, want))) return rc;
+        if ((rc = reserve_set(c, b, c->max_batch, want))) return rc;
+    }
+    if (transport && (rc = reserve_transport(c, b))) return rc;
+    if ((rc = ensure_pid_table(c, pids_ub, Mmax))) return rc;
+
+    // ---- from here on the batch is accepted ---------------------------------------------------
+    const bool pipelined = prev.state == BatchSet::SUBMITTED && !c->no_pipeline;
+    if (prev.state == BatchSet::SUBMITTED && c->no_pipeline && (rc = complete_batch(c, prev))) return rc;
+    if (c->fetched == t) c->fetched = -1;
+    b.state = BatchSet::FREE;
+    b.n = n;
+    b.base = base;
+    b.P_ub = P_ub;
+    b.pids_ub = pids_ub;
+    b.Mmax = Mmax;
+    b.S = b.M = b.W = b.chains = 0;
+    b.records = nullptr;
+    b.slots = nullptr;
+    b.explicit_arrival = b.exchanged = b.filter_timed = false;
+    b.pipelined = pipelined;
+    b.rc = CHRONOS_OK;
+    c->launches = 0;
+    c->scan_slot = 0;
+    if (pipelined && !c->stream_f) CK(cudaStreamCreateWithPriority(&c->stream_f, cudaStreamNonBlocking, c->prio_lo));
+    cudaStream_t s1 = pipelined ? c->stream_f : c->stream;
+    if (pipelined) CK(cudaStreamWaitEvent(s1, prev.ev_stage1, 0));  // the stage-1 temporaries are shared
+    CK(cudaStreamWaitEvent(s1, b.ev_packed, 0));                    // a download may still read this set
+    CK(cudaEventRecord(b.ev_start, s1));
+    if (!c->x_sent && !pipelined) {  // (stage 2 of an exchange step keeps the marks of its stage 1)
+        c->n_tev = 0;
+        mark(c, "start");
+    }
+    *out = &b;
+    *sf = s1;
+    return CHRONOS_OK;
+}
+
+// The batch is fully enqueued: it becomes the newest one.
+void commit_batch(chronos_ctx *c, BatchSet &b) {
+    b.seq = ++c->seq;
+    b.launches = c->launches;
+    b.state = BatchSet::SUBMITTED;
+    c->last = (&b == &c->set[0]) ? 0 : 1;
+}
+
+// stage 1 -> tail hand-over: the tail stream waits for the survivors when they were produced on
+// the other stream
+int join_stage1(chronos_ctx *c, BatchSet &b, cudaStream_t s1) {
+    CK(cudaEventRecord(b.ev_stage1, s1));
+    if (s1 != c->stream) CK(cudaStreamWaitEvent(c->stream, b.ev_stage1, 0));
+    return CHRONOS_OK;
+}
+
+int no_batch_in_flight(chronos_ctx *c) {
+    for (BatchSet &b : c->set)
+        if (b.state == BatchSet::SUBMITTED || b.state == BatchSet::DONE) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
     return CHRONOS_OK;
 }
 
@@ -813,45 +1027,68 @@ int chronos_device_ok(int device) {
 
 const char *chronos_last_error(const chronos_ctx *ctx) { return ctx ? ctx->err : g_static_err; }
 
-int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
-    if (!out || max_batch_events == 0 || max_batch_events >= (1ull << 32)) return CHRONOS_E_ARG;
+int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pending_events, chronos_ctx **out) {
+    if (!out || max_batch_events == 0 || max_batch_events > MAX_GROUPED) return CHRONOS_E_ARG;
     *out = nullptr;
     if (chronos_device_ok(device) != CHRONOS_OK) return CHRONOS_E_CUDA;
     chronos_ctx *c = new (std::nothrow) chronos_ctx();
     if (!c) return CHRONOS_E_NOMEM;
     c->device = device;
     c->max_batch = max_batch_events;
+    c->max_pending = std::min<uint64_t>(max_pending_events, MAX_GROUPED - max_batch_events);
     const char *fv = getenv("CHRONOS_FILTER_VARIANT");
     c->filter_variant = fv ? atoi(fv) : -1;  // -1: the tuned default (TILE 32, 1 stage)
+    const char *gc = getenv("CHRONOS_GATHER_CTAS");
+    c->gather_ctas_per_sm = gc ? std::max(1, atoi(gc)) : 2;
+    c->no_pipeline = getenv("CHRONOS_NO_PIPELINE") != nullptr;
+    const char *gf = getenv("CHRONOS_GATHER_FIRST");
+    c->gather_first = gf ? atoi(gf) != 0 : true;
+    const bool gather_low = getenv("CHRONOS_GATHER_LOW") != nullptr;
     c->trace = getenv("CHRONOS_TRACE") != nullptr;
     auto boot = [&]() -> int {
         CK(cudaSetDevice(device));
-        cudaDeviceProp p;
-        CK(cudaGetDeviceProperties(&p, device));
-        c->sm_count = p.multiProcessorCount;
+        c->sm_count = device_sm_count(device);
+        int rc;
+        if ((rc = configure_kernels(c))) return rc;
         int prio_lo = 0, prio_hi = 0;
         CK(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-        // the latency-bound scans get priority over the bandwidth-bound record gather
+        // the latency-bound scans get priority over the bandwidth-bound work beside them
         CK(cudaStreamCreateWithPriority(&c->stream, cudaStreamNonBlocking, prio_hi));
-        CK(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, prio_lo));
-        CK(cudaEventCreateWithFlags(&c->ev_sorted, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&c->ev_gathered, cudaEventDisableTiming));
-        CK(cudaEventCreate(&c->ev_start));
-        CK(cudaEventCreate(&c->ev_filter));
-        CK(cudaEventCreate(&c->ev_end));
-        CK(cudaEventCreate(&c->ev_f0));
-        CK(cudaEventCreate(&c->ev_f1));
-        CK(cudaMallocHost(reinterpret_cast<void **>(&c->h_scalars), RESULT_BLOCK_BYTES));
-        memset(c->h_scalars, 0, RESULT_BLOCK_BYTES);
-        c->h_plan = reinterpret_cast<Plan *>(reinterpret_cast<uint8_t *>(c->h_scalars) + 64);
-        int rc;
-        if ((rc = ensure(c, c->tickets, TICKET_BYTES))) return rc;
-        if ((rc = ensure(c, c->scalars, RESULT_BLOCK_BYTES))) return rc;
+        CK(cudaStreamCreateWithPriority(&c->stream3, cudaStreamNonBlocking, prio_hi));
+        CK(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, gather_low ? prio_lo : prio_hi));
+        c->prio_lo = prio_lo;  // stream_f and dl_stream are created when first needed
+        for (cudaEvent_t *e : {&c->ev_sorted, &c->ev_gathered, &c->ev_fwd, &c->ev_emitted, &c->dl_ready, &c->dl_done[0],
+                               &c->dl_done[1]})
+            CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
+        CK(cudaEventCreate(&c->ev_x0));
+        for (BatchSet &b : c->set) {
+            for (cudaEvent_t *e : {&b.ev_start, &b.ev_stage1, &b.ev_end, &b.ev_f0, &b.ev_f1}) CK(cudaEventCreate(e));
+            CK(cudaEventCreateWithFlags(&b.ev_packed, cudaEventDisableTiming));
+            CK(cudaMallocHost(reinterpret_cast<void **>(&b.h_scalars), RESULT_BLOCK_BYTES));
+            memset(b.h_scalars, 0, RESULT_BLOCK_BYTES);
+            b.h_plan = reinterpret_cast<Plan *>(reinterpret_cast<uint8_t *>(b.h_scalars) + 64);
+            if ((rc = ensure(c, b.result, RESULT_BLOCK_BYTES))) return rc;
+            CK(cudaMemsetAsync(b.result.p, 0, RESULT_BLOCK_BYTES, c->stream));
+        }
+        if ((rc = ensure(c, c->tickets_f, TICKET_BYTES))) return rc;
+        if ((rc = ensure(c, c->tickets_t, TICKET_BYTES))) return rc;
+        if ((rc = ensure(c, c->carry, 256))) return rc;
         if ((rc = ensure(c, c->pt_count, 256))) return rc;
         if ((rc = ensure(c, c->comm_memo, (size_t)COMM_MEMO_SLOTS * 24))) return rc;
+        if ((rc = ensure(c, c->x_totals, 512))) return rc;
+        if ((rc = ensure(c, c->dl_ticket, 256))) return rc;
+        if ((rc = ensure(c, c->dl_scan_status, 1 << 16))) return rc;
+        if ((rc = ensure(c, c->pack_off, 1 << 16))) return rc;
+        CK(cudaMemsetAsync(c->dl_scan_status.p, 0, c->dl_scan_status.bytes, c->stream));
         CK(cudaMemsetAsync(c->comm_memo.p, 0, (size_t)COMM_MEMO_SLOTS * 24, c->stream));
         CK(cudaMemsetAsync(c->pt_count.p, 0, 256, c->stream));
-        return CHRONOS_OK;
+        // every buffer a submit touches, for the largest batch on top of the pending budget
+        const uint64_t M = c->max_batch + c->max_pending;
+        if ((rc = reserve_shared(c, c->max_batch, M))) return rc;
+        for (BatchSet &b : c->set)
+            if ((rc = reserve_set(c, b, c->max_batch, M))) return rc;
+        if ((rc = ensure_pid_table(c, 0, M))) return rc;
+        return set_carry(c, 0u, 0u, 0xffffffffu);
     };
     int rc = boot();
     if (rc != CHRONOS_OK) {
@@ -862,68 +1099,85 @@ int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
     return CHRONOS_OK;
 }
 
+int chronos_create(int device, uint64_t max_batch_events, chronos_ctx **out) {
+    // default pending budget: as many pending events as one full batch holds (at least 64 K)
+    return chronos_create_sized(device, max_batch_events, std::max<uint64_t>(max_batch_events, 65536), out);
+}
+
 int chronos_destroy(chronos_ctx *c) {
     if (!c) return CHRONOS_E_ARG;
     cudaSetDevice(c->device);
-    if (c->stream) cudaStreamSynchronize(c->stream);
-    DevBuf *all[] = {&c->d_batch, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->surv_src, &c->surv_meta, &c->pflag,
-                     &c->entry_out, &c->wsorted, &c->comm_memo, &c->sp_ns, &c->surv_pid, &c->surv_ns, &c->slot_off, &c->pid_tab, &c->pt_count, &c->chain_pid, &c->chain_idx, &c->sp_key, &c->sp_src, &c->sp_meta, &c->tile_count, &c->windows, &c->owner_table, &c->surv_arrival, &c->arena[0],
-                     &c->arena[1], &c->pend_key[0], &c->pend_key[1], &c->pend_slot[0], &c->pend_slot[1],
-                     &c->pend_arrival[0], &c->pend_arrival[1], &c->pend_meta[0], &c->pend_meta[1], &c->status,
-                     &c->tickets, &c->scalars, &c->scan_status, &c->sweep_status, &c->pack, &c->pack_off};
+    cudaDeviceSynchronize();
+    for (BatchSet &b : c->set) {
+        DevBuf *all[] = {&b.arena, &b.pend_key, &b.pend_slot, &b.pend_arrival, &b.pend_meta, &b.surv_src, &b.surv_meta,
+                         &b.surv_pid, &b.surv_ns, &b.surv_arrival, &b.slot_off, &b.windows, &b.chain_pid, &b.chain_idx,
+                         &b.d_batch, &b.result};
+        for (DevBuf *d : all) release(*d);
+        if (b.h_scalars) cudaFreeHost(b.h_scalars);
+        for (cudaEvent_t e : {b.ev_start, b.ev_stage1, b.ev_end, b.ev_f0, b.ev_f1, b.ev_packed})
+            if (e) cudaEventDestroy(e);
+    }
+    DevBuf *all[] = {&c->carry, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->pflag, &c->entry_out, &c->wsorted, &c->status,
+                     &c->sweep_status, &c->sp_key, &c->sp_src, &c->sp_meta, &c->sp_ns, &c->tile_count, &c->scan_status,
+                     &c->tickets_f, &c->tickets_t, &c->owner_table, &c->comm_memo, &c->pid_tab, &c->pt_count, &c->pack,
+                     &c->pack_off, &c->dl_scan_status, &c->dl_ticket, &c->dl_stage[0], &c->dl_stage[1], &c->x_totals};
     for (DevBuf *b : all) release(*b);
     for (int d = 0; d < XCHG_MAX_WORLD; d++)
         if (c->x_opened[d] && c->x_peer[d]) cudaIpcCloseMemHandle(c->x_peer[d]);
     release(c->x_window);
-    release(c->x_totals);
-    if (c->dl_stream) {
-        cudaStreamSynchronize(c->dl_stream);
-        cudaStreamDestroy(c->dl_stream);
-        cudaEventDestroy(c->dl_ready);
-        cudaEventDestroy(c->dl_done[0]);
-        cudaEventDestroy(c->dl_done[1]);
-    }
-    release(c->dl_stage[0]);
-    release(c->dl_stage[1]);
-    if (c->ev_x0) cudaEventDestroy(c->ev_x0);
-    if (c->h_scalars) cudaFreeHost(c->h_scalars);
-    if (c->ev_start) cudaEventDestroy(c->ev_start);
-    if (c->ev_filter) cudaEventDestroy(c->ev_filter);
-    if (c->ev_end) cudaEventDestroy(c->ev_end);
-    if (c->ev_f0) cudaEventDestroy(c->ev_f0);
-    if (c->ev_f1) cudaEventDestroy(c->ev_f1);
-    if (c->ev_sorted) cudaEventDestroy(c->ev_sorted);
-    if (c->ev_gathered) cudaEventDestroy(c->ev_gathered);
-    if (c->stream2) cudaStreamDestroy(c->stream2);
-    if (c->stream) cudaStreamDestroy(c->stream);
+    for (cudaEvent_t e : {c->ev_sorted, c->ev_gathered, c->ev_fwd, c->ev_emitted, c->dl_ready, c->dl_done[0], c->dl_done[1],
+                          c->ev_x0})
+        if (e) cudaEventDestroy(e);
+    for (int i = 0; i < 24; i++)
+        if (c->tev[i]) cudaEventDestroy(c->tev[i]);
+    for (cudaStream_t s : {c->stream, c->stream_f, c->stream2, c->stream3, c->dl_stream})
+        if (s) cudaStreamDestroy(s);
     cudaGetLastError();
     delete c;
     return CHRONOS_OK;
 }
 
+// upload of a host batch into the set's staging buffer (allocated on the first host-memory submit)
+static int stage_records(chronos_ctx *c, BatchSet &b, const void *records, uint64_t n, cudaStream_t st,
+                         const uint8_t **d_recs) {
+    *d_recs = nullptr;
+    if (!n) return CHRONOS_OK;
+    if (is_device_pointer(records)) {
+        *d_recs = static_cast<const uint8_t *>(records);
+        return CHRONOS_OK;
+    }
+    int rc;
+    if ((rc = ensure(c, b.d_batch, c->max_batch * CH_REC_BYTES))) return rc;
+    CK(cudaMemcpyAsync(b.d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, st));
+    *d_recs = ptr<uint8_t>(b.d_batch);
+    return CHRONOS_OK;
+}
+
+static int check_records_arg(chronos_ctx *c, const void *records, uint64_t n) {
+    if (n && !records) return fail(c, CHRONOS_E_ARG, "records is NULL");
+    if (n && is_device_pointer(records) && ((uintptr_t)records & 15))
+        return fail(c, CHRONOS_E_ARG, "device records pointer must be 16-byte aligned");
+    return CHRONOS_OK;
+}
+
 int chronos_submit(chronos_ctx *c, const void *records, uint64_t n, uint64_t base_arrival_index) {
     if (!c) return CHRONOS_E_ARG;
-    if (n && !records) return fail(c, CHRONOS_E_ARG, "records is NULL");
-    int rc = begin_batch(c, n, base_arrival_index);
-    if (rc) return rc;
+    int rc;
+    if ((rc = check_records_arg(c, records, n))) return rc;
+    if (c->x_sent) return fail(c, CHRONOS_E_STATE, "an exchange step is half done: call chronos_submit_exchanged");
+    BatchSet *bp;
+    cudaStream_t s1;
+    if ((rc = begin_batch(c, n, base_arrival_index, false, &bp, &s1))) return rc;
+    BatchSet &b = *bp, &prev = c->set[c->last];
     const uint8_t *d_recs = nullptr;
-    if (n) {
-        if (is_device_pointer(records)) {
-            if ((uintptr_t)records & 15) return fail(c, CHRONOS_E_ARG, "device records pointer must be 16-byte aligned");
-            d_recs = static_cast<const uint8_t *>(records);
-        } else {
-            if ((rc = ensure(c, c->d_batch, n * CH_REC_BYTES))) return rc;
-            CK(cudaMemcpyAsync(c->d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, c->stream));
-            d_recs = ptr<uint8_t>(c->d_batch);
-        }
-    }
-    c->b_records = d_recs;
-    c->b_slots = nullptr;
-    c->b_explicit_arrival = false;
-    c->b_exchanged = false;
-    if (n && (rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA) + c->b_P))) return rc;
-    if ((rc = run_window_stage(c))) return rc;
-    c->phase = chronos_ctx::SUBMITTED;
+    if ((rc = stage_records(c, b, records, n, s1, &d_recs))) return rc;
+    b.records = d_recs;
+    init_batch_kernel<<<1, 256, 0, s1>>>(dscal(b), ptr<uint32_t>(c->tickets_f), ptr<uint32_t>(c->tickets_t), 1);
+    c->launches++;
+    if (n && (rc = run_filter_stage(c, b, d_recs, n, s1))) return rc;
+    if ((rc = join_stage1(c, b, s1))) return rc;
+    if ((rc = run_window_stage(c, b, prev))) return rc;
+    commit_batch(c, b);
     return CHRONOS_OK;
 }
 
@@ -933,141 +1187,191 @@ int chronos_submit_survivors(chronos_ctx *c, const void *slots, const uint64_t *
     if (n && (!is_device_pointer(slots) || ((uintptr_t)slots & 15) || !is_device_pointer(hdr)))
         return fail(c, CHRONOS_E_ARG, "slots and hdr must be device pointers (slots 16-byte aligned)");
     if (n_slots < 3 * n || n_slots > 18 * n) return fail(c, CHRONOS_E_ARG, "slot count inconsistent with entry count");
-    int rc = begin_batch(c, n, 0);
-    if (rc) return rc;
-    c->b_records = nullptr;
-    c->b_slots = static_cast<const uint4 *>(slots);
-    c->b_explicit_arrival = true;
-    c->b_exchanged = false;
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
+    if (c->x_sent) return fail(c, CHRONOS_E_STATE, "an exchange step is half done: call chronos_submit_exchanged");
+    int rc;
+    BatchSet *bp;
+    cudaStream_t s1;
+    if ((rc = begin_batch(c, n, 0, true, &bp, &s1))) return rc;
+    BatchSet &b = *bp, &prev = c->set[c->last];
+    b.slots = static_cast<const uint4 *>(slots);
+    b.explicit_arrival = true;
+    DeviceScalars *ds = dscal(b);
+    init_batch_kernel<<<1, 256, 0, s1>>>(ds, ptr<uint32_t>(c->tickets_f), ptr<uint32_t>(c->tickets_t), 1);
+    c->launches++;
     if (n) {
-        if ((rc = ensure(c, c->surv_arrival, n * 8))) return rc;
-        if ((rc = ensure(c, c->surv_pid, (n + 1) * 4))) return rc;
-        if ((rc = ensure(c, c->surv_ns, n + 1))) return rc;
-        if ((rc = ensure(c, c->slot_off, (n + 8) * 4))) return rc;
         const unsigned blocks = (unsigned)std::min<uint64_t>((n + 255) / 256, 2048);
-        unpack_hdr_kernel<<<blocks, 256, 0, c->stream>>>(hdr, (uint32_t)n, ptr<uint64_t>(c->surv_arrival),
-                                                         ptr<uint8_t>(c->surv_meta), ptr<uint8_t>(c->surv_ns),
-                                                         ptr<uint32_t>(c->slot_off));
-        if ((rc = launch_scan(c, ptr<uint32_t>(c->slot_off), n))) return rc;
-        extract_pid_kernel<<<blocks, 256, 0, c->stream>>>(c->b_slots, ptr<uint32_t>(c->slot_off), (uint32_t)n,
-                                                          ptr<uint32_t>(c->keyA) + c->b_P, ptr<uint32_t>(c->surv_pid),
-                                                          ptr<uint32_t>(c->surv_src), &ds->key_or, &ds->key_and);
+        unpack_hdr_kernel<<<blocks, 256, 0, s1>>>(hdr, (uint32_t)n, ptr<uint64_t>(b.surv_arrival), ptr<uint8_t>(b.surv_meta),
+                                                  ptr<uint8_t>(b.surv_ns), ptr<uint32_t>(b.slot_off));
+        if ((rc = launch_scan(c, s1, ptr<uint32_t>(b.slot_off), n))) return rc;
+        extract_pid_kernel<<<blocks, 256, 0, s1>>>(b.slots, ptr<uint32_t>(b.slot_off), (uint32_t)n, ptr<uint32_t>(b.surv_pid),
+                                                   ptr<uint32_t>(b.surv_src), &ds->key_or, &ds->key_and);
         CK(cudaGetLastError());
-        c->launches += 2;
-        set_u32_kernel<<<1, 1, 0, c->stream>>>(&ds->surv_count, (uint32_t)n);
-        c->launches++;
+        set_u32_kernel<<<1, 1, 0, s1>>>(&ds->surv_count, (uint32_t)n);
+        c->launches += 3;
     }
-    if ((rc = run_window_stage(c))) return rc;
-    c->phase = chronos_ctx::SUBMITTED;
+    if ((rc = join_stage1(c, b, s1))) return rc;
+    if ((rc = run_window_stage(c, b, prev))) return rc;
+    commit_batch(c, b);
     return CHRONOS_OK;
 }
 
 int chronos_fetch(chronos_ctx *c, chronos_counts *out) {
     if (!c || !out) return CHRONOS_E_ARG;
-    if (c->phase == chronos_ctx::IDLE) return fail(c, CHRONOS_E_STATE, "nothing submitted");
     CK(cudaSetDevice(c->device));
-    if (c->phase == chronos_ctx::SUBMITTED) {
-        int rc = finish_batch(c);
+    // the oldest batch not fetched yet; else the one fetched last (its counts again)
+    int k = -1;
+    const int older = c->last ^ 1;
+    if (c->set[older].state == BatchSet::SUBMITTED || c->set[older].state == BatchSet::DONE) k = older;
+    else if (c->set[c->last].state == BatchSet::SUBMITTED || c->set[c->last].state == BatchSet::DONE) k = c->last;
+    else if (c->fetched >= 0 && c->set[c->fetched].state == BatchSet::FETCHED) k = c->fetched;
+    if (k < 0) return fail(c, CHRONOS_E_STATE, "nothing submitted");
+    BatchSet &b = c->set[k];
+    if (b.state != BatchSet::FETCHED) {
+        int rc = complete_batch(c, b);
         if (rc) return rc;
+        b.state = BatchSet::FETCHED;
+        c->fetched = k;
+        if (b.rc) return b.rc;  // (c->err was written when the batch completed)
     }
     memset(out, 0, sizeof(*out));
-    out->n_events = c->b_n;
-    out->n_survivors = c->b_S;
-    out->n_windows = c->b_W;
-    out->n_arena = c->b_M;
-    out->n_pending = c->n_pending;
-    out->n_chains = c->b_chains;
-    out->n_pids_seen = c->n_pids_seen;
+    out->n_events = b.n;
+    out->n_survivors = b.S;
+    out->n_windows = b.W;
+    out->n_arena = b.M;
+    out->n_pending = b.pending_after;
+    out->n_chains = b.chains;
+    out->n_pids_seen = b.pids_after;
     return CHRONOS_OK;
 }
 
-static int need_fetched(chronos_ctx *c) {
+static int need_fetched(chronos_ctx *c, BatchSet **b) {
     if (!c) return CHRONOS_E_ARG;
-    if (c->phase != chronos_ctx::FETCHED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    if (c->fetched < 0 || c->set[c->fetched].state != BatchSet::FETCHED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
     cudaError_t e = cudaSetDevice(c->device);
     if (e != cudaSuccess) return fail(c, CHRONOS_E_CUDA, "cudaSetDevice: %s", cudaGetErrorString(e));
+    *b = &c->set[c->fetched];
     return CHRONOS_OK;
 }
 
+// copies for the host run on dl_stream: a younger batch may be busy on the other streams
 int chronos_copy_survivors(chronos_ctx *c, uint64_t *global_idx, uint8_t *meta, uint64_t cap) {
-    int rc = need_fetched(c);
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
     if (rc) return rc;
-    const uint64_t S = c->b_S;
+    BatchSet &b = *bp;
+    const uint64_t S = b.S;
     if (cap < S || (S && !global_idx)) return fail(c, CHRONOS_E_ARG, "survivor buffer too small (%llu < %llu)",
                                                    (unsigned long long)cap, (unsigned long long)S);
     if (!S) return CHRONOS_OK;
-    if (c->b_explicit_arrival) {
-        CK(cudaMemcpyAsync(global_idx, c->surv_arrival.p, S * 8, cudaMemcpyDeviceToHost, c->stream));
+    cudaStream_t st;
+    if ((rc = host_stream(c, &st))) return rc;
+    if (b.explicit_arrival) {
+        CK(cudaMemcpyAsync(global_idx, b.surv_arrival.p, S * 8, cudaMemcpyDeviceToHost, st));
     } else {
         if ((rc = ensure(c, c->pack, S * 8))) return rc;
-        add_base_kernel<<<(unsigned)std::min<uint64_t>((S + 255) / 256, 2048), 256, 0, c->stream>>>(
-            ptr<uint32_t>(c->surv_src), (uint32_t)S, c->b_base, ptr<uint64_t>(c->pack));
+        add_base_kernel<<<(unsigned)std::min<uint64_t>((S + 255) / 256, 2048), 256, 0, st>>>(
+            ptr<uint32_t>(b.surv_src), (uint32_t)S, b.base, ptr<uint64_t>(c->pack));
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(global_idx, c->pack.p, S * 8, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(global_idx, c->pack.p, S * 8, cudaMemcpyDeviceToHost, st));
     }
-    if (meta) CK(cudaMemcpyAsync(meta, c->surv_meta.p, S, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    if (meta) CK(cudaMemcpyAsync(meta, b.surv_meta.p, S, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return CHRONOS_OK;
 }
 
 int chronos_copy_windows(chronos_ctx *c, chronos_window *dst, uint64_t cap) {
-    int rc = need_fetched(c);
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
     if (rc) return rc;
-    if (cap < c->b_W || (c->b_W && !dst)) return fail(c, CHRONOS_E_ARG, "window buffer too small");
-    if (!c->b_W) return CHRONOS_OK;
-    CK(cudaMemcpyAsync(dst, c->windows.p, c->b_W * sizeof(chronos_window), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    if (cap < bp->W || (bp->W && !dst)) return fail(c, CHRONOS_E_ARG, "window buffer too small");
+    if (!bp->W) return CHRONOS_OK;
+    cudaStream_t st;
+    if ((rc = host_stream(c, &st))) return rc;
+    CK(cudaMemcpyAsync(dst, bp->windows.p, bp->W * sizeof(chronos_window), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return CHRONOS_OK;
 }
 
 int chronos_copy_arena(chronos_ctx *c, void *dst, uint64_t cap_records) {
-    int rc = need_fetched(c);
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
     if (rc) return rc;
-    if (cap_records < c->b_M || (c->b_M && !dst)) return fail(c, CHRONOS_E_ARG, "arena buffer too small");
-    if (!c->b_M) return CHRONOS_OK;
-    CK(cudaMemcpyAsync(dst, c->arena[c->cur].p, c->b_M * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    if (cap_records < bp->M || (bp->M && !dst)) return fail(c, CHRONOS_E_ARG, "arena buffer too small");
+    if (!bp->M) return CHRONOS_OK;
+    cudaStream_t st;
+    if ((rc = host_stream(c, &st))) return rc;
+    CK(cudaMemcpyAsync(dst, bp->arena.p, bp->M * CH_REC_BYTES, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return CHRONOS_OK;
+}
+
+// exclusive scan of n counters on dl_stream (own status words and ticket: a stage 1 may be
+// scanning on another stream at the same time)
+static int dl_scan(chronos_ctx *c, cudaStream_t st, uint32_t *data, uint64_t n) {
+    if (n == 0) return CHRONOS_OK;
+    const uint32_t n_tiles = (uint32_t)((n + SCAN_TILE - 1) / SCAN_TILE);
+    int rc;
+    const void *before = c->dl_scan_status.p;
+    if ((rc = ensure(c, c->dl_scan_status, std::max<size_t>((size_t)n_tiles * 8, 1 << 16)))) return rc;
+    if (c->dl_scan_status.p != before || c->dl_scan_epoch == 0)
+        CK(cudaMemsetAsync(c->dl_scan_status.p, 0, c->dl_scan_status.bytes, st));
+    CK(cudaMemsetAsync(c->dl_ticket.p, 0, 4, st));
+    ScanParams sp;
+    sp.data = data;
+    sp.n = (uint32_t)n;
+    sp.n_ptr = nullptr;
+    sp.ticket = ptr<uint32_t>(c->dl_ticket);
+    sp.status = ptr<uint64_t>(c->dl_scan_status);
+    sp.epoch = ++c->dl_scan_epoch;
+    if (c->dl_scan_epoch >= (1u << 29)) c->dl_scan_epoch = 0;
+    scan_exclusive_u32<<<std::min<uint32_t>(n_tiles, (uint32_t)c->sm_count * 2), SCAN_THREADS, 0, st>>>(sp);
+    CK(cudaGetLastError());
     return CHRONOS_OK;
 }
 
 // records of all windows of the fetched batch, window after window, into a DEVICE buffer
 // (every grouped entry is in a window or pending, so the total is known without a read-back)
-static int pack_window_records(chronos_ctx *c, uint8_t *dst_dev) {
-    const uint64_t W = c->b_W;
+static int pack_window_records(chronos_ctx *c, cudaStream_t st, BatchSet &b, uint8_t *dst_dev) {
+    const uint64_t W = b.W;
     if (!W) return CHRONOS_OK;
     int rc;
     if ((rc = ensure(c, c->pack_off, (W + 8) * 4))) return rc;
     const unsigned blocks = (unsigned)std::min<uint64_t>((W + 255) / 256, 2048);
-    window_len_kernel<<<blocks, 256, 0, c->stream>>>(ptr<chronos_window>(c->windows), (uint32_t)W, ptr<uint32_t>(c->pack_off));
-    if ((rc = launch_scan(c, ptr<uint32_t>(c->pack_off), W, nullptr, 56))) return rc;
-    pack_windows_kernel<<<(unsigned)std::min<uint64_t>((W + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
-        ptr<uint8_t>(c->arena[c->cur]), ptr<chronos_window>(c->windows), ptr<uint32_t>(c->pack_off), (uint32_t)W, dst_dev);
+    window_len_kernel<<<blocks, 256, 0, st>>>(ptr<chronos_window>(b.windows), (uint32_t)W, ptr<uint32_t>(c->pack_off));
+    if ((rc = dl_scan(c, st, ptr<uint32_t>(c->pack_off), W))) return rc;
+    pack_windows_kernel<<<(unsigned)std::min<uint64_t>((W + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, st>>>(
+        ptr<uint8_t>(b.arena), ptr<chronos_window>(b.windows), ptr<uint32_t>(c->pack_off), (uint32_t)W, dst_dev);
     CK(cudaGetLastError());
     return CHRONOS_OK;
 }
 
 int chronos_copy_window_records(chronos_ctx *c, void *dst, uint64_t cap_records) {
-    int rc = need_fetched(c);
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
     if (rc) return rc;
-    const uint64_t tot = c->b_M - c->n_pending;  // grouped entries that left in a window
-    if (!c->b_W) return CHRONOS_OK;
+    BatchSet &b = *bp;
+    const uint64_t tot = b.M - b.pending_after;  // grouped entries that left in a window
+    if (!b.W) return CHRONOS_OK;
     if (cap_records < tot || !dst) return fail(c, CHRONOS_E_ARG, "window record buffer too small (%llu < %llu)",
                                                (unsigned long long)cap_records, (unsigned long long)tot);
     if ((rc = ensure(c, c->pack, tot * CH_REC_BYTES))) return rc;
-    if ((rc = pack_window_records(c, ptr<uint8_t>(c->pack)))) return rc;
-    CK(cudaMemcpyAsync(dst, c->pack.p, tot * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    cudaStream_t st;
+    if ((rc = host_stream(c, &st))) return rc;
+    if ((rc = pack_window_records(c, st, b, ptr<uint8_t>(c->pack)))) return rc;
+    CK(cudaMemcpyAsync(dst, c->pack.p, tot * CH_REC_BYTES, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return CHRONOS_OK;
 }
 
 // ---- asynchronous download of a fetched batch's results ---------------------------------------
 int chronos_download_begin(chronos_ctx *c, void *host_dst, uint64_t cap_bytes, chronos_download *out) {
-    int rc = need_fetched(c);
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
     if (rc) return rc;
+    BatchSet &b = *bp;
     if (!out) return fail(c, CHRONOS_E_ARG, "out is NULL");
     auto al = [](uint64_t v) { return (v + 255) & ~255ull; };
-    const uint64_t S = c->b_S, W = c->b_W, R = c->b_W ? c->b_M - c->n_pending : 0;
+    const uint64_t S = b.S, W = b.W, R = b.W ? b.M - b.pending_after : 0;
     memset(out, 0, sizeof(*out));
     out->n_survivors = S;
     out->n_windows = W;
@@ -1081,11 +1385,6 @@ int chronos_download_begin(chronos_ctx *c, void *host_dst, uint64_t cap_bytes, c
     if (!host_dst || cap_bytes < out->total_bytes)
         return fail(c, CHRONOS_E_ARG, "download buffer too small (%llu < %llu bytes)", (unsigned long long)cap_bytes,
                     (unsigned long long)out->total_bytes);
-    if (!c->dl_stream) {
-        CK(cudaStreamCreateWithFlags(&c->dl_stream, cudaStreamNonBlocking));
-        CK(cudaEventCreateWithFlags(&c->dl_ready, cudaEventDisableTiming));
-        for (int k = 0; k < 2; k++) CK(cudaEventCreateWithFlags(&c->dl_done[k], cudaEventDisableTiming));
-    }
     const int k = c->dl_k;
     if (c->dl_inflight[k]) {  // the copy started two calls ago still reads this staging buffer
         CK(cudaEventSynchronize(c->dl_done[k]));
@@ -1093,22 +1392,25 @@ int chronos_download_begin(chronos_ctx *c, void *host_dst, uint64_t cap_bytes, c
     }
     if ((rc = ensure(c, c->dl_stage[k], out->total_bytes))) return rc;
     uint8_t *st = ptr<uint8_t>(c->dl_stage[k]);
+    if (!c->dl_stream) CK(cudaStreamCreateWithPriority(&c->dl_stream, cudaStreamNonBlocking, c->prio_lo));
+    cudaStream_t ds;  // packing: main stream while idle; the copy to the host always on dl_stream
+    if ((rc = host_stream(c, &ds))) return rc;
     if (S) {
-        if (c->b_explicit_arrival) {
-            CK(cudaMemcpyAsync(st + out->off_survivor_idx, c->surv_arrival.p, S * 8, cudaMemcpyDeviceToDevice, c->stream));
+        if (b.explicit_arrival) {
+            CK(cudaMemcpyAsync(st + out->off_survivor_idx, b.surv_arrival.p, S * 8, cudaMemcpyDeviceToDevice, ds));
         } else {
-            add_base_kernel<<<(unsigned)std::min<uint64_t>((S + 255) / 256, 2048), 256, 0, c->stream>>>(
-                ptr<uint32_t>(c->surv_src), (uint32_t)S, c->b_base, reinterpret_cast<uint64_t *>(st + out->off_survivor_idx));
+            add_base_kernel<<<(unsigned)std::min<uint64_t>((S + 255) / 256, 2048), 256, 0, ds>>>(
+                ptr<uint32_t>(b.surv_src), (uint32_t)S, b.base, reinterpret_cast<uint64_t *>(st + out->off_survivor_idx));
             CK(cudaGetLastError());
         }
-        CK(cudaMemcpyAsync(st + out->off_survivor_meta, c->surv_meta.p, S, cudaMemcpyDeviceToDevice, c->stream));
+        CK(cudaMemcpyAsync(st + out->off_survivor_meta, b.surv_meta.p, S, cudaMemcpyDeviceToDevice, ds));
     }
     if (W) {
-        CK(cudaMemcpyAsync(st + out->off_windows, c->windows.p, W * sizeof(chronos_window), cudaMemcpyDeviceToDevice, c->stream));
-        if ((rc = pack_window_records(c, st + out->off_window_records))) return rc;
+        CK(cudaMemcpyAsync(st + out->off_windows, b.windows.p, W * sizeof(chronos_window), cudaMemcpyDeviceToDevice, ds));
+        if ((rc = pack_window_records(c, ds, b, st + out->off_window_records))) return rc;
     }
-    CK(cudaEventRecord(c->dl_ready, c->stream));
-    CK(cudaStreamWaitEvent(c->dl_stream, c->dl_ready, 0));
+    CK(cudaEventRecord(b.ev_packed, ds));  // the set itself may be written again from here on
+    CK(cudaStreamWaitEvent(c->dl_stream, b.ev_packed, 0));
     CK(cudaMemcpyAsync(host_dst, st, out->total_bytes, cudaMemcpyDeviceToHost, c->dl_stream));
     CK(cudaEventRecord(c->dl_done[k], c->dl_stream));
     c->dl_inflight[k] = true;
@@ -1118,70 +1420,73 @@ int chronos_download_begin(chronos_ctx *c, void *host_dst, uint64_t cap_bytes, c
 
 int chronos_download_wait(chronos_ctx *c) {
     if (!c) return CHRONOS_E_ARG;
-    if (!c->dl_stream) return CHRONOS_OK;
     CK(cudaSetDevice(c->device));
-    CK(cudaStreamSynchronize(c->dl_stream));
+    if (c->dl_stream) CK(cudaStreamSynchronize(c->dl_stream));
     c->dl_inflight[0] = c->dl_inflight[1] = false;
     return CHRONOS_OK;
 }
 
 int chronos_copy_chains(chronos_ctx *c, uint32_t *pid, uint64_t *global_idx, uint64_t cap) {
-    int rc = need_fetched(c);
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
     if (rc) return rc;
-    const uint64_t K = c->b_chains;
+    const uint64_t K = bp->chains;
     if (cap < K) return fail(c, CHRONOS_E_ARG, "chain buffer too small (%llu < %llu)", (unsigned long long)cap,
                              (unsigned long long)K);
     if (!K) return CHRONOS_OK;
-    if (pid) CK(cudaMemcpyAsync(pid, c->chain_pid.p, K * 4, cudaMemcpyDeviceToHost, c->stream));
-    if (global_idx) CK(cudaMemcpyAsync(global_idx, c->chain_idx.p, K * 8, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    cudaStream_t st;
+    if ((rc = host_stream(c, &st))) return rc;
+    if (pid) CK(cudaMemcpyAsync(pid, bp->chain_pid.p, K * 4, cudaMemcpyDeviceToHost, st));
+    if (global_idx) CK(cudaMemcpyAsync(global_idx, bp->chain_idx.p, K * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return CHRONOS_OK;
 }
 
+// process_memory lives in the set of the newest batch; it can be read once that batch (and
+// therefore every batch) has been fetched
 int chronos_state(chronos_ctx *c, uint32_t *pid, uint64_t *global_idx, void *records, uint64_t cap) {
     if (!c) return CHRONOS_E_ARG;
-    if (c->phase == chronos_ctx::SUBMITTED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    int rc;
+    if ((rc = no_batch_in_flight(c))) return rc;
     CK(cudaSetDevice(c->device));
     const uint64_t P = c->n_pending;
     if (cap < P) return fail(c, CHRONOS_E_ARG, "state buffer too small (%llu < %llu)", (unsigned long long)cap,
                              (unsigned long long)P);
     if (!P) return CHRONOS_OK;
-    const int cur = c->cur;
-    const uint64_t pc = c->pend_cap[cur];
-    if (pid) CK(cudaMemcpyAsync(pid, ptr<uint32_t>(c->pend_key[cur]) + (pc - P), P * 4, cudaMemcpyDeviceToHost, c->stream));
-    if (global_idx)
-        CK(cudaMemcpyAsync(global_idx, ptr<uint64_t>(c->pend_arrival[cur]) + (pc - P), P * 8, cudaMemcpyDeviceToHost,
-                           c->stream));
+    BatchSet &b = c->set[c->last];
+    const uint64_t pc = b.pend_cap;
+    cudaStream_t st = c->stream;  // (nothing is in flight)
+    if (pid) CK(cudaMemcpyAsync(pid, ptr<uint32_t>(b.pend_key) + (pc - P), P * 4, cudaMemcpyDeviceToHost, st));
+    if (global_idx) CK(cudaMemcpyAsync(global_idx, ptr<uint64_t>(b.pend_arrival) + (pc - P), P * 8, cudaMemcpyDeviceToHost, st));
     if (records) {
-        int rc;
         if ((rc = ensure(c, c->pack, P * CH_REC_BYTES))) return rc;
-        pack_by_slot_kernel<<<(unsigned)std::min<uint64_t>((P + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
-            ptr<uint8_t>(c->arena[cur]), ptr<uint32_t>(c->pend_slot[cur]) + (pc - P), (uint32_t)P, ptr<uint8_t>(c->pack));
+        pack_by_slot_kernel<<<(unsigned)std::min<uint64_t>((P + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, st>>>(
+            ptr<uint8_t>(b.arena), ptr<uint32_t>(b.pend_slot) + (pc - P), (uint32_t)P, ptr<uint8_t>(c->pack));
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(records, c->pack.p, P * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
+        CK(cudaMemcpyAsync(records, c->pack.p, P * CH_REC_BYTES, cudaMemcpyDeviceToHost, st));
     }
-    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaStreamSynchronize(st));
     return CHRONOS_OK;
 }
 
 int chronos_state_pids(chronos_ctx *c, uint32_t *pid, uint64_t cap) {
     if (!c) return CHRONOS_E_ARG;
-    if (c->phase == chronos_ctx::SUBMITTED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    int rc;
+    if ((rc = no_batch_in_flight(c))) return rc;
     CK(cudaSetDevice(c->device));
     const uint64_t K = c->n_pids_seen;
     if (cap < K || (K && !pid)) return fail(c, CHRONOS_E_ARG, "pid buffer too small (%llu < %llu)",
                                             (unsigned long long)cap, (unsigned long long)K);
     if (!K) return CHRONOS_OK;
-    int rc;
     if ((rc = ensure(c, c->pack, K * 4 + 256))) return rc;
-    if ((rc = ensure(c, c->pack_off, 256))) return rc;
-    uint32_t *cnt = ptr<uint32_t>(c->pack_off);
-    CK(cudaMemsetAsync(cnt, 0, 4, c->stream));
-    pt_dump_kernel<<<(unsigned)std::min<uint32_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
+    cudaStream_t st = c->stream;
+    uint32_t *cnt = ptr<uint32_t>(c->dl_ticket) + 8;
+    CK(cudaMemsetAsync(cnt, 0, 4, st));
+    pt_dump_kernel<<<(unsigned)std::min<uint32_t>((c->pt_cap + 255) / 256, 4096), 256, 0, st>>>(
         ptr<uint64_t>(c->pid_tab), c->pt_cap, c->pt_epoch, ptr<uint32_t>(c->pack), cnt);
     CK(cudaGetLastError());
-    CK(cudaMemcpyAsync(pid, c->pack.p, K * 4, cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaMemcpyAsync(pid, c->pack.p, K * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
     return CHRONOS_OK;
 }
 
@@ -1214,14 +1519,16 @@ __global__ void iota_u32_kernel(uint32_t *p, uint32_t n) {
 
 int chronos_checkpoint_bytes(chronos_ctx *c, uint64_t *bytes) {
     if (!c || !bytes) return CHRONOS_E_ARG;
-    if (c->phase == chronos_ctx::SUBMITTED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    int rc;
+    if ((rc = no_batch_in_flight(c))) return rc;
     *bytes = ckpt_layout(c->n_pending, c->n_pids_seen).total;
     return CHRONOS_OK;
 }
 
 int chronos_checkpoint_save(chronos_ctx *c, void *dst, uint64_t cap) {
     if (!c || !dst) return CHRONOS_E_ARG;
-    if (c->phase == chronos_ctx::SUBMITTED) return fail(c, CHRONOS_E_STATE, "call chronos_fetch first");
+    int rc;
+    if ((rc = no_batch_in_flight(c))) return rc;
     CK(cudaSetDevice(c->device));
     const uint64_t P = c->n_pending, K = c->n_pids_seen;
     const CkptLayout L = ckpt_layout(P, K);
@@ -1237,34 +1544,33 @@ int chronos_checkpoint_save(chronos_ctx *c, void *dst, uint64_t cap) {
     h.n_pending = P;
     h.n_pids = K;
     memcpy(out, &h, sizeof(h));
-    int rc;
+    cudaStream_t st = c->stream;
     if (K) {
         if ((rc = ensure(c, c->pack, K * 8 + 256))) return rc;
-        if ((rc = ensure(c, c->pack_off, 256))) return rc;
-        uint32_t *cnt = ptr<uint32_t>(c->pack_off);
-        CK(cudaMemsetAsync(cnt, 0, 4, c->stream));
-        pt_dump64_kernel<<<(unsigned)std::min<uint32_t>((c->pt_cap + 255) / 256, 4096), 256, 0, c->stream>>>(
+        uint32_t *cnt = ptr<uint32_t>(c->dl_ticket) + 8;
+        CK(cudaMemsetAsync(cnt, 0, 4, st));
+        pt_dump64_kernel<<<(unsigned)std::min<uint32_t>((c->pt_cap + 255) / 256, 4096), 256, 0, st>>>(
             ptr<uint64_t>(c->pid_tab), c->pt_cap, c->pt_epoch, ptr<uint64_t>(c->pack), cnt);
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(out + L.off_tab, c->pack.p, K * 8, cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaStreamSynchronize(c->stream));
+        CK(cudaMemcpyAsync(out + L.off_tab, c->pack.p, K * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
         uint64_t *e = reinterpret_cast<uint64_t *>(out + L.off_tab);
         std::sort(e, e + K, [](uint64_t a, uint64_t b) { return (uint32_t)a < (uint32_t)b; });  // by pid: files compare equal
     }
     if (P) {
         memset(out + L.off_pid, 0, L.off_arr - L.off_pid);
         memset(out + L.off_meta, 0, L.off_rec - L.off_meta);
-        const int cur = c->cur;
-        const uint64_t pc = c->pend_cap[cur];
-        CK(cudaMemcpyAsync(out + L.off_pid, ptr<uint32_t>(c->pend_key[cur]) + (pc - P), P * 4, cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaMemcpyAsync(out + L.off_arr, ptr<uint64_t>(c->pend_arrival[cur]) + (pc - P), P * 8, cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaMemcpyAsync(out + L.off_meta, ptr<uint8_t>(c->pend_meta[cur]) + (pc - P), P, cudaMemcpyDeviceToHost, c->stream));
+        BatchSet &b = c->set[c->last];
+        const uint64_t pc = b.pend_cap;
+        CK(cudaMemcpyAsync(out + L.off_pid, ptr<uint32_t>(b.pend_key) + (pc - P), P * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(out + L.off_arr, ptr<uint64_t>(b.pend_arrival) + (pc - P), P * 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(out + L.off_meta, ptr<uint8_t>(b.pend_meta) + (pc - P), P, cudaMemcpyDeviceToHost, st));
         if ((rc = ensure(c, c->pack, P * CH_REC_BYTES))) return rc;
-        pack_by_slot_kernel<<<(unsigned)std::min<uint64_t>((P + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, c->stream>>>(
-            ptr<uint8_t>(c->arena[cur]), ptr<uint32_t>(c->pend_slot[cur]) + (pc - P), (uint32_t)P, ptr<uint8_t>(c->pack));
+        pack_by_slot_kernel<<<(unsigned)std::min<uint64_t>((P + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, st>>>(
+            ptr<uint8_t>(b.arena), ptr<uint32_t>(b.pend_slot) + (pc - P), (uint32_t)P, ptr<uint8_t>(c->pack));
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(out + L.off_rec, c->pack.p, P * CH_REC_BYTES, cudaMemcpyDeviceToHost, c->stream));
-        CK(cudaStreamSynchronize(c->stream));
+        CK(cudaMemcpyAsync(out + L.off_rec, c->pack.p, P * CH_REC_BYTES, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
     }
     return CHRONOS_OK;
 }
@@ -1278,83 +1584,114 @@ int chronos_checkpoint_load(chronos_ctx *c, const void *src, uint64_t bytes) {
     if (memcmp(h.magic, CKPT_MAGIC, 8) != 0 || h.version != 1 || h.record_bytes != CH_REC_BYTES)
         return fail(c, CHRONOS_E_ARG, "not a version-1 checkpoint of 288-byte records");
     const uint64_t P = h.n_pending, K = h.n_pids;
-    if (P >= (1ull << VAL_ID_BITS) || K >= (1ull << 31)) return fail(c, CHRONOS_E_CAPACITY, "checkpoint too large");
+    if (P + c->max_batch > MAX_GROUPED || K >= (1ull << 30)) return fail(c, CHRONOS_E_CAPACITY, "checkpoint too large for this context");
     const CkptLayout L = ckpt_layout(P, K);
     if (bytes < L.total) return fail(c, CHRONOS_E_ARG, "checkpoint truncated (%llu < %llu bytes)", (unsigned long long)bytes,
                                      (unsigned long long)L.total);
-    // the pending list must be what window_reverse would have written: ascending pid, ascending
-    // arrival inside a pid; every pending pid must be in the key set
-    const uint32_t *ppid = reinterpret_cast<const uint32_t *>(in + L.off_pid);
-    const uint64_t *parr = reinterpret_cast<const uint64_t *>(in + L.off_arr);
-    for (uint64_t i = 1; i < P; i++)
-        if (ppid[i] < ppid[i - 1] || (ppid[i] == ppid[i - 1] && parr[i] <= parr[i - 1]))
+    // Everything is validated before the context is touched (memcpy: the blob need not be aligned).
+    // PID entries: (dfa << 32 | pid), strictly ascending pid, DFA state 0..2, nothing above bit 33.
+    std::vector<uint64_t> tab(K);
+    if (K) memcpy(tab.data(), in + L.off_tab, K * 8);
+    for (uint64_t i = 0; i < K; i++) {
+        if ((tab[i] >> 34) != 0 || ((tab[i] >> 32) & 3u) == 3u)
+            return fail(c, CHRONOS_E_ARG, "checkpoint: PID entry %llu malformed", (unsigned long long)i);
+        if (i && (uint32_t)tab[i] <= (uint32_t)tab[i - 1])
+            return fail(c, CHRONOS_E_ARG, "checkpoint: PID entries not strictly ascending at %llu", (unsigned long long)i);
+    }
+    // Pending list: what window_reverse would have written -- ascending pid, ascending arrival
+    // inside a pid -- and every pending pid is a key of process_memory.
+    std::vector<uint32_t> ppid(P);
+    std::vector<uint64_t> parr(P);
+    if (P) {
+        memcpy(ppid.data(), in + L.off_pid, P * 4);
+        memcpy(parr.data(), in + L.off_arr, P * 8);
+    }
+    uint32_t k_or = 0, k_and = 0xffffffffu;
+    for (uint64_t i = 0; i < K; i++) {  // bit range of every pid seen (the sort plans with it)
+        k_or |= (uint32_t)tab[i];
+        k_and &= (uint32_t)tab[i];
+    }
+    uint64_t ti = 0;
+    for (uint64_t i = 0; i < P; i++) {
+        if (i && (ppid[i] < ppid[i - 1] || (ppid[i] == ppid[i - 1] && parr[i] <= parr[i - 1])))
             return fail(c, CHRONOS_E_ARG, "checkpoint: pending entry %llu out of order", (unsigned long long)i);
+        if (parr[i] >= MAX_ARRIVAL) return fail(c, CHRONOS_E_ARG, "checkpoint: arrival index of entry %llu too large", (unsigned long long)i);
+        while (ti < K && (uint32_t)tab[ti] < ppid[i]) ti++;  // both lists ascend: one merge walk
+        if (ti == K || (uint32_t)tab[ti] != ppid[i])
+            return fail(c, CHRONOS_E_ARG, "checkpoint: pending pid %u is not among the PID entries", ppid[i]);
+    }
     int rc = chronos_reset(c);
     if (rc) return rc;
+    BatchSet &b = c->set[c->last];
+    if (P + c->max_batch > c->cap_M || P > b.cap_M) {  // state larger than the pending budget: grow once
+        const uint64_t want = std::min<uint64_t>(MAX_GROUPED, P + c->max_batch);
+        if ((rc = reserve_shared(c, c->max_batch, want))) return rc;
+        for (BatchSet &s : c->set)
+            if ((rc = reserve_set(c, s, c->max_batch, want))) return rc;
+    }
+    if ((rc = ensure_pid_table(c, K, c->max_batch + P))) return rc;
+    cudaStream_t st = c->stream;
     if (K) {
-        if ((rc = ensure_pid_table(c, K))) return rc;
         if ((rc = ensure(c, c->pack, K * 8))) return rc;
-        CK(cudaMemcpyAsync(c->pack.p, in + L.off_tab, K * 8, cudaMemcpyHostToDevice, c->stream));
-        pt_load_kernel<<<(unsigned)std::min<uint64_t>((K + 255) / 256, 2048), 256, 0, c->stream>>>(
+        CK(cudaMemcpyAsync(c->pack.p, tab.data(), K * 8, cudaMemcpyHostToDevice, st));
+        pt_load_kernel<<<(unsigned)std::min<uint64_t>((K + 255) / 256, 2048), 256, 0, st>>>(
             ptr<uint64_t>(c->pid_tab), c->pt_cap - 1, c->pt_epoch, ptr<uint64_t>(c->pack), (uint32_t)K);
         CK(cudaGetLastError());
         const uint32_t k32 = (uint32_t)K;
-        CK(cudaMemcpyAsync(c->pt_count.p, &k32, 4, cudaMemcpyHostToDevice, c->stream));
-        CK(cudaStreamSynchronize(c->stream));
+        CK(cudaMemcpyAsync(c->pt_count.p, &k32, 4, cudaMemcpyHostToDevice, st));
+        CK(cudaStreamSynchronize(st));
     }
-    const int cur = c->cur;
     if (P) {
-        if ((rc = ensure(c, c->arena[cur], (P + 1) * CH_REC_BYTES))) return rc;
-        if ((rc = ensure(c, c->pend_key[cur], (P + 1) * 4))) return rc;
-        if ((rc = ensure(c, c->pend_slot[cur], (P + 1) * 4))) return rc;
-        if ((rc = ensure(c, c->pend_arrival[cur], (P + 1) * 8))) return rc;
-        if ((rc = ensure(c, c->pend_meta[cur], P + 1))) return rc;
-        c->pend_cap[cur] = P;  // right-aligned in a layout of exactly P entries
-        CK(cudaMemcpyAsync(c->pend_key[cur].p, ppid, P * 4, cudaMemcpyHostToDevice, c->stream));
-        CK(cudaMemcpyAsync(c->pend_arrival[cur].p, parr, P * 8, cudaMemcpyHostToDevice, c->stream));
-        CK(cudaMemcpyAsync(c->pend_meta[cur].p, in + L.off_meta, P, cudaMemcpyHostToDevice, c->stream));
-        CK(cudaMemcpyAsync(c->arena[cur].p, in + L.off_rec, P * CH_REC_BYTES, cudaMemcpyHostToDevice, c->stream));
-        iota_u32_kernel<<<(unsigned)std::min<uint64_t>((P + 255) / 256, 2048), 256, 0, c->stream>>>(
-            ptr<uint32_t>(c->pend_slot[cur]), (uint32_t)P);
+        const uint64_t off = b.pend_cap - P;  // right-aligned, as window_reverse leaves them
+        CK(cudaMemcpyAsync(ptr<uint32_t>(b.pend_key) + off, ppid.data(), P * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(ptr<uint64_t>(b.pend_arrival) + off, parr.data(), P * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(ptr<uint8_t>(b.pend_meta) + off, in + L.off_meta, P, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(b.arena.p, in + L.off_rec, P * CH_REC_BYTES, cudaMemcpyHostToDevice, st));
+        iota_u32_kernel<<<(unsigned)std::min<uint64_t>((P + 255) / 256, 2048), 256, 0, st>>>(ptr<uint32_t>(b.pend_slot) + off,
+                                                                                           (uint32_t)P);
         CK(cudaGetLastError());
-        CK(cudaStreamSynchronize(c->stream));
+        CK(cudaStreamSynchronize(st));
     }
     c->n_pending = P;
     c->n_pids_seen = K;
-    c->phase = chronos_ctx::IDLE;
-    return CHRONOS_OK;
+    return set_carry(c, (uint32_t)P, k_or, k_and);
 }
 
 int chronos_get_device_view(chronos_ctx *c, chronos_device_view *out) {
-    int rc = need_fetched(c);
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
     if (rc) return rc;
     if (!out) return CHRONOS_E_ARG;
-    const int cur = c->cur;
-    const uint64_t P = c->n_pending, pc = c->pend_cap[cur];
-    out->arena = c->arena[cur].p;
-    out->windows = ptr<chronos_window>(c->windows);
-    out->survivor_idx = ptr<uint32_t>(c->surv_src);
-    out->survivor_meta = ptr<uint8_t>(c->surv_meta);
-    out->pending_pid = P ? ptr<uint32_t>(c->pend_key[cur]) + (pc - P) : nullptr;
-    out->pending_slot = P ? ptr<uint32_t>(c->pend_slot[cur]) + (pc - P) : nullptr;
-    out->pending_arrival = P ? ptr<uint64_t>(c->pend_arrival[cur]) + (pc - P) : nullptr;
+    BatchSet &b = *bp;
+    const uint64_t P = b.pending_after, pc = b.pend_cap;
+    out->arena = b.arena.p;
+    out->windows = ptr<chronos_window>(b.windows);
+    out->survivor_idx = ptr<uint32_t>(b.surv_src);
+    out->survivor_meta = ptr<uint8_t>(b.surv_meta);
+    out->pending_pid = P ? ptr<uint32_t>(b.pend_key) + (pc - P) : nullptr;
+    out->pending_slot = P ? ptr<uint32_t>(b.pend_slot) + (pc - P) : nullptr;
+    out->pending_arrival = P ? ptr<uint64_t>(b.pend_arrival) + (pc - P) : nullptr;
     return CHRONOS_OK;
 }
 
 int chronos_last_timing(chronos_ctx *c, float *total_ms, float *filter_ms) {
-    int rc = need_fetched(c);
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
     if (rc) return rc;
-    if (total_ms) *total_ms = c->t_total;
-    if (filter_ms) *filter_ms = c->t_filter_kernel;
+    if (total_ms) *total_ms = bp->t_total;
+    if (filter_ms) *filter_ms = bp->t_filter_kernel;
     return CHRONOS_OK;
 }
 
 int chronos_reset(chronos_ctx *c) {
     if (!c) return CHRONOS_E_ARG;
     CK(cudaSetDevice(c->device));
-    CK(cudaStreamSynchronize(c->stream));
+    CK(cudaDeviceSynchronize());
+    for (BatchSet &b : c->set) b.state = BatchSet::FREE;
+    c->fetched = -1;
     c->n_pending = 0;
     c->n_pids_seen = 0;
+    c->x_sent = false;
     // slots written under an older epoch count as empty: a reset costs nothing on the device
     c->pt_epoch = (c->pt_epoch + 1) & 0xFFu;
     if (c->pt_epoch == 0) {  // tags wrapped: really clear the table once every 255 resets
@@ -1362,13 +1699,13 @@ int chronos_reset(chronos_ctx *c) {
         if (c->pt_cap) CK(cudaMemsetAsync(c->pid_tab.p, 0, (size_t)c->pt_cap * 8, c->stream));
     }
     CK(cudaMemsetAsync(c->pt_count.p, 0, 256, c->stream));
-    c->phase = chronos_ctx::IDLE;
-    return CHRONOS_OK;
+    return set_carry(c, 0u, 0u, 0xffffffffu);
 }
 
 int chronos_last_launches(chronos_ctx *c, uint64_t *launches) {
     if (!c || !launches) return CHRONOS_E_ARG;
-    *launches = c->launches;
+    const int k = (c->fetched >= 0 && c->set[c->fetched].state == BatchSet::FETCHED) ? c->fetched : c->last;
+    *launches = c->set[k].launches;
     return CHRONOS_OK;
 }
 
@@ -1378,59 +1715,56 @@ uint32_t chronos_owner_of(uint32_t pid, uint32_t world) { return world ? hash32(
 
 // Stage 1 of the sharded path: filter the slice, partition the survivors by owner rank and
 // deliver them (pk.direct: into the owners' windows; else into the caller's send buffers):
-// filter -> compact_scan -> xchg_hist -> scan -> xchg_pack, all on the main stream. The
-// per-PID state of the context is not touched.
+// filter -> compact_scan -> xchg_hist -> scan -> xchg_pack, all on the main stream, in the
+// buffer set the NEXT batch will use. The per-PID state of the context is not touched.
 // (Cutting the slice into pieces so that the delivery of piece k overlaps the filter of piece
 //  k+1 was built and measured on 2xB200, 12.5 M events per rank: stage 1 got SLOWER, 0.80 ->
 //  1.15 ms with four pieces -- the filter loses its ~19 single-warp CTAs per SM to the pack
 //  kernel -- so it was removed again.)
 static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base, XchgPackParams &pk) {
     int rc;
+    if ((rc = check_records_arg(c, records, n))) return rc;
+    if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
+                                      (unsigned long long)n, (unsigned long long)c->max_batch);
+    if (base >= MAX_ARRIVAL || base + n > MAX_ARRIVAL) return fail(c, CHRONOS_E_ARG, "arrival indices must stay below 2^48");
+    BatchSet &b = c->set[c->last ^ 1];
+    if (b.state == BatchSet::SUBMITTED && (rc = complete_batch(c, b))) return rc;
+    BatchSet &newest = c->set[c->last];
+    if (newest.state == BatchSet::SUBMITTED && (rc = complete_batch(c, newest))) return rc;  // no overlap on this path
+    if (c->fetched == (c->last ^ 1)) c->fetched = -1;
+    b.state = BatchSet::FREE;
+    cudaStream_t st = c->stream;
+    CK(cudaStreamWaitEvent(st, b.ev_packed, 0));
     const uint8_t *d_recs = nullptr;
-    if (n == 0) {
-        // an empty slice still takes part in the exchange (zero counts, flag raised)
-    } else if (is_device_pointer(records)) {
-        if ((uintptr_t)records & 15) return fail(c, CHRONOS_E_ARG, "device records pointer must be 16-byte aligned");
-        d_recs = static_cast<const uint8_t *>(records);
-    } else {
-        if ((rc = ensure(c, c->d_batch, n * CH_REC_BYTES))) return rc;
-        CK(cudaMemcpyAsync(c->d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, c->stream));
-        d_recs = ptr<uint8_t>(c->d_batch);
-    }
+    if ((rc = stage_records(c, b, records, n, st, &d_recs))) return rc;
     c->launches = 0;
     c->scan_slot = 0;
     c->n_tev = 0;
-    if ((rc = ensure(c, c->keyA, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_src, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_meta, n + 1))) return rc;
-    if ((rc = ensure(c, c->surv_pid, (n + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_ns, n + 1))) return rc;
-    if ((rc = ensure(c, c->x_totals, 512))) return rc;
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    init_scalars_kernel<<<1, 256, 0, c->stream>>>(ds, ptr<uint32_t>(c->tickets));
-    set_u32_kernel<<<1, 1, 0, c->stream>>>(&ds->xchg_err, 0u);
+    DeviceScalars *ds = dscal(b);
+    init_batch_kernel<<<1, 256, 0, st>>>(ds, ptr<uint32_t>(c->tickets_f), ptr<uint32_t>(c->tickets_t), 1);
+    set_u32_kernel<<<1, 1, 0, st>>>(&ds->xchg_err, 0u);
     c->launches += 2;
     mark(c, "stage 1 start");
-    if (n && (rc = run_filter_stage(c, d_recs, n, ptr<uint32_t>(c->keyA)))) return rc;
+    b.filter_timed = false;
+    if (n && (rc = run_filter_stage(c, b, d_recs, n, st))) return rc;
     c->x_filter_timed = n != 0;
     mark(c, "filter + compact");
 
     const uint32_t W = pk.world;
     const uint32_t T = (uint32_t)std::max<uint64_t>((n + XCHG_TILE - 1) / XCHG_TILE, 1);  // upper bound of the tile count
     const uint64_t table_len = (uint64_t)2 * W * T + 1;
-    if ((rc = ensure(c, c->owner_table, table_len * 4))) return rc;
+    if ((rc = ensure(c, c->owner_table, (2ull * XCHG_MAX_WORLD * ((c->max_batch + XCHG_TILE - 1) / XCHG_TILE + 1) + 1) * 4))) return rc;
     uint32_t *table = ptr<uint32_t>(c->owner_table);
     const unsigned xblocks = std::min<uint32_t>(T, (uint32_t)c->sm_count * 4);  // persistent CTAs
-    xchg_hist<<<xblocks, XCHG_THREADS, 0, c->stream>>>(ptr<uint32_t>(c->surv_pid), ptr<uint8_t>(c->surv_ns), &ds->surv_count, W, T,
-                                                     table);
+    xchg_hist<<<xblocks, XCHG_THREADS, 0, st>>>(ptr<uint32_t>(b.surv_pid), ptr<uint8_t>(b.surv_ns), &ds->surv_count, W, T, table);
     if ((rc = dbg_sync(c, "xchg_hist"))) return rc;
-    if ((rc = launch_scan(c, table, table_len))) return rc;
+    if ((rc = launch_scan(c, st, table, table_len))) return rc;
     if ((rc = dbg_sync(c, "owner table scan"))) return rc;
     mark(c, "owner histogram + scan");
-    pk.pid = ptr<uint32_t>(c->surv_pid);
-    pk.surv_src = ptr<uint32_t>(c->surv_src);
-    pk.surv_meta = ptr<uint8_t>(c->surv_meta);
-    pk.surv_ns = ptr<uint8_t>(c->surv_ns);
+    pk.pid = ptr<uint32_t>(b.surv_pid);
+    pk.surv_src = ptr<uint32_t>(b.surv_src);
+    pk.surv_meta = ptr<uint8_t>(b.surv_meta);
+    pk.surv_ns = ptr<uint8_t>(b.surv_ns);
     pk.n_ptr = &ds->surv_count;
     pk.batch = d_recs;
     pk.base_arrival = base;
@@ -1438,13 +1772,8 @@ static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base
     pk.T = T;
     pk.totals = ptr<uint32_t>(c->x_totals);
     pk.err = &ds->xchg_err;
-    pk.done = ptr<uint32_t>(c->tickets) + 58;
-    static bool pack_configured[16] = {false};
-    if (!pack_configured[c->device & 15]) {
-        CK(cudaFuncSetAttribute(xchg_pack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XCHG_PACK_SMEM));
-        pack_configured[c->device & 15] = true;
-    }
-    xchg_pack<<<xblocks, XCHG_THREADS, XCHG_PACK_SMEM, c->stream>>>(pk);
+    pk.done = ptr<uint32_t>(c->tickets_f) + 58;
+    xchg_pack<<<xblocks, XCHG_THREADS, XCHG_PACK_SMEM, st>>>(pk);
     CK(cudaGetLastError());
     c->launches += 2;
     if ((rc = dbg_sync(c, "xchg_pack"))) return rc;
@@ -1459,16 +1788,9 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
         return c ? fail(c, CHRONOS_E_ARG, "bad argument (world must be 1..%d)", XCHG_MAX_WORLD) : CHRONOS_E_ARG;
     if (n && (!records || !send_slots || !send_hdr)) return fail(c, CHRONOS_E_ARG, "NULL argument");
     CK(cudaSetDevice(c->device));
-    if (c->phase == chronos_ctx::SUBMITTED) {
-        int rc0 = finish_batch(c);
-        if (rc0) return rc0;
-    }
-    if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
-                                      (unsigned long long)n, (unsigned long long)c->max_batch);
     for (uint32_t d = 0; d < world; d++) entry_counts_host[d] = slot_counts_host[d] = 0;
     if (!n) return CHRONOS_OK;
     int rc;
-    CK(cudaEventRecord(c->ev_start, c->stream));
     XchgPackParams pk;
     memset(&pk, 0, sizeof(pk));
     pk.world = world;
@@ -1478,11 +1800,10 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
     pk.cap_entries = cap_entries;
     pk.cap_slots = cap_slots;
     if ((rc = stage1(c, records, n, base_arrival_index, pk))) return rc;
+    BatchSet &b = c->set[c->last ^ 1];
     uint32_t hc[2 * XCHG_MAX_WORLD];
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
     CK(cudaMemcpyAsync(hc, c->x_totals.p, sizeof(hc), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaMemcpyAsync(c->h_scalars, ds, sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
-    CK(cudaEventRecord(c->ev_end, c->stream));
+    CK(cudaMemcpyAsync(b.h_scalars, dscal(b), sizeof(DeviceScalars), cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     uint64_t tot_e = 0, tot_s = 0;
     for (uint32_t d = 0; d < world; d++) {
@@ -1491,9 +1812,10 @@ int chronos_filter_partition(chronos_ctx *c, const void *records, uint64_t n, ui
         tot_e += hc[d];
         tot_s += hc[XCHG_MAX_WORLD + d];
     }
-    cudaEventElapsedTime(&c->t_filter_kernel, c->ev_f0, c->ev_f1);
+    cudaEventElapsedTime(&b.t_filter_kernel, b.ev_f0, b.ev_f1);
     cudaGetLastError();
-    if (c->h_scalars->xchg_err & XERR_OVERFLOW)
+    c->set[c->last].launches = c->launches;  // (chronos_last_launches right after this call)
+    if (b.h_scalars->xchg_err & XERR_OVERFLOW)
         return fail(c, CHRONOS_E_CAPACITY, "%llu survivors / %llu transport slots do not fit the send buffers (%llu / %llu)",
                     (unsigned long long)tot_e, (unsigned long long)tot_s, (unsigned long long)cap_entries,
                     (unsigned long long)cap_slots);
@@ -1516,10 +1838,11 @@ int chronos_exchange_create(chronos_ctx *c, uint32_t world, uint32_t rank, uint6
     c->x_L = xchg_layout(world, rank, (uint32_t)cap_entries_per_peer, (uint32_t)cap_slots_per_peer);
     int rc;
     if ((rc = ensure(c, c->x_window, 2 * c->x_L.half_bytes))) return rc;
-    if ((rc = ensure(c, c->x_totals, 512))) return rc;
+    for (BatchSet &b : c->set)
+        if ((rc = reserve_transport(c, b))) return rc;
+    if ((rc = ensure(c, c->owner_table, (2ull * XCHG_MAX_WORLD * ((c->max_batch + XCHG_TILE - 1) / XCHG_TILE + 1) + 1) * 4))) return rc;
     CK(cudaMemsetAsync(c->x_window.p, 0, 2 * c->x_L.half_bytes, c->stream));
     CK(cudaStreamSynchronize(c->stream));  // peers may write as soon as they hold the address
-    if (!c->ev_x0) CK(cudaEventCreate(&c->ev_x0));
     if (ipc_handle_out) {
         cudaIpcMemHandle_t h;
         static_assert(sizeof(h) == CHRONOS_IPC_HANDLE_BYTES, "IPC handle size");
@@ -1569,12 +1892,6 @@ int chronos_filter_exchange(chronos_ctx *c, const void *records, uint64_t n, uin
     if (c->x_sent) return fail(c, CHRONOS_E_STATE, "previous exchange not consumed: call chronos_submit_exchanged");
     if (n && !records) return fail(c, CHRONOS_E_ARG, "records is NULL");
     CK(cudaSetDevice(c->device));
-    if (c->phase == chronos_ctx::SUBMITTED) {
-        int rc0 = finish_batch(c);
-        if (rc0) return rc0;
-    }
-    if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
-                                      (unsigned long long)n, (unsigned long long)c->max_batch);
     int rc;
     CK(cudaEventRecord(c->ev_x0, c->stream));
     XchgPackParams pk;
@@ -1597,43 +1914,45 @@ int chronos_submit_exchanged(chronos_ctx *c) {
     const XchgLayout &L = c->x_L;
     const uint64_t n_max = (uint64_t)L.world * L.cap_e;
     const uint64_t stage1_launches = c->x_launches;
-    int rc = begin_batch(c, n_max, 0);
+    BatchSet *bp;
+    cudaStream_t s1;
+    int rc = begin_batch(c, n_max, 0, true, &bp, &s1);
     if (rc) return rc;
+    BatchSet &b = *bp, &prev = c->set[c->last];
     c->launches += stage1_launches;
     const uint8_t *hb = ptr<uint8_t>(c->x_window) + (size_t)(c->x_epoch & 1u) * L.half_bytes;
-    c->b_records = nullptr;
-    c->b_slots = reinterpret_cast<const uint4 *>(hb + L.off_slots);
-    c->b_explicit_arrival = true;
-    c->b_exchanged = true;
+    b.slots = reinterpret_cast<const uint4 *>(hb + L.off_slots);
+    b.explicit_arrival = true;
+    b.exchanged = true;
+    b.x_epoch = c->x_epoch;
     c->x_sent = false;
-    DeviceScalars *ds = ptr<DeviceScalars>(c->scalars);
-    if ((rc = ensure(c, c->surv_arrival, n_max * 8))) return rc;
-    if ((rc = ensure(c, c->surv_pid, (n_max + 1) * 4))) return rc;
-    if ((rc = ensure(c, c->surv_ns, n_max + 1))) return rc;
-    if ((rc = ensure(c, c->slot_off, (n_max + 8) * 4))) return rc;
+    DeviceScalars *ds = dscal(b);
     XchgUnpackParams u;
     memset(&u, 0, sizeof(u));
     u.window = ptr<uint8_t>(c->x_window);
     u.L = L;
     u.epoch = c->x_epoch;
     u.timeout_ns = c->x_timeout_ns;
-    u.arrival = ptr<uint64_t>(c->surv_arrival);
-    u.meta = ptr<uint8_t>(c->surv_meta);
-    u.ns = ptr<uint8_t>(c->surv_ns);
-    u.slot_off = ptr<uint32_t>(c->slot_off);
-    u.key = ptr<uint32_t>(c->keyA) + c->b_P;
-    u.pid_copy = ptr<uint32_t>(c->surv_pid);
-    u.src = ptr<uint32_t>(c->surv_src);
+    u.arrival = ptr<uint64_t>(b.surv_arrival);
+    u.meta = ptr<uint8_t>(b.surv_meta);
+    u.ns = ptr<uint8_t>(b.surv_ns);
+    u.slot_off = ptr<uint32_t>(b.slot_off);
+    u.key = nullptr;
+    u.pid_copy = ptr<uint32_t>(b.surv_pid);
+    u.src = ptr<uint32_t>(b.surv_src);
     u.n_out = &ds->surv_count;
     u.k_or = &ds->key_or;
     u.k_and = &ds->key_and;
     u.err = &ds->xchg_err;
     u.n_cap = (uint32_t)n_max;
-    xchg_unpack<<<(unsigned)std::min<uint64_t>((n_max + 255) / 256, (uint64_t)c->sm_count * 4), 256, 0, c->stream>>>(u);
+    // (the survivor scalars of this set were used by stage 1: back to neutral before the receive)
+    init_batch_kernel<<<1, 256, 0, s1>>>(ds, ptr<uint32_t>(c->tickets_f), ptr<uint32_t>(c->tickets_t), 1);
+    xchg_unpack<<<(unsigned)std::min<uint64_t>((n_max + 255) / 256, (uint64_t)c->sm_count * 4), 256, 0, s1>>>(u);
     CK(cudaGetLastError());
-    c->launches++;
-    if ((rc = run_window_stage(c))) return rc;
-    c->phase = chronos_ctx::SUBMITTED;
+    c->launches += 2;
+    if ((rc = join_stage1(c, b, s1))) return rc;
+    if ((rc = run_window_stage(c, b, prev))) return rc;
+    commit_batch(c, b);
     return CHRONOS_OK;
 }
 
@@ -1656,8 +1975,8 @@ int chronos_tracegen_device(int device, const chronos_tracegen_cfg *cfg, const u
     if (!cfg || (n && !dst_dev) || cfg->n_pids == 0 || (cfg->use_cdf && !cdf_dev)) return CHRONOS_E_ARG;
     if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
     if (!n) return CHRONOS_OK;
-    tracegen_kernel<<<(unsigned)std::min<uint64_t>((n + 127) / 128, 148 * 16), 128>>>(*cfg, cdf_dev, first, n,
-                                                                                      static_cast<uint8_t *>(dst_dev));
+    tracegen_kernel<<<(unsigned)std::min<uint64_t>((n + 127) / 128, (uint64_t)device_sm_count(device) * 16), 128>>>(
+        *cfg, cdf_dev, first, n, static_cast<uint8_t *>(dst_dev));
     if (cudaGetLastError() != cudaSuccess) return CHRONOS_E_CUDA;
     return cudaDeviceSynchronize() == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
 }
@@ -1705,8 +2024,22 @@ int chronos_flush_l2(int device) {
         return CHRONOS_E_NOMEM;
     }
     static uint32_t v = 1;
-    l2_flush_kernel<<<148 * 8, 256>>>(static_cast<uint4 *>(buf[device]), bytes / 16, v++);
+    l2_flush_kernel<<<device_sm_count(device) * 8, 256>>>(static_cast<uint4 *>(buf[device]), bytes / 16, v++);
     return cudaDeviceSynchronize() == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+
+int chronos_device_synchronize(int device) {
+    if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
+    return cudaDeviceSynchronize() == cudaSuccess ? CHRONOS_OK : CHRONOS_E_CUDA;
+}
+
+int chronos_device_mem_info(int device, uint64_t *free_bytes, uint64_t *total_bytes) {
+    if (cudaSetDevice(device) != cudaSuccess) return CHRONOS_E_CUDA;
+    size_t f = 0, t = 0;
+    if (cudaMemGetInfo(&f, &t) != cudaSuccess) return CHRONOS_E_CUDA;
+    if (free_bytes) *free_bytes = f;
+    if (total_bytes) *total_bytes = t;
+    return CHRONOS_OK;
 }
 
 // ---- the allocation-free entry point ------------------------------------------------------------

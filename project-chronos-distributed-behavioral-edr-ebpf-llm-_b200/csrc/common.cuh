@@ -107,8 +107,16 @@ struct Plan {
     uint32_t tile_keys, n_tiles, table_len;  // radix tiling of M
     uint32_t tiles_m, tiles_s;               // window tiling of M and of S
     uint32_t overflow;         // set when M exceeds what the buffers were sized for
+    uint32_t key_or, key_and;  // over every pid seen since the last reset
     const uint32_t *skey;      // where the sorted (pid, value) arrays ended up
     const uint32_t *sval;
+};
+
+// What one batch hands to the next ON THE DEVICE (so that a submit never needs the host to know
+// it): the number of pending entries it left in process_memory (chronos_sensor.py:105) and
+// the OR / AND over every pid seen since the last reset (the bit range the sort covers).
+struct Carry {
+    uint32_t P, key_or, key_and, pad;
 };
 
 // owner rank of a pid for PID-hash sharding (also exported through the C ABI)

@@ -447,7 +447,7 @@ __global__ void __launch_bounds__(256) xchg_unpack(const XchgUnpackParams g) {
         g.meta[j] = (uint8_t)(h >> 48);
         g.ns[j] = (uint8_t)(h >> 56);
         g.slot_off[j] = so;
-        g.key[j] = k;
+        if (g.key) g.key[j] = k;
         g.pid_copy[j] = k;
         g.src[j] = j;
         o |= k;

@@ -580,7 +580,7 @@ struct CompactScanParams {
     uint32_t tile;               // records (= slots) per filter tile
     const uint32_t *sp_key, *sp_src;
     const uint8_t *sp_meta, *sp_ns;
-    uint32_t *out_key, *out_src, *out_pid;
+    uint32_t *out_key, *out_src, *out_pid;  // out_key: optional second copy of the pids (may be nullptr)
     uint8_t *out_meta, *out_ns;
     uint32_t *ticket;            // zeroed
     uint64_t *status;            // ceil(n_tiles / CS_CHUNK) epoch-tagged words
@@ -669,7 +669,7 @@ __global__ void __launch_bounds__(CS_THREADS) compact_scan(const CompactScanPara
                 const uint32_t j = j0 + u * CS_THREADS;
                 if (j < total) {
                     const uint32_t dst = base + j;
-                    p.out_key[dst] = k[u];
+                    if (p.out_key) p.out_key[dst] = k[u];
                     p.out_pid[dst] = k[u];
                     p.out_src[dst] = sr[u];
                     p.out_meta[dst] = me[u];

@@ -27,29 +27,25 @@ constexpr int RADIX_WARPS = RADIX_THREADS / 32;
 constexpr uint32_t RADIX_TILE_KEYS = CHRONOS_RADIX_TILE;  // keys per tile (multiple of RADIX_WARPS*32)
 constexpr int RADIX_MAX_PASSES = 4;
 
-// Pass 0 synthesises the sort values instead of reading them: the entry id in the low 27
-// bits and the event's class bits (CHRONOS_META_*) above, so that the kernels after the
-// sort never gather them again. Carried-in entries lose the trigger bit (a pending event
-// cannot trigger again, chronos_sensor.py:141 looks at the current event only).
-__device__ __forceinline__ uint32_t synth_value(const uint8_t *meta_lo, const uint8_t *meta_hi, uint32_t split, uint32_t i) {
-    uint32_t m = 0;
-    if (i < split) m = meta_lo ? (uint32_t)(meta_lo[i] & 0x1Eu) : 0u;
-    else m = meta_hi ? (uint32_t)(meta_hi[i - split] & 0x1Fu) : 0u;
-    return i | (m << 27);
-}
-
-// What the filter stage leaves on the device for the planner.
+// What the filter stage and the previous batch leave on the device for the planner.
 struct SortInputs {
     const uint32_t *surv_count, *key_or, *key_and;  // scalars of the batch in flight
-    uint32_t P, m_max, win_tile;
+    Carry *carry;                                   // pending count and pid bit range carried in
+    uint32_t m_max, win_tile;
 };
 
 struct SortParams {
     Plan *plan;               // written by sort_prepare (block 0), read by everything after it
     SortInputs in;
     uint32_t *keyA, *keyB, *valA, *valB;   // pass i reads set A when i is even, set B when odd
-    const uint8_t *meta_lo;   // class bits of entries [0, P) (carried-in pending), may be nullptr
-    const uint8_t *meta_hi;   // class bits of entries [P, M) (this batch's survivors)
+    // The unsorted entries are never materialised: entry i < P is the i-th pending entry of the
+    // previous batch (arrays right-aligned in a layout of pend_cap entries), entry i >= P the
+    // (i-P)-th survivor of this batch. Pass 0 reads its keys from these two sources.
+    const uint32_t *pend_key;
+    const uint8_t *pend_meta;
+    uint32_t pend_cap;
+    const uint32_t *surv_pid;
+    const uint8_t *surv_meta;
     uint32_t *ghist;          // RADIX_MAX_PASSES x RADIX_BINS global digit counts, zeroed per batch
     int pass;                 // onesweep_pass only
     uint32_t *ticket;         // zeroed per batch, one per pass
@@ -57,18 +53,34 @@ struct SortParams {
     uint32_t epoch;           // unique per onesweep_pass launch
 };
 
+__device__ __forceinline__ uint32_t entry_key(const SortParams &p, uint32_t P, uint32_t i) {
+    return i < P ? p.pend_key[p.pend_cap - P + i] : p.surv_pid[i - P];
+}
+// Pass 0 synthesises the sort values instead of reading them: the entry id in the low 27
+// bits and the event's class bits (CHRONOS_META_*) above, so that the kernels after the
+// sort never gather them again. Carried-in entries lose the trigger bit (a pending event
+// cannot trigger again, chronos_sensor.py:141 looks at the current event only).
+__device__ __forceinline__ uint32_t synth_value(const SortParams &p, uint32_t P, uint32_t i) {
+    const uint32_t m = i < P ? (uint32_t)(p.pend_meta[p.pend_cap - P + i] & 0x1Eu) : (uint32_t)(p.surv_meta[i - P] & 0x1Fu);
+    return i | (m << 27);
+}
+
 // Sizes of the batch, decided on the device once the survivor count is there (no host round
 // trip): radix passes over the bits in which the pids differ, tilings, and where the sorted
 // arrays end up after n_passes ping-pong passes.
 __device__ __forceinline__ void make_plan(const SortParams &p, Plan &pl) {
-    const uint32_t S = *p.in.surv_count, P = p.in.P;
+    const uint32_t S = *p.in.surv_count, P = p.in.carry->P;
     uint32_t M = P + S;
     pl.overflow = M > p.in.m_max ? 1u : 0u;
     if (M > p.in.m_max) M = p.in.m_max;  // never run past the buffers; the host reports the overflow
-    pl.S = M - P;
+    pl.S = M > P ? M - P : 0u;
     pl.P = P;
     pl.M = M;
-    const uint32_t diff = *p.in.key_or ^ *p.in.key_and;
+    // bit range of every pid seen since the last reset: a superset of what this batch needs,
+    // and known without reading the pending keys again
+    pl.key_or = p.in.carry->key_or | *p.in.key_or;
+    pl.key_and = p.in.carry->key_and & *p.in.key_and;
+    const uint32_t diff = pl.key_or ^ pl.key_and;
     uint32_t passes = 0;
     for (int i = 0; i < RADIX_MAX_PASSES; i++) { pl.shift[i] = 0; pl.mask[i] = 0; }
     if (M >= 2 && diff != 0) {
@@ -101,18 +113,25 @@ __global__ void __launch_bounds__(RADIX_THREADS) sort_prepare(const SortParams p
     __shared__ uint32_t h[RADIX_MAX_PASSES][RADIX_BINS];
     if (threadIdx.x == 0) {
         make_plan(p, pl);
-        if (blockIdx.x == 0) *p.plan = pl;
+        if (blockIdx.x == 0) {
+            *p.plan = pl;
+            // (other blocks may read the carry before or after this: OR / AND are idempotent)
+            p.in.carry->key_or = pl.key_or;
+            p.in.carry->key_and = pl.key_and;
+        }
     }
     for (int i = threadIdx.x; i < RADIX_MAX_PASSES * RADIX_BINS; i += RADIX_THREADS) (&h[0][0])[i] = 0;
     __syncthreads();
     const uint32_t M = pl.M, np = pl.n_passes;
-    if (np == 0) {  // nothing to sort: the "sorted" values are the synthesised ones, in place
-        for (uint32_t i = blockIdx.x * RADIX_THREADS + threadIdx.x; i < M; i += gridDim.x * RADIX_THREADS)
-            p.valA[i] = synth_value(p.meta_lo, p.meta_hi, pl.P, i);
+    if (np == 0) {  // nothing to sort: the entries themselves, in place
+        for (uint32_t i = blockIdx.x * RADIX_THREADS + threadIdx.x; i < M; i += gridDim.x * RADIX_THREADS) {
+            p.keyA[i] = entry_key(p, pl.P, i);
+            p.valA[i] = synth_value(p, pl.P, i);
+        }
         return;
     }
     for (uint32_t i = blockIdx.x * RADIX_THREADS + threadIdx.x; i < M; i += gridDim.x * RADIX_THREADS) {
-        const uint32_t k = p.keyA[i];
+        const uint32_t k = entry_key(p, pl.P, i);
         for (uint32_t q = 0; q < np; q++) atomicAdd(&h[q][(k >> pl.shift[q]) & pl.mask[q]], 1u);
     }
     __syncthreads();
@@ -137,8 +156,9 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
     if ((uint32_t)p.pass >= pl.n_passes) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const bool odd = p.pass & 1;
-    const uint32_t *keys_in = odd ? p.keyB : p.keyA;
-    const uint32_t *vals_in = p.pass == 0 ? nullptr : (odd ? p.valB : p.valA);
+    const bool first = p.pass == 0;
+    const uint32_t *keys_in = odd ? p.keyB : p.keyA;   // (pass 0 reads the entries instead)
+    const uint32_t *vals_in = first ? nullptr : (odd ? p.valB : p.valA);
     uint32_t *keys_out = odd ? p.keyA : p.keyB;
     uint32_t *vals_out = odd ? p.valA : p.valB;
     const uint32_t n = pl.M, n_tiles = pl.n_tiles, shift = pl.shift[p.pass], mask = pl.mask[p.pass], split = pl.P;
@@ -172,7 +192,8 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
         const uint32_t w_lo = min(t_hi, t_lo + warp * sub);
         const uint32_t w_hi = min(t_hi, w_lo + sub);
         // 1) per-warp digit counts over the warp's contiguous sub-range
-        for (uint32_t i = w_lo + lane; i < w_hi; i += 32) atomicAdd(&whist[warp][(keys_in[i] >> shift) & mask], 1u);
+        for (uint32_t i = w_lo + lane; i < w_hi; i += 32)
+            atomicAdd(&whist[warp][((first ? entry_key(p, split, i) : keys_in[i]) >> shift) & mask], 1u);
         __syncthreads();
         // 2) digit d = tid: tile total, published; keys of digit d in earlier tiles by look-back
         uint32_t total = 0;
@@ -213,7 +234,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
             const bool valid = i < w_hi;
             uint32_t key = 0, d = RADIX_BINS;  // invalid lanes form their own group
             if (valid) {
-                key = keys_in[i];
+                key = first ? entry_key(p, split, i) : keys_in[i];
                 d = (key >> shift) & mask;
             }
             const uint32_t peers = __match_any_sync(0xffffffffu, d);
@@ -226,7 +247,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
             if (valid) {
                 const uint32_t dst = base + before;
                 keys_out[dst] = key;
-                vals_out[dst] = vals_in ? vals_in[i] : synth_value(p.meta_lo, p.meta_hi, split, i);
+                vals_out[dst] = first ? synth_value(p, split, i) : vals_in[i];
             }
         }
     }

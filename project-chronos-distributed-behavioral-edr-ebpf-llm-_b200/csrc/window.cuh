@@ -63,7 +63,9 @@ struct WinParams {
     const uint32_t *surv_src;       // S batch-local record index
     const uint64_t *surv_arrival;   // S explicit arrival indices, or nullptr => base_arrival + surv_src
     uint64_t base_arrival;
-    const uint64_t *pend_arrival;   // P (previous batch)
+    const uint64_t *pend_arrival;   // previous batch's pending arrival indices, right-aligned in
+    uint32_t pend_cap_prev;         //   an array of pend_cap_prev entries (P of them, device-side count)
+    Carry *carry;                   // window_reverse leaves the new pending count here for the next batch
     const uint32_t *surv_pid;       // S pids in arrival order (the sort consumed the key array)
     // per-PID table (chain.cuh)
     uint64_t *pid_tab;
@@ -97,7 +99,7 @@ struct WinParams {
 // (Patching a by-value copy of the parameter struct from the plan did not work: nvcc 12.9
 // kept reading the ORIGINAL skey pointer out of the parameter bank)
 __device__ __forceinline__ uint64_t win_arrival_of(const WinParams &p, uint32_t P, uint32_t e) {
-    if (e < P) return p.pend_arrival[e];
+    if (e < P) return p.pend_arrival[p.pend_cap_prev - P + e];
     const uint32_t j = e - P;
     return p.surv_arrival ? p.surv_arrival[j] : p.base_arrival + p.surv_src[j];
 }
@@ -319,7 +321,11 @@ __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p)
             St2 in = fn_lookback<Fn2>(p.status, tile, total, St2{0u, 0u, NONE32}, lane);
             if (lane == 0) {
                 s_in = in;
-                if (tile == n_tiles - 1) *p.n_pending = Fn2::apply(total, in).a;
+                if (tile == n_tiles - 1) {
+                    const uint32_t np = Fn2::apply(total, in).a;
+                    *p.n_pending = np;
+                    p.carry->P = np;  // every kernel of this batch takes P from the plan, not from here
+                }
             }
         }
         __syncthreads();
@@ -467,7 +473,8 @@ struct GatherParams {
     uint32_t M, P;
     const uint32_t *surv_src;
     const uint8_t *batch;        // this batch's records (device)
-    const uint32_t *pend_slot;   // P
+    const uint32_t *pend_slot;   // previous batch's pending arena slots, right-aligned in an array of
+    uint32_t pend_cap_prev;      //   pend_cap_prev entries
     const uint8_t *prev_arena;
     uint8_t *arena;
     // transport form (chronos_submit_survivors): entry j's record is slot_ns[j] 16-byte slots
@@ -478,49 +485,93 @@ struct GatherParams {
     const Plan *plan;            // when set, sval / M / P are taken from it on the device
 };
 
-__global__ void __launch_bounds__(256) gather_records(const GatherParams g) {
+// One warp moves 16 records (288 chunks of 16 bytes, 9 per lane) per step. The chunks travel
+// global -> shared memory with cp.async (LDGSTS): the data in flight sits in shared memory, not
+// in registers, so the kernel is small enough (about 32 registers a thread) to share every SM
+// with the window scans that run beside it; two stages per warp keep the next group's loads
+// in flight while the current one is stored.
+constexpr int GATHER_THREADS = 256;
+constexpr int GATHER_WARPS = GATHER_THREADS / 32;
+constexpr uint32_t GATHER_GROUP = 16;
+constexpr int GATHER_STAGES = 2;
+constexpr size_t GATHER_SMEM = (size_t)GATHER_WARPS * GATHER_STAGES * GATHER_GROUP * CH_REC_BYTES;
+
+__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src, uint32_t src_bytes) {
+    // src_bytes = 16: plain copy; 0: the 16 bytes are zero-filled, nothing is read
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst_smem)), "l"(src), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+__global__ void __launch_bounds__(GATHER_THREADS) gather_records(const GatherParams g) {
+    extern __shared__ uint4 gather_smem[];
     const uint32_t gM = g.plan ? g.plan->M : g.M, gP = g.plan ? g.plan->P : g.P;
     const uint32_t *const gsval = g.plan ? g.plan->sval : g.sval;
-    const int lane = threadIdx.x & 31;
-    const uint32_t warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
-    constexpr uint32_t GROUP = 16;  // records per warp step: 16*18 = 288 chunks = 9 per lane
-    for (uint32_t base = warp_global * GROUP; base < gM; base += n_warps * GROUP) {
-        const uint32_t cnt = min(GROUP, gM - base);
-        // lane r (< cnt) resolves the source of record base+r
-        const uint8_t *src = nullptr;
-        uint32_t ns = 0;  // 0: plain 288-byte record at src; else transport form of ns slots
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t warp_global = blockIdx.x * GATHER_WARPS + warp;
+    const uint32_t n_warps = gridDim.x * GATHER_WARPS;
+    constexpr uint32_t GROUP_CHUNKS = GATHER_GROUP * CH_REC_CHUNKS;  // 288
+    uint4 *const my = gather_smem + (size_t)warp * GATHER_STAGES * GROUP_CHUNKS;
+
+    // all chunks of the group starting at `base` into stage `s` (asynchronous)
+    auto issue = [&](uint32_t base, int s) {
+        const uint32_t cnt = min(GATHER_GROUP, gM - base);
+        const uint8_t *src = nullptr;  // lane r (< cnt) resolves the source of record base + r
+        uint32_t ns = 0;               // 0: plain 288-byte record at src; else transport form of ns slots
         if ((uint32_t)lane < cnt) {
             const uint32_t e = gsval[base + lane] & VAL_ID_MASK;
-            if (e < gP) src = g.prev_arena + (size_t)g.pend_slot[e] * CH_REC_BYTES;
+            if (e < gP) src = g.prev_arena + (size_t)g.pend_slot[g.pend_cap_prev - gP + e] * CH_REC_BYTES;
             else if (g.slots) {
                 src = reinterpret_cast<const uint8_t *>(g.slots + g.slot_off[e - gP]);
                 ns = g.slot_ns[e - gP];
             } else src = g.batch + (size_t)g.surv_src[e - gP] * CH_REC_BYTES;
         }
-        uint4 *dst = reinterpret_cast<uint4 *>(g.arena + (size_t)base * CH_REC_BYTES);
-        // all nine loads of a lane are issued before the first store: one load in flight per
-        // warp (load -> store -> next load) left this kernel latency-bound at 4.1 TB/s
-        uint4 v[9];
+        uint4 *stage = my + (size_t)s * GROUP_CHUNKS;
 #pragma unroll
         for (int it = 0; it < 9; it++) {
             const uint32_t c = it * 32 + lane;        // chunk id within the group
             const uint32_t r = c / CH_REC_CHUNKS;     // record within the group
             const uint32_t ch = c - r * CH_REC_CHUNKS;
-            const unsigned long long sp =
-                __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, (int)(r & 31u));
+            const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, (int)(r & 31u));
             const uint32_t rns = __shfl_sync(0xffffffffu, ns, (int)(r & 31u));
-            // transport form: slot 0,1 = chunks 0,1; slot 2 = chunk 17; slots 3.. = chunks 2..
+            // transport form: slot 0,1 = chunks 0,1; slot 2 = chunk 17; slots 3.. = chunks 2..;
+            // chunks the entry does not carry are zeros (nothing but NUL padding was there)
             const uint32_t sl = rns == 0 ? ch : (ch < 2 ? ch : (ch == 17 ? 2u : ch + 1u));
-            const bool ok = r < cnt && (rns == 0 || sl < rns);
-            v[it] = make_uint4(0u, 0u, 0u, 0u);
-            if (ok) v[it] = __ldg(reinterpret_cast<const uint4 *>((uintptr_t)sp) + sl);
+            const bool have = rns == 0 || sl < rns;
+            if (r < cnt) cp_async16(stage + c, reinterpret_cast<const uint4 *>((uintptr_t)sp) + (have ? sl : 0u), have ? 16u : 0u);
         }
-#pragma unroll
-        for (int it = 0; it < 9; it++) {
-            const uint32_t c = it * 32 + lane;
-            if (c / CH_REC_CHUNKS < cnt) dst[c] = v[it];
+        cp_async_commit();
+    };
+
+    // software pipeline: step k issues group k (if any) and then stores group k-1
+    const uint32_t stride = n_warps * GATHER_GROUP;
+    uint32_t prev = 0xffffffffu;
+    int s = 0;
+#pragma unroll 1
+    for (uint32_t base = warp_global * GATHER_GROUP;; base += stride) {
+        const bool have = base < gM;
+        if (have) issue(base, s);
+        else cp_async_commit();  // (an empty group keeps the wait count uniform)
+        if (prev != 0xffffffffu) {
+            cp_async_wait<1>();  // everything but the group just issued has landed
+            __syncwarp();
+            const uint32_t cnt = min(GATHER_GROUP, gM - prev);
+            const uint4 *stage = my + (size_t)(s ^ 1) * GROUP_CHUNKS;
+            uint4 *dst = reinterpret_cast<uint4 *>(g.arena + (size_t)prev * CH_REC_BYTES);
+#pragma unroll 3
+            for (int it = 0; it < 9; it++) {
+                const uint32_t c = it * 32 + lane;
+                if (c < cnt * CH_REC_CHUNKS) dst[c] = stage[c];
+            }
+            __syncwarp();  // the stage is refilled by the next issue
         }
+        if (!have) break;
+        prev = base;
+        s ^= 1;
     }
 }
 

@@ -43,16 +43,25 @@ class BatchResult:
 
 
 class Context:
-    def __init__(self, device=0, max_batch_events=1 << 20):
+    """One GPU's state. All device memory is allocated here (chronos_create): room for batches
+    of max_batch_events on top of max_pending_events pending in process_memory (default: as many
+    as one batch holds). Two batches may be in flight: a second submit() before fetch() lets
+    the filter of the new batch run beside the window stage of the previous one; fetch()
+    returns batches in submit order."""
+
+    def __init__(self, device=0, max_batch_events=1 << 20, max_pending_events=None):
         self._L = _ffi.lib()
         self.device = int(device)
         self._h = c_void_p()
-        rc = self._L.chronos_create(self.device, int(max_batch_events), byref(self._h))
+        if max_pending_events is None:
+            rc = self._L.chronos_create(self.device, int(max_batch_events), byref(self._h))
+        else:
+            rc = self._L.chronos_create_sized(self.device, int(max_batch_events), int(max_pending_events), byref(self._h))
         if rc != _ffi.OK:
             self._h = c_void_p()
             raise _ffi.ChronosError(rc, "chronos_create failed (no usable sm_100 GPU? there is no CPU fallback)")
         self.max_batch_events = int(max_batch_events)
-        self._keep = None
+        self._keep = []
 
     def _check(self, rc):
         if rc != _ffi.OK:
@@ -84,8 +93,8 @@ class Context:
     def submit(self, records, base_arrival_index=0):
         """records: bytes-like / numpy array of n*288 bytes on the host."""
         a = as_record_bytes(records)
-        self._keep = a  # the async H2D copy reads it until fetch
         self._check(self._L.chronos_submit(self._h, a.ctypes.data, a.size // RECORD_BYTES, int(base_arrival_index)))
+        self._keep = (self._keep + [a])[-2:]  # the async H2D copies of the (at most two) batches in flight read them
 
     def submit_ptr(self, ptr, n, base_arrival_index=0):
         """ptr: raw host or device address of n records (device pointers are used in place)."""
@@ -159,8 +168,8 @@ class Context:
 
     def filter_exchange(self, records, base_arrival_index=0):
         a = as_record_bytes(records)
-        self._keep = a
         self.filter_exchange_ptr(a.ctypes.data if a.size else 0, a.size // RECORD_BYTES, base_arrival_index)
+        self._keep = (self._keep + [a])[-2:]
 
     def submit_exchanged(self):
         """Stage 2 on what the peers delivered for this step."""
@@ -173,7 +182,6 @@ class Context:
     def fetch_counts(self):
         c = _ffi.Counts()
         self._check(self._L.chronos_fetch(self._h, byref(c)))
-        self._keep = None
         return {k: int(getattr(c, k)) for k, _ in _ffi.Counts._fields_ if k != "reserved"}
 
     def fetch(self, records=True):

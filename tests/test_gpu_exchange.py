@@ -8,12 +8,17 @@ whole trace (PIDs are independent: chronos_sensor.py:105, :138, :142, :157).
 
 Emulation caveat: a rank's stage 2 SPINS on the GPU until its peers have delivered. With every
 rank on one GPU, a peer's stage 1 must therefore never queue up behind that spin: _step()
-enqueues stage 1 of all ranks before any stage 2, and conftest.py raises
-CUDA_DEVICE_MAX_CONNECTIONS so that the streams of different contexts do not share a hardware
-queue. Real ranks are one process per GPU and cannot block each other this way."""
+enqueues stage 1 of all ranks before any stage 2. Streams of different contexts may still share
+a hardware queue (there are at most 32, CUDA_DEVICE_MAX_CONNECTIONS in conftest.py, and a long
+pytest process creates hundreds of streams), and then a stage 1 sits behind a spinning stage 2
+until that times out. Unless a test says otherwise, _step() therefore waits for all stage 1s
+before it enqueues the first stage 2; the waiting path itself is covered by the time-out test
+here and by the real ranks of test_gpu_multiprocess.py, which are one process per GPU and
+cannot block each other this way."""
 import numpy as np
 import pytest
 
+from chronos_b200 import _ffi
 from helpers import canonical
 from oracle import coracle
 
@@ -30,12 +35,14 @@ def _make_ranks(world, n_max, cap_pair):
     return ctxs
 
 
-def _step(ctxs, slices, bases, order=None):
+def _step(ctxs, slices, bases, order=None, drain=True):
     """One step on every emulated rank; returns per-rank BatchResult."""
     world = len(ctxs)
     order = list(order or range(world))
     for r in order:
         ctxs[r].filter_exchange(slices[r], bases[r])
+    if drain:
+        assert _ffi.lib().chronos_device_synchronize(0) == 0
     for r in order:
         ctxs[r].submit_exchanged()
     return [ctxs[r].fetch(records=True) for r in range(world)]
@@ -131,6 +138,7 @@ def test_window_overflow_is_reported_not_truncated():
     ctxs = _make_ranks(world, len(rows), cap_pair=256)  # far too small
     for r in range(world):
         ctxs[r].filter_exchange(rows[r * 30_000:(r + 1) * 30_000], r * 30_000)
+    assert _ffi.lib().chronos_device_synchronize(0) == 0
     for r in range(world):
         ctxs[r].submit_exchanged()
     for r in range(world):
