@@ -133,6 +133,12 @@ int chronos_copy_arena(chronos_ctx *ctx, void *dst, uint64_t cap_records);
  * analyze_sequence caller needs (chronos_sensor.py:147). */
 int chronos_copy_window_records(chronos_ctx *ctx, void *dst, uint64_t cap_records);
 int chronos_copy_chains(chronos_ctx *ctx, uint32_t *pid, uint64_t *global_idx, uint64_t cap);
+/* One 64-bit digest per window of the fetched batch (same order as chronos_copy_windows),
+ * computed on the GPU over the window's records in canonical form: bytes behind a field's
+ * first NUL -- which the reference never reads, chronos_sensor.py:125-130 -- count as zero.
+ * Equal digests = the same (pid, history) would reach analyze_sequence (:147). Used to compare
+ * the output of a sharded multi-GPU run with a single-GPU run without moving the records. */
+int chronos_window_digests(chronos_ctx *ctx, uint64_t *dst, uint64_t cap);
 
 /* Replaces: reading process_memory (chronos_sensor.py:105) -- the pending per-PID
  * lists after the last fetched batch, ascending pid, arrival order inside a pid.
@@ -148,6 +154,11 @@ int chronos_get_device_view(chronos_ctx *ctx, chronos_device_view *out);
  * stream: the whole submit and the filter kernel alone (events right around its
  * launch), in milliseconds. */
 int chronos_last_timing(chronos_ctx *ctx, float *total_ms, float *filter_ms);
+/* Stage boundaries of the last fetched batch (CUDA events on the context's streams), in
+ * milliseconds: [0] filter kernel, [1] cross-tile compaction (sharded path: + owner histogram and
+ * scan), [2] sharded path only: pack into the owners' windows, [3] sharded path only: wait for the
+ * peers + unpack, [4] init + sort, [5] window kernels + record gather. cap <= 6 values are written. */
+int chronos_last_stage_times(chronos_ctx *ctx, float *ms, uint32_t cap);
 /* Number of kernel launches the last submit issued (bench.py's gpu_launches). */
 int chronos_last_launches(chronos_ctx *ctx, uint64_t *launches);
 /* The CUDA stream the context launches on (cudaStream_t as void*), for callers that

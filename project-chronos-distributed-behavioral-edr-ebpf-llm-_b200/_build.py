@@ -36,5 +36,19 @@ def build(force=False, verbose=False):
     return LIB_PATH
 
 
+HOSTGEN_PATH = os.path.join(ROOT, "tools", "libchronos_tracegen_host.so")
+
+
+def build_hostgen(force=False):
+    """g++ build of the trace generator alone (tools/tracegen_host.cpp): no CUDA inside."""
+    src = os.path.join(ROOT, "tools", "tracegen_host.cpp")
+    deps = [src, os.path.join(SRC_DIR, "tracegen.cuh"), os.path.join(ROOT, "include", "chronos.h")]
+    if not force and os.path.exists(HOSTGEN_PATH) and all(os.path.getmtime(d) <= os.path.getmtime(HOSTGEN_PATH) for d in deps):
+        return HOSTGEN_PATH
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-x", "c++", "-fPIC", "-shared", "-I", SRC_DIR,
+                           "-I", os.path.join(ROOT, "include"), "-o", HOSTGEN_PATH, src])
+    return HOSTGEN_PATH
+
+
 if __name__ == "__main__":
     print(build(force=True, verbose=True))

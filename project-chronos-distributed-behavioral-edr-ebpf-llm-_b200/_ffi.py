@@ -64,11 +64,13 @@ SIGNATURES = {
     "chronos_copy_windows": (c_int, [c_void_p, c_void_p, c_uint64]),
     "chronos_copy_arena": (c_int, [c_void_p, c_void_p, c_uint64]),
     "chronos_copy_window_records": (c_int, [c_void_p, c_void_p, c_uint64]),
+    "chronos_window_digests": (c_int, [c_void_p, c_void_p, c_uint64]),
     "chronos_copy_chains": (c_int, [c_void_p, c_void_p, c_void_p, c_uint64]),
     "chronos_state": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_uint64]),
     "chronos_state_pids": (c_int, [c_void_p, c_void_p, c_uint64]),
     "chronos_get_device_view": (c_int, [c_void_p, POINTER(DeviceView)]),
     "chronos_last_timing": (c_int, [c_void_p, POINTER(c_float), POINTER(c_float)]),
+    "chronos_last_stage_times": (c_int, [c_void_p, POINTER(c_float), c_uint32]),
     "chronos_last_launches": (c_int, [c_void_p, POINTER(c_uint64)]),
     "chronos_stream": (c_void_p, [c_void_p]),
     "chronos_owner_of": (c_uint32, [c_uint32, c_uint32]),

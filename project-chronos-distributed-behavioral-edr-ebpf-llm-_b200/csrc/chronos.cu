@@ -100,6 +100,8 @@ struct BatchSet {
     Plan *h_plan = nullptr;
     cudaEvent_t ev_start = nullptr, ev_stage1 = nullptr, ev_end = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
     cudaEvent_t ev_packed = nullptr;  // last read of this set's results by a download
+    cudaEvent_t ev_prepack = nullptr, ev_s1end = nullptr, ev_sort = nullptr;  // stage boundaries (timing only)
+    float stage_ms[8] = {0};
     enum State { FREE, SUBMITTED, DONE, FETCHED } state = FREE;
     // the batch
     uint64_t n = 0, base = 0, P_ub = 0, pids_ub = 0, Mmax = 0;
@@ -169,7 +171,7 @@ struct chronos_ctx {
     uint64_t launches = 0;  // of the submit being enqueued
     int filter_variant = 0;
     int gather_ctas_per_sm = 0;
-    bool gather_first = true;
+    int gather_when = 0;  // 0: right after the sort, launched before group_forward; 1: same, launched behind it; 2: once group_forward has finished
     int prio_lo = 0;
     bool no_pipeline = false;
     // CHRONOS_TRACE=1: CUDA events between the stages of a submit, printed at fetch
@@ -356,6 +358,63 @@ __global__ void pack_windows_kernel(const uint8_t *arena, const chronos_window *
         uint4 *d = reinterpret_cast<uint4 *>(dst + (size_t)off[w] * CH_REC_BYTES);
         const uint32_t chunks = win[w].len * CH_REC_CHUNKS;
         for (uint32_t ch = lane; ch < chunks; ch += 32) d[ch] = s[ch];
+    }
+}
+
+// One warp per window: a 64-bit digest of the window's records in CANONICAL form -- bytes behind
+// a field's first NUL count as zero (that is all the reference ever reads of a field, ctypes
+// c_char arrays stop at the NUL, chronos_sensor.py:125-130) and so do the two bytes of tail
+// padding. Two runs produce equal digests exactly when analyze_sequence (:147) would be handed
+// the same history, record by record, in the same order.
+__device__ __forceinline__ uint64_t digest_mix(uint64_t z) {
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL;
+    return z ^ (z >> 31);
+}
+__global__ void window_digest_kernel(const uint8_t *arena, const chronos_window *win, uint32_t nw, uint64_t *out) {
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const uint32_t n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t w = warp; w < nw; w += n_warps) {
+        uint64_t acc = 0;
+        for (uint32_t r = 0; r < win[w].len; r++) {
+            const uint32_t *rec = reinterpret_cast<const uint32_t *>(arena + (size_t)(win[w].start + r) * CH_REC_BYTES);
+            uint32_t wd[3];
+            uint32_t end_comm = 20, end_argv = 276, end_type = 286;  // byte offset of each field's first NUL
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const uint32_t i = lane + 32 * k;  // word index, 72 words per record
+                wd[k] = i < CH_REC_WORDS ? rec[i] : 0u;
+                if (i >= 1 && i < CH_REC_WORDS) {
+                    uint32_t x = wd[k];
+                    if (i == 71) x |= 0xFFFF0000u;  // the padding bytes are not part of `type`
+                    const uint32_t z = zero_bytes(x);
+                    if (z) {
+                        const uint32_t pos = 4 * i + (uint32_t)first_zero_index(z);
+                        if (i < 5) end_comm = min(end_comm, pos);
+                        else if (i < 69) end_argv = min(end_argv, pos);
+                        else end_type = min(end_type, pos);
+                    }
+                }
+            }
+            end_comm = __reduce_min_sync(0xffffffffu, end_comm);
+            end_argv = __reduce_min_sync(0xffffffffu, end_argv);
+            end_type = __reduce_min_sync(0xffffffffu, end_type);
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+                const uint32_t i = lane + 32 * k;
+                if (i >= CH_REC_WORDS) continue;
+                uint32_t x = wd[k];
+                if (i >= 1) {
+                    const uint32_t end = i < 5 ? end_comm : (i < 69 ? end_argv : end_type);
+                    const uint32_t b0 = 4 * i;  // keep the bytes before `end`
+                    if (end <= b0) x = 0;
+                    else if (end < b0 + 4) x = keep_low_bytes(x, (int)(end - b0));
+                }
+                acc += digest_mix(((uint64_t)(r * CH_REC_WORDS + i) << 32) ^ x ^ 0x9E3779B97F4A7C15ULL);
+            }
+        }
+        for (int d = 16; d >= 1; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+        if (lane == 0) out[w] = digest_mix(acc ^ ((uint64_t)win[w].len << 40) ^ win[w].pid);
     }
 }
 
@@ -708,6 +767,7 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     }
     CK(cudaGetLastError());
     CK(cudaEventRecord(c->ev_sorted, st));
+    CK(cudaEventRecord(b.ev_sort, st));
     mark(c, "sort done");
 
     WinParams w;
@@ -764,7 +824,7 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
         g.slot_ns = b.slots ? ptr<uint8_t>(b.surv_ns) : nullptr;
         const uint32_t blocks = (uint32_t)std::min<uint64_t>((Mmax + GATHER_WARPS * GATHER_GROUP - 1) / (GATHER_WARPS * GATHER_GROUP),
                                                              (uint64_t)c->sm_count * (uint64_t)c->gather_ctas_per_sm);
-        CK(cudaStreamWaitEvent(c->stream2, c->ev_sorted, 0));
+        CK(cudaStreamWaitEvent(c->stream2, c->gather_when == 2 ? c->ev_fwd : c->ev_sorted, 0));
         mark(c, "gather starts", c->stream2);
         gather_records<<<std::max(1u, blocks), GATHER_THREADS, GATHER_SMEM, c->stream2>>>(g);
         CK(cudaGetLastError());
@@ -774,7 +834,7 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
         if ((rc = dbg_sync(c, "gather_records"))) return rc;
         return CHRONOS_OK;
     };
-    if (c->gather_first && (rc = launch_gather())) return rc;
+    if (c->gather_when == 0 && (rc = launch_gather())) return rc;
 
     // ---- flush automaton + chain labeller ----------------------------------------------------
     w.ticket = tk + 60;
@@ -786,7 +846,7 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     CK(cudaEventRecord(c->ev_fwd, st));
     mark(c, "group_forward done");
 
-    if (!c->gather_first && (rc = launch_gather())) return rc;
+    if (c->gather_when != 0 && (rc = launch_gather())) return rc;
 
     // ---- windows in arrival order (stream3) beside the reverse scan (main stream) ----------
     {
@@ -870,6 +930,24 @@ int complete_batch(chronos_ctx *c, BatchSet &b) {
             cudaEventElapsedTime(&ms, c->tev[0], c->tev[i]);
             fprintf(stderr, "[chronos trace] %-28s at %8.3f ms\n", c->tname[i], ms);
         }
+    }
+    {   // stage boundaries of the batch (chronos_last_stage_times)
+        float *t = b.stage_ms;
+        for (int i = 0; i < 8; i++) t[i] = 0.f;
+        const bool filtered = b.filter_timed || (b.exchanged && c->x_filter_timed);
+        if (filtered) cudaEventElapsedTime(&t[0], b.ev_f0, b.ev_f1);
+        if (b.exchanged) {
+            if (filtered) cudaEventElapsedTime(&t[1], b.ev_f1, b.ev_prepack);
+            cudaEventElapsedTime(&t[2], b.ev_prepack, b.ev_s1end);
+            cudaEventElapsedTime(&t[3], b.ev_start, b.ev_stage1);
+        } else if (filtered) {
+            cudaEventElapsedTime(&t[1], b.ev_f1, b.ev_stage1);
+        }
+        if (any) {
+            cudaEventElapsedTime(&t[4], b.ev_stage1, b.ev_sort);
+            cudaEventElapsedTime(&t[5], b.ev_sort, b.ev_end);
+        }
+        cudaGetLastError();
     }
     cudaEventElapsedTime(&b.t_filter, b.ev_start, b.ev_stage1);
     // (a stage-2-only batch keeps the filter time measured by its stage 1)
@@ -1041,8 +1119,8 @@ int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pen
     const char *gc = getenv("CHRONOS_GATHER_CTAS");
     c->gather_ctas_per_sm = gc ? std::max(1, atoi(gc)) : 2;
     c->no_pipeline = getenv("CHRONOS_NO_PIPELINE") != nullptr;
-    const char *gf = getenv("CHRONOS_GATHER_FIRST");
-    c->gather_first = gf ? atoi(gf) != 0 : true;
+    const char *gf = getenv("CHRONOS_GATHER_WHEN");
+    c->gather_when = gf ? atoi(gf) : 0;
     const bool gather_low = getenv("CHRONOS_GATHER_LOW") != nullptr;
     c->trace = getenv("CHRONOS_TRACE") != nullptr;
     auto boot = [&]() -> int {
@@ -1062,7 +1140,8 @@ int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pen
             CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
         CK(cudaEventCreate(&c->ev_x0));
         for (BatchSet &b : c->set) {
-            for (cudaEvent_t *e : {&b.ev_start, &b.ev_stage1, &b.ev_end, &b.ev_f0, &b.ev_f1}) CK(cudaEventCreate(e));
+            for (cudaEvent_t *e : {&b.ev_start, &b.ev_stage1, &b.ev_end, &b.ev_f0, &b.ev_f1, &b.ev_prepack, &b.ev_s1end, &b.ev_sort})
+                CK(cudaEventCreate(e));
             CK(cudaEventCreateWithFlags(&b.ev_packed, cudaEventDisableTiming));
             CK(cudaMallocHost(reinterpret_cast<void **>(&b.h_scalars), RESULT_BLOCK_BYTES));
             memset(b.h_scalars, 0, RESULT_BLOCK_BYTES);
@@ -1114,7 +1193,7 @@ int chronos_destroy(chronos_ctx *c) {
                          &b.d_batch, &b.result};
         for (DevBuf *d : all) release(*d);
         if (b.h_scalars) cudaFreeHost(b.h_scalars);
-        for (cudaEvent_t e : {b.ev_start, b.ev_stage1, b.ev_end, b.ev_f0, b.ev_f1, b.ev_packed})
+        for (cudaEvent_t e : {b.ev_start, b.ev_stage1, b.ev_end, b.ev_f0, b.ev_f1, b.ev_packed, b.ev_prepack, b.ev_s1end, b.ev_sort})
             if (e) cudaEventDestroy(e);
     }
     DevBuf *all[] = {&c->carry, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->pflag, &c->entry_out, &c->wsorted, &c->status,
@@ -1426,6 +1505,24 @@ int chronos_download_wait(chronos_ctx *c) {
     return CHRONOS_OK;
 }
 
+int chronos_window_digests(chronos_ctx *c, uint64_t *dst, uint64_t cap) {
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
+    if (rc) return rc;
+    BatchSet &b = *bp;
+    if (cap < b.W || (b.W && !dst)) return fail(c, CHRONOS_E_ARG, "digest buffer too small");
+    if (!b.W) return CHRONOS_OK;
+    if ((rc = ensure(c, c->pack, b.W * 8))) return rc;
+    cudaStream_t st;
+    if ((rc = host_stream(c, &st))) return rc;
+    window_digest_kernel<<<(unsigned)std::min<uint64_t>((b.W + 7) / 8, (uint64_t)c->sm_count * 8), 256, 0, st>>>(
+        ptr<uint8_t>(b.arena), ptr<chronos_window>(b.windows), (uint32_t)b.W, ptr<uint64_t>(c->pack));
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(dst, c->pack.p, b.W * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    return CHRONOS_OK;
+}
+
 int chronos_copy_chains(chronos_ctx *c, uint32_t *pid, uint64_t *global_idx, uint64_t cap) {
     BatchSet *bp;
     int rc = need_fetched(c, &bp);
@@ -1683,6 +1780,15 @@ int chronos_last_timing(chronos_ctx *c, float *total_ms, float *filter_ms) {
     return CHRONOS_OK;
 }
 
+int chronos_last_stage_times(chronos_ctx *c, float *ms, uint32_t cap) {
+    BatchSet *bp;
+    int rc = need_fetched(c, &bp);
+    if (rc) return rc;
+    if (!ms) return CHRONOS_E_ARG;
+    for (uint32_t i = 0; i < cap && i < 6; i++) ms[i] = bp->stage_ms[i];
+    return CHRONOS_OK;
+}
+
 int chronos_reset(chronos_ctx *c) {
     if (!c) return CHRONOS_E_ARG;
     CK(cudaSetDevice(c->device));
@@ -1773,8 +1879,10 @@ static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base
     pk.totals = ptr<uint32_t>(c->x_totals);
     pk.err = &ds->xchg_err;
     pk.done = ptr<uint32_t>(c->tickets_f) + 58;
+    CK(cudaEventRecord(b.ev_prepack, st));
     xchg_pack<<<xblocks, XCHG_THREADS, XCHG_PACK_SMEM, st>>>(pk);
     CK(cudaGetLastError());
+    CK(cudaEventRecord(b.ev_s1end, st));
     c->launches += 2;
     if ((rc = dbg_sync(c, "xchg_pack"))) return rc;
     mark(c, "pack into owners' windows");

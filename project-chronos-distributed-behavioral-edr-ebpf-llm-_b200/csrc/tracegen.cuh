@@ -17,7 +17,7 @@
 #if defined(__CUDACC__)
 #define CH_HD __host__ __device__ __forceinline__
 #else
-#define CH_HD static inline
+#define CH_HD inline
 #endif
 
 #include "chronos.h"  // struct chronos_tracegen_cfg

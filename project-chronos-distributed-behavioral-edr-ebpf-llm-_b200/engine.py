@@ -207,6 +207,12 @@ class Context:
         self._check(self._L.chronos_last_launches(self._h, byref(ln)))
         return BatchResult(counts, surv, meta, win, wrec, t.value, f.value, ln.value, cpid, cidx)
 
+    def window_digests(self, n_windows):
+        """uint64 digest of every window of the fetched batch (canonical record bytes), window order."""
+        out = np.zeros(int(n_windows), dtype=np.uint64)
+        self._check(self._L.chronos_window_digests(self._h, out.ctypes.data, out.size))
+        return out
+
     def arena(self):
         c = _ffi.Counts()
         self._check(self._L.chronos_fetch(self._h, byref(c)))
@@ -218,6 +224,14 @@ class Context:
         t, f = c_float(), c_float()
         self._check(self._L.chronos_last_timing(self._h, byref(t), byref(f)))
         return t.value, f.value
+
+    STAGES = ("filter", "compact", "pack", "wait_unpack", "sort", "windows_gather")
+
+    def last_stage_times(self):
+        """{stage: ms} of the last fetched batch (see chronos_last_stage_times)."""
+        a = (c_float * 6)()
+        self._check(self._L.chronos_last_stage_times(self._h, a, 6))
+        return dict(zip(self.STAGES, [float(x) for x in a]))
 
     def last_launches(self):
         ln = c_uint64()

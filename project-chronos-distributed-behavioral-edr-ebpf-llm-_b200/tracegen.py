@@ -76,6 +76,22 @@ def generate_host(spec, first=0, n=None):
     return out
 
 
+def generate_host_nocuda(spec, first=0, n=None):
+    """generate_host through the host-only helper library (tools/libchronos_tracegen_host.so):
+    the same bytes without loading the CUDA library (bench.py's CPU reference arm)."""
+    from . import _build
+
+    n = spec["n"] if n is None else int(n)
+    cfg, cdf = make_cfg(spec)
+    L = ctypes.CDLL(_build.build_hostgen())
+    L.chronos_hostgen.argtypes = [ctypes.POINTER(_ffi.TracegenCfg), c_void_p, ctypes.c_uint64, ctypes.c_uint64, c_void_p]
+    out = np.zeros((n, RECORD_BYTES), dtype=np.uint8)
+    rc = L.chronos_hostgen(byref(cfg), cdf.ctypes.data if cdf is not None else None, int(first), n, out.ctypes.data)
+    if rc != 0:
+        raise ValueError("chronos_hostgen: bad arguments")
+    return out
+
+
 class DeviceBuffer:
     """A raw device allocation made through the C ABI (no torch needed)."""
 

@@ -92,3 +92,14 @@ def test_event_str_formatter_matches_reference_format():
     assert event_str(pack_record(1, b"chmod", b"", b"OPEN")) == "[OPEN] chmod -> "
     assert event_str(pack_record(1, b"attack_chain.sh", b"curl", b"EXEC")) == "[EXEC] attack_chain.sh -> curl"
     assert event_str(pack_record(1, b"caf\xc3\xa9", b"/tmp/\xe2\x82\xac", b"OPEN")) == "[OPEN] café -> /tmp/€"
+
+
+def test_host_only_generator_matches_the_library():
+    """tools/libchronos_tracegen_host.so (g++ build of csrc/tracegen.cuh) == chronos_tracegen_host."""
+    from chronos_b200 import tracegen
+
+    for name in ("attack_replay_10k", "skewed_zipf_chains", "sharded_100m_1m"):
+        spec = tracegen.WORKLOADS[name]
+        a = tracegen.generate_host(spec, first=12_345, n=3_000)
+        b = tracegen.generate_host_nocuda(spec, first=12_345, n=3_000)
+        assert np.array_equal(a, b), name
