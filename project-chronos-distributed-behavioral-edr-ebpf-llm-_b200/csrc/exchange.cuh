@@ -128,7 +128,13 @@ struct XchgPackParams {
 };
 
 constexpr uint32_t XCHG_SUB = XCHG_TILE / XCHG_WARPS;   // contiguous sub-range of a warp
-constexpr uint32_t XCHG_STAGE_PER_WARP = 32 * 18 + 32;   // uint4: slots of one step + its descriptors
+// Staging of one warp step: a WINDOW of XCHG_STAGE_SLOTS transport slots (a step of 32 survivors
+// holds 96..576, about 180 on the bench workloads) + its 32 descriptors. A full-size buffer
+// (576 slots) made the kernel shared-memory bound at 2 CTAs per SM, 24 % of the warp slots:
+// the kernel is a chain of dependent loads, it needs the warps. Steps with more slots than the
+// window take several rounds through it.
+constexpr uint32_t XCHG_STAGE_SLOTS = 224;
+constexpr uint32_t XCHG_STAGE_PER_WARP = XCHG_STAGE_SLOTS + 32;
 constexpr size_t XCHG_PACK_SMEM = (size_t)XCHG_WARPS * XCHG_STAGE_PER_WARP * 16;
 constexpr uint32_t NONE_AT = 0xffffffffu;
 constexpr int XCHG_STEPS = XCHG_SUB / 32;               // 32 survivors per step
@@ -264,13 +270,13 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
                 if (lane >= d) { end_s += t1; end_e += t2; }
             }
             const uint32_t total = __shfl_sync(0xffffffffu, end_s, 31), n_live = __shfl_sync(0xffffffffu, end_e, 31);
-            uint4 *stg = stage + (size_t)warp * XCHG_STAGE_PER_WARP;  // [0, 576) slots, [576, 608) descriptors
+            uint4 *stg = stage + (size_t)warp * XCHG_STAGE_PER_WARP;  // [0, STAGE_SLOTS) slots, then 32 descriptors
             const uint32_t my_soff = lower_s + pre_s;                 // first staged slot of this lane's entry
             const uint4 *src = nullptr;
             if (live) {
                 const uint64_t hdr = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)metav[q] << 48) | ((uint64_t)ns << 56);
                 src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
-                if (g.direct) stg[576 + lower_e + rank_e] = make_uint4((uint32_t)hdr, (uint32_t)(hdr >> 32), bs + pre_s, 0u);
+                if (g.direct) stg[XCHG_STAGE_SLOTS + lower_e + rank_e] = make_uint4((uint32_t)hdr, (uint32_t)(hdr >> 32), bs + pre_s, 0u);
                 else g.send_hdr[be + rank_e] = hdr;
             }
             // the slots of the 32 entries, read cooperatively in lane order (4 x 32 loads in flight)
@@ -282,52 +288,59 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
                 if (lane >= d) incl += t;
             }
             const uint32_t excl = incl - cnt;
-            for (uint32_t b0 = 0; b0 < total; b0 += 128) {
-                uint4 v[4];
-                uint32_t at[4];
+            for (uint32_t w0 = 0; w0 < total; w0 += XCHG_STAGE_SLOTS) {  // staged slots [w0, w1) this round
+                const uint32_t w1 = min(total, w0 + XCHG_STAGE_SLOTS);
+                for (uint32_t b0 = 0; b0 < total; b0 += 128) {
+                    uint4 v[4];
+                    uint32_t at[4];
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const uint32_t k = b0 + u * 32 + lane;
-                    int sidx = 0;  // lane that owns slot k (shuffle binary search, as in filter.cuh phase B2)
+                    for (int u = 0; u < 4; u++) {
+                        const uint32_t k = b0 + u * 32 + lane;
+                        int sidx = 0;  // lane that owns slot k (shuffle binary search, as in filter.cuh phase B2)
 #pragma unroll
-                    for (int step = 16; step >= 1; step >>= 1) {
-                        const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
-                        if (vv <= k) sidx += step;
+                        for (int step = 16; step >= 1; step >>= 1) {
+                            const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
+                            if (vv <= k) sidx += step;
+                        }
+                        sidx &= 31;
+                        const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
+                        const uint32_t so = __shfl_sync(0xffffffffu, my_soff, sidx);
+                        const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
+                        at[u] = NONE_AT;
+                        v[u] = make_uint4(0u, 0u, 0u, 0u);
+                        if (k < total) {
+                            const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
+                            const uint32_t pos = so + sl;  // where it stands in the owner-major order
+                            if (pos >= w0 && pos < w1) {
+                                const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
+                                v[u] = __ldg(reinterpret_cast<const uint4 *>((uintptr_t)sp) + ch);
+                                at[u] = pos - w0;
+                            }
+                        }
                     }
-                    sidx &= 31;
-                    const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
-                    const uint32_t so = __shfl_sync(0xffffffffu, my_soff, sidx);
-                    const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
-                    at[u] = NONE_AT;
-                    v[u] = make_uint4(0u, 0u, 0u, 0u);
-                    if (k < total) {
-                        const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
-                        const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
-                        v[u] = __ldg(reinterpret_cast<const uint4 *>((uintptr_t)sp) + ch);
-                        at[u] = so + sl;
+#pragma unroll
+                    for (int u = 0; u < 4; u++)
+                        if (at[u] != NONE_AT) stg[at[u]] = v[u];
+                }
+                __syncwarp();
+                // every owner's run leaves with consecutive lanes on consecutive 16-byte slots
+                for (uint32_t j0 = w0; j0 < w1; j0 += 128) {
+#pragma unroll
+                    for (int u = 0; u < 4; u++) {
+                        const uint32_t j = j0 + u * 32 + lane;
+                        int w = 0;  // owner whose run holds staged slot j: first lane with end_s > j
+#pragma unroll
+                        for (int step = 16; step >= 1; step >>= 1) {
+                            const uint32_t vv = __shfl_sync(0xffffffffu, end_s, w + step - 1);
+                            if (vv <= j) w += step;
+                        }
+                        w &= 31;
+                        const uint32_t st = __shfl_sync(0xffffffffu, end_s - tot_s, w);
+                        const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)run_dst, w);
+                        if (j < w1) reinterpret_cast<uint4 *>((uintptr_t)dp)[j - st] = stg[j - w0];
                     }
                 }
-#pragma unroll
-                for (int u = 0; u < 4; u++)
-                    if (at[u] != NONE_AT) stg[at[u]] = v[u];
-            }
-            __syncwarp();
-            // every owner's run leaves with consecutive lanes on consecutive 16-byte slots
-            for (uint32_t j0 = 0; j0 < total; j0 += 128) {
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const uint32_t j = j0 + u * 32 + lane;
-                    int w = 0;  // owner whose run holds staged slot j: first lane with end_s > j
-#pragma unroll
-                    for (int step = 16; step >= 1; step >>= 1) {
-                        const uint32_t vv = __shfl_sync(0xffffffffu, end_s, w + step - 1);
-                        if (vv <= j) w += step;
-                    }
-                    w &= 31;
-                    const uint32_t st = __shfl_sync(0xffffffffu, end_s - tot_s, w);
-                    const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)run_dst, w);
-                    if (j < total) reinterpret_cast<uint4 *>((uintptr_t)dp)[j - st] = stg[j];
-                }
+                __syncwarp();  // the window is refilled by the next round
             }
             if (g.direct) {  // descriptors: at most 32 per step, same owner-major order
                 int w = 0;
@@ -339,7 +352,7 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
                 w &= 31;
                 const uint32_t st = __shfl_sync(0xffffffffu, end_e - tot_e, w);
                 const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)desc_dst, w);
-                if ((uint32_t)lane < n_live) reinterpret_cast<uint4 *>((uintptr_t)dp)[lane - st] = stg[576 + lane];
+                if ((uint32_t)lane < n_live) reinterpret_cast<uint4 *>((uintptr_t)dp)[lane - st] = stg[XCHG_STAGE_SLOTS + lane];
             }
             __syncwarp();  // the staging buffer is reused by the next step
         }

@@ -15,16 +15,20 @@ import torch.distributed as dist  # noqa: E402
 
 from chronos_b200 import sharded, tracegen  # noqa: E402
 
-STEPS = [(0, 250_000), (250_000, 400_000)]
+# (workload, steps): the skewed 4 K-PID trace of configs[3], then the 1 M-PID trace the 8-GPU
+# bench runs (configs[2]) at 2.2 M events, one large step and one that continues the state
+CASES = [("skewed_zipf_chains", [(0, 250_000), (250_000, 400_000)]),
+         ("sharded_100m_1m", [(0, 1_600_000), (1_600_000, 2_200_000)])]
 
 
-def run_rank(rank, world, lr, rows):
-    """Both steps on this rank; returns per step (windows, survivors, n_pending) and the mode."""
-    dev = tracegen.DeviceBuffer(lr, 250_000 * 288)
-    runner = sharded.ShardedRunner(dev.ptr, 0, 0, lr, rank, world, cap=200_000, mode="direct",
-                                   cap_entries_per_peer=100_000)
+def run_rank(rank, world, lr, rows, steps):
+    """All steps on this rank; returns per step (windows, survivors, n_pending) and the runner."""
+    biggest = max(hi - lo for lo, hi in steps)
+    dev = tracegen.DeviceBuffer(lr, biggest * 288)
+    runner = sharded.ShardedRunner(dev.ptr, 0, 0, lr, rank, world, cap=biggest, mode="direct",
+                                   cap_entries_per_peer=max(biggest // world, 100_000))
     out = []
-    for lo, hi in STEPS:
+    for lo, hi in steps:
         n = hi - lo
         a, b = lo + rank * n // world, lo + (rank + 1) * n // world
         mine = np.ascontiguousarray(rows[a:b])
@@ -42,13 +46,13 @@ def run_rank(rank, world, lr, rows):
     return out, runner
 
 
-def check(rows, per_step):
+def check(rows, per_step, steps):
     from helpers import canonical
     from oracle import coracle
 
     eng = coracle.COracle()
     ok = True
-    for (lo, hi), gathered in zip(STEPS, per_step):
+    for (lo, hi), gathered in zip(steps, per_step):
         ref = eng.feed(rows[lo:hi], lo)
         merged = sorted((w for g in gathered for w in g[0]), key=lambda t: t[0])
         surv = np.sort(np.concatenate([np.asarray(g[1], dtype=np.int64) for g in gathered]))
@@ -66,22 +70,24 @@ def main():
     rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(lr)
     dist.init_process_group("cpu:gloo,cuda:nccl", device_id=torch.device("cuda", lr))
-    rows = tracegen.generate_host(dict(tracegen.WORKLOADS["skewed_zipf_chains"]), n=400_000)
-    mine, runner = run_rank(rank, world, lr, rows)
-    per_step = []
-    for s in range(len(STEPS)):
-        gathered = [None] * world if rank == 0 else None
-        dist.gather_object(mine[s], gathered, dst=0)
-        per_step.append(gathered)
-    ok = True
-    if rank == 0:
-        ok = check(rows, per_step)
-        print("MP_EXCHANGE", "OK" if ok else "MISMATCH", "mode", runner.mode, "windows",
-              sum(len(g[0]) for g in per_step[-1]), flush=True)
-    dist.barrier()
-    runner.ctx.close()
+    all_ok = True
+    for name, steps in CASES:
+        rows = tracegen.generate_host(dict(tracegen.WORKLOADS[name]), n=steps[-1][1])
+        mine, runner = run_rank(rank, world, lr, rows, steps)
+        per_step = []
+        for s in range(len(steps)):
+            gathered = [None] * world if rank == 0 else None
+            dist.gather_object(mine[s], gathered, dst=0)
+            per_step.append(gathered)
+        if rank == 0:
+            ok = check(rows, per_step, steps)
+            all_ok &= ok
+            print("MP_EXCHANGE", "OK" if ok else "MISMATCH", "mode", runner.mode, "workload", name, "events", steps[-1][1],
+                  "windows", sum(len(g[0]) for g in per_step[-1]), flush=True)
+        dist.barrier()
+        runner.ctx.close()
     dist.destroy_process_group()
-    sys.exit(0 if ok else 1)
+    sys.exit(0 if all_ok else 1)
 
 
 if __name__ == "__main__":

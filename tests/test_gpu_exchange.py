@@ -60,12 +60,15 @@ def _merge(results):
     return merged
 
 
-@pytest.mark.parametrize("world,n_rows", [(1, 120_000), (2, 120_000), (3, 120_000), (8, 120_000), (2, 1_200_000)])
-def test_direct_exchange_matches_oracle_over_two_steps(world, n_rows):
+@pytest.mark.parametrize("world,n_rows,name", [(1, 120_000, "skewed_zipf_chains"), (2, 120_000, "skewed_zipf_chains"),
+                                               (3, 120_000, "skewed_zipf_chains"), (8, 120_000, "skewed_zipf_chains"),
+                                               (2, 1_200_000, "skewed_zipf_chains"),
+                                               (4, 1_400_000, "sharded_100m_1m")])   # the 8-GPU bench's 1 M-PID trace
+def test_direct_exchange_matches_oracle_over_two_steps(world, n_rows, name):
     import chronos_b200
     from chronos_b200 import tracegen
 
-    spec = dict(tracegen.WORKLOADS["skewed_zipf_chains"])
+    spec = dict(tracegen.WORKLOADS[name])
     rows = tracegen.generate_host(spec, n=n_rows)
     half = len(rows) // 2
     eng = coracle.COracle()

@@ -243,3 +243,32 @@ def test_create_rejects_sizes_the_entry_ids_cannot_address():
 
     with pytest.raises(_ffi.ChronosError):
         chronos_b200.Context(device=0, max_batch_events=1 << 27)
+
+
+def test_window_digests_see_content_and_ignore_bytes_behind_the_nul():
+    """chronos_window_digests (what bench.py --gpus N compares a sharded run with): equal for
+    records that differ only behind a field's NUL -- the reference never reads those bytes
+    (chronos_sensor.py:125-130) -- and different as soon as anything it does read differs."""
+    import chronos_b200
+
+    def batch(tail, path=b"/tmp/cat"):
+        a = bytearray(R(7, b"sh", b"/tmp/a", b"OPEN") + R(9, b"zsh", b"/tmp/b", b"OPEN") + R(7, b"sh", path, b"OPEN") +
+                      R(9, b"zsh", b"curl", b"EXEC"))
+        for r in range(4):
+            a[r * REC + 4 + 8:r * REC + 4 + 12] = tail      # comm bytes 8..11, behind the NUL
+            a[r * REC + 20 + 200:r * REC + 20 + 204] = tail  # argv bytes 200..203, behind the NUL
+            a[r * REC + 286:r * REC + 288] = tail[:2]        # tail padding
+        return bytes(a)
+
+    digs = []
+    zero = bytes(4)
+    for recs in (batch(zero), batch(b"junk"), batch(b"junk", path=b"/tmp/cab"), batch(zero, path=b"/tmp/catx")):
+        with chronos_b200.Context(device=0, max_batch_events=16) as ctx:
+            ctx.submit(recs, 0)
+            res = ctx.fetch(records=True)
+            digs.append((res.counts["n_windows"], ctx.window_digests(res.counts["n_windows"])))
+    assert digs[0][0] == 2 and digs[1][0] == 2
+    np.testing.assert_array_equal(digs[0][1], digs[1][1])          # garbage behind the NUL does not count
+    assert digs[2][0] == 1                                        # "/tmp/cab" no longer triggers: one window less
+    assert digs[3][0] == 2 and digs[3][1][0] != digs[0][1][0]     # one more byte in a path: another digest
+    assert digs[3][1][1] == digs[0][1][1]                         # ... while the untouched window keeps its digest

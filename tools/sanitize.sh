@@ -10,8 +10,8 @@ tests/test_gpu_parity.py::test_golden_vectors_from_the_unmodified_reference \
 tests/test_gpu_parity.py::test_random_adversarial_records tests/test_gpu_parity.py::test_streaming_state_carries_over \
 tests/test_gpu_parity.py::test_workload_parity[attack_replay_10k-10000] \
 tests/test_gpu_parity.py::test_one_pid_across_many_tiles_and_extreme_pids \
-tests/test_gpu_exchange.py::test_direct_exchange_matches_oracle_over_two_steps[2-120000] \
-tests/test_gpu_exchange.py::test_direct_exchange_matches_oracle_over_two_steps[3-120000] \
+tests/test_gpu_exchange.py::test_direct_exchange_matches_oracle_over_two_steps[2-120000-skewed_zipf_chains] \
+tests/test_gpu_exchange.py::test_direct_exchange_matches_oracle_over_two_steps[3-120000-skewed_zipf_chains] \
 tests/test_gpu_exchange.py::test_empty_slices_and_empty_steps \
 tests/test_gpu_checkpoint.py tests/test_zz_no_alloc.py"
 for t in $tools; do
