@@ -489,11 +489,10 @@ def run_gpu_arm(args, rank, world, local_rank):
     stage_ms = []
     e0.record(ext)
     t_wall0 = time.perf_counter()
-    for _ in range(args.steps):
-        last = runner.step()
+    for last in runner.timed_steps(args.steps):
         filt_ms.append(last["filter_ms"])
         step_ms.append(last["gpu_ms"])
-        stage_ms.append(runner.ctx.last_stage_times())
+        stage_ms.append(last["stages"])
         launches += last["launches"]
     e1.record(ext)
     e1.synchronize()
@@ -564,6 +563,8 @@ def run_gpu_arm(args, rank, world, local_rank):
                        "single_gpu_same_slice_ms": same_slice,
                        "l2": "input per step (2.88 GB+) exceeds the 126 MB L2; no flush needed",
                        "timing": "torch CUDA events on the library stream around all K steps, max over ranks",
+                       "steps_on_gpu": ("one batch at a time (a batch starts when the previous one has ended); the host "
+                                        "enqueues one step ahead" if world == 1 else "one batch at a time, enqueued after the previous fetch"),
                        "warmup_extra_steps": extra,
                        "exchange": (None if world == 1 else
                                     ("direct: stage 1 writes survivors into the owners' HBM over NVLink (CUDA IPC windows), "
@@ -644,6 +645,26 @@ class SingleGpuRunner:
         t, f = self.ctx.last_timing()
         c.update(gpu_ms=t, filter_ms=f, launches=self.ctx.last_launches())
         return c
+
+    def timed_steps(self, steps):
+        """K steps for the timed region. Every step is the same one-shot batch on a fresh
+        process_memory (chronos_reset), and the GPU runs the batches strictly one after the other
+        (chronos_set_overlap(0): a batch starts when the previous one has ended); only the HOST
+        works ahead -- step k+1 is enqueued before step k is fetched, so the GPU does not sit idle
+        while Python and the driver prepare the next launch sequence."""
+        ctx = self.ctx
+        ctx.set_overlap(False)
+        ctx.reset()
+        ctx.submit_ptr(self.dev.ptr, self.n, 0)
+        for k in range(steps):
+            if k + 1 < steps:
+                ctx.reset()
+                ctx.submit_ptr(self.dev.ptr, self.n, 0)
+            c = ctx.fetch_counts()
+            t, f = ctx.last_timing()
+            c.update(gpu_ms=t, filter_ms=f, launches=ctx.last_launches(), stages=ctx.last_stage_times())
+            yield c
+        ctx.set_overlap(True)
 
     def e2e(self, steps, barrier, dist):
         """The same step through the public host API: the batch starts in pinned HOST memory

@@ -97,8 +97,14 @@ int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pen
 int chronos_destroy(chronos_ctx *ctx);
 
 /* Replaces: restarting the sensor, i.e. a fresh `process_memory` (chronos_sensor.py:105).
- * Drops all per-PID state and any unfetched results; buffers stay allocated. */
+ * Takes effect in submit order and waits for nothing: batches submitted before the call finish
+ * against the old state and stay fetchable, batches submitted after it start from an empty
+ * process_memory. Buffers stay allocated. */
 int chronos_reset(chronos_ctx *ctx);
+/* on = 0: a batch starts on the GPU only when the previous batch has ended, even when it was
+ * submitted earlier (the host still enqueues ahead); on = 1 (default): its filter stage may run
+ * beside the previous batch's window stage. No reference counterpart. */
+int chronos_set_overlap(chronos_ctx *ctx, int on);
 
 /* Human-readable text for the last non-OK status on this context (or a static string
  * for ctx == NULL).  No reference counterpart. */

@@ -57,6 +57,7 @@ SIGNATURES = {
     "chronos_create_sized": (c_int, [c_int, c_uint64, c_uint64, POINTER(c_void_p)]),
     "chronos_destroy": (c_int, [c_void_p]),
     "chronos_reset": (c_int, [c_void_p]),
+    "chronos_set_overlap": (c_int, [c_void_p, c_int]),
     "chronos_last_error": (c_char_p, [c_void_p]),
     "chronos_submit": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64]),
     "chronos_fetch": (c_int, [c_void_p, POINTER(Counts)]),

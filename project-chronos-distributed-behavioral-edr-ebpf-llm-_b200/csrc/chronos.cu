@@ -110,6 +110,7 @@ struct BatchSet {
     const uint4 *slots = nullptr;      // transport-form batch (chronos_submit_survivors / exchange)
     bool explicit_arrival = false, exchanged = false, filter_timed = false, pipelined = false;
     uint32_t x_epoch = 0;  // exchange step this batch consumed
+    uint64_t gen = 0;      // state generation (chronos_reset starts a new one) the batch belongs to
     float t_total = 0.f, t_filter = 0.f, t_filter_kernel = 0.f;
     int rc = CHRONOS_OK;  // outcome found when the batch completed
 };
@@ -131,6 +132,8 @@ struct chronos_ctx {
     int last = 0;       // set of the most recently submitted batch (or of the loaded / reset state)
     int fetched = -1;   // set whose results the copy calls return
     uint64_t seq = 0;
+    uint64_t gen = 0;  // bumped by chronos_reset: batches of an older generation no longer describe the state
+    bool overlap = true;  // stage 1 of a batch may run beside the previous batch's tail
     uint64_t n_pending = 0, n_pids_seen = 0;  // exact once every submitted batch has completed
 
     // shared by all batches
@@ -449,6 +452,12 @@ int configure_kernels(chronos_ctx *c) {
     CK(cudaFuncSetAttribute(filter_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)filter_smem_bytes<2>()));
     CK(cudaFuncSetAttribute(xchg_pack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XCHG_PACK_SMEM));
     CK(cudaFuncSetAttribute(gather_records, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GATHER_SMEM));
+    if (!getenv("CHRONOS_NO_CARVEOUT")) {
+        // The filter's residency (19 single-warp CTAs per SM) is bounded by shared memory: ask for
+        // the largest shared-memory carve-out instead of leaving the split to the driver's guess.
+        CK(cudaFuncSetAttribute(filter_kernel<1>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+        CK(cudaFuncSetAttribute(filter_kernel<2>, cudaFuncAttributePreferredSharedMemoryCarveout, (int)cudaSharedmemCarveoutMaxShared));
+    }
     if (c->device < 64) g_attr_done[c->device] = true;
     return CHRONOS_OK;
 }
@@ -734,6 +743,8 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     sp.in.carry = ptr<Carry>(c->carry);
     sp.in.m_max = (uint32_t)std::min<uint64_t>(Mmax, std::min(c->cap_M, b.cap_M));
     sp.in.win_tile = WIN_TILE;
+    sp.in.s_max = (uint32_t)std::min<uint64_t>(b.n, b.cap_n);
+    sp.in.w_max = (uint32_t)(std::min(std::min(c->cap_n, b.cap_n), std::min(c->cap_M, b.cap_M) / 2) + 1);
     sp.keyA = ptr<uint32_t>(c->keyA);
     sp.keyB = ptr<uint32_t>(c->keyB);
     sp.valA = ptr<uint32_t>(c->valA);
@@ -891,11 +902,13 @@ int complete_batch(chronos_ctx *c, BatchSet &b) {
     b.pending_after = any && b.M ? b.h_scalars->n_pending : 0;
     b.pids_after = b.h_scalars->n_pids_seen;
     const bool newest = b.seq == c->seq;
+    BatchSet &y = c->set[(&b == &c->set[0]) ? 1 : 0];
     if (newest) {
-        c->n_pending = b.pending_after;
-        c->n_pids_seen = b.pids_after;
-    } else {  // a younger batch is in flight: what it carries in is now known exactly
-        BatchSet &y = c->set[(&b == &c->set[0]) ? 1 : 0];
+        if (b.gen == c->gen) {  // (else the state was reset after this batch was submitted)
+            c->n_pending = b.pending_after;
+            c->n_pids_seen = b.pids_after;
+        }
+    } else if (y.gen == b.gen) {  // a younger batch of the same state is in flight: what it carries in is now exact
         y.P_ub = std::min(y.P_ub, b.pending_after);
         y.pids_ub = std::min(y.pids_ub, b.pids_after);
     }
@@ -959,7 +972,7 @@ int complete_batch(chronos_ctx *c, BatchSet &b) {
 // Upper bounds of what the next batch carries in, from the host's point of view.
 void carried_bounds(chronos_ctx *c, uint64_t &P_ub, uint64_t &pids_ub) {
     BatchSet &l = c->set[c->last];
-    if (l.state == BatchSet::SUBMITTED) {
+    if (l.state == BatchSet::SUBMITTED && l.gen == c->gen) {
         P_ub = l.P_ub + l.n;
         pids_ub = l.pids_ub + l.n;
     } else {
@@ -1023,12 +1036,14 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base, bool transport, Batch
     b.slots = nullptr;
     b.explicit_arrival = b.exchanged = b.filter_timed = false;
     b.pipelined = pipelined;
+    b.gen = c->gen;
     b.rc = CHRONOS_OK;
     c->launches = 0;
     c->scan_slot = 0;
     if (pipelined && !c->stream_f) CK(cudaStreamCreateWithPriority(&c->stream_f, cudaStreamNonBlocking, c->prio_lo));
     cudaStream_t s1 = pipelined ? c->stream_f : c->stream;
-    if (pipelined) CK(cudaStreamWaitEvent(s1, prev.ev_stage1, 0));  // the stage-1 temporaries are shared
+    // the stage-1 temporaries are shared; without overlap the batch starts when the previous one has ended
+    if (pipelined) CK(cudaStreamWaitEvent(s1, c->overlap ? prev.ev_stage1 : prev.ev_end, 0));
     CK(cudaStreamWaitEvent(s1, b.ev_packed, 0));                    // a download may still read this set
     CK(cudaEventRecord(b.ev_start, s1));
     if (!c->x_sent && !pipelined) {  // (stage 2 of an exchange step keeps the marks of its stage 1)
@@ -1717,8 +1732,11 @@ int chronos_checkpoint_load(chronos_ctx *c, const void *src, uint64_t bytes) {
         if (ti == K || (uint32_t)tab[ti] != ppid[i])
             return fail(c, CHRONOS_E_ARG, "checkpoint: pending pid %u is not among the PID entries", ppid[i]);
     }
-    int rc = chronos_reset(c);
-    if (rc) return rc;
+    int rc;
+    for (BatchSet &f : c->set)  // nothing may be in flight while the state is replaced
+        if (f.state == BatchSet::SUBMITTED && (rc = complete_batch(c, f))) return rc;
+    if ((rc = chronos_reset(c))) return rc;
+    CK(cudaDeviceSynchronize());
     BatchSet &b = c->set[c->last];
     if (P + c->max_batch > c->cap_M || P > b.cap_M) {  // state larger than the pending budget: grow once
         const uint64_t want = std::min<uint64_t>(MAX_GROUPED, P + c->max_batch);
@@ -1789,12 +1807,19 @@ int chronos_last_stage_times(chronos_ctx *c, float *ms, uint32_t cap) {
     return CHRONOS_OK;
 }
 
+int chronos_set_overlap(chronos_ctx *c, int on) {
+    if (!c) return CHRONOS_E_ARG;
+    c->overlap = on != 0;
+    return CHRONOS_OK;
+}
+
 int chronos_reset(chronos_ctx *c) {
     if (!c) return CHRONOS_E_ARG;
     CK(cudaSetDevice(c->device));
-    CK(cudaDeviceSynchronize());
-    for (BatchSet &b : c->set) b.state = BatchSet::FREE;
-    c->fetched = -1;
+    // Takes effect in submit order and waits for nothing: the resets below are queued on the main
+    // stream behind the window stage of every batch submitted so far. Those batches finish against
+    // the old state and stay fetchable; batches submitted from now on start from an empty one.
+    c->gen++;
     c->n_pending = 0;
     c->n_pids_seen = 0;
     c->x_sent = false;

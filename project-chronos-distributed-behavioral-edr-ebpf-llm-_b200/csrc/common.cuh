@@ -8,6 +8,18 @@
 #define CH_REC_WORDS 72
 #define CH_REC_CHUNKS 18  // 16-byte chunks per record
 
+// Bounds checks of every index a kernel computes before it writes through it. They cost
+// registers and branches, so they are compiled in only by tools/checked_build.sh
+// (-DCHRONOS_CHECKED: the -m gpu suite is then run against that library; a violated check traps
+// the kernel and the next API call reports cudaErrorAssert). compute-sanitizer is not available
+// on this pool (profiles/r02_sanitizer_unavailable.txt); this is what stands in for memcheck.
+#ifdef CHRONOS_CHECKED
+#include <assert.h>
+#define CH_ASSERT(x) assert(x)
+#else
+#define CH_ASSERT(x) ((void)0)
+#endif
+
 namespace chronos {
 
 // ---------------------------------------------------------------------------------
@@ -108,6 +120,7 @@ struct Plan {
     uint32_t tiles_m, tiles_s;               // window tiling of M and of S
     uint32_t overflow;         // set when M exceeds what the buffers were sized for
     uint32_t key_or, key_and;  // over every pid seen since the last reset
+    uint32_t cap_m, cap_s, cap_w;  // what the buffers of this batch hold: grouped entries, survivors, windows
     const uint32_t *skey;      // where the sorted (pid, value) arrays ended up
     const uint32_t *sval;
 };

@@ -320,7 +320,10 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
                     }
 #pragma unroll
                     for (int u = 0; u < 4; u++)
-                        if (at[u] != NONE_AT) stg[at[u]] = v[u];
+                        if (at[u] != NONE_AT) {
+                        CH_ASSERT(at[u] < XCHG_STAGE_SLOTS);
+                        stg[at[u]] = v[u];
+                    }
                 }
                 __syncwarp();
                 // every owner's run leaves with consecutive lanes on consecutive 16-byte slots
@@ -337,6 +340,7 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
                         w &= 31;
                         const uint32_t st = __shfl_sync(0xffffffffu, end_s - tot_s, w);
                         const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)run_dst, w);
+                        CH_ASSERT(j >= w1 || (j >= st && j - w0 < XCHG_STAGE_SLOTS));
                         if (j < w1) reinterpret_cast<uint4 *>((uintptr_t)dp)[j - st] = stg[j - w0];
                     }
                 }
@@ -451,6 +455,7 @@ __global__ void __launch_bounds__(256) xchg_unpack(const XchgUnpackParams g) {
 #pragma unroll
         for (int k = 1; k < XCHG_MAX_WORLD; k++)
             if (k < (int)W && j >= es[k]) s = k;
+        CH_ASSERT(j - es[s] < g.L.cap_e);
         const size_t r = (size_t)s * g.L.cap_e + (j - es[s]);
         const uint4 dsc = desc[r];
         const uint64_t h = (uint64_t)dsc.x | ((uint64_t)dsc.y << 32);

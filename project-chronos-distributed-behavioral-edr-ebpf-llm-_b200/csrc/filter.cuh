@@ -669,6 +669,7 @@ __global__ void __launch_bounds__(CS_THREADS) compact_scan(const CompactScanPara
                 const uint32_t j = j0 + u * CS_THREADS;
                 if (j < total) {
                     const uint32_t dst = base + j;
+                    CH_ASSERT(dst < p.n_tiles * p.tile);
                     if (p.out_key) p.out_key[dst] = k[u];
                     p.out_pid[dst] = k[u];
                     p.out_src[dst] = sr[u];

@@ -32,6 +32,7 @@ struct SortInputs {
     const uint32_t *surv_count, *key_or, *key_and;  // scalars of the batch in flight
     Carry *carry;                                   // pending count and pid bit range carried in
     uint32_t m_max, win_tile;
+    uint32_t s_max, w_max;  // capacities of the survivor / window arrays (checked builds assert against them)
 };
 
 struct SortParams {
@@ -71,6 +72,9 @@ __device__ __forceinline__ uint32_t synth_value(const SortParams &p, uint32_t P,
 __device__ __forceinline__ void make_plan(const SortParams &p, Plan &pl) {
     const uint32_t S = *p.in.surv_count, P = p.in.carry->P;
     uint32_t M = P + S;
+    pl.cap_m = p.in.m_max;
+    pl.cap_s = p.in.s_max;
+    pl.cap_w = p.in.w_max;
     pl.overflow = M > p.in.m_max ? 1u : 0u;
     if (M > p.in.m_max) M = p.in.m_max;  // never run past the buffers; the host reports the overflow
     pl.S = M > P ? M - P : 0u;
@@ -246,6 +250,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
             __syncwarp();
             if (valid) {
                 const uint32_t dst = base + before;
+                CH_ASSERT(dst < n);
                 keys_out[dst] = key;
                 vals_out[dst] = first ? synth_value(p, split, i) : vals_in[i];
             }

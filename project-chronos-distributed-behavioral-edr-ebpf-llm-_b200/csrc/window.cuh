@@ -226,6 +226,7 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
                 fl = true;
                 wi = st.w.a++;
                 st.w.s = 0;
+                CH_ASSERT(wi < p.plan->cap_w);
                 p.wsorted[wi] = WinSorted{key[k], e, st.w.b, pos - st.w.b + 1};
             }
             // ---- chain DFA
@@ -240,6 +241,7 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
                 if (st.c.s == 2u) { if (meta & META_EXEC) { m = true; st.c.s = 0; st.c.a++; } }
                 else if (st.c.s == 1u) { if (meta & META_CHMOD) st.c.s = 2; }
                 else if (meta & META_CURL) st.c.s = 1;
+                CH_ASSERT(e >= P && e - P < p.plan->cap_s);
                 p.entry_out[e - P] = wi | (m ? EO_MATCH : 0u);
             }
             pf[k] = (fl ? PF_FLUSH : 0u) | (m ? PF_MATCH : 0u) | (st.c.a << 2);
@@ -337,6 +339,7 @@ __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p)
             const uint32_t pos = M - 1 - q;
             if (kd[k] & 1u) st.s = (kd[k] & 2u) ? 0u : 1u;
             if (st.s == 1u) {
+                CH_ASSERT(st.a < p.pend_cap && pos < M);
                 const uint32_t slot = p.pend_cap - 1u - st.a;
                 st.a++;
                 const uint32_t v = sval[pos];
@@ -448,6 +451,7 @@ __global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) {
                     o.pid = d[u].pid;
                     o.flags = hi[u] != lo[u] ? 1u : 0u;  // a chain-complete event lies inside the window
                     o.reserved = 0;
+                    CH_ASSERT(rw < p.plan->cap_w && d[u].start + d[u].len <= M);
                     p.windows[rw++] = o;
                 }
             }
@@ -456,6 +460,7 @@ __global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) {
         for (int k = 0; k < WIN_ITEMS; k++) {
             if (eo[k] & EO_MATCH) {
                 const uint32_t j = j0 + k;
+                CH_ASSERT(rc < p.plan->cap_s);
                 p.chain_pid[rc] = p.surv_pid[j];
                 p.chain_idx[rc] = p.surv_arrival ? p.surv_arrival[j] : p.base_arrival + p.surv_src[j];
                 rc++;
@@ -524,6 +529,7 @@ __global__ void __launch_bounds__(GATHER_THREADS) gather_records(const GatherPar
         uint32_t ns = 0;               // 0: plain 288-byte record at src; else transport form of ns slots
         if ((uint32_t)lane < cnt) {
             const uint32_t e = gsval[base + lane] & VAL_ID_MASK;
+            CH_ASSERT(e < gM && gM <= g.plan->cap_m);
             if (e < gP) src = g.prev_arena + (size_t)g.pend_slot[g.pend_cap_prev - gP + e] * CH_REC_BYTES;
             else if (g.slots) {
                 src = reinterpret_cast<const uint8_t *>(g.slots + g.slot_off[e - gP]);

@@ -86,8 +86,13 @@ class Context:
         self.close()
 
     def reset(self):
-        """Forget all per-PID state (a fresh process_memory, chronos_sensor.py:105)."""
+        """Forget all per-PID state (a fresh process_memory, chronos_sensor.py:105). Takes effect in
+        submit order: batches already submitted finish against the old state and stay fetchable."""
         self._check(self._L.chronos_reset(self._h))
+
+    def set_overlap(self, on):
+        """False: batches run strictly one after the other on the GPU even when submitted ahead."""
+        self._check(self._L.chronos_set_overlap(self._h, 1 if on else 0))
 
     # ---- submit ------------------------------------------------------------------------
     def submit(self, records, base_arrival_index=0):

@@ -172,6 +172,13 @@ class ShardedRunner:
                  n_received=n_recv, slots_sent=int(sc.sum()))
         return c
 
+    def timed_steps(self, steps):
+        """K steps for bench.py's timed region (each one enqueued after the previous fetch)."""
+        for _ in range(steps):
+            c = self.step()
+            c["stages"] = self.ctx.last_stage_times()
+            yield c
+
     def e2e(self, steps, barrier, dist_mod):
         """Same step, but the slice starts in pinned HOST memory (H2D inside the timed region)
         and survivors, windows and window records are read back to pinned host memory; the

@@ -44,6 +44,16 @@ def _noalloc(L, dev, rows):
     return cnt, idx, pid, meta
 
 
+def _oracle(rows):
+    """What the CPU oracle says survives, with pid and class bits (the checker of every other test)."""
+    from oracle import coracle
+
+    keep, meta = coracle.classify(rows)
+    idx = np.nonzero(keep)[0].astype(np.uint32)
+    pid = rows[idx.astype(np.int64), :4].copy().view("<u4").reshape(-1) if len(idx) else np.zeros(0, np.uint32)
+    return idx, pid, meta[keep == 1] & 0x0F
+
+
 def _existing(rows):
     import chronos_b200
 
@@ -66,6 +76,10 @@ def test_noalloc_matches_existing_entry_point_twice_in_a_row():
         np.testing.assert_array_equal(idx, exp_idx)
         np.testing.assert_array_equal(meta, exp_meta)
         np.testing.assert_array_equal(pid, rows[exp_idx.astype(np.int64), :4].copy().view("<u4").reshape(-1))
+        o_idx, o_pid, o_meta = _oracle(rows)   # ... and both agree with the oracle
+        np.testing.assert_array_equal(idx, o_idx)
+        np.testing.assert_array_equal(pid, o_pid)
+        np.testing.assert_array_equal(meta & 0x0F, o_meta)
     # an empty batch is legal and reports zero survivors
     cnt, idx, _, _ = _noalloc(L, 0, a[:0])
     assert cnt == 0 and idx.size == 0
@@ -81,3 +95,61 @@ def test_noalloc_rejects_oversized_batches():
                                   c_void_p(16), err, 256)
     assert rc == _ffi.E_CAPACITY
     assert b"exceed" in err.value and str(_ffi.NOALLOC_MAX_EVENTS).encode() in err.value
+
+
+@pytest.mark.parametrize("n", [1, 31, 33, 262_144])
+def test_noalloc_edge_sizes_against_the_oracle(n):
+    """One record, one short of a tile, one over a tile, and exactly the documented maximum."""
+    from chronos_b200 import _ffi, tracegen
+
+    assert _ffi.NOALLOC_MAX_EVENTS == 262_144
+    rows = tracegen.generate_host(tracegen.WORKLOADS["skewed_zipf_chains"], first=4_321, n=n)
+    for _ in range(2):   # twice: the second call starts from the first one's leftovers
+        cnt, idx, pid, meta = _noalloc(_ffi.lib(), 0, rows)
+        o_idx, o_pid, o_meta = _oracle(rows)
+        assert cnt == len(o_idx)
+        np.testing.assert_array_equal(idx, o_idx)
+        np.testing.assert_array_equal(pid, o_pid)
+        np.testing.assert_array_equal(meta & 0x0F, o_meta)
+
+
+def test_noalloc_two_streams_ordered_by_an_event():
+    """The documented way to share the one scratch array between streams: the second call's
+    stream waits for an event recorded behind the first call. Both results must be right."""
+    import torch
+
+    from chronos_b200 import _ffi, tracegen
+
+    L = _ffi.lib()
+    a = tracegen.generate_host(tracegen.WORKLOADS["uniform_10m_4k"], first=0, n=100_000)
+    b = tracegen.generate_host(tracegen.WORKLOADS["sharded_100m_1m"], first=5_000, n=70_000)
+    bufs = []
+    for rows in (a, b):
+        n = len(rows)
+        d = {k: tracegen.DeviceBuffer(0, sz) for k, sz in (("rec", n * 288), ("idx", n * 4), ("pid", n * 4), ("meta", n), ("cnt", 4))}
+        d["rec"].upload(rows)
+        bufs.append(d)
+    s1, s2 = torch.cuda.Stream(device=0), torch.cuda.Stream(device=0)
+    err = ctypes.create_string_buffer(256)
+
+    def call(stream, d, n):
+        rc = L.chronos_filter_noalloc(0, c_void_p(stream.cuda_stream), c_void_p(d["rec"].ptr), n, c_void_p(d["idx"].ptr),
+                                      c_void_p(d["pid"].ptr), c_void_p(d["meta"].ptr), c_void_p(d["cnt"].ptr), err, 256)
+        assert rc == 0, err.value
+
+    call(s1, bufs[0], len(a))
+    done = torch.cuda.Event()
+    done.record(s1)
+    s2.wait_event(done)          # without this the two calls would race on the shared scratch
+    call(s2, bufs[1], len(b))
+    s2.synchronize()
+    for rows, d in ((a, bufs[0]), (b, bufs[1])):
+        n = len(rows)
+        cnt = int(d["cnt"].download(4).view(np.uint32)[0])
+        o_idx, o_pid, o_meta = _oracle(rows)
+        assert cnt == len(o_idx)
+        np.testing.assert_array_equal(d["idx"].download(n * 4).view(np.uint32)[:cnt], o_idx)
+        np.testing.assert_array_equal(d["pid"].download(n * 4).view(np.uint32)[:cnt], o_pid)
+        np.testing.assert_array_equal(d["meta"].download(n)[:cnt] & 0x0F, o_meta)
+        for v in d.values():
+            v.free()
