@@ -209,15 +209,35 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
             st_relaxed_u64(st, tag | (ST_PREFIX << 32) | total);
         } else {
             st_relaxed_u64(st, tag | (ST_AGG << 32) | total);
-            const uint64_t *q = st - RADIX_BINS;
-            while (true) {
-                uint64_t v;
-                do {
-                    v = ld_relaxed_u64(q);
-                } while ((v >> 34) != p.epoch || ((v >> 32) & 3u) == ST_NONE);
-                excl += (uint32_t)v;
-                if (((v >> 32) & 3u) == ST_PREFIX) break;
-                q -= RADIX_BINS;
+            // The chain of this digit, LB predecessors per round: their status words are loaded
+            // together (independent loads, one round trip) and consumed nearest first, up to the
+            // first PREFIX or the first word that is not written yet. One word per round made a
+            // pass a chain of up to n_tiles dependent L2 round trips (all tiles of a batch this
+            // size run in one wave, so nobody finds a PREFIX nearby).
+            constexpr int LB = 8;
+            const uint64_t *q = st - RADIX_BINS;  // nearest predecessor not consumed yet
+            uint32_t left = tile;                 // predecessors not consumed yet (tile 0 always ends the walk)
+            bool done = false;
+            while (!done) {
+                uint64_t v[LB];
+                const int nb = (int)min((uint32_t)LB, left);
+#pragma unroll
+                for (int k = 0; k < LB; k++)
+                    if (k < nb) v[k] = ld_relaxed_u64(q - (size_t)k * RADIX_BINS);
+                int used = 0;
+#pragma unroll
+                for (int k = 0; k < LB; k++) {
+                    if (k < nb && used == k && !done) {
+                        const uint32_t stt = (uint32_t)(v[k] >> 32) & 3u;
+                        if ((v[k] >> 34) == p.epoch && stt != ST_NONE) {
+                            excl += (uint32_t)v[k];
+                            used = k + 1;
+                            done = stt == ST_PREFIX;
+                        }
+                    }
+                }
+                q -= (size_t)used * RADIX_BINS;
+                left -= (uint32_t)used;
             }
             st_relaxed_u64(st, tag | (ST_PREFIX << 32) | (uint64_t)(excl + total));
         }
