@@ -48,14 +48,7 @@ struct FilterParams {
     uint32_t *out_count;     // total survivors (atomicAdd, one per CTA)
     uint32_t *key_or;        // OR / AND over survivor pids (radix pass planning)
     uint32_t *key_and;
-    // optional second-level comm memo shared by all CTAs and batches (nullptr: none).
-    // Insert-only: a slot is claimed with a CAS on its lock, its key written, then its value
-    // published with release semantics; a published slot never changes, so a reader that
-    // sees a valid value (acquire) reads a stable key.
-    uint32_t *gm_lock;
-    uint32_t *gm_val;
-    uint4 *gm_key;
-    uint32_t gm_mask;
+    uint32_t dbg_nowrite;    // experiments only: 1 = no per-survivor stores, 2 = no per-tile count store, 3 = neither
 };
 
 // ---- needle tests on one 4-byte window `t` (bytes k..k+3) and the byte after it ------
@@ -261,7 +254,8 @@ __host__ __device__ __forceinline__ uint32_t transport_slots(int alen) {
 }
 
 constexpr int FILTER_TILE = 32;  // records per tile: one per lane of the (single) warp of a CTA
-constexpr int MEMO_SLOTS = 64;   // comm memo entries per CTA
+constexpr int MEMO_WAYS = 4;
+constexpr int MEMO_SLOTS = 32 * MEMO_WAYS;   // comm memo entries per CTA (32 sets)
 constexpr int SHORT_CHUNKS = 4;  // argv NUL search done lane-per-record over chunks 1..4 (60 bytes)
 
 template <int NSTAGE>
@@ -312,13 +306,18 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
     constexpr uint32_t STAGE_BYTES = FILTER_TILE * CH_REC_BYTES;
     const int lane = threadIdx.x;
 
+    const uint64_t l2_evict_first = l2_policy_evict_first();  // the batch is read once
     auto issue = [&](int s, uint32_t t) {  // lane 0 only
         S.tile[s] = t;
         if (t < p.tile_end) {
             const uint64_t first = (uint64_t)t * FILTER_TILE;
             const uint32_t bytes = (uint32_t)min((uint64_t)FILTER_TILE, p.n - first) * CH_REC_BYTES;
             mbar_arrive_expect_tx(&S.bar[s], bytes);
+#ifndef CHRONOS_NO_L2_HINT
+            bulk_g2s_hint(stages + (size_t)s * STAGE_BYTES, p.recs + first * CH_REC_BYTES, bytes, &S.bar[s], l2_evict_first);
+#else
             bulk_g2s(stages + (size_t)s * STAGE_BYTES, p.recs + first * CH_REC_BYTES, bytes, &S.bar[s]);
+#endif
         }
     };
 
@@ -366,37 +365,31 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
         uint32_t meta = 0, hi = 0;
         if (__any_sync(FULL, alive)) {
             const uint32_t c0 = w[1], c1 = w[2], c2 = w[3], c3 = w[4];
-            const uint32_t h =
-                ((c0 * 0x9E3779B1u) ^ (c1 * 0x85EBCA77u) ^ (c2 * 0xC2B2AE3Du) ^ (c3 * 0x27D4EB2Fu)) >> 26;
-            const uint4 mk = S.memo_key[h];
-            uint32_t cres = S.memo_val[h];
-            const bool hit = (cres & CR_VALID) && mk.x == c0 && mk.y == c1 && mk.z == c2 && mk.w == c3;
-            const bool miss = alive && !hit;
-            if (miss) {
-                bool done = false;
-                uint32_t g = 0;
-                if (p.gm_val) {
-                    g = ((c0 * 0x85EBCA77u) ^ (c1 * 0xC2B2AE3Du) ^ (c2 * 0x27D4EB2Fu) ^ (c3 * 0x9E3779B1u)) >> 7 & p.gm_mask;
-                    const uint32_t gv = ld_acquire_u32(p.gm_val + g);
-                    if (gv & CR_VALID) {
-                        const uint4 gk = p.gm_key[g];
-                        if (gk.x == c0 && gk.y == c1 && gk.z == c2 && gk.w == c3) { cres = gv; done = true; }
-                    }
-                }
-                if (!done) {
-                    cres = comm_classify(w) | CR_VALID;
-                    if (p.gm_val && atomicCAS(p.gm_lock + g, 0u, 1u) == 0u) {
-                        p.gm_key[g] = make_uint4(c0, c1, c2, c3);
-                        __threadfence();
-                        st_release_u32(p.gm_val + g, cres);
-                    }
-                }
+            // 4-way set-associative memo in shared memory, 32 sets: a CTA sees a few dozen process
+            // names, and in a direct-mapped table two names that share a slot evict each other on
+            // every occurrence.
+            const uint32_t set =
+                (((c0 * 0x9E3779B1u) ^ (c1 * 0x85EBCA77u) ^ (c2 * 0xC2B2AE3Du) ^ (c3 * 0x27D4EB2Fu)) >> 27) * MEMO_WAYS;
+            uint32_t cres = 0;
+            bool hit = false;
+            int free_way = -1;
+#pragma unroll
+            for (int wy = 0; wy < MEMO_WAYS; wy++) {
+                const uint32_t mv = S.memo_val[set + wy];
+                const uint4 mk = S.memo_key[set + wy];
+                if ((mv & CR_VALID) && mk.x == c0 && mk.y == c1 && mk.z == c2 && mk.w == c3) { hit = true; cres = mv; }
+                if (!(mv & CR_VALID) && free_way < 0) free_way = wy;
             }
+            const bool miss = alive && !hit;
+            if (miss) cres = comm_classify(w) | CR_VALID;
             {
-                const uint32_t peers = __match_any_sync(FULL, miss ? h : 0x100u + lane);
+                // one writer per set and tile (the lowest missing lane of the set); a full set loses
+                // the way the tile number points at
+                const uint32_t peers = __match_any_sync(FULL, miss ? set : 0x1000u + lane);
                 if (miss && (peers & lanemask_lt()) == 0) {
-                    S.memo_key[h] = make_uint4(c0, c1, c2, c3);
-                    S.memo_val[h] = cres;
+                    const uint32_t victim = set + (free_way >= 0 ? (uint32_t)free_way : (tile & (MEMO_WAYS - 1)));
+                    S.memo_key[victim] = make_uint4(c0, c1, c2, c3);
+                    S.memo_val[victim] = cres;
                 }
                 __syncwarp();
             }
@@ -511,7 +504,7 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
         const uint32_t kb = __ballot_sync(FULL, keep);
         if (kb) {
             const uint32_t rank = __popc(kb & lanemask_lt());
-            if (keep) {
+            if (keep && !(p.dbg_nowrite & 1u)) {
                 const size_t slot = (size_t)tile * FILTER_TILE + rank;
                 p.sp_key[slot] = pid;
                 p.sp_src[slot] = (uint32_t)first + lane;
@@ -521,7 +514,7 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
             k_or |= __reduce_or_sync(FULL, keep ? pid : 0u);
             k_and &= __reduce_and_sync(FULL, keep ? pid : 0xffffffffu);
         }
-        if (lane == 0) p.tile_count[tile] = __popc(kb);
+        if (lane == 0 && !(p.dbg_nowrite & 2u)) p.tile_count[tile] = __popc(kb);
         cta_total += __popc(kb);
     }
     if (lane == 0 && cta_total) {

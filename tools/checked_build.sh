@@ -5,5 +5,5 @@ set -e
 cd "$(dirname "$0")/.."
 P=$(ls -d project-chronos*/)
 nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC -shared -I include \
-     -DCHRONOS_CHECKED -o ${P}libchronos_b200_checked.so ${P}csrc/chronos.cu
+     -DCHRONOS_CHECKED -o ${P}libchronos_b200_checked.so ${P}csrc/chronos.cu ${P}csrc/tracegen_tu.cu
 echo ${P}libchronos_b200_checked.so
