@@ -171,6 +171,7 @@ struct chronos_ctx {
     uint64_t launches = 0;  // of the submit being enqueued
     int filter_variant = 0;
     int gather_ctas_per_sm = 0;
+    int filter_ctas_per_sm = -1;  // > 0: that many; 0: as many as fit; -1 (default): one fewer than fit
     int dbg_skip = 0;  // CHRONOS_DBG_SKIP: bit mask of tail kernels NOT launched (timing experiments only, results are wrong)
     int gather_when = 0;  // 0: right after the sort, launched before group_forward; 1: same, launched behind it; 2: once group_forward has finished
     int prio_lo = 0;
@@ -466,6 +467,8 @@ int launch_filter_t(chronos_ctx *c, FilterParams fp, cudaStream_t st) {
         if (c->device < 64) per_sm_of[c->device] = per_sm;
     }
     const uint32_t tiles = fp.tile_end - fp.tile_begin;
+    if (c->filter_ctas_per_sm > 0) per_sm = std::min(per_sm, c->filter_ctas_per_sm);
+    else if (c->filter_ctas_per_sm < 0 && per_sm > 2) per_sm -= 1;
     const uint32_t grid = std::min<uint32_t>(tiles, (uint32_t)(per_sm * c->sm_count));
     kern<<<grid, FILTER_TILE, smem, st>>>(fp);
     CK(cudaGetLastError());
@@ -1126,6 +1129,11 @@ int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pen
     const char *gc = getenv("CHRONOS_GATHER_CTAS");
     c->gather_ctas_per_sm = gc ? std::max(1, atoi(gc)) : 2;
     c->no_pipeline = getenv("CHRONOS_NO_PIPELINE") != nullptr;
+    // One CTA per SM fewer than shared memory would allow (18 instead of 19 on B200). At full
+    // residency the filter is bistable: whole runs of batches take 0.72-0.87 ms instead of 0.49 ms
+    // per 10 M events, depending on what the previous kernels left in L2; at 18 it is steady at
+    // 0.50 ms, at 17 at 0.515 ms (sweep in profiles/README.md, "filter residency").
+    c->filter_ctas_per_sm = getenv("CHRONOS_FILTER_CTAS") ? atoi(getenv("CHRONOS_FILTER_CTAS")) : -1;
     c->dbg_skip = getenv("CHRONOS_DBG_SKIP") ? atoi(getenv("CHRONOS_DBG_SKIP")) : 0;
     const char *gf = getenv("CHRONOS_GATHER_WHEN");
     c->gather_when = gf ? atoi(gf) : 0;

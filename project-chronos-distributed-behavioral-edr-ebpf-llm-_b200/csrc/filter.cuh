@@ -254,8 +254,12 @@ __host__ __device__ __forceinline__ uint32_t transport_slots(int alen) {
 }
 
 constexpr int FILTER_TILE = 32;  // records per tile: one per lane of the (single) warp of a CTA
+#ifndef CHRONOS_MEMO_SETS_LOG2
+#define CHRONOS_MEMO_SETS_LOG2 4
+#endif
 constexpr int MEMO_WAYS = 4;
-constexpr int MEMO_SLOTS = 32 * MEMO_WAYS;   // comm memo entries per CTA (32 sets)
+constexpr int MEMO_SETS_LOG2 = CHRONOS_MEMO_SETS_LOG2;
+constexpr int MEMO_SLOTS = (1 << MEMO_SETS_LOG2) * MEMO_WAYS;   // comm memo entries per CTA
 constexpr int SHORT_CHUNKS = 4;  // argv NUL search done lane-per-record over chunks 1..4 (60 bytes)
 
 template <int NSTAGE>
@@ -365,11 +369,11 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
         uint32_t meta = 0, hi = 0;
         if (__any_sync(FULL, alive)) {
             const uint32_t c0 = w[1], c1 = w[2], c2 = w[3], c3 = w[4];
-            // 4-way set-associative memo in shared memory, 32 sets: a CTA sees a few dozen process
+            // 4-way set-associative memo in shared memory: a CTA sees a few dozen process
             // names, and in a direct-mapped table two names that share a slot evict each other on
             // every occurrence.
             const uint32_t set =
-                (((c0 * 0x9E3779B1u) ^ (c1 * 0x85EBCA77u) ^ (c2 * 0xC2B2AE3Du) ^ (c3 * 0x27D4EB2Fu)) >> 27) * MEMO_WAYS;
+                (((c0 * 0x9E3779B1u) ^ (c1 * 0x85EBCA77u) ^ (c2 * 0xC2B2AE3Du) ^ (c3 * 0x27D4EB2Fu)) >> (32 - MEMO_SETS_LOG2)) * MEMO_WAYS;
             uint32_t cres = 0;
             bool hit = false;
             int free_way = -1;
