@@ -564,7 +564,7 @@ def run_gpu_arm(args, rank, world, local_rank):
                        "l2": "input per step (2.88 GB+) exceeds the 126 MB L2; no flush needed",
                        "timing": "torch CUDA events on the library stream around all K steps, max over ranks",
                        "steps_on_gpu": ("one batch at a time (a batch starts when the previous one has ended); the host "
-                                        "enqueues one step ahead" if world == 1 else "one batch at a time, enqueued after the previous fetch"),
+                                        "enqueues one step ahead"),
                        "warmup_extra_steps": extra,
                        "exchange": (None if world == 1 else
                                     ("direct: stage 1 writes survivors into the owners' HBM over NVLink (CUDA IPC windows), "

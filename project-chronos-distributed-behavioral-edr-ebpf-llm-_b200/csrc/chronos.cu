@@ -99,6 +99,8 @@ struct BatchSet {
     cudaEvent_t ev_start = nullptr, ev_stage1 = nullptr, ev_end = nullptr, ev_f0 = nullptr, ev_f1 = nullptr;
     cudaEvent_t ev_packed = nullptr;  // last read of this set's results by a download
     cudaEvent_t ev_prepack = nullptr, ev_s1end = nullptr, ev_sort = nullptr;  // stage boundaries (timing only)
+    cudaEvent_t ev_x0 = nullptr;   // start of the exchange step this set serves
+    bool x_filter_timed = false;   // stage 1 of that step ran the filter (non-empty slice)
     float stage_ms[8] = {0};
     enum State { FREE, SUBMITTED, DONE, FETCHED } state = FREE;
     // the batch
@@ -164,9 +166,7 @@ struct chronos_ctx {
     bool x_opened[XCHG_MAX_WORLD] = {false};
     uint32_t x_epoch = 0;
     uint64_t x_launches = 0;
-    bool x_filter_timed = false;  // stage 1 of this step ran the filter (non-empty slice)
     uint64_t x_timeout_ns = 20ull * 1000000000ull;
-    cudaEvent_t ev_x0 = nullptr;
 
     uint64_t launches = 0;  // of the submit being enqueued
     int filter_variant = 0;
@@ -930,7 +930,7 @@ int complete_batch(chronos_ctx *c, BatchSet &b) {
                         "exchange: survivors for one owner rank exceed the window (%u entries / %u slots per peer)",
                         c->x_L.cap_e, c->x_L.cap_s);
     }
-    cudaEventElapsedTime(&b.t_total, b.exchanged ? c->ev_x0 : b.ev_start, b.ev_end);
+    cudaEventElapsedTime(&b.t_total, b.exchanged ? b.ev_x0 : b.ev_start, b.ev_end);
     if (c->trace && !b.pipelined) {
         for (int i = 1; i < c->n_tev; i++) {  // time since the first mark (marks sit on several streams)
             float ms = 0;
@@ -942,7 +942,7 @@ int complete_batch(chronos_ctx *c, BatchSet &b) {
     {   // stage boundaries of the batch (chronos_last_stage_times)
         float *t = b.stage_ms;
         for (int i = 0; i < 8; i++) t[i] = 0.f;
-        const bool filtered = b.filter_timed || (b.exchanged && c->x_filter_timed);
+        const bool filtered = b.filter_timed || (b.exchanged && b.x_filter_timed);
         if (filtered) cudaEventElapsedTime(&t[0], b.ev_f0, b.ev_f1);
         if (b.exchanged) {
             if (filtered) cudaEventElapsedTime(&t[1], b.ev_f1, b.ev_prepack);
@@ -959,7 +959,7 @@ int complete_batch(chronos_ctx *c, BatchSet &b) {
     }
     cudaEventElapsedTime(&b.t_filter, b.ev_start, b.ev_stage1);
     // (a stage-2-only batch keeps the filter time measured by its stage 1)
-    if (b.filter_timed || (b.exchanged && c->x_filter_timed)) cudaEventElapsedTime(&b.t_filter_kernel, b.ev_f0, b.ev_f1);
+    if (b.filter_timed || (b.exchanged && b.x_filter_timed)) cudaEventElapsedTime(&b.t_filter_kernel, b.ev_f0, b.ev_f1);
     cudaGetLastError();
     return CHRONOS_OK;
 }
@@ -979,7 +979,8 @@ void carried_bounds(chronos_ctx *c, uint64_t &P_ub, uint64_t &pids_ub) {
 // Start of a submit of n events. Everything that can refuse the batch happens BEFORE any state
 // of the context changes: a refused submit leaves process_memory exactly as it was.
 // On success *out is the set the batch runs in and *sf the stream of its stage 1.
-int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base, bool transport, BatchSet **out, cudaStream_t *sf) {
+int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base, bool transport, BatchSet **out, cudaStream_t *sf,
+                bool main_stream_only = false) {
     CK(cudaSetDevice(c->device));
     if (n > c->max_batch) return fail(c, CHRONOS_E_CAPACITY, "batch of %llu events > max_batch_events %llu",
                                       (unsigned long long)n, (unsigned long long)c->max_batch);
@@ -1017,8 +1018,9 @@ int begin_batch(chronos_ctx *c, uint64_t n, uint64_t base, bool transport, Batch
     if ((rc = ensure_pid_table(c, pids_ub, Mmax))) return rc;
 
     // ---- from here on the batch is accepted ---------------------------------------------------
-    const bool pipelined = prev.state == BatchSet::SUBMITTED && !c->no_pipeline;
-    if (prev.state == BatchSet::SUBMITTED && c->no_pipeline && (rc = complete_batch(c, prev))) return rc;
+    // (main_stream_only: the caller's stage 1 already sits on the main stream, behind the previous batch)
+    const bool pipelined = prev.state == BatchSet::SUBMITTED && !c->no_pipeline && !main_stream_only;
+    if (prev.state == BatchSet::SUBMITTED && c->no_pipeline && !main_stream_only && (rc = complete_batch(c, prev))) return rc;
     if (c->fetched == t) c->fetched = -1;
     b.state = BatchSet::FREE;
     b.n = n;
@@ -1154,9 +1156,8 @@ int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pen
         for (cudaEvent_t *e : {&c->ev_sorted, &c->ev_gathered, &c->ev_fwd, &c->ev_emitted, &c->dl_ready, &c->dl_done[0],
                                &c->dl_done[1]})
             CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
-        CK(cudaEventCreate(&c->ev_x0));
         for (BatchSet &b : c->set) {
-            for (cudaEvent_t *e : {&b.ev_start, &b.ev_stage1, &b.ev_end, &b.ev_f0, &b.ev_f1, &b.ev_prepack, &b.ev_s1end, &b.ev_sort})
+            for (cudaEvent_t *e : {&b.ev_start, &b.ev_stage1, &b.ev_end, &b.ev_f0, &b.ev_f1, &b.ev_prepack, &b.ev_s1end, &b.ev_sort, &b.ev_x0})
                 CK(cudaEventCreate(e));
             CK(cudaEventCreateWithFlags(&b.ev_packed, cudaEventDisableTiming));
             CK(cudaMallocHost(reinterpret_cast<void **>(&b.h_scalars), RESULT_BLOCK_BYTES));
@@ -1207,7 +1208,7 @@ int chronos_destroy(chronos_ctx *c) {
                          &b.d_batch, &b.result};
         for (DevBuf *d : all) release(*d);
         if (b.h_scalars) cudaFreeHost(b.h_scalars);
-        for (cudaEvent_t e : {b.ev_start, b.ev_stage1, b.ev_end, b.ev_f0, b.ev_f1, b.ev_packed, b.ev_prepack, b.ev_s1end, b.ev_sort})
+        for (cudaEvent_t e : {b.ev_start, b.ev_stage1, b.ev_end, b.ev_f0, b.ev_f1, b.ev_packed, b.ev_prepack, b.ev_s1end, b.ev_sort, b.ev_x0})
             if (e) cudaEventDestroy(e);
     }
     DevBuf *all[] = {&c->carry, &c->keyA, &c->keyB, &c->valA, &c->valB, &c->pflag, &c->entry_out, &c->wsorted, &c->status,
@@ -1218,8 +1219,7 @@ int chronos_destroy(chronos_ctx *c) {
     for (int d = 0; d < XCHG_MAX_WORLD; d++)
         if (c->x_opened[d] && c->x_peer[d]) cudaIpcCloseMemHandle(c->x_peer[d]);
     release(c->x_window);
-    for (cudaEvent_t e : {c->ev_sorted, c->ev_gathered, c->ev_fwd, c->ev_emitted, c->dl_ready, c->dl_done[0], c->dl_done[1],
-                          c->ev_x0})
+    for (cudaEvent_t e : {c->ev_sorted, c->ev_gathered, c->ev_fwd, c->ev_emitted, c->dl_ready, c->dl_done[0], c->dl_done[1]})
         if (e) cudaEventDestroy(e);
     for (int i = 0; i < 24; i++)
         if (c->tev[i]) cudaEventDestroy(c->tev[i]);
@@ -1859,8 +1859,8 @@ static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base
     if (base >= MAX_ARRIVAL || base + n > MAX_ARRIVAL) return fail(c, CHRONOS_E_ARG, "arrival indices must stay below 2^48");
     BatchSet &b = c->set[c->last ^ 1];
     if (b.state == BatchSet::SUBMITTED && (rc = complete_batch(c, b))) return rc;
-    BatchSet &newest = c->set[c->last];
-    if (newest.state == BatchSet::SUBMITTED && (rc = complete_batch(c, newest))) return rc;  // no overlap on this path
+    // (the newest batch may still be in flight: stage 1 is queued on the main stream behind its tail,
+    //  it only touches the other buffer set and the stage-1 temporaries)
     if (c->fetched == (c->last ^ 1)) c->fetched = -1;
     b.state = BatchSet::FREE;
     cudaStream_t st = c->stream;
@@ -1877,7 +1877,7 @@ static int stage1(chronos_ctx *c, const void *records, uint64_t n, uint64_t base
     mark(c, "stage 1 start");
     b.filter_timed = false;
     if (n && (rc = run_filter_stage(c, b, d_recs, n, st))) return rc;
-    c->x_filter_timed = n != 0;
+    b.x_filter_timed = n != 0;
     mark(c, "filter + compact");
 
     const uint32_t W = pk.world;
@@ -2025,7 +2025,7 @@ int chronos_filter_exchange(chronos_ctx *c, const void *records, uint64_t n, uin
     if (n && !records) return fail(c, CHRONOS_E_ARG, "records is NULL");
     CK(cudaSetDevice(c->device));
     int rc;
-    CK(cudaEventRecord(c->ev_x0, c->stream));
+    CK(cudaEventRecord(c->set[c->last ^ 1].ev_x0, c->stream));
     XchgPackParams pk;
     memset(&pk, 0, sizeof(pk));
     pk.world = c->x_L.world;
@@ -2048,7 +2048,7 @@ int chronos_submit_exchanged(chronos_ctx *c) {
     const uint64_t stage1_launches = c->x_launches;
     BatchSet *bp;
     cudaStream_t s1;
-    int rc = begin_batch(c, n_max, 0, true, &bp, &s1);
+    int rc = begin_batch(c, n_max, 0, true, &bp, &s1, true);
     if (rc) return rc;
     BatchSet &b = *bp, &prev = c->set[c->last];
     c->launches += stage1_launches;

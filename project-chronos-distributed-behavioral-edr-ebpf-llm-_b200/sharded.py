@@ -173,10 +173,29 @@ class ShardedRunner:
         return c
 
     def timed_steps(self, steps):
-        """K steps for bench.py's timed region (each one enqueued after the previous fetch)."""
-        for _ in range(steps):
-            c = self.step()
-            c["stages"] = self.ctx.last_stage_times()
+        """K steps for bench.py's timed region. Direct mode: every step is a fresh process_memory
+        and the GPU runs the steps strictly one after the other (everything of a step is queued on
+        one stream); only the host works ahead -- step k+1 is enqueued before step k is fetched."""
+        if self.mode != "direct":
+            for _ in range(steps):
+                c = self.step()
+                c["stages"] = self.ctx.last_stage_times()
+                yield c
+            return
+
+        def enqueue():
+            self.ctx.reset()
+            self.ctx.filter_exchange_ptr(self.rec_ptr, self.n, self.first)
+            self.ctx.submit_exchanged()
+
+        enqueue()
+        for k in range(steps):
+            if k + 1 < steps:
+                enqueue()
+            c = self.ctx.fetch_counts()
+            t, f = self.ctx.last_timing()
+            c.update(gpu_ms=t, filter_ms=f, launches=self.ctx.last_launches(), n_received=c["n_survivors"],
+                     stages=self.ctx.last_stage_times())
             yield c
 
     def e2e(self, steps, barrier, dist_mod):
