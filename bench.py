@@ -480,7 +480,7 @@ def run_gpu_arm(args, rank, world, local_rank):
             break
     barrier()
     sampler = ClockSampler(device)
-    if rank == 0:
+    if rank == 0 and not os.environ.get("CHRONOS_BENCH_NO_SAMPLER"):
         sampler.start()
     ext = torch.cuda.ExternalStream(runner.stream_ptr(), device=torch.device("cuda", device))
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -653,11 +653,15 @@ class SingleGpuRunner:
         works ahead -- step k+1 is enqueued before step k is fetched, so the GPU does not sit idle
         while Python and the driver prepare the next launch sequence."""
         ctx = self.ctx
+        ahead = not os.environ.get("CHRONOS_BENCH_NO_AHEAD")
         ctx.set_overlap(False)
         ctx.reset()
         ctx.submit_ptr(self.dev.ptr, self.n, 0)
         for k in range(steps):
-            if k + 1 < steps:
+            if not ahead and k > 0:
+                ctx.reset()
+                ctx.submit_ptr(self.dev.ptr, self.n, 0)
+            if ahead and k + 1 < steps:
                 ctx.reset()
                 ctx.submit_ptr(self.dev.ptr, self.n, 0)
             c = ctx.fetch_counts()

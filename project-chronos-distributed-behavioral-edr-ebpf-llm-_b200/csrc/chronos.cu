@@ -125,7 +125,7 @@ struct chronos_ctx {
     // submitted while the previous one is still running; stream2: record gather; stream3: ordered
     // emission beside the reverse scan; dl_stream: everything the host asks for after a fetch
     cudaStream_t stream = nullptr, stream_f = nullptr, stream2 = nullptr, stream3 = nullptr, dl_stream = nullptr;
-    cudaEvent_t ev_sorted = nullptr, ev_gathered = nullptr, ev_fwd = nullptr, ev_emitted = nullptr;
+    cudaEvent_t ev_sorted = nullptr, ev_gathered = nullptr, ev_fwd = nullptr, ev_emitted = nullptr, ev_tailinit = nullptr;
     char err[256] = {0};
 
     BatchSet set[2];
@@ -724,9 +724,15 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     const uint64_t Smax = b.n;
     int rc;
     const uint32_t max_rtiles = (uint32_t)((Mmax + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS);
-    CK(cudaMemsetAsync(c->status.p, 0, status_words(Mmax) * 8, st));
-    init_batch_kernel<<<1, 256, 0, st>>>(ds, ptr<uint32_t>(c->tickets_f), ptr<uint32_t>(c->tickets_t), 2);
+    // The tail's counters and look-back words start at zero. Nothing of stage 1 is needed for
+    // that, so it is done on stream3 while the filter runs (behind the previous batch's tail, which
+    // uses the same words), and the main stream picks it up with an event.
+    if (prev.state == BatchSet::SUBMITTED) CK(cudaStreamWaitEvent(c->stream3, prev.ev_end, 0));
+    CK(cudaMemsetAsync(c->status.p, 0, status_words(Mmax) * 8, c->stream3));
+    init_batch_kernel<<<1, 256, 0, c->stream3>>>(ds, ptr<uint32_t>(c->tickets_f), ptr<uint32_t>(c->tickets_t), 2);
     c->launches++;
+    CK(cudaEventRecord(c->ev_tailinit, c->stream3));
+    CK(cudaStreamWaitEvent(st, c->ev_tailinit, 0));
 
     // ---- stable sort by pid: plan + global digit histograms, then one kernel per pass --------
     SortParams sp;
@@ -1153,8 +1159,8 @@ int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pen
         CK(cudaStreamCreateWithPriority(&c->stream3, cudaStreamNonBlocking, prio_hi));
         CK(cudaStreamCreateWithPriority(&c->stream2, cudaStreamNonBlocking, gather_low ? prio_lo : prio_hi));
         c->prio_lo = prio_lo;  // stream_f and dl_stream are created when first needed
-        for (cudaEvent_t *e : {&c->ev_sorted, &c->ev_gathered, &c->ev_fwd, &c->ev_emitted, &c->dl_ready, &c->dl_done[0],
-                               &c->dl_done[1]})
+        for (cudaEvent_t *e : {&c->ev_sorted, &c->ev_gathered, &c->ev_fwd, &c->ev_emitted, &c->ev_tailinit, &c->dl_ready,
+                               &c->dl_done[0], &c->dl_done[1]})
             CK(cudaEventCreateWithFlags(e, cudaEventDisableTiming));
         for (BatchSet &b : c->set) {
             for (cudaEvent_t *e : {&b.ev_start, &b.ev_stage1, &b.ev_end, &b.ev_f0, &b.ev_f1, &b.ev_prepack, &b.ev_s1end, &b.ev_sort, &b.ev_x0})
@@ -1219,7 +1225,7 @@ int chronos_destroy(chronos_ctx *c) {
     for (int d = 0; d < XCHG_MAX_WORLD; d++)
         if (c->x_opened[d] && c->x_peer[d]) cudaIpcCloseMemHandle(c->x_peer[d]);
     release(c->x_window);
-    for (cudaEvent_t e : {c->ev_sorted, c->ev_gathered, c->ev_fwd, c->ev_emitted, c->dl_ready, c->dl_done[0], c->dl_done[1]})
+    for (cudaEvent_t e : {c->ev_sorted, c->ev_gathered, c->ev_fwd, c->ev_emitted, c->ev_tailinit, c->dl_ready, c->dl_done[0], c->dl_done[1]})
         if (e) cudaEventDestroy(e);
     for (int i = 0; i < 24; i++)
         if (c->tev[i]) cudaEventDestroy(c->tev[i]);

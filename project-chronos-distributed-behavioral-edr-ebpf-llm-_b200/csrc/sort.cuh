@@ -195,9 +195,24 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
         constexpr uint32_t sub = RADIX_TILE_KEYS / RADIX_WARPS;  // multiple of 32
         const uint32_t w_lo = min(t_hi, t_lo + warp * sub);
         const uint32_t w_hi = min(t_hi, w_lo + sub);
-        // 1) per-warp digit counts over the warp's contiguous sub-range
-        for (uint32_t i = w_lo + lane; i < w_hi; i += 32)
-            atomicAdd(&whist[warp][((first ? entry_key(p, split, i) : keys_in[i]) >> shift) & mask], 1u);
+        // 1) per-warp digit counts over the warp's contiguous sub-range. The warp's keys and values
+        //    stay in registers for the placement in step 3: read there, step by step, every one of
+        //    its rounds began with a dependent trip to L2.
+        constexpr int PER_LANE = (int)(sub / 32);
+        uint32_t kreg[PER_LANE], vreg[PER_LANE];
+#pragma unroll
+        for (int it = 0; it < PER_LANE; it++) {
+            const uint32_t i = w_lo + it * 32 + lane;
+            kreg[it] = 0;
+            vreg[it] = 0;
+            if (i < w_hi) {
+                kreg[it] = first ? entry_key(p, split, i) : keys_in[i];
+                vreg[it] = first ? synth_value(p, split, i) : vals_in[i];
+            }
+        }
+#pragma unroll
+        for (int it = 0; it < PER_LANE; it++)
+            if (w_lo + it * 32 + lane < w_hi) atomicAdd(&whist[warp][(kreg[it] >> shift) & mask], 1u);
         __syncthreads();
         // 2) digit d = tid: tile total, published; keys of digit d in earlier tiles by look-back
         uint32_t total = 0;
@@ -253,12 +268,14 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
         }
         __syncthreads();
         // 3) stable placement, 32 keys per step, in index order
-        for (uint32_t i0 = w_lo; i0 < w_hi; i0 += 32) {
-            const uint32_t i = i0 + lane;
+#pragma unroll
+        for (int it = 0; it < PER_LANE; it++) {
+            const uint32_t i = w_lo + it * 32 + lane;
+            if (w_lo + it * 32 >= w_hi) break;  // (uniform over the warp)
             const bool valid = i < w_hi;
             uint32_t key = 0, d = RADIX_BINS;  // invalid lanes form their own group
             if (valid) {
-                key = first ? entry_key(p, split, i) : keys_in[i];
+                key = kreg[it];
                 d = (key >> shift) & mask;
             }
             const uint32_t peers = __match_any_sync(0xffffffffu, d);
@@ -272,7 +289,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
                 const uint32_t dst = base + before;
                 CH_ASSERT(dst < n);
                 keys_out[dst] = key;
-                vals_out[dst] = first ? synth_value(p, split, i) : vals_in[i];
+                vals_out[dst] = vreg[it];
             }
         }
     }
