@@ -144,6 +144,9 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
     __shared__ uint32_t wb_e[XCHG_WARPS][XCHG_MAX_WORLD], wb_s[XCHG_WARPS][XCHG_MAX_WORLD];
     __shared__ uint32_t sh_ns[XCHG_WARPS][32];
     __shared__ uint32_t s_skip, s_last;
+    // owner-major order of the tile's survivors (stable inside an owner): perm[j] = index in the tile
+    __shared__ uint16_t perm[XCHG_TILE];
+    __shared__ uint32_t o_start[XCHG_MAX_WORLD + 1], o_run[XCHG_MAX_WORLD];
     extern __shared__ uint4 stage[];  // XCHG_PACK_SMEM bytes
     const uint32_t T = g.T, W = g.world, S = *g.n_ptr;
     const uint32_t used = (S + XCHG_TILE - 1) / XCHG_TILE;
@@ -173,15 +176,53 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
         }
         __syncthreads();
         const uint32_t t_lo = tile * XCHG_TILE, t_hi = min(S, t_lo + XCHG_TILE);
-        const uint32_t w_lo = min(t_hi, t_lo + warp * XCHG_SUB), w_hi = min(t_hi, w_lo + XCHG_SUB);
+        // 0) The tile's survivors in OWNER-MAJOR order (a stable counting sort of 1024 indices in
+        //    shared memory). The warps then walk that order, so the 32 survivors of a warp step
+        //    nearly always share one owner and leave as ONE run of a few KB: in arrival order a
+        //    step's run per owner was about 360 bytes of slots (eight owners), too short for NVLink.
+        if (tid == 0) {
+            uint32_t run = 0;
+            for (uint32_t d = 0; d < W; d++) {  // entries of this tile per owner, from the scanned table
+                o_start[d] = run;
+                run += g.table[(size_t)d * T + tile + 1] - g.table[(size_t)d * T + tile];
+            }
+            o_start[W] = run;
+        }
+        if (tid < XCHG_MAX_WORLD) o_run[tid] = 0;
+        __syncthreads();
+        for (uint32_t r0 = 0; r0 < XCHG_TILE; r0 += XCHG_THREADS) {
+            const uint32_t i = t_lo + r0 + tid;
+            const uint32_t o = i < t_hi ? hash32(g.pid[i]) % W : 0xFFu;
+            const uint32_t peers = __match_any_sync(0xffffffffu, o);
+            const uint32_t below = __popc(peers & lanemask_lt());
+            if (o != 0xFFu && below == 0) wb_e[warp][o] = __popc(peers);  // (wb_e is zero here: see the reset above)
+            __syncthreads();
+            if (tid < (int)W) {  // where each warp's group of owner `tid` starts
+                uint32_t run = o_run[tid];
+                for (int w = 0; w < (int)XCHG_WARPS; w++) {
+                    const uint32_t cnt = wb_e[w][tid];
+                    wb_e[w][tid] = run;
+                    run += cnt;
+                }
+                o_run[tid] = run;
+            }
+            __syncthreads();
+            if (o != 0xFFu) perm[o_start[o] + wb_e[warp][o] + below] = (uint16_t)(r0 + tid);
+            __syncthreads();
+            for (int k = tid; k < (int)(XCHG_WARPS * XCHG_MAX_WORLD); k += XCHG_THREADS) (&wb_e[0][0])[k] = 0;
+            __syncthreads();
+        }
+        const uint32_t n_tile = t_hi - t_lo;
+        const uint32_t w_lo = min(n_tile, warp * XCHG_SUB), w_hi = min(n_tile, w_lo + XCHG_SUB);  // in owner-major positions
         // 1) this warp's survivors, all steps at once (the loads of the later steps are in
         //    flight while the first step is placed), and the per-warp counts per owner
         uint32_t ow[XCHG_STEPS], nsv[XCHG_STEPS], recv[XCHG_STEPS], metav[XCHG_STEPS];
 #pragma unroll
         for (int q = 0; q < XCHG_STEPS; q++) {
-            const uint32_t i = w_lo + q * 32 + lane;
+            const uint32_t j = w_lo + q * 32 + lane;
+            const uint32_t i = j < w_hi ? t_lo + perm[j] : 0xffffffffu;
             ow[q] = 0xFFu; nsv[q] = 0; recv[q] = 0; metav[q] = 0;
-            if (i < w_hi) {
+            if (j < w_hi) {
                 ow[q] = hash32(g.pid[i]) % W;
                 nsv[q] = g.surv_ns[i];
                 recv[q] = g.surv_src[i];

@@ -9,7 +9,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 import chronos_b200  # noqa: E402
-from chronos_b200 import tracegen  # noqa: E402
+from chronos_b200 import _ffi, tracegen  # noqa: E402
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 12_500_000
 world = int(sys.argv[2]) if len(sys.argv) > 2 else 2
@@ -26,9 +26,14 @@ for it in range(steps):
         c.reset()
     for r, c in enumerate(ctxs):
         c.filter_exchange_ptr(devs[r].ptr, n, r * n)
+    # ranks share ONE GPU here: all stage 1s must have finished before a stage 2 starts to spin
+    # (see tests/test_gpu_exchange.py)
+    assert _ffi.lib().chronos_device_synchronize(0) == 0
     for c in ctxs:
         c.submit_exchanged()
     for r, c in enumerate(ctxs):
         k = c.fetch_counts()
         t, f = c.last_timing()
-        print(f"it{it} rank{r}: {k['n_survivors']} received, {k['n_windows']} windows, library {t:.3f} ms, filter {f:.3f} ms, launches {c.last_launches()}", flush=True)
+        st = c.last_stage_times()
+        print(f"it{it} rank{r}: {k['n_survivors']} received, {k['n_windows']} windows, library {t:.3f} ms, filter {f:.3f} ms, "
+              f"pack {st['pack']:.3f} ms, launches {c.last_launches()}", flush=True)
