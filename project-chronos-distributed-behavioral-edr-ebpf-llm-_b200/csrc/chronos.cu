@@ -172,8 +172,7 @@ struct chronos_ctx {
     int filter_variant = 0;
     int gather_ctas_per_sm = 0;
     int filter_ctas_per_sm = -1;  // > 0: that many; 0: as many as fit; -1 (default): one fewer than fit
-    int dbg_skip = 0;  // CHRONOS_DBG_SKIP: bit mask of tail kernels NOT launched (timing experiments only, results are wrong)
-    int gather_when = 0;  // 0: right after the sort, launched before group_forward; 1: same, launched behind it; 2: once group_forward has finished
+    uint64_t fused_max = 0;  // batches whose grouped entries cannot exceed this run the tail as ONE kernel
     int prio_lo = 0;
     bool no_pipeline = false;
     // CHRONOS_TRACE=1: CUDA events between the stages of a submit, printed at fetch
@@ -442,6 +441,7 @@ int configure_kernels(chronos_ctx *c) {
 #endif
     CK(cudaFuncSetAttribute(xchg_pack, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)XCHG_PACK_SMEM));
     CK(cudaFuncSetAttribute(gather_records, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GATHER_SMEM));
+    CK(cudaFuncSetAttribute(fused_tail, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GATHER_SMEM));
     if (!getenv("CHRONOS_NO_CARVEOUT")) {
         // The filter's residency (19 single-warp CTAs per SM) is bounded by shared memory: ask for
         // the largest shared-memory carve-out instead of leaving the split to the driver's guess.
@@ -521,9 +521,6 @@ void filter_setup(chronos_ctx *c, BatchSet &b, const uint8_t *d_recs, uint64_t n
     fp.out_count = &ds->surv_count;
     fp.key_or = &ds->key_or;
     fp.key_and = &ds->key_and;
-    static const int nowrite = getenv("CHRONOS_DBG_NOWRITE") ? atoi(getenv("CHRONOS_DBG_NOWRITE")) : 0;
-    static int setups = 0;  // (the first two batches always write: later ones then find sane counts)
-    fp.dbg_nowrite = ++setups > 2 ? (uint32_t)nowrite : 0u;
 }
 
 // Cross-tile prefix + dense, arrival-ordered survivor arrays of the set, one kernel.
@@ -724,17 +721,18 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     const uint64_t Smax = b.n;
     int rc;
     const uint32_t max_rtiles = (uint32_t)((Mmax + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS);
+    uint32_t *tk = ptr<uint32_t>(c->tickets_t);
     // The tail's counters and look-back words start at zero. Nothing of stage 1 is needed for
     // that, so it is done on stream3 while the filter runs (behind the previous batch's tail, which
     // uses the same words), and the main stream picks it up with an event.
     if (prev.state == BatchSet::SUBMITTED) CK(cudaStreamWaitEvent(c->stream3, prev.ev_end, 0));
     CK(cudaMemsetAsync(c->status.p, 0, status_words(Mmax) * 8, c->stream3));
-    init_batch_kernel<<<1, 256, 0, c->stream3>>>(ds, ptr<uint32_t>(c->tickets_f), ptr<uint32_t>(c->tickets_t), 2);
+    init_batch_kernel<<<1, 256, 0, c->stream3>>>(ds, ptr<uint32_t>(c->tickets_f), tk, 2);
     c->launches++;
     CK(cudaEventRecord(c->ev_tailinit, c->stream3));
     CK(cudaStreamWaitEvent(st, c->ev_tailinit, 0));
 
-    // ---- stable sort by pid: plan + global digit histograms, then one kernel per pass --------
+    // ---- parameters of every tail kernel --------------------------------------------------------
     SortParams sp;
     memset(&sp, 0, sizeof(sp));
     sp.plan = plan;
@@ -755,32 +753,14 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     sp.pend_cap = (uint32_t)prev.pend_cap;
     sp.surv_pid = ptr<uint32_t>(b.surv_pid);
     sp.surv_meta = ptr<uint8_t>(b.surv_meta);
-    sp.ghist = ptr<uint32_t>(c->tickets_t) + N_TICKETS;  // zeroed with the tickets
+    sp.ghist = tk + N_TICKETS;  // zeroed with the tickets
     if (c->sweep_epoch == 0) CK(cudaMemsetAsync(c->sweep_status.p, 0, c->sweep_status.bytes, st));  // wrapped epoch
     sp.status = ptr<uint64_t>(c->sweep_status);
-    const unsigned sort_blocks = std::max(1u, std::min(max_rtiles, (uint32_t)c->sm_count * 4));
-    if (!(c->dbg_skip & 32)) sort_prepare<<<sort_blocks, RADIX_THREADS, 0, st>>>(sp);
-    c->launches++;
-    if ((rc = dbg_sync(c, "sort_prepare"))) return rc;
-    if (Mmax == 0) {  // nothing pending, nothing submitted: only the (empty) counts go back
-        copy_u32_kernel<<<1, 1, 0, st>>>(&ds->n_pids_seen, ptr<uint32_t>(c->pt_count));
-        CK(cudaMemcpyAsync(b.h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, st));
-        CK(cudaEventRecord(b.ev_end, st));
-        return CHRONOS_OK;
-    }
-    for (int i = 0; i < RADIX_MAX_PASSES; i++) {  // passes beyond plan->n_passes return at once
-        sp.pass = i;
-        sp.ticket = ptr<uint32_t>(c->tickets_t) + 40 + i;
-        sp.epoch = ++c->sweep_epoch;
+    uint32_t pass_epoch[RADIX_MAX_PASSES];
+    for (int i = 0; i < RADIX_MAX_PASSES; i++) {
+        pass_epoch[i] = ++c->sweep_epoch;
         if (c->sweep_epoch >= (1u << 29)) c->sweep_epoch = 0;  // re-zero on the next batch
-        if (!(c->dbg_skip & 1)) onesweep_pass<<<sort_blocks, RADIX_THREADS, 0, st>>>(sp);
-        c->launches++;
-        if ((rc = dbg_sync(c, "onesweep_pass"))) return rc;
     }
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(c->ev_sorted, st));
-    CK(cudaEventRecord(b.ev_sort, st));
-    mark(c, "sort done");
 
     WinParams w;
     memset(&w, 0, sizeof(w));
@@ -814,68 +794,118 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     const uint32_t tiles_m = (uint32_t)((Mmax + WIN_TILE - 1) / WIN_TILE);  // upper bounds
     const uint32_t tiles_s = (uint32_t)((Smax + WIN_TILE - 1) / WIN_TILE);
     uint64_t *stw = ptr<uint64_t>(c->status);
-    uint32_t *tk = ptr<uint32_t>(c->tickets_t);
+    WinParams w_fwd = w, w_rev = w, w_emit = w;
+    w_fwd.ticket = tk + 60;
+    w_fwd.status = stw;  // 5 words per tile
+    w_rev.ticket = tk + 61;
+    w_rev.status = stw + 5 * (size_t)tiles_m;  // 2 words per tile
+    w_emit.ticket = tk + 62;
+    w_emit.status = stw + 7 * (size_t)tiles_m;  // 1 word per tile
+
+    GatherParams g;
+    memset(&g, 0, sizeof(g));
+    g.plan = plan;
+    g.surv_src = ptr<uint32_t>(b.surv_src);
+    g.batch = b.records;
+    g.pend_slot = ptr<uint32_t>(prev.pend_slot);
+    g.pend_cap_prev = (uint32_t)prev.pend_cap;
+    g.prev_arena = ptr<uint8_t>(prev.arena);
+    g.arena = ptr<uint8_t>(b.arena);
+    g.slots = b.slots;
+    g.slot_off = b.slots ? ptr<uint32_t>(b.slot_off) : nullptr;
+    g.slot_ns = b.slots ? ptr<uint8_t>(b.surv_ns) : nullptr;
+
+    auto finish = [&]() -> int {
+        CK(cudaMemcpyAsync(b.h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(b.ev_end, st));
+        return CHRONOS_OK;
+    };
+
+    // ---- small batches: the whole tail in one launch (window.cuh fused_tail) ----------------------
+    if (Mmax != 0 && Mmax <= c->fused_max) {
+        FusedTailParams f;
+        memset(&f, 0, sizeof(f));
+        f.sort = sp;
+        for (int i = 0; i < RADIX_MAX_PASSES; i++) {
+            f.pass_ticket[i] = tk + 40 + i;
+            f.pass_epoch[i] = pass_epoch[i];
+        }
+        f.fwd = w_fwd;
+        f.rev = w_rev;
+        f.emit = w_emit;
+        f.gather = g;
+        f.barrier = tk + 63;
+        // every CTA must be resident (they meet at grid barriers): never more CTAs than SMs
+        const uint32_t grid = std::max(8u, std::min<uint32_t>((uint32_t)c->sm_count, (uint32_t)((Mmax + 1023) / 1024)));
+        CK(cudaEventRecord(b.ev_sort, st));
+        // a cooperative launch: the grid starts only when all of it fits on the GPU at once, so two
+        // contexts on one GPU cannot end up holding half of the SMs each while both wait at a barrier
+        void *args[] = {&f};
+        CK(cudaLaunchCooperativeKernel(reinterpret_cast<const void *>(fused_tail), dim3(grid), dim3(WIN_THREADS), args,
+                                       GATHER_SMEM, st));
+        c->launches++;
+        if ((rc = dbg_sync(c, "fused_tail"))) return rc;
+        mark(c, "fused tail done");
+        return finish();
+    }
+
+    // ---- stable sort by pid: plan + global digit histograms, then one kernel per pass --------
+    const unsigned sort_blocks = std::max(1u, std::min(max_rtiles, (uint32_t)c->sm_count * 4));
+    sort_prepare<<<sort_blocks, RADIX_THREADS, 0, st>>>(sp);
+    c->launches++;
+    if ((rc = dbg_sync(c, "sort_prepare"))) return rc;
+    if (Mmax == 0) {  // nothing pending, nothing submitted: only the (empty) counts go back
+        copy_u32_kernel<<<1, 1, 0, st>>>(&ds->n_pids_seen, ptr<uint32_t>(c->pt_count));
+        return finish();
+    }
+    for (int i = 0; i < RADIX_MAX_PASSES; i++) {  // passes beyond plan->n_passes return at once
+        sp.pass = i;
+        sp.ticket = tk + 40 + i;
+        sp.epoch = pass_epoch[i];
+        onesweep_pass<<<sort_blocks, RADIX_THREADS, 0, st>>>(sp);
+        c->launches++;
+        if ((rc = dbg_sync(c, "onesweep_pass"))) return rc;
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev_sorted, st));
+    CK(cudaEventRecord(b.ev_sort, st));
+    mark(c, "sort done");
     const uint32_t cap_blocks = (uint32_t)c->sm_count * (WIN_ITEMS >= 16 ? 2 : 4);
 
     // ---- records into the grouped arena: a bandwidth-bound copy on its own stream. It keeps
     // its data in flight in shared memory and takes a bounded number of CTAs per SM, so that the
     // latency-bound scans find registers and warp slots on every SM beside it (a gather that
     // fills the SMs, or scans that fill the register file, serialise the two: profiles/README.md).
-    auto launch_gather = [&]() -> int     {
-        GatherParams g;
-        memset(&g, 0, sizeof(g));
-        g.plan = plan;
-        g.surv_src = ptr<uint32_t>(b.surv_src);
-        g.batch = b.records;
-        g.pend_slot = ptr<uint32_t>(prev.pend_slot);
-        g.pend_cap_prev = (uint32_t)prev.pend_cap;
-        g.prev_arena = ptr<uint8_t>(prev.arena);
-        g.arena = ptr<uint8_t>(b.arena);
-        g.slots = b.slots;
-        g.slot_off = b.slots ? ptr<uint32_t>(b.slot_off) : nullptr;
-        g.slot_ns = b.slots ? ptr<uint8_t>(b.surv_ns) : nullptr;
+    {
         const uint32_t blocks = (uint32_t)std::min<uint64_t>((Mmax + GATHER_WARPS * GATHER_GROUP - 1) / (GATHER_WARPS * GATHER_GROUP),
                                                              (uint64_t)c->sm_count * (uint64_t)c->gather_ctas_per_sm);
-        CK(cudaStreamWaitEvent(c->stream2, c->gather_when == 2 ? c->ev_fwd : c->ev_sorted, 0));
+        CK(cudaStreamWaitEvent(c->stream2, c->ev_sorted, 0));
         mark(c, "gather starts", c->stream2);
-        if (!(c->dbg_skip & 2)) gather_records<<<std::max(1u, blocks), GATHER_THREADS, GATHER_SMEM, c->stream2>>>(g);
+        gather_records<<<std::max(1u, blocks), GATHER_THREADS, GATHER_SMEM, c->stream2>>>(g);
         CK(cudaGetLastError());
         CK(cudaEventRecord(c->ev_gathered, c->stream2));
         mark(c, "gather done", c->stream2);
         c->launches++;
         if ((rc = dbg_sync(c, "gather_records"))) return rc;
-        return CHRONOS_OK;
-    };
-    if (c->gather_when == 0 && (rc = launch_gather())) return rc;
+    }
 
     // ---- flush automaton + chain labeller ----------------------------------------------------
-    w.ticket = tk + 60;
-    w.status = stw;  // 5 words per tile
-    if (!(c->dbg_skip & 4)) group_forward<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, st>>>(w);
+    group_forward<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, st>>>(w_fwd);
     c->launches++;
     CK(cudaGetLastError());
     if ((rc = dbg_sync(c, "group_forward"))) return rc;
     CK(cudaEventRecord(c->ev_fwd, st));
     mark(c, "group_forward done");
 
-    if (c->gather_when != 0 && (rc = launch_gather())) return rc;
-
     // ---- windows in arrival order (stream3) beside the reverse scan (main stream) ----------
-    {
-        WinParams we = w;
-        we.ticket = tk + 62;
-        we.status = stw + 7 * (size_t)tiles_m;  // 1 word per tile
-        CK(cudaStreamWaitEvent(c->stream3, c->ev_fwd, 0));
-        if (!(c->dbg_skip & 8)) emit_ordered<<<std::max(1u, std::min(tiles_s, cap_blocks)), WIN_THREADS, 0, c->stream3>>>(we);
-        CK(cudaGetLastError());
-        CK(cudaEventRecord(c->ev_emitted, c->stream3));
-        mark(c, "emit_ordered done", c->stream3);
-        c->launches++;
-        if ((rc = dbg_sync(c, "emit_ordered"))) return rc;
-    }
-    w.ticket = tk + 61;
-    w.status = stw + 5 * (size_t)tiles_m;  // 2 words per tile
-    if (!(c->dbg_skip & 16)) window_reverse<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, st>>>(w);
+    CK(cudaStreamWaitEvent(c->stream3, c->ev_fwd, 0));
+    emit_ordered<<<std::max(1u, std::min(tiles_s, cap_blocks)), WIN_THREADS, 0, c->stream3>>>(w_emit);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev_emitted, c->stream3));
+    mark(c, "emit_ordered done", c->stream3);
+    c->launches++;
+    if ((rc = dbg_sync(c, "emit_ordered"))) return rc;
+    window_reverse<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, st>>>(w_rev);
     c->launches++;
     CK(cudaGetLastError());
     if ((rc = dbg_sync(c, "window_reverse"))) return rc;
@@ -883,9 +913,7 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     CK(cudaStreamWaitEvent(st, c->ev_emitted, 0));
     CK(cudaStreamWaitEvent(st, c->ev_gathered, 0));
     mark(c, "all joined");
-    CK(cudaMemcpyAsync(b.h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, st));
-    CK(cudaEventRecord(b.ev_end, st));
-    return CHRONOS_OK;
+    return finish();
 }
 
 // ---- batch bookkeeping --------------------------------------------------------------------------
@@ -1142,9 +1170,8 @@ int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pen
     // per 10 M events, depending on what the previous kernels left in L2; at 18 it is steady at
     // 0.50 ms, at 17 at 0.515 ms (sweep in profiles/README.md, "filter residency").
     c->filter_ctas_per_sm = getenv("CHRONOS_FILTER_CTAS") ? atoi(getenv("CHRONOS_FILTER_CTAS")) : -1;
-    c->dbg_skip = getenv("CHRONOS_DBG_SKIP") ? atoi(getenv("CHRONOS_DBG_SKIP")) : 0;
-    const char *gf = getenv("CHRONOS_GATHER_WHEN");
-    c->gather_when = gf ? atoi(gf) : 0;
+    // (CHRONOS_FUSED_MAX=0 switches the one-launch tail off)
+    c->fused_max = getenv("CHRONOS_FUSED_MAX") ? strtoull(getenv("CHRONOS_FUSED_MAX"), nullptr, 10) : 262144ull;
     const bool gather_low = getenv("CHRONOS_GATHER_LOW") != nullptr;
     c->trace = getenv("CHRONOS_TRACE") != nullptr;
     auto boot = [&]() -> int {
@@ -2236,7 +2263,6 @@ int chronos_filter_noalloc(int device, void *stream, const void *records, uint64
         fp.out_count = hdr + 2;
         fp.key_or = hdr + 3;
         fp.key_and = hdr + 4;
-        fp.dbg_nowrite = 0;
         filter_kernel<1><<<std::min<uint32_t>(fp.tile_end, (uint32_t)grid_cap), FILTER_TILE, filter_smem_bytes<1>(), st>>>(fp);
         ScanParams sp;
         sp.data = fp.tile_count;

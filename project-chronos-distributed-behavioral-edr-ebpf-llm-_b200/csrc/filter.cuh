@@ -48,7 +48,6 @@ struct FilterParams {
     uint32_t *out_count;     // total survivors (atomicAdd, one per CTA)
     uint32_t *key_or;        // OR / AND over survivor pids (radix pass planning)
     uint32_t *key_and;
-    uint32_t dbg_nowrite;    // experiments only: 1 = no per-survivor stores, 2 = no per-tile count store, 3 = neither
 };
 
 // ---- needle tests on one 4-byte window `t` (bytes k..k+3) and the byte after it ------
@@ -508,7 +507,7 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
         const uint32_t kb = __ballot_sync(FULL, keep);
         if (kb) {
             const uint32_t rank = __popc(kb & lanemask_lt());
-            if (keep && !(p.dbg_nowrite & 1u)) {
+            if (keep) {
                 const size_t slot = (size_t)tile * FILTER_TILE + rank;
                 p.sp_key[slot] = pid;
                 p.sp_src[slot] = (uint32_t)first + lane;
@@ -518,7 +517,7 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
             k_or |= __reduce_or_sync(FULL, keep ? pid : 0u);
             k_and &= __reduce_and_sync(FULL, keep ? pid : 0xffffffffu);
         }
-        if (lane == 0 && !(p.dbg_nowrite & 2u)) p.tile_count[tile] = __popc(kb);
+        if (lane == 0) p.tile_count[tile] = __popc(kb);
         cta_total += __popc(kb);
     }
     if (lane == 0 && cta_total) {

@@ -112,7 +112,7 @@ __device__ __forceinline__ void make_plan(const SortParams &p, Plan &pl) {
 
 // Kernel 1 of the sort: the plan, and the GLOBAL digit histogram of every pass in one read of
 // the keys (the passes then need no histogram kernel and no table scan of their own).
-__global__ void __launch_bounds__(RADIX_THREADS) sort_prepare(const SortParams p) {
+__device__ __forceinline__ void sort_prepare_body(const SortParams &p) {
     __shared__ Plan pl;
     __shared__ uint32_t h[RADIX_MAX_PASSES][RADIX_BINS];
     if (threadIdx.x == 0) {
@@ -145,30 +145,35 @@ __global__ void __launch_bounds__(RADIX_THREADS) sort_prepare(const SortParams p
     }
 }
 
+__global__ void __launch_bounds__(RADIX_THREADS) sort_prepare(const SortParams p) { sort_prepare_body(p); }
+
 // Kernel 2..: one radix pass in ONE kernel. Tiles are taken in ticket order; a tile counts its
 // digits, publishes the counts, learns how many keys with the same digit precede it from its
 // predecessors' status words (decoupled look-back, one chain per digit = one per thread) and
 // scatters: stable, because a tile's keys go behind those of every earlier tile and the
 // placement inside the tile is in index order.
 // status word: [63:34] epoch | [33:32] ST_* | [31:0] count
-__global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams p) {
+// (pass, ticket and epoch are explicit arguments: the fused tail kernel runs all passes of one
+//  parameter block)
+__device__ __forceinline__ void onesweep_pass_body(const SortParams &p, const int pass, uint32_t *const ticket,
+                                                   const uint32_t epoch) {
     __shared__ uint32_t whist[RADIX_WARPS][RADIX_BINS];
     __shared__ uint32_t gbase[RADIX_BINS];
     __shared__ uint32_t warp_tot[RADIX_WARPS];
     __shared__ uint32_t s_tile;
     const Plan &pl = *p.plan;
-    if ((uint32_t)p.pass >= pl.n_passes) return;
+    if ((uint32_t)pass >= pl.n_passes) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const bool odd = p.pass & 1;
-    const bool first = p.pass == 0;
+    const bool odd = pass & 1;
+    const bool first = pass == 0;
     const uint32_t *keys_in = odd ? p.keyB : p.keyA;   // (pass 0 reads the entries instead)
     const uint32_t *vals_in = first ? nullptr : (odd ? p.valB : p.valA);
     uint32_t *keys_out = odd ? p.keyA : p.keyB;
     uint32_t *vals_out = odd ? p.valA : p.valB;
-    const uint32_t n = pl.M, n_tiles = pl.n_tiles, shift = pl.shift[p.pass], mask = pl.mask[p.pass], split = pl.P;
-    const uint64_t tag = (uint64_t)p.epoch << 34;
+    const uint32_t n = pl.M, n_tiles = pl.n_tiles, shift = pl.shift[pass], mask = pl.mask[pass], split = pl.P;
+    const uint64_t tag = (uint64_t)epoch << 34;
     {   // where digit d starts in the output: exclusive scan of the global digit counts
-        const uint32_t c = p.ghist[p.pass * RADIX_BINS + tid];
+        const uint32_t c = p.ghist[pass * RADIX_BINS + tid];
         uint32_t inc = c;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -185,7 +190,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
     }
     while (true) {
         __syncthreads();
-        if (tid == 0) s_tile = atomicAdd(p.ticket, 1u);
+        if (tid == 0) s_tile = atomicAdd(ticket, 1u);
         for (int i = tid; i < RADIX_WARPS * RADIX_BINS; i += RADIX_THREADS) (&whist[0][0])[i] = 0;
         __syncthreads();
         const uint32_t tile = s_tile;
@@ -244,7 +249,7 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
                 for (int k = 0; k < LB; k++) {
                     if (k < nb && used == k && !done) {
                         const uint32_t stt = (uint32_t)(v[k] >> 32) & 3u;
-                        if ((v[k] >> 34) == p.epoch && stt != ST_NONE) {
+                        if ((v[k] >> 34) == epoch && stt != ST_NONE) {
                             excl += (uint32_t)v[k];
                             used = k + 1;
                             done = stt == ST_PREFIX;
@@ -293,6 +298,10 @@ __global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams 
             }
         }
     }
+}
+
+__global__ void __launch_bounds__(RADIX_THREADS) onesweep_pass(const SortParams p) {
+    onesweep_pass_body(p, p.pass, p.ticket, p.epoch);
 }
 
 // Exclusive scan of n counters in place: persistent CTAs, 4096 counters per tile, chained

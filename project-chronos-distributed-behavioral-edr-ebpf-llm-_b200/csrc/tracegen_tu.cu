@@ -1,13 +1,11 @@
 // tracegen_tu.cu -- the synthetic trace generator as a translation unit (and therefore a CUDA
 // module) of its own.
 //
-// Why it is not part of chronos.cu: gen_record inlines to about 218 KB of machine code. With it
-// the module that holds filter_kernel grew past ~552 KB of code, and from that size on the filter
-// -- 2812 single-warp CTAs walking 23 KB of code in different phases, so it lives on instruction
-// fetch -- ran 1.75x slower (0.87 ms instead of 0.49 ms per 10 M events) although not one of its
-// instructions had changed: measured by bisecting builds, then by removing 24 KB of unrelated
-// code from the slow build (profiles/README.md, "module size"). _build.py checks the size of the
-// filter's module after every build.
+// gen_record inlines to about 218 KB of machine code, as much as all other kernels together; it
+// is benchmark scaffolding, not the hot path, and compiles separately so that a change to the
+// kernels does not pay for it. (While the filter's bistable timing was hunted it was suspected of
+// pushing the filter's module over a code-size threshold; that turned out to be chance, see
+// profiles/README.md.)
 #include <cuda_runtime.h>
 #include <stdint.h>
 

@@ -121,7 +121,7 @@ __device__ __forceinline__ Fn3 chain_event(uint32_t meta) {
 // forward. Flush automaton: E=0 / N=1, marker b = start position of the current group,
 // counter a = windows flushed so far. Chain DFA: counter a = chain-complete events so far.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) {
+__device__ __forceinline__ void group_forward_body(const WinParams &p) {
     const uint32_t M = p.plan ? p.plan->M : p.M, P = p.plan ? p.plan->P : p.P;
     const uint32_t *const skey = p.plan ? p.plan->skey : p.skey;
     const uint32_t *const sval = p.plan ? p.plan->sval : p.sval;
@@ -271,11 +271,13 @@ __global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) 
     }
 }
 
+__global__ void __launch_bounds__(WIN_THREADS) group_forward(const WinParams p) { group_forward_body(p); }
+
 // ---------------------------------------------------------------------------------------
 // reverse: walking positions downward, state C=0 (group closed by a later flush) /
 // O=1 (open: reaches its PID's end unflushed => stays in process_memory).
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p) {
+__device__ __forceinline__ void window_reverse_body(const WinParams &p) {
     const uint32_t M = p.plan ? p.plan->M : p.M, P = p.plan ? p.plan->P : p.P;
     const uint32_t *const skey = p.plan ? p.plan->skey : p.skey;
     const uint32_t *const sval = p.plan ? p.plan->sval : p.sval;
@@ -354,11 +356,13 @@ __global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p)
     }
 }
 
+__global__ void __launch_bounds__(WIN_THREADS) window_reverse(const WinParams p) { window_reverse_body(p); }
+
 // ---------------------------------------------------------------------------------------
 // ordered emission: compaction of entry_out over this batch's survivors, whose entry order
 // IS arrival order: windows by trigger arrival (:143-147) and chain matches by arrival.
 // ---------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) {
+__device__ __forceinline__ void emit_ordered_body(const WinParams &p) {
     const uint32_t M = p.plan ? p.plan->M : p.M, P = p.plan ? p.plan->P : p.P;
     __shared__ uint32_t warp_w[WIN_THREADS / 32], warp_c[WIN_THREADS / 32];
     __shared__ uint32_t s_tile, s_base_w, s_base_c;
@@ -469,6 +473,8 @@ __global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) {
     }
 }
 
+__global__ void __launch_bounds__(WIN_THREADS) emit_ordered(const WinParams p) { emit_ordered_body(p); }
+
 // ---------------------------------------------------------------------------------------
 // gather: arena[pos] = record of entry sval[pos]; every surviving event is written
 // exactly once (the 288*S term of the algorithmic bytes).
@@ -512,8 +518,7 @@ __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-__global__ void __launch_bounds__(GATHER_THREADS) gather_records(const GatherParams g) {
-    extern __shared__ uint4 gather_smem[];
+__device__ __forceinline__ void gather_records_body(const GatherParams &g, uint4 *gather_smem) {
     const uint32_t gM = g.plan ? g.plan->M : g.M, gP = g.plan ? g.plan->P : g.P;
     const uint32_t *const gsval = g.plan ? g.plan->sval : g.sval;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -579,6 +584,59 @@ __global__ void __launch_bounds__(GATHER_THREADS) gather_records(const GatherPar
         prev = base;
         s ^= 1;
     }
+}
+
+__global__ void __launch_bounds__(GATHER_THREADS) gather_records(const GatherParams g) {
+    extern __shared__ uint4 gather_smem_dyn[];
+    gather_records_body(g, gather_smem_dyn);
+}
+
+// ---------------------------------------------------------------------------------------
+// The whole tail in ONE launch, for batches small enough that launches, not bytes, are what
+// they cost (a 64 K-event micro-batch groups about 12 K entries: every kernel above is a few
+// microseconds of work behind a launch and a dependency). The kernel bodies are the ones
+// above, run one after the other by a grid of at most one CTA per SM, with a grid-wide barrier
+// where a phase needs everything of the previous one; window_reverse, emit_ordered and
+// gather_records only depend on group_forward and follow without a barrier between them.
+// All CTAs must be resident at the same time (they spin at the barriers): the host launches
+// no more CTAs than there are SMs.
+// ---------------------------------------------------------------------------------------
+struct FusedTailParams {
+    SortParams sort;
+    uint32_t *pass_ticket[RADIX_MAX_PASSES];
+    uint32_t pass_epoch[RADIX_MAX_PASSES];
+    WinParams fwd, rev, emit;
+    GatherParams gather;
+    uint32_t *barrier;  // zero at launch
+};
+
+__device__ __forceinline__ void grid_barrier(uint32_t *counter, uint32_t target) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        atomicAdd(counter, 1u);
+        while (ld_acquire_u32(counter) < target) {
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
+
+__global__ void __launch_bounds__(WIN_THREADS) fused_tail(const FusedTailParams f) {
+    extern __shared__ uint4 fused_smem_dyn[];
+    uint32_t target = 0;
+    sort_prepare_body(f.sort);
+    grid_barrier(f.barrier, target += gridDim.x);
+    const uint32_t n_passes = f.sort.plan->n_passes;
+    for (uint32_t i = 0; i < n_passes; i++) {
+        onesweep_pass_body(f.sort, (int)i, f.pass_ticket[i], f.pass_epoch[i]);
+        grid_barrier(f.barrier, target += gridDim.x);
+    }
+    group_forward_body(f.fwd);
+    grid_barrier(f.barrier, target += gridDim.x);
+    window_reverse_body(f.rev);
+    emit_ordered_body(f.emit);
+    gather_records_body(f.gather, fused_smem_dyn);
 }
 
 }  // namespace chronos
