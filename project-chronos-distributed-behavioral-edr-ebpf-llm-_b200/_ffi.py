@@ -58,6 +58,8 @@ SIGNATURES = {
     "chronos_destroy": (c_int, [c_void_p]),
     "chronos_reset": (c_int, [c_void_p]),
     "chronos_set_overlap": (c_int, [c_void_p, c_int]),
+    "chronos_set_host_trim": (c_int, [c_void_p, c_int]),
+    "chronos_last_upload_bytes": (c_int, [c_void_p, POINTER(c_uint64)]),
     "chronos_last_error": (c_char_p, [c_void_p]),
     "chronos_submit": (c_int, [c_void_p, c_void_p, c_uint64, c_uint64]),
     "chronos_fetch": (c_int, [c_void_p, POINTER(Counts)]),

@@ -28,6 +28,8 @@
 #include <algorithm>
 #include <mutex>
 #include <new>
+#include <atomic>
+#include <thread>
 #include <vector>
 
 #include "chronos.h"
@@ -167,6 +169,18 @@ struct chronos_ctx {
     uint32_t x_epoch = 0;
     uint64_t x_launches = 0;
     uint64_t x_timeout_ns = 20ull * 1000000000ull;
+
+    // host-side trimming of uploads (chronos_set_host_trim): per worker thread a stream, two pinned and
+    // two device staging buffers and the events that guard their reuse
+    int trim_threads = 0;
+    uint64_t upload_bytes = 0;  // bytes the last host-memory submit sent over PCIe
+    struct TrimWorker {
+        cudaStream_t stream = nullptr;
+        void *pinned[2] = {nullptr, nullptr};
+        void *dev[2] = {nullptr, nullptr};
+        cudaEvent_t done[2] = {nullptr, nullptr};
+    };
+    std::vector<TrimWorker> trim;
 
     uint64_t launches = 0;  // of the submit being enqueued
     int filter_variant = 0;
@@ -1256,10 +1270,141 @@ int chronos_destroy(chronos_ctx *c) {
         if (e) cudaEventDestroy(e);
     for (int i = 0; i < 24; i++)
         if (c->tev[i]) cudaEventDestroy(c->tev[i]);
+    for (auto &w : c->trim) {
+        for (int k = 0; k < 2; k++) {
+            if (w.pinned[k]) cudaFreeHost(w.pinned[k]);
+            if (w.dev[k]) cudaFree(w.dev[k]);
+            if (w.done[k]) cudaEventDestroy(w.done[k]);
+        }
+        if (w.stream) cudaStreamDestroy(w.stream);
+    }
     for (cudaStream_t s : {c->stream, c->stream_f, c->stream2, c->stream3, c->dl_stream})
         if (s) cudaStreamDestroy(s);
     cudaGetLastError();
     delete c;
+    return CHRONOS_OK;
+}
+
+// ---- trimmed upload -------------------------------------------------------------------------
+// A record in host memory is mostly NUL padding (a 40-byte path in a 256-byte field). With
+// chronos_set_host_trim the host threads cut every record, losslessly, to the 16-byte chunks that
+// hold anything -- chunks 0, 1 and 17 always, the argv chunks up to the last one that is not all
+// zero -- and only those cross PCIe (about a third of the bytes); expand_kernel rebuilds the
+// 288-byte records in the staging buffer, byte for byte, and the pipeline runs on them unchanged.
+// All DECISIONS about a record stay on the GPU; the host only drops zeros.
+constexpr uint64_t TRIM_CHUNK = 32768;  // records per unit of work of a host thread
+constexpr size_t TRIM_OFF_BYTES = (TRIM_CHUNK + 64) * 4;                 // u32 slot offset per record (+1)
+constexpr size_t TRIM_BUF_BYTES = TRIM_OFF_BYTES + TRIM_CHUNK * CH_REC_BYTES;  // worst case: nothing to drop
+
+// dst[r] = record r of the chunk: slot order 0, 1, 17, 2.. (the transport form of filter.cuh)
+__global__ void __launch_bounds__(256) expand_kernel(const uint8_t *stage, uint32_t cnt, uint8_t *dst) {
+    const uint32_t *off = reinterpret_cast<const uint32_t *>(stage);
+    const uint4 *slots = reinterpret_cast<const uint4 *>(stage + TRIM_OFF_BYTES);
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t base = warp * 16; base < cnt; base += n_warps * 16) {
+        const uint32_t m = min(16u, cnt - base);
+        uint32_t o = 0, ns = 0;
+        if ((uint32_t)lane < m) {
+            o = off[base + lane];
+            ns = off[base + lane + 1] - o;
+        }
+        uint4 *d = reinterpret_cast<uint4 *>(dst + (size_t)base * CH_REC_BYTES);
+        uint4 v[9];
+#pragma unroll
+        for (int it = 0; it < 9; it++) {
+            const uint32_t c = it * 32 + lane, r = c / CH_REC_CHUNKS, ch = c - r * CH_REC_CHUNKS;
+            const uint32_t ro = __shfl_sync(0xffffffffu, o, (int)(r & 31u)), rn = __shfl_sync(0xffffffffu, ns, (int)(r & 31u));
+            const uint32_t sl = ch < 2 ? ch : (ch == 17 ? 2u : ch + 1u);
+            v[it] = make_uint4(0u, 0u, 0u, 0u);
+            if (r < m && sl < rn) v[it] = __ldg(slots + ro + sl);
+        }
+#pragma unroll
+        for (int it = 0; it < 9; it++) {
+            const uint32_t c = it * 32 + lane;
+            if (c < m * CH_REC_CHUNKS) d[c] = v[it];
+        }
+    }
+}
+
+// one chunk on the host: offsets and slots into `out` (TRIM_BUF_BYTES); returns the bytes to copy
+static size_t trim_chunk(const uint8_t *recs, uint32_t cnt, uint8_t *out) {
+    uint32_t *off = reinterpret_cast<uint32_t *>(out);
+    uint8_t *slots = out + TRIM_OFF_BYTES;
+    uint32_t s = 0;
+    for (uint32_t i = 0; i < cnt; i++) {
+        const uint8_t *r = recs + (size_t)i * CH_REC_BYTES;
+        int last = 1;  // last argv chunk (2..16) that is not all zero
+        for (int ch = 16; ch >= 2; ch--) {
+            uint64_t a, b2;
+            memcpy(&a, r + ch * 16, 8);
+            memcpy(&b2, r + ch * 16 + 8, 8);
+            if ((a | b2) != 0) { last = ch; break; }
+        }
+        off[i] = s;
+        uint8_t *o = slots + (size_t)s * 16;
+        memcpy(o, r, 32);
+        memcpy(o + 32, r + 272, 16);
+        memcpy(o + 48, r + 32, (size_t)(last - 1) * 16);
+        s += 2u + (uint32_t)last;
+    }
+    off[cnt] = s;
+    return TRIM_OFF_BYTES + (size_t)s * 16;
+}
+
+static int trim_pools(chronos_ctx *c) {
+    if ((int)c->trim.size() == c->trim_threads) return CHRONOS_OK;
+    c->trim.resize((size_t)c->trim_threads);
+    for (auto &w : c->trim) {
+        if (w.stream) continue;
+        CK(cudaStreamCreateWithFlags(&w.stream, cudaStreamNonBlocking));
+        for (int k = 0; k < 2; k++) {
+            CK(cudaMallocHost(&w.pinned[k], TRIM_BUF_BYTES));
+            CK(cudaMalloc(&w.dev[k], TRIM_BUF_BYTES));
+            CK(cudaEventCreateWithFlags(&w.done[k], cudaEventDisableTiming));
+        }
+    }
+    return CHRONOS_OK;
+}
+
+// records (host memory) -> d_batch through the trimmed form, host threads working in parallel;
+// on return everything is queued and stream `st` waits for it
+static int trimmed_upload(chronos_ctx *c, BatchSet &b, const uint8_t *records, uint64_t n, cudaStream_t st) {
+    int rc;
+    if ((rc = trim_pools(c))) return rc;
+    const uint64_t n_chunks = (n + TRIM_CHUNK - 1) / TRIM_CHUNK;
+    const int T = c->trim_threads;
+    uint8_t *dst = ptr<uint8_t>(b.d_batch);
+    // the worker streams must not run ahead of what `st` is ordered behind (the last readers of this set)
+    CK(cudaEventRecord(c->ev_tailinit, st));
+    for (auto &w : c->trim) CK(cudaStreamWaitEvent(w.stream, c->ev_tailinit, 0));
+    std::atomic<uint64_t> next{0}, sent{0};
+    std::atomic<int> failed{0};
+    const int device = c->device;
+    auto work = [&](int t) {
+        if (cudaSetDevice(device) != cudaSuccess) { failed = 1; return; }
+        chronos_ctx::TrimWorker &w = c->trim[(size_t)t];
+        int k = 0;
+        for (uint64_t ch = next.fetch_add(1); ch < n_chunks; ch = next.fetch_add(1), k ^= 1) {
+            const uint64_t first = ch * TRIM_CHUNK;
+            const uint32_t cnt = (uint32_t)std::min<uint64_t>(TRIM_CHUNK, n - first);
+            if (cudaEventSynchronize(w.done[k]) != cudaSuccess) { failed = 1; return; }  // this buffer pair is free again
+            const size_t bytes = trim_chunk(records + first * CH_REC_BYTES, cnt, static_cast<uint8_t *>(w.pinned[k]));
+            sent += bytes;
+            if (cudaMemcpyAsync(w.dev[k], w.pinned[k], bytes, cudaMemcpyHostToDevice, w.stream) != cudaSuccess) { failed = 1; return; }
+            expand_kernel<<<64, 256, 0, w.stream>>>(static_cast<const uint8_t *>(w.dev[k]), cnt, dst + first * CH_REC_BYTES);
+            if (cudaEventRecord(w.done[k], w.stream) != cudaSuccess) { failed = 1; return; }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back(work, t);
+    work(0);
+    for (auto &x : th) x.join();
+    if (failed) return fail(c, CHRONOS_E_CUDA, "trimmed upload: %s", cudaGetErrorString(cudaGetLastError()));
+    for (auto &w : c->trim)
+        for (int k = 0; k < 2; k++) CK(cudaStreamWaitEvent(st, w.done[k], 0));
+    c->launches += n_chunks;
+    c->upload_bytes = sent.load();
     return CHRONOS_OK;
 }
 
@@ -1274,8 +1419,12 @@ static int stage_records(chronos_ctx *c, BatchSet &b, const void *records, uint6
     }
     int rc;
     if ((rc = ensure(c, b.d_batch, c->max_batch * CH_REC_BYTES))) return rc;
-    CK(cudaMemcpyAsync(b.d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, st));
     *d_recs = ptr<uint8_t>(b.d_batch);
+    if (c->trim_threads > 0 && n >= 4 * TRIM_CHUNK) {
+        return trimmed_upload(c, b, static_cast<const uint8_t *>(records), n, st);
+    }
+    CK(cudaMemcpyAsync(b.d_batch.p, records, n * CH_REC_BYTES, cudaMemcpyHostToDevice, st));
+    c->upload_bytes = n * CH_REC_BYTES;
     return CHRONOS_OK;
 }
 
@@ -1836,6 +1985,32 @@ int chronos_last_stage_times(chronos_ctx *c, float *ms, uint32_t cap) {
     if (rc) return rc;
     if (!ms) return CHRONOS_E_ARG;
     for (uint32_t i = 0; i < cap && i < 6; i++) ms[i] = bp->stage_ms[i];
+    return CHRONOS_OK;
+}
+
+int chronos_set_host_trim(chronos_ctx *c, int threads) {
+    if (!c || threads < 0 || threads > 256) return CHRONOS_E_ARG;
+    CK(cudaSetDevice(c->device));
+    CK(cudaDeviceSynchronize());  // (nothing may be using the worker buffers while their number changes)
+    if (threads < (int)c->trim.size()) {
+        for (size_t t = (size_t)threads; t < c->trim.size(); t++) {
+            auto &w = c->trim[t];
+            for (int k = 0; k < 2; k++) {
+                if (w.pinned[k]) cudaFreeHost(w.pinned[k]);
+                if (w.dev[k]) cudaFree(w.dev[k]);
+                if (w.done[k]) cudaEventDestroy(w.done[k]);
+            }
+            if (w.stream) cudaStreamDestroy(w.stream);
+        }
+        c->trim.resize((size_t)threads);
+    }
+    c->trim_threads = threads;
+    return threads ? trim_pools(c) : CHRONOS_OK;
+}
+
+int chronos_last_upload_bytes(chronos_ctx *c, uint64_t *bytes) {
+    if (!c || !bytes) return CHRONOS_E_ARG;
+    *bytes = c->upload_bytes;
     return CHRONOS_OK;
 }
 

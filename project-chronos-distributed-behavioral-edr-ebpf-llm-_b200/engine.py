@@ -90,6 +90,16 @@ class Context:
         submit order: batches already submitted finish against the old state and stay fetchable."""
         self._check(self._L.chronos_reset(self._h))
 
+    def set_host_trim(self, threads):
+        """threads > 0: large submits from host memory are cut to their non-zero 16-byte chunks by that
+        many host threads before they cross PCIe and rebuilt on the GPU (lossless); 0: off."""
+        self._check(self._L.chronos_set_host_trim(self._h, int(threads)))
+
+    def last_upload_bytes(self):
+        n = c_uint64()
+        self._check(self._L.chronos_last_upload_bytes(self._h, byref(n)))
+        return int(n.value)
+
     def set_overlap(self, on):
         """False: batches run strictly one after the other on the GPU even when submitted ahead."""
         self._check(self._L.chronos_set_overlap(self._h, 1 if on else 0))

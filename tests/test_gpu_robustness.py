@@ -272,3 +272,27 @@ def test_window_digests_see_content_and_ignore_bytes_behind_the_nul():
     assert digs[2][0] == 1                                        # "/tmp/cab" no longer triggers: one window less
     assert digs[3][0] == 2 and digs[3][1][0] != digs[0][1][0]     # one more byte in a path: another digest
     assert digs[3][1][1] == digs[0][1][1]                         # ... while the untouched window keeps its digest
+
+
+def test_trimmed_host_upload_is_lossless():
+    """chronos_set_host_trim: host threads cut every record to its non-zero 16-byte chunks, the GPU
+    rebuilds it. The result -- survivors, windows, the window records BYTE FOR BYTE, the pending
+    state -- must be what the plain upload and the oracle give, also for records with garbage
+    behind a NUL, fields without a NUL and bytes in the very last argv chunk."""
+    import chronos_b200
+    from chronos_b200 import tracegen
+
+    rows = tracegen.generate_host(tracegen.WORKLOADS["skewed_zipf_chains"], n=300_000).copy()
+    rng = np.random.default_rng(7)
+    for i in rng.integers(0, len(rows), 400):           # garbage everywhere behind the first bytes
+        rows[i, 60:276] = rng.integers(1, 256, 216, dtype=np.uint8)
+    for i in rng.integers(0, len(rows), 200):           # a lone byte in the last argv chunk
+        rows[i, 20 + 250] = 0x41
+    rows[5] = 0xFF
+    rows[6] = 0
+    eng, tr = coracle.COracle(), Trace()
+    with chronos_b200.Context(device=0, max_batch_events=len(rows)) as ctx:
+        for threads in (3, 0, 8):
+            ctx.set_host_trim(threads)
+            base = 0 if threads == 3 else (len(rows) if threads == 0 else 2 * len(rows))
+            compare_batch(ctx, eng, tr, rows, base)
