@@ -706,7 +706,7 @@ class SingleGpuRunner:
         # there are cores to spare for it; both figures are reported, the better one is `value`
         threads = os.cpu_count() or 1
         dt_trim = up_trim = None
-        if threads >= 10 and not os.environ.get("CHRONOS_BENCH_NO_TRIM"):
+        if threads >= 2 and not os.environ.get("CHRONOS_BENCH_NO_TRIM"):
             self.ctx.set_host_trim(threads)
             loop()
             dt_trim, lay, c, up_trim = loop()
@@ -727,8 +727,8 @@ class SingleGpuRunner:
                 "host_trim": (None if dt_trim is None else
                               {"value": n / dt_trim, "ms_per_step": 1e3 * dt_trim, "host_threads": threads,
                                "h2d_bytes_per_step": int(up_trim),
-                               "note": "host threads drop the NUL padding of every record before PCIe (lossless), "
-                                       "a kernel rebuilds the records"}),
+                               "note": "host threads drop the NUL padding of the records they take (lossless, a kernel "
+                                       "rebuilds them) while the copy engine moves the rest of the batch as it is"}),
                 "upload": "host_trim" if trimmed else "plain_copy",
                 "path": "Context.submit(pinned host records) -> fetch -> download_begin(pinned host results: survivors, "
                         "windows, window records); the download of step k overlaps the upload of step k+1, all "

@@ -181,6 +181,9 @@ struct chronos_ctx {
         cudaEvent_t done[2] = {nullptr, nullptr};
     };
     std::vector<TrimWorker> trim;
+    cudaStream_t trim_dma = nullptr;    // the copy engine's share of a trimmed upload
+    cudaEvent_t ev_trim_dma = nullptr;
+    bool trim_no_dma = false;           // CHRONOS_TRIM_NO_DMA: the threads take everything
 
     uint64_t launches = 0;  // of the submit being enqueued
     int filter_variant = 0;
@@ -1278,6 +1281,8 @@ int chronos_destroy(chronos_ctx *c) {
         }
         if (w.stream) cudaStreamDestroy(w.stream);
     }
+    if (c->trim_dma) cudaStreamDestroy(c->trim_dma);
+    if (c->ev_trim_dma) cudaEventDestroy(c->ev_trim_dma);
     for (cudaStream_t s : {c->stream, c->stream_f, c->stream2, c->stream3, c->dl_stream})
         if (s) cudaStreamDestroy(s);
     cudaGetLastError();
@@ -1353,6 +1358,11 @@ static size_t trim_chunk(const uint8_t *recs, uint32_t cnt, uint8_t *out) {
 }
 
 static int trim_pools(chronos_ctx *c) {
+    if (!c->trim_dma) {
+        CK(cudaStreamCreateWithFlags(&c->trim_dma, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&c->ev_trim_dma, cudaEventDisableTiming));
+        c->trim_no_dma = getenv("CHRONOS_TRIM_NO_DMA") != nullptr;
+    }
     if ((int)c->trim.size() == c->trim_threads) return CHRONOS_OK;
     c->trim.resize((size_t)c->trim_threads);
     for (auto &w : c->trim) {
@@ -1367,8 +1377,13 @@ static int trim_pools(chronos_ctx *c) {
     return CHRONOS_OK;
 }
 
-// records (host memory) -> d_batch through the trimmed form, host threads working in parallel;
-// on return everything is queued and stream `st` waits for it
+// records (host memory) -> d_batch, host threads and the copy engine working side by side: the
+// threads take chunks from the FRONT of the batch, trim them and send the trimmed form; the calling
+// thread takes pieces from the BACK and copies them as they are (cudaMemcpyAsync), one piece at a
+// time, claiming the next when the previous one has arrived. Both ends move until they meet, so
+// the split follows what cores and bus deliver (pageable memory, which the driver copies slowly
+// and synchronously, simply leaves more to the threads). On return everything is queued and
+// stream `st` waits for it.
 static int trimmed_upload(chronos_ctx *c, BatchSet &b, const uint8_t *records, uint64_t n, cudaStream_t st) {
     int rc;
     if ((rc = trim_pools(c))) return rc;
@@ -1378,15 +1393,35 @@ static int trimmed_upload(chronos_ctx *c, BatchSet &b, const uint8_t *records, u
     // the worker streams must not run ahead of what `st` is ordered behind (the last readers of this set)
     CK(cudaEventRecord(c->ev_tailinit, st));
     for (auto &w : c->trim) CK(cudaStreamWaitEvent(w.stream, c->ev_tailinit, 0));
-    std::atomic<uint64_t> next{0}, sent{0};
+    CK(cudaStreamWaitEvent(c->trim_dma, c->ev_tailinit, 0));
+    std::atomic<uint64_t> range{n_chunks};  // chunks [lo, hi) are unclaimed: lo in the high, hi in the low 32 bits
+    std::atomic<uint64_t> sent{0};
     std::atomic<int> failed{0};
     const int device = c->device;
+    auto take_front = [&]() -> int64_t {
+        uint64_t r = range.load();
+        while (true) {
+            const uint64_t lo = r >> 32, hi = r & 0xffffffffu;
+            if (lo >= hi) return -1;
+            if (range.compare_exchange_weak(r, ((lo + 1) << 32) | hi)) return (int64_t)lo;
+        }
+    };
+    auto take_back = [&](uint64_t want, uint64_t &first, uint64_t &cnt) -> bool {
+        uint64_t r = range.load();
+        while (true) {
+            const uint64_t lo = r >> 32, hi = r & 0xffffffffu;
+            if (lo >= hi) return false;
+            cnt = std::min(want, hi - lo);
+            first = hi - cnt;
+            if (range.compare_exchange_weak(r, (lo << 32) | first)) return true;
+        }
+    };
     auto work = [&](int t) {
         if (cudaSetDevice(device) != cudaSuccess) { failed = 1; return; }
         chronos_ctx::TrimWorker &w = c->trim[(size_t)t];
         int k = 0;
-        for (uint64_t ch = next.fetch_add(1); ch < n_chunks; ch = next.fetch_add(1), k ^= 1) {
-            const uint64_t first = ch * TRIM_CHUNK;
+        for (int64_t ch = take_front(); ch >= 0; ch = take_front(), k ^= 1) {
+            const uint64_t first = (uint64_t)ch * TRIM_CHUNK;
             const uint32_t cnt = (uint32_t)std::min<uint64_t>(TRIM_CHUNK, n - first);
             if (cudaEventSynchronize(w.done[k]) != cudaSuccess) { failed = 1; return; }  // this buffer pair is free again
             const size_t bytes = trim_chunk(records + first * CH_REC_BYTES, cnt, static_cast<uint8_t *>(w.pinned[k]));
@@ -1397,12 +1432,28 @@ static int trimmed_upload(chronos_ctx *c, BatchSet &b, const uint8_t *records, u
         }
     };
     std::vector<std::thread> th;
-    for (int t = 1; t < T; t++) th.emplace_back(work, t);
-    work(0);
+    for (int t = 0; t < T; t++) th.emplace_back(work, t);
+    {   // the copy engine's share, paced by completion
+        uint64_t first, cnt, pieces = 0;
+        while (!c->trim_no_dma && take_back(4, first, cnt)) {
+            const uint64_t r0 = first * TRIM_CHUNK, r1 = std::min<uint64_t>(n, (first + cnt) * TRIM_CHUNK);
+            if (cudaMemcpyAsync(dst + r0 * CH_REC_BYTES, records + r0 * CH_REC_BYTES, (r1 - r0) * CH_REC_BYTES, cudaMemcpyHostToDevice,
+                                c->trim_dma) != cudaSuccess ||
+                cudaEventRecord(c->ev_trim_dma, c->trim_dma) != cudaSuccess || cudaEventSynchronize(c->ev_trim_dma) != cudaSuccess) {
+                failed = 1;
+                break;
+            }
+            sent += (r1 - r0) * CH_REC_BYTES;
+            pieces++;
+        }
+        c->launches += pieces;
+    }
     for (auto &x : th) x.join();
     if (failed) return fail(c, CHRONOS_E_CUDA, "trimmed upload: %s", cudaGetErrorString(cudaGetLastError()));
     for (auto &w : c->trim)
         for (int k = 0; k < 2; k++) CK(cudaStreamWaitEvent(st, w.done[k], 0));
+    CK(cudaEventRecord(c->ev_trim_dma, c->trim_dma));
+    CK(cudaStreamWaitEvent(st, c->ev_trim_dma, 0));
     c->launches += n_chunks;
     c->upload_bytes = sent.load();
     return CHRONOS_OK;

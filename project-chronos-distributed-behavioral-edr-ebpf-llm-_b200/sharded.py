@@ -229,12 +229,12 @@ class ShardedRunner:
             return (time.perf_counter() - t0) / steps, d2h, self.ctx.last_upload_bytes()
 
         dt_plain, d2h, up_plain = loop()
-        # with host cores to spare (>= 10 per rank) the upload is also tried trimmed (chronos_set_host_trim)
+        # the upload is also tried with the host's cores trimming part of it (chronos_set_host_trim)
         import os
 
         threads = (os.cpu_count() or 1) // self.world
         dt_trim = up_trim = None
-        if threads >= 10 and not os.environ.get("CHRONOS_BENCH_NO_TRIM"):
+        if threads >= 2 and not os.environ.get("CHRONOS_BENCH_NO_TRIM"):
             self.ctx.set_host_trim(threads)
             loop()
             dt_trim, d2h, up_trim = loop()
