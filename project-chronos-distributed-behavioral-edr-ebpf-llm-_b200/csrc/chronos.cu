@@ -19,6 +19,7 @@
 // keeps two buffer sets, and stage 1 of batch k+1 runs beside the tail of batch k.
 // All device memory for batches of up to max_batch_events is allocated by chronos_create.
 #include <cuda_runtime.h>
+#include <cuda_profiler_api.h>
 #include <stdarg.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -192,6 +193,7 @@ struct chronos_ctx {
     uint64_t fused_max = 0;  // batches whose grouped entries cannot exceed this run the tail as ONE kernel
     int prio_lo = 0;
     bool no_pipeline = false;
+    int gather_serial = 0;  // experiments (CHRONOS_GATHER_SERIAL): 1 = gather on the main stream after window_reverse, 2 = before group_forward, 3 = own stream, after group_forward
     // CHRONOS_TRACE=1: CUDA events between the stages of a submit, printed at fetch
     bool trace = false;
     cudaEvent_t tev[24] = {nullptr};
@@ -735,6 +737,8 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     Plan *plan = dplan(b);
     cudaStream_t st = c->stream;
     mark(c, "filter+compact done");
+    static const bool prof_tail = getenv("CHRONOS_PROFILE_TAIL") != nullptr;  // ncu range replay over the concurrent tail
+    if (prof_tail) { cudaDeviceSynchronize(); cudaProfilerStart(); }
     const uint64_t Smax = b.n;
     int rc;
     const uint32_t max_rtiles = (uint32_t)((Mmax + RADIX_TILE_KEYS - 1) / RADIX_TILE_KEYS);
@@ -833,6 +837,7 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     g.slot_ns = b.slots ? ptr<uint8_t>(b.surv_ns) : nullptr;
 
     auto finish = [&]() -> int {
+        if (prof_tail) { cudaDeviceSynchronize(); cudaProfilerStop(); }
         CK(cudaMemcpyAsync(b.h_scalars, ds, RESULT_BLOCK_BYTES, cudaMemcpyDeviceToHost, st));
         CK(cudaEventRecord(b.ev_end, st));
         return CHRONOS_OK;
@@ -893,18 +898,20 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     // its data in flight in shared memory and takes a bounded number of CTAs per SM, so that the
     // latency-bound scans find registers and warp slots on every SM beside it (a gather that
     // fills the SMs, or scans that fill the register file, serialise the two: profiles/README.md).
-    {
+    auto launch_gather = [&](cudaStream_t gs) -> int {
         const uint32_t blocks = (uint32_t)std::min<uint64_t>((Mmax + GATHER_WARPS * GATHER_GROUP - 1) / (GATHER_WARPS * GATHER_GROUP),
                                                              (uint64_t)c->sm_count * (uint64_t)c->gather_ctas_per_sm);
-        CK(cudaStreamWaitEvent(c->stream2, c->ev_sorted, 0));
-        mark(c, "gather starts", c->stream2);
-        gather_records<<<std::max(1u, blocks), GATHER_THREADS, GATHER_SMEM, c->stream2>>>(g);
+        if (gs != st) CK(cudaStreamWaitEvent(gs, c->gather_serial == 3 ? c->ev_fwd : c->ev_sorted, 0));
+        mark(c, "gather starts", gs);
+        gather_records<<<std::max(1u, blocks), GATHER_THREADS, GATHER_SMEM, gs>>>(g);
         CK(cudaGetLastError());
-        CK(cudaEventRecord(c->ev_gathered, c->stream2));
-        mark(c, "gather done", c->stream2);
+        if (gs != st) CK(cudaEventRecord(c->ev_gathered, gs));
+        mark(c, "gather done", gs);
         c->launches++;
-        if ((rc = dbg_sync(c, "gather_records"))) return rc;
-    }
+        return dbg_sync(c, "gather_records");
+    };
+    if (c->gather_serial == 0 && (rc = launch_gather(c->stream2))) return rc;
+    if (c->gather_serial == 2 && (rc = launch_gather(st))) return rc;
 
     // ---- flush automaton + chain labeller ----------------------------------------------------
     group_forward<<<std::max(1u, std::min(tiles_m, cap_blocks)), WIN_THREADS, 0, st>>>(w_fwd);
@@ -913,6 +920,7 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     if ((rc = dbg_sync(c, "group_forward"))) return rc;
     CK(cudaEventRecord(c->ev_fwd, st));
     mark(c, "group_forward done");
+    if (c->gather_serial == 3 && (rc = launch_gather(c->stream2))) return rc;  // beside window_reverse / emit_ordered only
 
     // ---- windows in arrival order (stream3) beside the reverse scan (main stream) ----------
     CK(cudaStreamWaitEvent(c->stream3, c->ev_fwd, 0));
@@ -927,8 +935,9 @@ int run_window_stage(chronos_ctx *c, BatchSet &b, BatchSet &prev) {
     CK(cudaGetLastError());
     if ((rc = dbg_sync(c, "window_reverse"))) return rc;
     mark(c, "window_reverse done");
+    if (c->gather_serial == 1 && (rc = launch_gather(st))) return rc;
     CK(cudaStreamWaitEvent(st, c->ev_emitted, 0));
-    CK(cudaStreamWaitEvent(st, c->ev_gathered, 0));
+    if (c->gather_serial == 0 || c->gather_serial == 3) CK(cudaStreamWaitEvent(st, c->ev_gathered, 0));
     mark(c, "all joined");
     return finish();
 }
@@ -1182,6 +1191,7 @@ int chronos_create_sized(int device, uint64_t max_batch_events, uint64_t max_pen
     const char *gc = getenv("CHRONOS_GATHER_CTAS");
     c->gather_ctas_per_sm = gc ? std::max(1, atoi(gc)) : 2;
     c->no_pipeline = getenv("CHRONOS_NO_PIPELINE") != nullptr;
+    c->gather_serial = getenv("CHRONOS_GATHER_SERIAL") ? atoi(getenv("CHRONOS_GATHER_SERIAL")) : 0;
     // One CTA per SM fewer than shared memory would allow (18 instead of 19 on B200). At full
     // residency the filter is bistable: whole runs of batches take 0.72-0.87 ms instead of 0.49 ms
     // per 10 M events, depending on what the previous kernels left in L2; at 18 it is steady at

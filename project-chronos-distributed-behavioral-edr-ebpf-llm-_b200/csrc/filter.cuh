@@ -309,14 +309,19 @@ __global__ void __launch_bounds__(FILTER_TILE) filter_kernel(const FilterParams 
     constexpr uint32_t STAGE_BYTES = FILTER_TILE * CH_REC_BYTES;
     const int lane = threadIdx.x;
 
-    const uint64_t l2_evict_first = l2_policy_evict_first();  // the batch is read once
+    // No L2 eviction hint on the tile loads: an evict-first policy (the batch is read once) costs
+    // nothing when the kernel is in its fast regime, but makes the slow one (profiles/README.md,
+    // "The filter is bistable") more likely -- with hinted loads in the gather before it, certain.
+#ifdef CHRONOS_L2_HINT
+    const uint64_t l2_evict_first = l2_policy_evict_first();
+#endif
     auto issue = [&](int s, uint32_t t) {  // lane 0 only
         S.tile[s] = t;
         if (t < p.tile_end) {
             const uint64_t first = (uint64_t)t * FILTER_TILE;
             const uint32_t bytes = (uint32_t)min((uint64_t)FILTER_TILE, p.n - first) * CH_REC_BYTES;
             mbar_arrive_expect_tx(&S.bar[s], bytes);
-#ifndef CHRONOS_NO_L2_HINT
+#ifdef CHRONOS_L2_HINT
             bulk_g2s_hint(stages + (size_t)s * STAGE_BYTES, p.recs + first * CH_REC_BYTES, bytes, &S.bar[s], l2_evict_first);
 #else
             bulk_g2s(stages + (size_t)s * STAGE_BYTES, p.recs + first * CH_REC_BYTES, bytes, &S.bar[s]);

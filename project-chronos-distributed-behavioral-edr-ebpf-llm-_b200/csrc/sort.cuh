@@ -24,6 +24,9 @@ constexpr int RADIX_WARPS = RADIX_THREADS / 32;
 #ifndef CHRONOS_RADIX_TILE
 #define CHRONOS_RADIX_TILE 2048  // (measured together with CHRONOS_WIN_ITEMS, window.cuh)
 #endif
+#ifndef CHRONOS_RADIX_LB
+#define CHRONOS_RADIX_LB 8     // predecessors' status words loaded per look-back round
+#endif
 constexpr uint32_t RADIX_TILE_KEYS = CHRONOS_RADIX_TILE;  // keys per tile (multiple of RADIX_WARPS*32)
 constexpr int RADIX_MAX_PASSES = 4;
 
@@ -234,7 +237,7 @@ __device__ __forceinline__ void onesweep_pass_body(const SortParams &p, const in
             // first PREFIX or the first word that is not written yet. One word per round made a
             // pass a chain of up to n_tiles dependent L2 round trips (all tiles of a batch this
             // size run in one wave, so nobody finds a PREFIX nearby).
-            constexpr int LB = 8;
+            constexpr int LB = CHRONOS_RADIX_LB;
             const uint64_t *q = st - RADIX_BINS;  // nearest predecessor not consumed yet
             uint32_t left = tile;                 // predecessors not consumed yet (tile 0 always ends the walk)
             bool done = false;
