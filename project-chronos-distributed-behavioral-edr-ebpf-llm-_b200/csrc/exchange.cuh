@@ -142,7 +142,6 @@ constexpr int XCHG_STEPS = XCHG_SUB / 32;               // 32 survivors per step
 __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g) {
     __shared__ uint32_t rs_e[XCHG_MAX_WORLD + 1], rs_s[XCHG_MAX_WORLD + 1];  // row starts = per-owner stream starts
     __shared__ uint32_t wb_e[XCHG_WARPS][XCHG_MAX_WORLD], wb_s[XCHG_WARPS][XCHG_MAX_WORLD];
-    __shared__ uint32_t sh_ns[XCHG_WARPS][32];
     __shared__ uint32_t s_skip, s_last;
     // owner-major order of the tile's survivors (stable inside an owner): perm[j] = index in the tile
     __shared__ uint16_t perm[XCHG_TILE];
@@ -253,151 +252,117 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
         __syncwarp();
         __syncthreads();
         // 3) stable placement, 32 survivors per step (every step is executed by the whole warp;
-        //    lanes past the end carry owner 0xFF and nothing to copy)
+        //    lanes past the end carry owner 0xFF and nothing to copy). The warp walks the tile in
+        //    owner-major order, so the lanes of one owner are NEIGHBOURS: a group is a lane range
+        //    [leader, last], and what a group needs -- ranks, slots in front of an entry, where the
+        //    group's run starts in the staging buffer and at the owner -- falls out of two warp
+        //    scans. (Per-owner ballots and a search per copied slot cost 41 warp instructions per
+        //    survivor, 60 % of the kernel: ncu, profiles/README.md.)
 #pragma unroll
         for (int q = 0; q < XCHG_STEPS; q++) {
+            constexpr uint32_t FULL = 0xffffffffu;
             const uint32_t o = ow[q], ns = nsv[q], rec = recv[q];
             const bool valid = o != 0xFFu;
-            // rank among the lanes with the same owner, and the slots those lanes hold
-            const uint32_t peers = __match_any_sync(0xffffffffu, o);
-            const uint32_t lower = peers & lanemask_lt();
-            const uint32_t rank_e = __popc(lower);
-            sh_ns[warp][lane] = ns;
-            __syncwarp();
-            uint32_t pre_s = 0;
-            for (uint32_t m = lower; m; m &= m - 1) pre_s += sh_ns[warp][__ffs((int)m) - 1];
+            const uint32_t peers = __match_any_sync(FULL, o);
+            const int leader = __ffs((int)peers) - 1, last = 31 - __clz((int)peers);
+            CH_ASSERT(__popc(peers) == last - leader + 1);  // the group is a lane range
+            const uint32_t rank_e = (uint32_t)(lane - leader);
+            const bool live = valid && !((skip >> (o & 31u)) & 1u);  // (an owner is skipped as a whole)
+            // slots in front of this lane: over all valid lanes (the books), over live lanes (the staging)
+            const uint32_t nv = valid ? ns : 0u, cnt = live ? ns : 0u;
+            uint32_t inc_v = nv, inc_l = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t1 = __shfl_up_sync(FULL, inc_v, d), t2 = __shfl_up_sync(FULL, inc_l, d);
+                if (lane >= d) { inc_v += t1; inc_l += t2; }
+            }
+            const uint32_t exc_v = inc_v - nv, exc_l = inc_l - cnt;
+            const uint32_t pre_s = exc_v - __shfl_sync(FULL, exc_v, leader);  // slots of my owner's lower lanes
             uint32_t be = 0, bs = 0;
             if (valid) { be = wb_e[warp][o]; bs = wb_s[warp][o]; }
             __syncwarp();
-            if (valid && (peers >> lane) == 1u) {  // highest lane of its group: it knows the group totals
+            if (valid && lane == last) {  // highest lane of its group: it knows the group totals
                 wb_e[warp][o] = be + rank_e + 1;
                 wb_s[warp][o] = bs + pre_s + ns;
             }
             __syncwarp();
-            const bool live = valid && !((skip >> (o & 31u)) & 1u);
             // ---- owner-major staging in shared memory ----------------------------------------
             // Written entry by entry, a survivor is an 80-byte fragment at some place in its
             // owner's window; NVLink moves such scattered fragments at about 375 GB/s, runs of
             // 128 bytes and more at 660 GB/s (tools/nvlink_probe.cu). All entries a warp step
-            // sends to ONE owner are neighbours at the destination, so the step is staged owner by
-            // owner and every owner's run then leaves with consecutive lanes on consecutive slots.
-            // Lane w keeps the books of owner w: slots / entries of the step, where its run starts
-            // in the staging buffer and where it goes.
-            uint32_t tot_s = 0, tot_e = 0, lower_s = 0, lower_e = 0;
-            uint4 *run_dst = nullptr, *desc_dst = nullptr;
-            for (uint32_t w = 0; w < W; w++) {
-                const bool mine = live && o == w;
-                const uint32_t bal = __ballot_sync(0xffffffffu, mine);
-                const uint32_t ts = __reduce_add_sync(0xffffffffu, mine ? ns : 0u);
-                const int f = bal ? __ffs((int)bal) - 1 : 0;
-                const uint32_t bs_w = __shfl_sync(0xffffffffu, bs, f), be_w = __shfl_sync(0xffffffffu, be, f);
-                if (live && w < o) { lower_s += ts; lower_e += __popc(bal); }
-                if ((uint32_t)lane == w && bal) {
-                    tot_s = ts;
-                    tot_e = __popc(bal);
-                    if (g.direct) {
-                        uint8_t *hb = g.peer[w] + (size_t)half * g.L.half_bytes;
-                        run_dst = reinterpret_cast<uint4 *>(hb + g.L.off_slots) + (size_t)g.L.rank * g.L.cap_s + bs_w;
-                        desc_dst = reinterpret_cast<uint4 *>(hb + g.L.off_desc) + (size_t)g.L.rank * g.L.cap_e + be_w;
-                    } else {
-                        run_dst = g.send_slots + bs_w;
-                    }
+            // sends to ONE owner are neighbours at the destination, so the step is staged in lane
+            // (= owner-major) order and every group's run then leaves with consecutive lanes on
+            // consecutive slots.
+            const uint32_t live_mask = __ballot_sync(FULL, live);
+            const uint32_t e_idx = __popc(live_mask & lanemask_lt());  // staged descriptor of this lane
+            const uint32_t total = __shfl_sync(FULL, inc_l, 31);
+            const uint32_t g_s0 = __shfl_sync(FULL, exc_l, leader), g_s1 = __shfl_sync(FULL, inc_l, last);  // the group's staged slots
+            const uint32_t g_e0 = __shfl_sync(FULL, e_idx, leader);
+            const uint32_t g_ne = live ? (uint32_t)(last - leader + 1) : 0u;
+            uint4 *run_dst = nullptr, *desc_dst = nullptr;  // where the group's run / descriptors go (same on all its lanes)
+            if (live) {
+                if (g.direct) {
+                    uint8_t *hb = g.peer[o] + (size_t)half * g.L.half_bytes;
+                    run_dst = reinterpret_cast<uint4 *>(hb + g.L.off_slots) + (size_t)g.L.rank * g.L.cap_s + bs;
+                    desc_dst = reinterpret_cast<uint4 *>(hb + g.L.off_desc) + (size_t)g.L.rank * g.L.cap_e + be;
+                } else {
+                    run_dst = g.send_slots + bs;
                 }
             }
-            uint32_t end_s = tot_s, end_e = tot_e;  // inclusive scans over the owners
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t t1 = __shfl_up_sync(0xffffffffu, end_s, d), t2 = __shfl_up_sync(0xffffffffu, end_e, d);
-                if (lane >= d) { end_s += t1; end_e += t2; }
-            }
-            const uint32_t total = __shfl_sync(0xffffffffu, end_s, 31), n_live = __shfl_sync(0xffffffffu, end_e, 31);
             uint4 *stg = stage + (size_t)warp * XCHG_STAGE_PER_WARP;  // [0, STAGE_SLOTS) slots, then 32 descriptors
-            const uint32_t my_soff = lower_s + pre_s;                 // first staged slot of this lane's entry
             const uint4 *src = nullptr;
             if (live) {
                 const uint64_t hdr = ((g.base_arrival + rec) & 0xFFFFFFFFFFFFull) | ((uint64_t)metav[q] << 48) | ((uint64_t)ns << 56);
                 src = reinterpret_cast<const uint4 *>(g.batch + (size_t)rec * CH_REC_BYTES);
-                if (g.direct) stg[XCHG_STAGE_SLOTS + lower_e + rank_e] = make_uint4((uint32_t)hdr, (uint32_t)(hdr >> 32), bs + pre_s, 0u);
+                if (g.direct) stg[XCHG_STAGE_SLOTS + e_idx] = make_uint4((uint32_t)hdr, (uint32_t)(hdr >> 32), bs + pre_s, 0u);
                 else g.send_hdr[be + rank_e] = hdr;
             }
-            // the slots of the 32 entries, read cooperatively in lane order (4 x 32 loads in flight)
-            const uint32_t cnt = live ? ns : 0u;
-            uint32_t incl = cnt;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
-                if (lane >= d) incl += t;
-            }
-            const uint32_t excl = incl - cnt;
+            const uint32_t group_leaders = __ballot_sync(FULL, live && lane == leader);
             for (uint32_t w0 = 0; w0 < total; w0 += XCHG_STAGE_SLOTS) {  // staged slots [w0, w1) this round
                 const uint32_t w1 = min(total, w0 + XCHG_STAGE_SLOTS);
-                for (uint32_t b0 = 0; b0 < total; b0 += 128) {
+                // every lane stages the slots [sa, sb) of its own entry that fall into the window, four
+                // per round trip (chunks 0, 1, 17, then 2..)
+                const uint32_t sa = exc_l < w0 ? min(cnt, w0 - exc_l) : 0u;
+                const uint32_t sb = exc_l >= w1 ? 0u : min(cnt, w1 - exc_l);
+                const uint32_t trips = __reduce_max_sync(FULL, sb > sa ? (sb - sa + 3u) / 4u : 0u);
+                for (uint32_t r = 0; r < trips; r++) {
                     uint4 v[4];
-                    uint32_t at[4];
 #pragma unroll
                     for (int u = 0; u < 4; u++) {
-                        const uint32_t k = b0 + u * 32 + lane;
-                        int sidx = 0;  // lane that owns slot k (shuffle binary search, as in filter.cuh phase B2)
-#pragma unroll
-                        for (int step = 16; step >= 1; step >>= 1) {
-                            const uint32_t vv = __shfl_sync(0xffffffffu, incl, sidx + step - 1);
-                            if (vv <= k) sidx += step;
-                        }
-                        sidx &= 31;
-                        const uint32_t ex = __shfl_sync(0xffffffffu, excl, sidx);
-                        const uint32_t so = __shfl_sync(0xffffffffu, my_soff, sidx);
-                        const unsigned long long sp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)src, sidx);
-                        at[u] = NONE_AT;
+                        const uint32_t sl = sa + r * 4u + (uint32_t)u;
                         v[u] = make_uint4(0u, 0u, 0u, 0u);
-                        if (k < total) {
-                            const uint32_t sl = k - ex;  // slot within the entry: chunks 0, 1, 17, then 2..
-                            const uint32_t pos = so + sl;  // where it stands in the owner-major order
-                            if (pos >= w0 && pos < w1) {
-                                const uint32_t ch = sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u);
-                                v[u] = __ldg(reinterpret_cast<const uint4 *>((uintptr_t)sp) + ch);
-                                at[u] = pos - w0;
-                            }
-                        }
+                        if (sl < sb) v[u] = __ldg(src + (sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u)));
                     }
 #pragma unroll
-                    for (int u = 0; u < 4; u++)
-                        if (at[u] != NONE_AT) {
-                        CH_ASSERT(at[u] < XCHG_STAGE_SLOTS);
-                        stg[at[u]] = v[u];
+                    for (int u = 0; u < 4; u++) {
+                        const uint32_t sl = sa + r * 4u + (uint32_t)u;
+                        if (sl < sb) {
+                            CH_ASSERT(exc_l + sl >= w0 && exc_l + sl - w0 < XCHG_STAGE_SLOTS);
+                            stg[exc_l + sl - w0] = v[u];
+                        }
                     }
                 }
                 __syncwarp();
-                // every owner's run leaves with consecutive lanes on consecutive 16-byte slots
-                for (uint32_t j0 = w0; j0 < w1; j0 += 128) {
-#pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const uint32_t j = j0 + u * 32 + lane;
-                        int w = 0;  // owner whose run holds staged slot j: first lane with end_s > j
-#pragma unroll
-                        for (int step = 16; step >= 1; step >>= 1) {
-                            const uint32_t vv = __shfl_sync(0xffffffffu, end_s, w + step - 1);
-                            if (vv <= j) w += step;
-                        }
-                        w &= 31;
-                        const uint32_t st = __shfl_sync(0xffffffffu, end_s - tot_s, w);
-                        const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)run_dst, w);
-                        CH_ASSERT(j >= w1 || (j >= st && j - w0 < XCHG_STAGE_SLOTS));
-                        if (j < w1) reinterpret_cast<uint4 *>((uintptr_t)dp)[j - st] = stg[j - w0];
+                // every group's run leaves with consecutive lanes on consecutive 16-byte slots
+                for (uint32_t lm = group_leaders; lm; lm &= lm - 1) {
+                    const int L = __ffs((int)lm) - 1;
+                    const uint32_t s0 = __shfl_sync(FULL, g_s0, L), s1 = __shfl_sync(FULL, g_s1, L);
+                    const unsigned long long dp = __shfl_sync(FULL, (unsigned long long)(uintptr_t)run_dst, L);
+                    const uint32_t hi = min(s1, w1);
+                    for (uint32_t j = max(s0, w0) + (uint32_t)lane; j < hi; j += 32) {
+                        CH_ASSERT(j - w0 < XCHG_STAGE_SLOTS);
+                        reinterpret_cast<uint4 *>((uintptr_t)dp)[j - s0] = stg[j - w0];
                     }
                 }
                 __syncwarp();  // the window is refilled by the next round
             }
-            if (g.direct) {  // descriptors: at most 32 per step, same owner-major order
-                int w = 0;
-#pragma unroll
-                for (int step = 16; step >= 1; step >>= 1) {
-                    const uint32_t vv = __shfl_sync(0xffffffffu, end_e, w + step - 1);
-                    if (vv <= (uint32_t)lane) w += step;
+            if (g.direct) {  // descriptors: at most 32 per step, group by group
+                for (uint32_t lm = group_leaders; lm; lm &= lm - 1) {
+                    const int L = __ffs((int)lm) - 1;
+                    const uint32_t e0 = __shfl_sync(FULL, g_e0, L), ne = __shfl_sync(FULL, g_ne, L);
+                    const unsigned long long dp = __shfl_sync(FULL, (unsigned long long)(uintptr_t)desc_dst, L);
+                    if ((uint32_t)lane < ne) reinterpret_cast<uint4 *>((uintptr_t)dp)[lane] = stg[XCHG_STAGE_SLOTS + e0 + lane];
                 }
-                w &= 31;
-                const uint32_t st = __shfl_sync(0xffffffffu, end_e - tot_e, w);
-                const unsigned long long dp = __shfl_sync(0xffffffffu, (unsigned long long)(uintptr_t)desc_dst, w);
-                if ((uint32_t)lane < n_live) reinterpret_cast<uint4 *>((uintptr_t)dp)[lane - st] = stg[XCHG_STAGE_SLOTS + lane];
             }
             __syncwarp();  // the staging buffer is reused by the next step
         }
