@@ -60,6 +60,33 @@ __device__ __forceinline__ uint64_t l2_policy_evict_first() {
     asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
     return pol;
 }
+// Loads of records or slots that lie SPARSELY in a large array (survivors in the batch, tile-local
+// slots): without a qualifier a miss fills the whole 128-byte line from DRAM; `.L2::64B` limits the
+// fill to the 64-byte half that is asked for (ncu: the record gather read 474 MB for 343 MB of
+// records before, 399 MB with it).
+__device__ __forceinline__ uint32_t ld_sparse_u32(const uint32_t *p) {
+    uint32_t v;
+    asm("ld.global.L2::64B.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ uint4 ld_sparse_nc_v4(const uint4 *p) {
+    uint4 v;
+    asm("ld.global.nc.L2::64B.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
+// 16 bytes global -> shared memory without passing through registers (LDGSTS)
+__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src, uint32_t src_bytes) {
+    // src_bytes = 16: plain copy; 0: the 16 bytes are zero-filled, nothing is read
+    // (.L2::64B: a record is 4.5 such halves; see ld_sparse_u32 in common.cuh)
+    asm volatile("cp.async.cg.shared.global.L2::64B [%0], [%1], 16, %2;" ::"r"(smem_u32(dst_smem)), "l"(src), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 // 1-D bulk copy through the TMA unit with an L2 cache hint; size and both addresses must be multiples of 16.
 __device__ __forceinline__ void bulk_g2s_hint(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar,
                                               uint64_t policy) {

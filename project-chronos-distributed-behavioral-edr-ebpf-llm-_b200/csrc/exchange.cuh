@@ -320,28 +320,18 @@ __global__ void __launch_bounds__(XCHG_THREADS) xchg_pack(const XchgPackParams g
             const uint32_t group_leaders = __ballot_sync(FULL, live && lane == leader);
             for (uint32_t w0 = 0; w0 < total; w0 += XCHG_STAGE_SLOTS) {  // staged slots [w0, w1) this round
                 const uint32_t w1 = min(total, w0 + XCHG_STAGE_SLOTS);
-                // every lane stages the slots [sa, sb) of its own entry that fall into the window, four
-                // per round trip (chunks 0, 1, 17, then 2..)
+                // every lane stages the slots [sa, sb) of its own entry that fall into the window (chunks
+                // 0, 1, 17, then 2..), global -> shared memory without passing through registers: all
+                // slots of the step are in flight together, one round trip to the batch per step (with
+                // register loads, four per trip, the wait for them was 40 % of the kernel's stall samples)
                 const uint32_t sa = exc_l < w0 ? min(cnt, w0 - exc_l) : 0u;
                 const uint32_t sb = exc_l >= w1 ? 0u : min(cnt, w1 - exc_l);
-                const uint32_t trips = __reduce_max_sync(FULL, sb > sa ? (sb - sa + 3u) / 4u : 0u);
-                for (uint32_t r = 0; r < trips; r++) {
-                    uint4 v[4];
-#pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const uint32_t sl = sa + r * 4u + (uint32_t)u;
-                        v[u] = make_uint4(0u, 0u, 0u, 0u);
-                        if (sl < sb) v[u] = __ldg(src + (sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u)));
-                    }
-#pragma unroll
-                    for (int u = 0; u < 4; u++) {
-                        const uint32_t sl = sa + r * 4u + (uint32_t)u;
-                        if (sl < sb) {
-                            CH_ASSERT(exc_l + sl >= w0 && exc_l + sl - w0 < XCHG_STAGE_SLOTS);
-                            stg[exc_l + sl - w0] = v[u];
-                        }
-                    }
+                for (uint32_t sl = sa; sl < sb; sl++) {
+                    CH_ASSERT(exc_l + sl >= w0 && exc_l + sl - w0 < XCHG_STAGE_SLOTS);
+                    cp_async16(stg + (exc_l + sl - w0), src + (sl < 2 ? sl : (sl == 2 ? 17u : sl - 1u)), 16u);
                 }
+                cp_async_commit();
+                cp_async_wait<0>();
                 __syncwarp();
                 // every group's run leaves with consecutive lanes on consecutive 16-byte slots
                 for (uint32_t lm = group_leaders; lm; lm &= lm - 1) {

@@ -660,8 +660,8 @@ __global__ void __launch_bounds__(CS_THREADS) compact_scan(const CompactScanPara
             }
 #pragma unroll
             for (int u = 0; u < CS_ILP; u++) {
-                k[u] = p.sp_key[src[u]];
-                sr[u] = p.sp_src[src[u]];
+                k[u] = ld_sparse_u32(p.sp_key + src[u]);  // (one 128-byte line per filter tile, its head in use)
+                sr[u] = ld_sparse_u32(p.sp_src + src[u]);
                 me[u] = p.sp_meta[src[u]];
                 nn[u] = p.sp_ns[src[u]];
             }

@@ -507,17 +507,6 @@ constexpr uint32_t GATHER_GROUP = 16;
 constexpr int GATHER_STAGES = 2;
 constexpr size_t GATHER_SMEM = (size_t)GATHER_WARPS * GATHER_STAGES * GATHER_GROUP * CH_REC_BYTES;
 
-__device__ __forceinline__ void cp_async16(void *dst_smem, const void *src, uint32_t src_bytes) {
-    // src_bytes = 16: plain copy; 0: the 16 bytes are zero-filled, nothing is read
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(dst_smem)), "l"(src), "r"(src_bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
-}
-
 __device__ __forceinline__ void gather_records_body(const GatherParams &g, uint4 *gather_smem) {
     const uint32_t gM = g.plan ? g.plan->M : g.M, gP = g.plan ? g.plan->P : g.P;
     const uint32_t *const gsval = g.plan ? g.plan->sval : g.sval;
